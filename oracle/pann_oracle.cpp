@@ -1,0 +1,415 @@
+// oracle/pann_oracle.cpp — TEST INFRASTRUCTURE ONLY (never linked or imported by the product path).
+//
+// A plain single-file C++ restatement of the reference's CPU algorithms for the hot path
+// (landrumb/ParlayANN @ 7e52da5), written from the behaviour described in SURVEY.md §8 /
+// Appendix A+B.  It is the checker the CUDA path is compared with where the real reference
+// binary (oracle/_ref/ref_driver, built from /root/reference by oracle/Makefile) cannot travel
+// or is inconvenient to call in-process.  PARITY IS PINNED: every entry point below is checked
+// against outputs of the unmodified reference (tests/golden/*, made by tests/golden/make_golden.py
+// through oracle/_ref/ref_driver) in tests/test_oracle_vs_reference.py.
+//
+// Each function cites the reference file:line it follows (paths relative to /root/reference).
+// Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+// load this library.
+#include <algorithm>
+#include <atomic>
+#include <cmath>
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <limits>
+#include <thread>
+#include <unordered_map>
+#include <unordered_set>
+#include <utility>
+#include <vector>
+
+#include "../parlayann_b200/csrc/datagen.h"
+
+namespace {
+
+enum { DT_F32 = 0, DT_U8 = 1, DT_I8 = 2 };
+enum { M_L2 = 0, M_MIPS = 1 };
+
+struct PointSet {
+  int dtype, metric;
+  const uint8_t* base;  // n rows
+  uint64_t n;
+  uint32_t d;
+  uint64_t stride;  // bytes between rows
+  const void* row(uint64_t i) const { return base + i * stride; }
+};
+
+// algorithms/utils/euclidian_point.h:54-62 (u8), :74-81 (i8), :83-90 (f32)
+// algorithms/utils/mips_point.h:43-49 (u8), :51-57 (i8), :59-65 (f32)
+// 8-bit: int32 accumulate then one cast to float.  f32: strictly sequential float accumulate.
+// NOTE the f32 loops are compiled with -ffp-contract=off here so that every square/product is
+// rounded before the add, which is what g++ -O3 emits for the reference's main loop when d%8==0
+// (vector sub/mul, scalar add chain).
+float dist_rows(int dtype, int metric, const void* a, const void* b, uint32_t d) {
+  if (dtype == DT_U8) {
+    const uint8_t *p = (const uint8_t*)a, *q = (const uint8_t*)b;
+    int32_t r = 0;
+    if (metric == M_L2) { for (uint32_t i = 0; i < d; i++) { int32_t t = (int32_t)p[i] - (int32_t)q[i]; r += t * t; } return (float)r; }
+    for (uint32_t i = 0; i < d; i++) r += (int32_t)p[i] * (int32_t)q[i];
+    return -((float)r);
+  }
+  if (dtype == DT_I8) {
+    const int8_t *p = (const int8_t*)a, *q = (const int8_t*)b;
+    int32_t r = 0;
+    if (metric == M_L2) { for (uint32_t i = 0; i < d; i++) { int32_t t = (int32_t)p[i] - (int32_t)q[i]; r += t * t; } return (float)r; }
+    for (uint32_t i = 0; i < d; i++) r += (int32_t)p[i] * (int32_t)q[i];
+    return -((float)r);
+  }
+  const float *p = (const float*)a, *q = (const float*)b;
+  float r = 0.0f;
+  if (metric == M_L2) { for (uint32_t i = 0; i < d; i++) { float t = q[i] - p[i]; float s = t * t; r = r + s; } return r; }
+  for (uint32_t i = 0; i < d; i++) { float s = q[i] * p[i]; r = r + s; }
+  return -r;
+}
+
+using idd = std::pair<uint32_t, float>;
+inline bool less_idd(const idd& a, const idd& b) {  // beamSearch.h:46-48, vamana/index.h:80-82
+  return a.second < b.second || (a.second == b.second && a.first < b.first);
+}
+
+// parlay/utilities.h:145-150
+inline uint64_t hash64_2(uint64_t x) {
+  x = (x ^ (x >> 30)) * UINT64_C(0xbf58476d1ce4e5b9);
+  x = (x ^ (x >> 27)) * UINT64_C(0x94d049bb133111eb);
+  return x ^ (x >> 31);
+}
+// parlay/utilities.h:132-142
+inline uint64_t hash64(uint64_t u) {
+  uint64_t v = u * 3935559000370003845ul + 2691343689449507681ul;
+  v ^= v >> 21; v ^= v << 37; v ^= v >> 4;
+  v *= 4768777513237032717ul;
+  v ^= v << 20; v ^= v >> 41; v ^= v << 5;
+  return v;
+}
+
+struct QP { long k, beam; double cut; long limit, degree_limit; };
+
+struct SearchOut {
+  std::vector<idd> frontier, visited;
+  size_t cmps = 0;
+};
+
+// algorithms/utils/beamSearch.h:22-214 with use_filtering == false, Points == Q_Points.
+// graph: n x (maxdeg+1) u32, slot 0 = degree (algorithms/utils/graph.h:134-141).
+// self >= 0: the query IS base row `self` (build mode) -> same_as() skips it (euclidian_point.h:178-180).
+void beam_search(const PointSet& P, const uint32_t* graph, uint32_t maxdeg, const void* q, long self,
+                 const uint32_t* starts, uint32_t nstarts, const QP& qp, SearchOut& out) {
+  const int beam = (int)qp.beam;
+  auto dist = [&](uint32_t a) { return dist_rows(P.dtype, P.metric, P.row(a), q, P.d); };
+  int bits = std::max<int>(10, (int)std::ceil(std::log2((double)(beam * beam))) - 2);  // :52
+  std::vector<uint32_t> filter((size_t)1 << bits, 0xffffffffu);
+  auto seen = [&](uint32_t a) {  // :54-59
+    size_t loc = hash64_2(a) & (((uint64_t)1 << bits) - 1);
+    if (filter[loc] == a) return true;
+    filter[loc] = a;
+    return false;
+  };
+  std::vector<idd> frontier, unvisited(std::max<size_t>(beam, nstarts)), visited, cand, nf;
+  for (uint32_t i = 0; i < nstarts; i++) { frontier.push_back(idd(starts[i], dist(starts[i]))); seen(starts[i]); }  // :64-69
+  std::sort(frontier.begin(), frontier.end(), less_idd);
+  for (size_t i = 0; i < frontier.size(); i++) unvisited[i] = frontier[i];
+  size_t cmps = nstarts;  // :84
+  int remain = (int)frontier.size(), nvis = 0, offset = 0;
+  nf.resize(2 * std::max<size_t>(beam, nstarts) + maxdeg);
+  while (remain > offset && nvis < qp.limit) {  // :107
+    idd cur = unvisited[offset];
+    visited.insert(std::upper_bound(visited.begin(), visited.end(), cur, less_idd), cur);  // :112-113
+    nvis++;
+    bool full = (int)frontier.size() == beam;  // :115
+    const uint32_t* row = graph + (uint64_t)cur.first * (maxdeg + 1);
+    long ne = std::min<long>(row[0], qp.degree_limit);  // :130
+    float cutoff = full ? frontier.back().second : (float)std::numeric_limits<int>::max();  // :150-152
+    for (long i = 0; i < ne; i++) {
+      uint32_t a = row[1 + i];
+      if (seen(a) || (long)a == self) continue;  // :133
+      float dd = dist(a);
+      cmps++;  // :155
+      if (dd >= cutoff) continue;
+      cand.push_back(idd(a, dd));
+    }
+    if (cand.empty() || (qp.limit >= 2 * beam && (long)cand.size() < beam / 8 && offset + 1 < remain)) {  // :162-168
+      offset++;
+      continue;
+    }
+    offset = 0;
+    std::sort(cand.begin(), cand.end(), less_idd);  // :173
+    auto ce = std::unique(cand.begin(), cand.end(), [](const idd& a, const idd& b) { return a.first == b.first; });
+    size_t nfs = std::set_union(frontier.begin(), frontier.end(), cand.begin(), ce, nf.begin(), less_idd) - nf.begin();
+    cand.clear();
+    nfs = std::min<size_t>(beam, nfs);  // :185
+    if (qp.k > 0 && (long)nfs > qp.k && P.metric == M_L2) {  // :190-195
+      idd thr((uint32_t)0, (float)(qp.cut * (double)nf[qp.k].second));
+      size_t c = std::upper_bound(nf.begin(), nf.begin() + nfs, thr, less_idd) - nf.begin();
+      nfs = std::max<uint32_t>((uint32_t)c, (uint32_t)frontier.size());
+    }
+    frontier.assign(nf.begin(), nf.begin() + nfs);  // :198-200
+    remain = (int)(std::set_difference(frontier.begin(), frontier.begin() + std::min<long>(frontier.size(), qp.beam),
+                                       visited.begin(), visited.end(), unvisited.begin(), less_idd) - unvisited.begin());
+  }
+  out.frontier = frontier;
+  out.visited = visited;
+  out.cmps = cmps;
+}
+
+// algorithms/vamana/index.h:63-120.  cand already carries d(c,p).
+long robust_prune(const PointSet& P, const uint32_t* graph, uint32_t maxdeg, uint32_t R, uint32_t p,
+                  std::vector<idd> cand, double alpha, bool add, std::vector<uint32_t>& out) {
+  long comps = 0;
+  const uint32_t* row = graph + (uint64_t)p * (maxdeg + 1);
+  if (add)
+    for (uint32_t i = 0; i < row[0]; i++) {  // :72-77
+      comps++;
+      cand.push_back(idd(row[1 + i], dist_rows(P.dtype, P.metric, P.row(row[1 + i]), P.row(p), P.d)));
+    }
+  std::sort(cand.begin(), cand.end(), less_idd);  // :80-83
+  cand.erase(std::unique(cand.begin(), cand.end(), [](const idd& a, const idd& b) { return a.first == b.first; }), cand.end());
+  std::vector<int> ids(cand.size());
+  for (size_t i = 0; i < cand.size(); i++) ids[i] = (int)cand[i].first;
+  out.clear();
+  size_t idx = 0;
+  while (out.size() < R && idx < cand.size()) {  // :95-116
+    int ps = ids[idx++];
+    if (ps == (int)p || ps == -1) continue;
+    out.push_back((uint32_t)ps);
+    for (size_t i = idx; i < cand.size(); i++) {
+      int pp = ids[i];
+      if (pp == -1) continue;
+      comps++;
+      float dsp = dist_rows(P.dtype, P.metric, P.row((uint32_t)ps), P.row((uint32_t)pp), P.d);
+      if (alpha * dsp <= cand[i].second) ids[i] = -1;  // double * float -> double compare (:111)
+    }
+  }
+  return comps;
+}
+
+// parlay/random.h:154-159 -> random_shuffle_ :91-137, seq_random_shuffle_ :80-89, count_sort (stable)
+void random_permutation(int64_t n, int32_t* out) {
+  struct rnd { uint64_t state; uint64_t ith(uint64_t i) const { return hash64(i + state); }
+               rnd fork(uint64_t i) const { return rnd{hash64(hash64(i + state))}; } };
+  auto knuth = [](int32_t* a, size_t m, rnd r) {
+    if (m < 2) return;
+    for (size_t i = m - 1; i > 0; i--) std::swap(a[i], a[r.ith(i) % (i + 1)]);
+  };
+  rnd r{0};
+  if (n < 8192) {  // parlay/internal/counting_sort.h:29
+    for (int64_t i = 0; i < n; i++) out[i] = (int32_t)i;
+    knuth(out, (size_t)n, r);
+    return;
+  }
+  auto log2_up = [](uint64_t i) { size_t a = 0; uint64_t b = i - 1; while (b > 0) { b >>= 1; a++; } return a; };
+  size_t bits = ((uint64_t)n < (1ull << 27)) ? (log2_up(n) - 7) / 2 : (log2_up(n) - 17);
+  size_t nb = (size_t)1 << bits, mask = nb - 1;
+  std::vector<size_t> off(nb + 1, 0);
+  for (int64_t i = 0; i < n; i++) off[(r.ith(i) & mask) + 1]++;
+  for (size_t b = 0; b < nb; b++) off[b + 1] += off[b];
+  std::vector<size_t> cur(off.begin(), off.end() - 1);
+  for (int64_t i = 0; i < n; i++) out[cur[r.ith(i) & mask]++] = (int32_t)i;
+  for (size_t b = 0; b < nb; b++) knuth(out + off[b], off[b + 1] - off[b], r.fork(b));
+}
+
+template <class F>
+void par_for(size_t lo, size_t hi, int nthreads, F f) {
+  if (nthreads <= 1 || hi - lo < 2) { for (size_t i = lo; i < hi; i++) f(i); return; }
+  std::atomic<size_t> next(lo);
+  std::vector<std::thread> ts;
+  for (int t = 0; t < nthreads; t++)
+    ts.emplace_back([&] { for (;;) { size_t i = next.fetch_add(16); if (i >= hi) return; for (size_t j = i; j < std::min(hi, i + 16); j++) f(j); } });
+  for (auto& t : ts) t.join();
+}
+
+}  // namespace
+
+extern "C" {
+
+int oracle_num_threads() { unsigned h = std::thread::hardware_concurrency(); return h ? (int)h : 1; }
+
+float oracle_distance(int dtype, int metric, const void* a, const void* b, uint32_t d) { return dist_rows(dtype, metric, a, b, d); }
+
+void oracle_random_permutation(int64_t n, int32_t* out) { random_permutation(n, out); }
+
+// batch driver = qsearchAll (beamSearch.h:537-565) / beam_search (:217-223) over nq queries.
+// self_base >= 0: query i is base row self_base+i? no -> selfs[i] (may be NULL) gives the base row a query aliases.
+// Outputs (any may be NULL): out_ids/out_dists nq*k (first k of the frontier), visited/cmps counters nq,
+// full lists: fr_* nq*fcap, vis_* nq*vcap with counts in nfr/nvis.
+int oracle_search_batch(int dtype, int metric, const void* points, uint64_t n, uint32_t d, uint64_t stride,
+                        const uint32_t* graph, uint32_t maxdeg, const void* queries, uint64_t nq, uint64_t qstride,
+                        const int64_t* selfs, const uint32_t* starts, uint32_t nstarts,
+                        long k, long beam, double cut, long limit, long degree_limit,
+                        uint32_t* out_ids, float* out_dists, uint32_t* out_visited, uint32_t* out_cmps,
+                        uint32_t fcap, uint32_t* fr_ids, float* fr_dists, uint32_t* nfr,
+                        uint32_t vcap, uint32_t* vis_ids, float* vis_dists, uint32_t* nvis, int nthreads) {
+  PointSet P{dtype, metric, (const uint8_t*)points, n, d, stride};
+  QP qp{k, beam, cut, limit, degree_limit};
+  std::atomic<int> bad(0);
+  par_for(0, nq, nthreads, [&](size_t i) {
+    SearchOut o;
+    beam_search(P, graph, maxdeg, (const uint8_t*)queries + i * qstride, selfs ? selfs[i] : -1, starts, nstarts, qp, o);
+    if ((long)o.frontier.size() < k) { bad = 1; return; }  // beamSearch.h:416-419 aborts
+    for (long j = 0; j < k; j++) { if (out_ids) out_ids[i * k + j] = o.frontier[j].first; if (out_dists) out_dists[i * k + j] = o.frontier[j].second; }
+    if (out_visited) out_visited[i] = (uint32_t)o.visited.size();
+    if (out_cmps) out_cmps[i] = (uint32_t)o.cmps;
+    if (nfr) nfr[i] = (uint32_t)o.frontier.size();
+    if (nvis) nvis[i] = (uint32_t)o.visited.size();
+    for (size_t j = 0; j < o.frontier.size() && j < fcap; j++) { if (fr_ids) fr_ids[i * fcap + j] = o.frontier[j].first; if (fr_dists) fr_dists[i * fcap + j] = o.frontier[j].second; }
+    for (size_t j = 0; j < o.visited.size() && j < vcap; j++) { if (vis_ids) vis_ids[i * vcap + j] = o.visited[j].first; if (vis_dists) vis_dists[i * vcap + j] = o.visited[j].second; }
+  });
+  return bad;
+}
+
+// knn_index::build_index (vamana/index.h:150-186) + batch_insert (:188-316), start_point = 0.
+// graph: n x (R+1) u32, zero-filled by the caller for a fresh build.  stats (may be NULL): n u32 each.
+int oracle_vamana_build(int dtype, int metric, const void* points, uint64_t n, uint32_t d, uint64_t stride,
+                        uint32_t R, uint32_t L, double alpha, int num_passes, int sort_neighbors,
+                        uint32_t* graph, uint32_t* st_visited, uint32_t* st_dists, int nthreads) {
+  PointSet P{dtype, metric, (const uint8_t*)points, n, d, stride};
+  const uint32_t maxdeg = R, start = 0;
+  std::vector<int32_t> perm(n);
+  random_permutation((int64_t)n, perm.data());  // :211-216 (inserts = identity, so shuffled = perm)
+  for (int pass = 0; pass < num_passes; pass++) {
+    double a = (pass == num_passes - 1) ? alpha : 1.0;  // :173-178
+    size_t m = n, inc = 0, count = 0;
+    size_t max_batch = std::min((size_t)(0.02 * (double)(float)n), (size_t)1000000);  // :206-207 (double .02 * float n)
+    if (max_batch == 0) max_batch = n;
+    while (count < m) {
+      size_t lo, hi;
+      if (pow(2.0, (double)inc) <= (double)max_batch) {  // :226-229
+        lo = (size_t)pow(2.0, (double)inc) - 1;
+        hi = std::min((size_t)pow(2.0, (double)(inc + 1)) - 1, m);
+        count = hi;
+      } else {  // :231-233
+        lo = count;
+        hi = std::min(count + max_batch, m);
+        count += max_batch;
+      }
+      std::vector<std::vector<uint32_t>> new_out(hi - lo);
+      par_for(lo, hi, nthreads, [&](size_t i) {  // phase 1 :247-266
+        uint32_t p = (uint32_t)perm[i];
+        QP qp{0, (long)L, 0.0, (long)n, (long)maxdeg};  // :250
+        SearchOut o;
+        beam_search(P, graph, maxdeg, P.row(p), (long)p, &start, 1, qp, o);
+        long c2 = robust_prune(P, graph, maxdeg, R, p, o.visited, a, true, new_out[i - lo]);
+        if (st_dists) st_dists[p] += (uint32_t)(o.cmps + c2);
+        if (st_visited) st_visited[p] += (uint32_t)o.visited.size();
+      });
+      for (size_t i = lo; i < hi; i++) {  // phase 2 :268-270
+        uint32_t* row = graph + (uint64_t)perm[i] * (maxdeg + 1);
+        row[0] = (uint32_t)new_out[i - lo].size();
+        std::copy(new_out[i - lo].begin(), new_out[i - lo].end(), row + 1);
+      }
+      // phase 3 :278-300 — group (nbr, p) by nbr, values keep batch order (parlay group_by_key)
+      std::vector<uint32_t> keys;
+      std::unordered_map<uint32_t, std::vector<uint32_t>> groups;
+      for (size_t i = lo; i < hi; i++)
+        for (uint32_t nb : new_out[i - lo]) {
+          auto it = groups.find(nb);
+          if (it == groups.end()) { keys.push_back(nb); it = groups.emplace(nb, std::vector<uint32_t>()).first; }
+          it->second.push_back((uint32_t)perm[i]);
+        }
+      par_for(0, keys.size(), nthreads, [&](size_t j) {
+        uint32_t t = keys[j];
+        std::vector<uint32_t>& c = groups.find(t)->second;
+        uint32_t* row = graph + (uint64_t)t * (maxdeg + 1);
+        if (c.size() + row[0] <= R) {  // :291-294, :140-146
+          std::unordered_set<uint32_t> have(c.begin(), c.end());
+          std::vector<uint32_t> merged = c;
+          for (uint32_t i = 0; i < row[0]; i++) if (!have.count(row[1 + i])) merged.push_back(row[1 + i]);
+          row[0] = (uint32_t)merged.size();
+          std::copy(merged.begin(), merged.end(), row + 1);
+        } else {  // :296-298, ids-only overload :124-137
+          std::vector<idd> cc;
+          long c0 = 0;
+          for (uint32_t x : c) { c0++; cc.push_back(idd(x, dist_rows(P.dtype, P.metric, P.row(x), P.row(t), P.d))); }
+          std::vector<uint32_t> res;
+          long c1 = robust_prune(P, graph, maxdeg, R, t, cc, a, true, res);
+          row[0] = (uint32_t)res.size();
+          std::copy(res.begin(), res.end(), row + 1);
+          if (st_dists) st_dists[t] += (uint32_t)(c0 + c1);
+        }
+      });
+      inc++;
+    }
+  }
+  if (sort_neighbors)  // :180-185 — dist-only comparator; ties unordered in the reference (std::sort)
+    par_for(0, n, nthreads, [&](size_t i) {
+      uint32_t* row = graph + (uint64_t)i * (maxdeg + 1);
+      std::sort(row + 1, row + 1 + row[0], [&](uint32_t j, uint32_t k) {
+        return dist_rows(P.dtype, P.metric, P.row(i), P.row(j), P.d) < dist_rows(P.dtype, P.metric, P.row(i), P.row(k), P.d);
+      });
+    });
+  return 0;
+}
+
+// the batch schedule alone (vamana/index.h:206-209, :223-234), for host-logic tests: returns #batches
+int64_t oracle_batch_schedule(uint64_t n, uint64_t m, int64_t* lo_out, int64_t* hi_out, int64_t cap) {
+  size_t inc = 0, count = 0;
+  size_t max_batch = std::min((size_t)(0.02 * (double)(float)n), (size_t)1000000);
+  if (max_batch == 0) max_batch = n;
+  int64_t nb = 0;
+  while (count < m) {
+    size_t lo, hi;
+    if (pow(2.0, (double)inc) <= (double)max_batch) { lo = (size_t)pow(2.0, (double)inc) - 1; hi = std::min((size_t)pow(2.0, (double)(inc + 1)) - 1, (size_t)m); count = hi; }
+    else { lo = count; hi = std::min(count + max_batch, (size_t)m); count += max_batch; }
+    if (nb < cap) { lo_out[nb] = (int64_t)lo; hi_out[nb] = (int64_t)hi; }
+    nb++; inc++;
+  }
+  return nb;
+}
+
+// data_tools/compute_groundtruth.cpp:22-60 then write_ibin's per-row sort by dist (:68-73).
+// Output rows are sorted by (dist, id) — the reference sorts by dist only with a non-stable sort, so
+// the order inside a tie group is unspecified there; tests compare tie groups as sets.
+int oracle_groundtruth(int dtype, int metric, const void* base, uint64_t nb, const void* queries, uint64_t nq,
+                       uint32_t d, uint64_t bstride, uint64_t qstride, uint32_t k, int32_t* out_ids, float* out_dists, int nthreads) {
+  if (nb < k) return 1;
+  const float dmin = metric == M_L2 ? 0.0f : -std::numeric_limits<float>::max();  // euclidian_point.h:111, mips_point.h:81
+  par_for(0, nq, nthreads, [&](size_t i) {
+    const void* q = (const uint8_t*)queries + i * qstride;
+    std::vector<std::pair<int, float>> top;
+    float topdist = dmin;
+    int toppos = 0;
+    for (uint64_t j = 0; j < nb; j++) {
+      float dd = dist_rows(dtype, metric, q, (const uint8_t*)base + j * bstride, d);  // Q[i].distance(B[j]) :34
+      if (top.size() < k) {  // :35-41
+        if (dd > topdist) { topdist = dd; toppos = (int)top.size(); }
+        top.push_back({(int)j, dd});
+      } else if (dd < topdist) {  // :42-54
+        float nt = dmin; int np = 0;
+        top[toppos] = {(int)j, dd};
+        for (size_t l = 0; l < top.size(); l++) if (top[l].second > nt) { nt = top[l].second; np = (int)l; }
+        topdist = nt; toppos = np;
+      }
+    }
+    std::sort(top.begin(), top.end(), [](auto& a, auto& b) { return a.second < b.second || (a.second == b.second && a.first < b.first); });
+    for (uint32_t j = 0; j < k; j++) { out_ids[i * k + j] = top[j].first; out_dists[i * k + j] = top[j].second; }
+  });
+  return 0;
+}
+
+// Synthetic data — CPU evaluation of parlayann_b200/csrc/datagen.h; the CUDA library
+// evaluates the same header on the device, bit-identically.
+void oracle_gen_points(int kind, uint64_t model_seed, uint64_t stream, uint64_t row0, uint64_t nrows, uint32_t d,
+                       uint32_t r, uint32_t nc, void* out, uint64_t stride, int nthreads) {
+  std::vector<int32_t> A((size_t)r * d), C((size_t)nc * r);
+  for (uint32_t k = 0; k < r; k++) for (uint32_t j = 0; j < d; j++) A[(size_t)k * d + j] = gen_A(model_seed, k, j);
+  for (uint32_t c = 0; c < nc; c++) for (uint32_t k = 0; k < r; k++) C[(size_t)c * r + k] = gen_C(model_seed, c, k);
+  par_for(0, nrows, nthreads, [&](size_t i) {
+    uint64_t row = row0 + i;
+    int32_t z[PANN_GEN_MAX_R];
+    gen_latent(model_seed, stream, row, r, nc, nc ? C.data() : nullptr, z);
+    uint8_t* o = (uint8_t*)out + i * stride;
+    std::vector<int32_t> x(d);
+    for (uint32_t j = 0; j < d; j++) x[j] = gen_coord(model_seed, stream, row, j, r, z, A.data() + j, d);
+    if (kind == PANN_GEN_U8) for (uint32_t j = 0; j < d; j++) o[j] = gen_to_u8(x[j]);
+    else if (kind == PANN_GEN_I8) for (uint32_t j = 0; j < d; j++) ((int8_t*)o)[j] = gen_to_i8(x[j]);
+    else if (kind == PANN_GEN_F32) for (uint32_t j = 0; j < d; j++) ((float*)o)[j] = gen_to_f32(x[j]);
+    else gen_normalize_row(x.data(), d, (float*)o);
+  });
+}
+
+}  // extern "C"

@@ -1,0 +1,144 @@
+"""ctypes access to the CHECKERS: oracle/_build/liboracle.so (our C++ restatement) and
+oracle/_ref/ref_driver (the unmodified reference, when it was built).  Test infrastructure only."""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+DT = {"float": 0, "uint8": 1, "int8": 2}
+NPDT = {"float": np.float32, "uint8": np.uint8, "int8": np.int8}
+METRIC = {"Euclidian": 0, "mips": 1}
+GEN = {"uint8": 0, "int8": 1, "float": 2, "float_norm": 3}
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        p = os.path.join(ORACLE_DIR, "_build", "liboracle.so")
+        if not os.path.exists(p):
+            subprocess.check_call(["make", "-C", ORACLE_DIR, "oracle"])
+        _lib = C.CDLL(p)
+        _lib.oracle_distance.restype = C.c_float
+        _lib.oracle_batch_schedule.restype = C.c_int64
+    return _lib
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def nthreads():
+    return lib().oracle_num_threads()
+
+
+def gen_points(kind, n, d, seed=1234, stream=0, r=24, nc=256, row0=0):
+    out = np.empty((n, d), dtype=np.float32 if kind.startswith("float") else NPDT[kind])
+    lib().oracle_gen_points(GEN[kind], C.c_uint64(seed), C.c_uint64(stream), C.c_uint64(row0), C.c_uint64(n),
+                            C.c_uint32(d), C.c_uint32(r), C.c_uint32(nc), _p(out), C.c_uint64(out.strides[0]),
+                            nthreads())
+    return out
+
+
+def random_permutation(n):
+    out = np.empty(n, dtype=np.int32)
+    lib().oracle_random_permutation(C.c_int64(n), _p(out))
+    return out
+
+
+def batch_schedule(n, m=None):
+    m = n if m is None else m
+    lo = np.zeros(4096, dtype=np.int64)
+    hi = np.zeros(4096, dtype=np.int64)
+    nb = lib().oracle_batch_schedule(C.c_uint64(n), C.c_uint64(m), _p(lo), _p(hi), C.c_int64(4096))
+    return [(int(lo[i]), int(hi[i])) for i in range(nb)]
+
+
+def search(points, graph, queries, data_type, metric="Euclidian", k=10, beam=10, cut=1.35, limit=None,
+           degree_limit=None, starts=(0,), selfs=None, full=False, fcap=None, vcap=4096):
+    n, d = points.shape
+    nq = queries.shape[0]
+    maxdeg = graph.shape[1] - 1
+    limit = n if limit is None or limit < 0 else limit
+    degree_limit = maxdeg if degree_limit is None or degree_limit < 0 else degree_limit
+    st = np.asarray(starts, dtype=np.uint32)
+    ids = np.zeros((nq, k), dtype=np.uint32)
+    dists = np.zeros((nq, k), dtype=np.float32)
+    vis = np.zeros(nq, dtype=np.uint32)
+    cmps = np.zeros(nq, dtype=np.uint32)
+    fcap = beam if fcap is None else fcap
+    fr_i = fr_d = nfr = vi_i = vi_d = nvi = None
+    if full:
+        fr_i = np.zeros((nq, fcap), dtype=np.uint32); fr_d = np.zeros((nq, fcap), dtype=np.float32)
+        vi_i = np.zeros((nq, vcap), dtype=np.uint32); vi_d = np.zeros((nq, vcap), dtype=np.float32)
+        nfr = np.zeros(nq, dtype=np.uint32); nvi = np.zeros(nq, dtype=np.uint32)
+    sf = None if selfs is None else np.ascontiguousarray(selfs, dtype=np.int64)
+    points = np.ascontiguousarray(points); queries = np.ascontiguousarray(queries)
+    graph = np.ascontiguousarray(graph, dtype=np.uint32)
+    rc = lib().oracle_search_batch(DT[data_type], METRIC[metric], _p(points), C.c_uint64(n), C.c_uint32(d),
+                                   C.c_uint64(points.strides[0]), _p(graph), C.c_uint32(maxdeg), _p(queries),
+                                   C.c_uint64(nq), C.c_uint64(queries.strides[0]), _p(sf), _p(st), C.c_uint32(len(st)),
+                                   C.c_long(k), C.c_long(beam), C.c_double(cut), C.c_long(limit), C.c_long(degree_limit),
+                                   _p(ids), _p(dists), _p(vis), _p(cmps),
+                                   C.c_uint32(fcap), _p(fr_i), _p(fr_d), _p(nfr),
+                                   C.c_uint32(vcap), _p(vi_i), _p(vi_d), _p(nvi), nthreads())
+    if rc:
+        raise RuntimeError("oracle: a query returned fewer than k results (the reference aborts here)")
+    out = dict(ids=ids, dists=dists, visited=vis, cmps=cmps)
+    if full:
+        out.update(fr_ids=fr_i, fr_dists=fr_d, nfr=nfr, vis_ids=vi_i, vis_dists=vi_d, nvis=nvi)
+    return out
+
+
+def vamana_build(points, data_type, metric="Euclidian", R=32, L=64, alpha=1.2, passes=1, sort_neighbors=True):
+    n, d = points.shape
+    points = np.ascontiguousarray(points)
+    g = np.zeros((n, R + 1), dtype=np.uint32)
+    sv = np.zeros(n, dtype=np.uint32)
+    sd = np.zeros(n, dtype=np.uint32)
+    lib().oracle_vamana_build(DT[data_type], METRIC[metric], _p(points), C.c_uint64(n), C.c_uint32(d),
+                              C.c_uint64(points.strides[0]), C.c_uint32(R), C.c_uint32(L), C.c_double(alpha),
+                              passes, int(sort_neighbors), _p(g), _p(sv), _p(sd), nthreads())
+    return g, sv, sd
+
+
+def groundtruth(base, queries, data_type, metric="Euclidian", k=100):
+    base = np.ascontiguousarray(base); queries = np.ascontiguousarray(queries)
+    nq = queries.shape[0]
+    ids = np.zeros((nq, k), dtype=np.int32)
+    dists = np.zeros((nq, k), dtype=np.float32)
+    rc = lib().oracle_groundtruth(DT[data_type], METRIC[metric], _p(base), C.c_uint64(base.shape[0]), _p(queries),
+                                  C.c_uint64(nq), C.c_uint32(base.shape[1]), C.c_uint64(base.strides[0]),
+                                  C.c_uint64(queries.strides[0]), C.c_uint32(k), _p(ids), _p(dists), nthreads())
+    if rc:
+        raise RuntimeError("oracle_groundtruth: k > nb")
+    return ids, dists
+
+
+# ---- the real reference (only where oracle/_ref/ref_driver exists and runs on this CPU) ----
+def ref_driver_path():
+    for name in ("ref_driver", "ref_driver_v3"):
+        p = os.path.join(ORACLE_DIR, "_ref", name)
+        if os.path.exists(p):
+            try:
+                if subprocess.run([p, "selftest"], capture_output=True, timeout=60).returncode == 0:
+                    return p
+            except Exception:
+                pass
+    return None
+
+
+def ref_run(args, threads=None):
+    p = ref_driver_path()
+    if p is None:
+        raise RuntimeError("oracle/_ref/ref_driver is not available")
+    env = dict(os.environ)
+    if threads:
+        env["PARLAY_NUM_THREADS"] = str(threads)
+    r = subprocess.run([p] + [str(a) for a in args], capture_output=True, text=True, env=env)
+    if r.returncode != 0:
+        raise RuntimeError(f"ref_driver failed ({r.returncode}): {r.stdout[-2000:]} {r.stderr[-2000:]}")
+    return r.stdout
