@@ -1,0 +1,123 @@
+/* pann.h — C ABI of libpann_cuda.so: the B200 (sm_100a) implementation of ParlayANN's data-parallel hot path.
+ *
+ * The reference (landrumb/ParlayANN) is a header-only C++ template library with no FFI layer; this
+ * boundary sits directly below its batch-level functions.  Each entry point names the reference
+ * interface it replaces (paths relative to the reference root).  INTEGRATION.md shows the binding a
+ * maintainer adds on the reference side (C++ header bodies and the pybind/ctypes stub).
+ *
+ * Conventions: every call returns 0 on success, non-zero on failure; pann_last_error() returns the
+ * message of the calling thread's last failure (the reference prints a message and abort()s, the
+ * header layer above this ABI keeps that behaviour).  "host" pointers are borrowed for the call;
+ * device memory is owned by the pann_index.  One host thread per pann_index; calls are synchronous
+ * unless the name ends in _async.  There is no CPU fallback: without a CUDA device every compute
+ * call fails with an error.
+ */
+#ifndef PANN_H_
+#define PANN_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum { PANN_F32 = 0, PANN_U8 = 1, PANN_I8 = 2 } pann_dtype;   /* Euclidian_Point<T> / Mips_Point<T> element types */
+typedef enum { PANN_L2 = 0, PANN_MIPS = 1 } pann_metric;               /* euclidian_point.h:92-242 / mips_point.h:67-139 */
+typedef enum { PANN_GEN_KIND_U8 = 0, PANN_GEN_KIND_I8 = 1, PANN_GEN_KIND_F32 = 2, PANN_GEN_KIND_F32_NORM = 3 } pann_gen_kind_t;
+
+/* = parlayANN::QueryParams (algorithms/utils/types.h:218-231).  limit < 0 means "number of points";
+ * degree_limit < 0 means "max degree of the graph". */
+typedef struct {
+  int64_t k;
+  int64_t beam;
+  double cut;
+  int64_t limit;
+  int64_t degree_limit;
+} pann_query_params;
+
+typedef struct pann_index pann_index;
+
+/* library / device */
+const char* pann_last_error(void);
+int pann_device_count(int* count);
+const char* pann_version(void);
+
+/* PointRange<Point> + Graph<unsigned> resident on one GPU.
+ * host_points = PointRange::location(0) with n rows of row_stride_bytes (point_range.h:42-141);
+ * host_graph  = Graph's flat n x (max_degree+1) uint32 array, slot 0 = degree (graph.h:125-250), may be NULL
+ * (an empty graph of that max degree is created: Graph(maxDeg, n), graph.h:134-145). */
+int pann_index_create(pann_index** out, int device, int dtype, int metric, uint64_t n, uint32_t dims,
+                      uint64_t row_stride_bytes, const void* host_points, uint32_t max_degree,
+                      const uint32_t* host_graph);
+/* same, but the points are synthesised on the device (SURVEY.md §8d generator; no host copy at all) */
+int pann_index_create_synthetic(pann_index** out, int device, int dtype, int metric, uint64_t n, uint32_t dims,
+                                uint32_t max_degree, int gen_kind, uint64_t seed, uint64_t stream, uint32_t latent_r,
+                                uint32_t n_clusters);
+void pann_index_destroy(pann_index* idx);
+int pann_index_set_graph(pann_index* idx, const uint32_t* host_graph);        /* Graph(char* gFile) after load */
+int pann_index_get_graph(pann_index* idx, uint32_t* host_graph_out);          /* for Graph::save */
+int pann_index_get_points(pann_index* idx, uint64_t row0, uint64_t nrows, void* host_out, uint64_t out_stride_bytes);
+int pann_index_info(pann_index* idx, uint64_t* n, uint32_t* dims, uint32_t* max_degree, int* dtype, int* metric);
+/* device time (ms, CUDA events on the index's stream) and kernel-launch count of the last compute call */
+int pann_index_last_timing(pann_index* idx, float* kernel_ms, int* launches);
+
+/* qsearchAll / searchAll (algorithms/utils/beamSearch.h:537-565, :353-387): one beam search per query
+ * (filtered_beam_search, beamSearch.h:22-214) from the given start points; writes the first k ids of each
+ * frontier (and their distances), and the per-query counters of stats<indexType> (stats.h:57-94):
+ * visited = |visited list|, cmps = full_dist_cmps.  HOST buffers; copies are part of the call.
+ * Fails if k > beam (beamSearch.h:549-553) or a query ends with fewer than k results (:416-419). */
+int pann_search_batch(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes,
+                      const uint32_t* starts, uint32_t nstarts, const pann_query_params* qp,
+                      uint32_t* out_ids, float* out_dists, uint32_t* out_visited, uint32_t* out_cmps);
+
+/* Device-resident variant: queries are uploaded once, results stay on the device until fetched.
+ * Used to time the search with inputs already in HBM. */
+int pann_queries_upload(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes);
+int pann_queries_synthetic(pann_index* idx, uint64_t nq, int gen_kind, uint64_t seed, uint64_t stream,
+                           uint32_t latent_r, uint32_t n_clusters);
+int pann_queries_download(pann_index* idx, void* host_out, uint64_t out_stride_bytes);
+int pann_search_resident(pann_index* idx, const uint32_t* starts, uint32_t nstarts, const pann_query_params* qp);
+int pann_search_fetch(pann_index* idx, uint32_t* out_ids, float* out_dists, uint32_t* out_visited, uint32_t* out_cmps);
+
+/* beam_search (beamSearch.h:217-223) with both result lists, for parity tests and the build:
+ * per query the whole frontier (<= beam entries) and the whole visited list (sorted by (dist,id)).
+ * self_ids (may be NULL): query i IS base row self_ids[i] (beam_search_rerank__ in the build,
+ * vamana/index.h:249-259) — host_queries is then ignored and same_as() skips that row. */
+int pann_search_full(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes,
+                     const uint32_t* self_ids, const uint32_t* starts, uint32_t nstarts, const pann_query_params* qp,
+                     uint32_t fcap, uint32_t* fr_ids, float* fr_dists, uint32_t* n_frontier,
+                     uint32_t vcap, uint32_t* vis_ids, float* vis_dists, uint32_t* n_visited, uint32_t* out_cmps);
+
+/* knn_index::build_index (algorithms/vamana/index.h:150-186): num_passes x batch_insert (:188-316) of all n
+ * points in parlay::random_permutation order, start point 0, robustPrune (:63-120) with alpha on the last
+ * pass and 1.0 before; optional final per-row sort by distance.  The graph of the index is replaced.
+ * stats (may be NULL): n u32 each, as stats<indexType> accumulates them during the build.
+ * phase_seconds (may be NULL): beam search+prune / bidirect / reverse-edge prune, as index.h:313-315. */
+int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double alpha, int num_passes, int sort_neighbors,
+                      uint32_t* out_visited, uint32_t* out_cmps, double phase_seconds[3]);
+
+/* parlay::random_permutation<int>(n) with the default seed (parlay/random.h:154-159) — the insertion order. */
+int pann_random_permutation(int64_t n, int32_t* out);
+/* batch boundaries of batch_insert (vamana/index.h:206-209, :223-234); returns the number of batches */
+int64_t pann_batch_schedule(uint64_t n, uint64_t m, int64_t* lo, int64_t* hi, int64_t cap);
+
+/* compute_groundtruth (data_tools/compute_groundtruth.cpp:22-60) + write_ibin's per-row sort (:68-73):
+ * exact k nearest base rows of every query; rows sorted by (distance, id).  The base rows are those of the
+ * index; id_offset is added to the ids (base sharding across GPUs).  HOST query/result buffers. */
+int pann_groundtruth(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes, uint32_t k,
+                     int64_t id_offset, int32_t* out_ids, float* out_dists);
+/* same on the resident query set; results stay on the device (pann_groundtruth_fetch) */
+int pann_groundtruth_resident(pann_index* idx, uint32_t k, int64_t id_offset);
+int pann_groundtruth_fetch(pann_index* idx, int32_t* out_ids, float* out_dists);
+/* k-way merge of per-shard results (each [nq, k], sorted) into the global top-k under the (dist,id) order */
+int pann_groundtruth_merge(int device, uint32_t nshards, uint64_t nq, uint32_t k, const int32_t* ids, const float* dists,
+                           int32_t* out_ids, float* out_dists);
+
+/* pinned host memory for callers that want asynchronous copies */
+int pann_host_alloc(void** p, size_t bytes);
+int pann_host_free(void* p);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PANN_H_ */

@@ -1,0 +1,357 @@
+// beam_search.cuh — K1: batched greedy beam search over the fixed-degree graph, one query per warp.
+//
+// Behavioural contract: parlayANN::filtered_beam_search (algorithms/utils/beamSearch.h:22-214) with
+// use_filtering == false, bit for bit: same visit order, same lossy hash filter (direct mapped,
+// overwrite on miss, :52-59), same "skip the merge until beam/8 candidates" rule (:162-168), same cut
+// rule with its float-rounded threshold (:190-195), same counters (visited, full_dist_cmps).
+//
+// How it is laid out for the GPU (not a translation of the CPU code):
+//  * the frontier is ONE sorted array of 64-bit keys (sortable-float distance, id, visited flag); the
+//    reference's separate unvisited_frontier is implied by the flags: "next to visit" is the first
+//    unflagged entry, and offset+1 < remain <=> another unflagged entry exists;
+//  * a hop reads the graph row with one coalesced warp load, runs the hash filter for 32 neighbours at
+//    once (__match_any resolves same-slot collisions in list order), compacts the survivors and gathers
+//    their vectors with 128-bit loads, LPR lanes per row, several rows in flight per lane;
+//  * the merge is rank based: candidates are rank-sorted, de-duplicated, and each element's slot in the
+//    union is (its rank) + (lower_bound in the other list) — no serial set_union;
+//  * frontier, candidates, the visited list and the hash filter live in shared memory per warp; for
+//    wide beams (hash filter > 16 KB) the filter and the visited list move to a per-warp global
+//    scratch slab that stays L2 resident.
+#pragma once
+#include "pann_common.cuh"
+
+#define PANN_WARPS_PER_CTA 4
+#define PANN_FULL 0xffffffffu
+
+struct BeamArgs {
+  // index
+  const uint8_t* points; uint64_t n; uint32_t stride, nch, lpr;
+  const uint32_t* graph; uint32_t maxdeg;
+  // queries: either rows of `queries` (qstride bytes apart, 16-byte padded) or base rows self_ids[i]
+  const uint8_t* queries; uint64_t nq; uint32_t qstride;
+  const uint32_t* self_ids;
+  const uint32_t* starts; uint32_t nstarts;
+  // QueryParams
+  int k, beam, bits, degree_limit, cut_rule;  // cut_rule = (k > 0 && metric is L2)
+  long long limit;
+  double cut;
+  // capacities and per-warp shared-memory layout (byte offsets)
+  uint32_t ccap, vcap;
+  uint32_t off_frontB, off_cand, off_scand, off_nbr, off_q, off_vis, off_hash, warp_bytes;
+  // outputs (any may be null)
+  uint32_t* out_ids; float* out_dists;       // nq * k
+  uint32_t* out_visited; uint32_t* out_cmps; // nq
+  uint32_t* fr_ids; float* fr_dists; uint32_t* n_frontier; uint32_t fcap;   // full frontier
+  uint32_t* vis_ids; float* vis_dists; uint32_t* n_visited; uint32_t vout;  // full visited list (capacity vout)
+  int* status;                               // nq: 0 ok, 1 visited overflow, 2 fewer than k results, 3 too many starts
+  int* any_status;                           // OR of all non-zero statuses (one word)
+  const uint32_t* qmap;                      // optional: launch index -> query index (retries of a subset)
+  // global scratch (GS variant): per resident warp
+  uint32_t* g_hash; u64* g_vis;
+};
+
+__device__ __forceinline__ int pann_lower_bound(const u64* a, int n, u64 k1) {  // #{x : x>>1 < k1}
+  int lo = 0, hi = n;
+  while (lo < hi) { int mid = (lo + hi) >> 1; if ((a[mid] >> 1) < k1) lo = mid + 1; else hi = mid; }
+  return lo;
+}
+__device__ __forceinline__ int pann_upper_bound(const u64* a, int n, u64 k1) {  // #{x : x>>1 <= k1}
+  int lo = 0, hi = n;
+  while (lo < hi) { int mid = (lo + hi) >> 1; if ((a[mid] >> 1) <= k1) lo = mid + 1; else hi = mid; }
+  return lo;
+}
+
+// Distances from the query to `cnt` rows listed in ids[] (shared memory); calls emit(id, dist, valid)
+// warp-uniformly once per pass with one row per lane group (valid only on the group's lane 0).
+template <int DT, int METRIC, int CPL, class Emit>
+__device__ __forceinline__ void pann_row_distances(const BeamArgs& A, const uint32_t* ids, int cnt, const uint4* qreg,
+                                                   const uint4* qsm, int lane, Emit emit) {
+  const int lpr = A.lpr, G = 32 / lpr, grp = lane / lpr, sub = lane % lpr;
+  constexpr int U = (CPL == 1) ? 4 : ((CPL == 2) ? 2 : 1);  // row groups in flight per lane
+  for (int base = 0; base < cnt; base += G * U) {
+    uint32_t rid[U];
+    DistAcc<DT, METRIC> acc[U];
+    if constexpr (CPL > 0) {
+      uint4 v[U][CPL];
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        int r = base + u * G + grp;
+        rid[u] = ids[r < cnt ? r : cnt - 1];
+        const uint8_t* row = A.points + (u64)rid[u] * A.stride;
+#pragma unroll
+        for (int c = 0; c < CPL; c++) {
+          int ch = sub + c * lpr;
+          v[u][c] = (ch < (int)A.nch) ? pann_ldg16(row + ch * 16) : make_uint4(0, 0, 0, 0);
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; u++)
+#pragma unroll
+        for (int c = 0; c < CPL; c++) acc[u].add(v[u][c], qreg[c]);
+    } else {
+#pragma unroll
+      for (int u = 0; u < U; u++) {
+        int r = base + u * G + grp;
+        rid[u] = ids[r < cnt ? r : cnt - 1];
+        const uint8_t* row = A.points + (u64)rid[u] * A.stride;
+        for (int ch = sub; ch < (int)A.nch; ch += lpr) acc[u].add(pann_ldg16(row + ch * 16), qsm[ch]);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      acc[u].reduce(lpr);
+      int r = base + u * G + grp;
+      emit(rid[u], acc[u].result(), (sub == 0) && (r < cnt));
+    }
+  }
+}
+
+template <int DT, int METRIC, int CPL, bool GS>
+__global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kernel(const BeamArgs A) {
+  extern __shared__ __align__(16) uint8_t pann_smem[];
+  const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  uint8_t* ws = pann_smem + (size_t)wic * A.warp_bytes;
+  u64* bufA = reinterpret_cast<u64*>(ws);
+  u64* bufB = reinterpret_cast<u64*>(ws + A.off_frontB);
+  u64* cand = reinterpret_cast<u64*>(ws + A.off_cand);
+  u64* scand = reinterpret_cast<u64*>(ws + A.off_scand);
+  uint32_t* nbr = reinterpret_cast<uint32_t*>(ws + A.off_nbr);
+  uint4* qsm = reinterpret_cast<uint4*>(ws + A.off_q);
+  const long long wglobal = (long long)blockIdx.x * PANN_WARPS_PER_CTA + wic;
+  u64* vis;
+  uint32_t* hashf;
+  if constexpr (GS) {
+    vis = A.g_vis + (u64)wglobal * A.vcap;
+    hashf = A.g_hash + ((u64)wglobal << A.bits);
+  } else {
+    vis = reinterpret_cast<u64*>(ws + A.off_vis);
+    hashf = reinterpret_cast<uint32_t*>(ws + A.off_hash);
+  }
+  const uint32_t hmask = (1u << A.bits) - 1u;
+  const int B = A.beam;
+  const long long wstride = (long long)gridDim.x * PANN_WARPS_PER_CTA;
+
+  for (long long ql = wglobal; ql < (long long)A.nq; ql += wstride) {
+    const long long q = A.qmap ? (long long)A.qmap[ql] : ql;
+    // ---- per-query init: hash filter := -1 (beamSearch.h:53), query chunks into registers / shared memory
+    {
+      uint4 ones = make_uint4(~0u, ~0u, ~0u, ~0u);
+      uint4* h4 = reinterpret_cast<uint4*>(hashf);
+      for (int i = lane; i < (1 << A.bits) / 4; i += 32) h4[i] = ones;
+    }
+    const long long self = A.self_ids ? (long long)A.self_ids[q] : -1;
+    const uint8_t* qrow = A.self_ids ? A.points + (u64)self * A.stride : A.queries + (u64)q * A.qstride;
+    uint4 qreg[CPL > 0 ? CPL : 1];
+    if constexpr (CPL > 0) {
+#pragma unroll
+      for (int c = 0; c < CPL; c++) {
+        int ch = (lane % A.lpr) + c * A.lpr;
+        qreg[c] = (ch < (int)A.nch) ? pann_ldg16(qrow + ch * 16) : make_uint4(0, 0, 0, 0);
+      }
+    } else {
+      for (int ch = lane; ch < (int)A.nch; ch += 32) qsm[ch] = pann_ldg16(qrow + ch * 16);
+    }
+    __syncwarp();
+
+    u64* front = bufA;
+    u64* nf = bufB;
+    int F = 0, V = 0, C = 0, status = 0;
+    unsigned cmps = A.nstarts;  // beamSearch.h:84
+
+    // ---- starting points (:64-70): distances, hash-filter insertion in list order, sort
+    if ((int)A.nstarts > B || A.nstarts > A.ccap) {
+      status = 3;
+    } else {
+      for (uint32_t s0 = 0; s0 < A.nstarts; s0 += A.maxdeg) {
+        int cnt = min((int)A.maxdeg, (int)(A.nstarts - s0));
+        for (int i = lane; i < cnt; i += 32) nbr[i] = A.starts[s0 + i];
+        __syncwarp();
+        pann_row_distances<DT, METRIC, CPL>(A, nbr, cnt, qreg, qsm, lane, [&](uint32_t id, float d, bool ok) {
+          unsigned m = __ballot_sync(PANN_FULL, ok);
+          if (ok) cand[C + __popc(m & lt_mask)] = pann_key(d, id);
+          C += __popc(m);
+        });
+        __syncwarp();
+      }
+      if (lane == 0)
+        for (uint32_t i = 0; i < A.nstarts; i++) { uint32_t a = A.starts[i]; hashf[(uint32_t)pann_hash64_2(a) & hmask] = a; }
+      for (int i = lane; i < C; i += 32) {  // rank sort into the frontier
+        u64 ci = cand[i];
+        int r = 0;
+        for (int j = 0; j < C; j++) { u64 cj = cand[j]; r += (cj < ci) || (cj == ci && j < i); }
+        front[r] = ci;
+      }
+      F = C;
+      C = 0;
+      __syncwarp();
+    }
+
+    // ---- main loop (:107-209)
+    while (status == 0) {
+      // next to visit = first unflagged frontier entry  (unvisited_frontier[offset], :109)
+      int pos = -1;
+      for (int base = 0; base < F && pos < 0; base += 32) {
+        int i = base + lane;
+        unsigned m = __ballot_sync(PANN_FULL, i < F && !(front[i] & 1ull));
+        if (m) pos = base + __ffs(m) - 1;
+      }
+      if (pos < 0 || (long long)V >= A.limit) break;  // remain <= offset, or visit limit reached (:107)
+      const u64 cur = front[pos];
+      __syncwarp();
+      if (lane == 0) front[pos] = cur | 1ull;
+      // visited.insert(upper_bound(cur)) (:112-113)
+      if (V >= (int)A.vcap) { status = 1; break; }
+      {
+        int ip = pann_upper_bound(vis, V, cur >> 1);
+        for (int top = V; top > ip; top -= 32) {  // shift [ip, V) up by one, highest block first
+          int i = top - 1 - lane;
+          u64 x = 0;
+          if (i >= ip) x = vis[i];
+          __syncwarp();
+          if (i >= ip) vis[i + 1] = x;
+          __syncwarp();
+        }
+        if (lane == 0) vis[ip] = cur & ~1ull;
+        V++;
+      }
+      const bool full = (F == B);  // :115
+      const float cutoff = full ? pann_key_dist(front[F - 1]) : 2147483648.0f;  // (float)INT_MAX (:150-152)
+      // neighbours that pass the hash filter, in list order (:130-136)
+      const uint32_t* grow = A.graph + (u64)pann_key_id(cur) * (A.maxdeg + 1);
+      const int deg = (int)__ldg(grow);
+      const int ne = min(deg, A.degree_limit);
+      int S = 0;
+      __syncwarp();
+      for (int base = 0; base < ne; base += 32) {
+        int i = base + lane;
+        bool act = i < ne;
+        uint32_t a = act ? __ldg(grow + 1 + i) : 0u;
+        uint32_t loc = act ? ((uint32_t)pann_hash64_2(a) & hmask) : (0x80000000u | lane);  // inactive lanes never match
+        unsigned peers = __match_any_sync(PANN_FULL, loc);
+        unsigned prev = peers & lt_mask;
+        uint32_t from_prev = __shfl_sync(PANN_FULL, a, prev ? (31 - __clz(prev)) : lane);
+        bool seen = false;
+        if (act) {
+          uint32_t slot = prev ? from_prev : hashf[loc];
+          seen = (slot == a);
+        }
+        __syncwarp();
+        if (act && (peers >> lane) <= 1u) hashf[loc] = a;  // last lane of each slot group leaves its id there
+        bool keep = act && !seen && ((long long)a != self);
+        unsigned km = __ballot_sync(PANN_FULL, keep);
+        if (keep) nbr[S + __popc(km & lt_mask)] = a;
+        S += __popc(km);
+        __syncwarp();
+      }
+      cmps += S;  // :155
+      if (S + C > (int)A.ccap) { status = 1; break; }  // cannot happen (ccap >= maxdeg + beam/8); guards memory
+      pann_row_distances<DT, METRIC, CPL>(A, nbr, S, qreg, qsm, lane, [&](uint32_t id, float d, bool ok) {
+        bool take = ok && (d < cutoff);  // :153-158
+        unsigned m = __ballot_sync(PANN_FULL, take);
+        if (take) cand[C + __popc(m & lt_mask)] = pann_key(d, id);
+        C += __popc(m);
+      });
+      __syncwarp();
+      // skip the merge while there are too few candidates (:162-168); candidates are kept
+      if (C == 0) continue;
+      if (A.limit >= 2ll * B && C < B / 8) {
+        bool more = false;
+        for (int base = 0; base < F && !more; base += 32) {
+          int i = base + lane;
+          more = __any_sync(PANN_FULL, i < F && !(front[i] & 1ull));
+        }
+        if (more) continue;
+      }
+      // ---- merge (:173-208).  (a) stable rank sort of the candidates
+      for (int i = lane; i < C; i += 32) {
+        u64 ci = cand[i];
+        int r = 0;
+        for (int j = 0; j < C; j++) { u64 cj = cand[j]; r += (cj < ci) || (cj == ci && j < i); }
+        scand[r] = ci;
+      }
+      __syncwarp();
+      // (b) drop duplicates (std::unique, :174) and entries already in the frontier (set_union keeps one),
+      //     place the rest: slot = rank among kept candidates + #frontier entries below it
+      int Cv = 0;
+      for (int base = 0; base < C; base += 32) {
+        int i = base + lane;
+        bool valid = false;
+        int lbf = 0;
+        u64 c = 0;
+        if (i < C) {
+          c = scand[i];
+          bool dup = i > 0 && scand[i - 1] == c;
+          lbf = pann_lower_bound(front, F, c >> 1);
+          bool infr = lbf < F && (front[lbf] >> 1) == (c >> 1);
+          valid = !dup && !infr;
+        }
+        unsigned m = __ballot_sync(PANN_FULL, valid);
+        int vr = Cv + __popc(m & lt_mask);
+        if (valid) {
+          cand[vr] = c;
+          int np = vr + lbf;
+          if (np < B) {
+            int vp = pann_lower_bound(vis, V, c >> 1);  // re-entering an already visited vertex keeps it visited
+            u64 fl = (vp < V && (vis[vp] >> 1) == (c >> 1)) ? 1ull : 0ull;
+            nf[np] = c | fl;
+          }
+        }
+        Cv += __popc(m);
+      }
+      __syncwarp();
+      // (c) frontier entries move up by the number of kept candidates below them
+      for (int i = lane; i < F; i += 32) {
+        u64 f = front[i];
+        int np = i + pann_lower_bound(cand, Cv, f >> 1);
+        if (np < B) nf[np] = f;
+      }
+      int nfs = min(B, F + Cv);  // :185
+      C = 0;
+      __syncwarp();
+      // (d) cut rule (:190-195): threshold (float)(cut * (double)dist[k]), never below the old size
+      if (A.cut_rule && nfs > A.k) {
+        float thr = (float)(A.cut * (double)pann_key_dist(nf[A.k]));
+        int c = pann_upper_bound(nf, nfs, (u64)pann_fsort(thr) << 31);
+        nfs = max(c, F);
+      }
+      u64* t = front; front = nf; nf = t;
+      F = nfs;
+    }
+
+    // ---- results
+    if (status == 0 && F < A.k) status = 2;  // beamSearch.h:416-419
+    if (A.out_ids)
+      for (int j = lane; j < A.k; j += 32) {
+        bool ok = j < F;
+        A.out_ids[q * A.k + j] = ok ? pann_key_id(front[j]) : 0xffffffffu;
+        if (A.out_dists) A.out_dists[q * A.k + j] = ok ? pann_key_dist(front[j]) : 0.f;
+      }
+    if (A.fr_ids)
+      for (int j = lane; j < F && j < (int)A.fcap; j += 32) {
+        A.fr_ids[q * A.fcap + j] = pann_key_id(front[j]);
+        A.fr_dists[q * A.fcap + j] = pann_key_dist(front[j]);
+      }
+    if (A.vis_ids) {
+      if (V > (int)A.vout && status == 0) status = 1;
+      for (int j = lane; j < V && j < (int)A.vout; j += 32) {
+        A.vis_ids[q * A.vout + j] = pann_key_id(vis[j]);
+        if (A.vis_dists) A.vis_dists[q * A.vout + j] = pann_key_dist(vis[j]);
+      }
+    }
+    if (lane == 0) {
+      if (A.out_visited) A.out_visited[q] = V;
+      if (A.out_cmps) A.out_cmps[q] = cmps;
+      if (A.n_frontier) A.n_frontier[q] = F;
+      if (A.n_visited) A.n_visited[q] = V;
+      if (A.status) A.status[q] = status;
+      if (status && A.any_status) atomicOr(A.any_status, 1 << status);
+    }
+    __syncwarp();
+  }
+}
+
+// kernel lookup, one translation unit per element type (beam_search_{f32,u8,i8}.cu)
+const void* pann_beam_kernel_dt0(int metric, int cpl, bool gs);
+const void* pann_beam_kernel_dt1(int metric, int cpl, bool gs);
+const void* pann_beam_kernel_dt2(int metric, int cpl, bool gs);

@@ -1,0 +1,76 @@
+// host_util.cpp — host-side pieces of the Vamana build that decide WHAT the device inserts and WHEN:
+// the insertion order and the batch schedule.  Both are part of the result (a different order or
+// schedule gives a different graph), so they follow the reference exactly.
+#include <math.h>
+#include <stdint.h>
+
+#include <algorithm>
+#include <utility>
+#include <vector>
+
+// parlay::hash64 (parlay/utilities.h:132-142)
+static inline uint64_t hash64(uint64_t u) {
+  uint64_t v = u * 3935559000370003845ull + 2691343689449507681ull;
+  v ^= v >> 21; v ^= v << 37; v ^= v >> 4;
+  v *= 4768777513237032717ull;
+  v ^= v << 20; v ^= v >> 41; v ^= v << 5;
+  return v;
+}
+
+namespace {
+struct Rnd {  // parlay::random (parlay/random.h:62-75)
+  uint64_t state;
+  uint64_t ith(uint64_t i) const { return hash64(i + state); }
+  Rnd fork(uint64_t i) const { return Rnd{hash64(hash64(i + state))}; }
+};
+void knuth_shuffle(int32_t* a, size_t m, Rnd r) {  // parlay/random.h:80-89
+  for (size_t i = m; i-- > 1;) std::swap(a[i], a[r.ith(i) % (i + 1)]);
+}
+}  // namespace
+
+// parlay::random_permutation<int>(n) with the default generator (parlay/random.h:154-159, :91-137):
+// below 8192 elements one sequential Knuth shuffle; otherwise a stable counting sort into 2^bits random
+// buckets followed by an independent Knuth shuffle of each bucket.
+void pann_host_random_permutation(int64_t n, int32_t* out) {
+  Rnd r{0};
+  if (n < 8192) {
+    for (int64_t i = 0; i < n; i++) out[i] = (int32_t)i;
+    if (n > 1) knuth_shuffle(out, (size_t)n, r);
+    return;
+  }
+  size_t lg = 0;
+  for (uint64_t b = (uint64_t)n - 1; b > 0; b >>= 1) lg++;
+  const size_t bits = ((uint64_t)n < (1ull << 27)) ? (lg - 7) / 2 : (lg - 17);
+  const size_t nb = (size_t)1 << bits, mask = nb - 1;
+  std::vector<size_t> start(nb + 1, 0);
+  for (int64_t i = 0; i < n; i++) start[(r.ith((uint64_t)i) & mask) + 1]++;
+  for (size_t b = 0; b < nb; b++) start[b + 1] += start[b];
+  std::vector<size_t> fill(start.begin(), start.end() - 1);
+  for (int64_t i = 0; i < n; i++) out[fill[r.ith((uint64_t)i) & mask]++] = (int32_t)i;
+  for (size_t b = 0; b < nb; b++)
+    if (start[b + 1] - start[b] > 1) knuth_shuffle(out + start[b], start[b + 1] - start[b], r.fork(b));
+}
+
+// batch_insert's schedule (algorithms/vamana/index.h:206-209, :223-234) with base = 2, max_fraction = .02:
+// prefix-doubling batches [2^i - 1, 2^(i+1) - 1) while 2^i <= max_batch, then fixed strides of max_batch.
+int64_t pann_host_batch_schedule(uint64_t n, uint64_t m, int64_t* lo, int64_t* hi, int64_t cap) {
+  size_t max_batch = std::min((size_t)(0.02 * (double)(float)n), (size_t)1000000);
+  if (max_batch == 0) max_batch = n;
+  size_t inc = 0, count = 0;
+  int64_t nb = 0;
+  while (count < m) {
+    size_t f, c;
+    if (pow(2.0, (double)inc) <= (double)max_batch) {
+      f = (size_t)pow(2.0, (double)inc) - 1;
+      c = std::min((size_t)pow(2.0, (double)(inc + 1)) - 1, (size_t)m);
+      count = c;
+    } else {
+      f = count;
+      c = std::min(count + max_batch, (size_t)m);
+      count += max_batch;
+    }
+    if (nb < cap) { lo[nb] = (int64_t)f; hi[nb] = (int64_t)c; }
+    nb++; inc++;
+  }
+  return nb;
+}

@@ -1,0 +1,441 @@
+// pann_api.cu — the C ABI (include/pann.h): index lifetime, query sets, batched beam search.
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "pann_internal.h"
+
+static thread_local std::string g_err;
+void pann_set_error(const std::string& msg) { g_err = msg; }
+
+extern "C" const char* pann_last_error(void) { return g_err.c_str(); }
+extern "C" const char* pann_version(void) { return "parlayann_b200 0.1 (sm_100a)"; }
+extern "C" int pann_device_count(int* count) {
+  int c = 0;
+  cudaError_t e = cudaGetDeviceCount(&c);
+  if (e != cudaSuccess) { *count = 0; pann_set_error(std::string("no CUDA device: ") + cudaGetErrorString(e)); return 1; }
+  *count = c;
+  return 0;
+}
+
+extern "C" int pann_host_alloc(void** p, size_t bytes) { PANN_CUDA(cudaHostAlloc(p, bytes, cudaHostAllocDefault)); return 0; }
+extern "C" int pann_host_free(void* p) { PANN_CUDA(cudaFreeHost(p)); return 0; }
+
+int pann_pinned(pann_index* idx, size_t bytes, void** p) {
+  if (bytes > idx->pinned_cap) {
+    if (idx->pinned) cudaFreeHost(idx->pinned);
+    idx->pinned = nullptr; idx->pinned_cap = 0;
+    size_t want = bytes + bytes / 4 + 4096;
+    PANN_CUDA(cudaHostAlloc(&idx->pinned, want, cudaHostAllocDefault));
+    idx->pinned_cap = want;
+  }
+  *p = idx->pinned;
+  return 0;
+}
+
+static int index_alloc(pann_index** out, int device, int dtype, int metric, uint64_t n, uint32_t dims, uint32_t maxdeg) {
+  if (dtype < 0 || dtype > 2) PANN_FAIL("pann_index_create: dtype must be PANN_F32, PANN_U8 or PANN_I8");
+  if (metric < 0 || metric > 1) PANN_FAIL("pann_index_create: metric must be PANN_L2 or PANN_MIPS");
+  if (n == 0 || dims == 0) PANN_FAIL("pann_index_create: empty point set");
+  if (n >= (1ull << 31)) PANN_FAIL("pann_index_create: n must be below 2^31");
+  int ndev = 0;
+  if (pann_device_count(&ndev) || ndev == 0) PANN_FAIL("pann_index_create: no CUDA device (this library has no CPU fallback)");
+  if (device < 0 || device >= ndev) PANN_FAIL("pann_index_create: bad device ordinal");
+  PANN_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  PANN_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major < 10) PANN_FAIL(std::string("pann_index_create: built for sm_100a (B200); device is ") + prop.name);
+  pann_index* idx = new pann_index();
+  idx->device = device; idx->dtype = dtype; idx->metric = metric; idx->n = n; idx->dims = dims; idx->maxdeg = maxdeg;
+  idx->sms = prop.multiProcessorCount;
+  idx->smem_optin = prop.sharedMemPerBlockOptin;
+  idx->geom = pann_row_geom(dims, dtype);
+  PANN_CUDA(cudaStreamCreateWithFlags(&idx->stream, cudaStreamNonBlocking));
+  PANN_CUDA(cudaEventCreate(&idx->ev0));
+  PANN_CUDA(cudaEventCreate(&idx->ev1));
+  PANN_CUDA(cudaMalloc(&idx->points, (size_t)n * idx->geom.stride));
+  PANN_CUDA(cudaMalloc(&idx->graph, (size_t)n * (maxdeg + 1) * sizeof(uint32_t)));
+  PANN_CUDA(cudaMemsetAsync(idx->graph, 0, (size_t)n * (maxdeg + 1) * sizeof(uint32_t), idx->stream));
+  *out = idx;
+  return 0;
+}
+
+extern "C" int pann_index_create(pann_index** out, int device, int dtype, int metric, uint64_t n, uint32_t dims,
+                                 uint64_t row_stride_bytes, const void* host_points, uint32_t max_degree,
+                                 const uint32_t* host_graph) {
+  if (!out || !host_points) PANN_FAIL("pann_index_create: null argument");
+  pann_index* idx = nullptr;
+  if (index_alloc(&idx, device, dtype, metric, n, dims, max_degree)) return 1;
+  const size_t rowb = (size_t)dims * idx->geom.elt;
+  if (row_stride_bytes < rowb) { pann_index_destroy(idx); PANN_FAIL("pann_index_create: row stride smaller than a row"); }
+  if (idx->geom.stride != rowb) PANN_CUDA(cudaMemsetAsync(idx->points, 0, (size_t)n * idx->geom.stride, idx->stream));
+  PANN_CUDA(cudaMemcpy2DAsync(idx->points, idx->geom.stride, host_points, row_stride_bytes, rowb, n, cudaMemcpyHostToDevice, idx->stream));
+  if (host_graph)
+    PANN_CUDA(cudaMemcpyAsync(idx->graph, host_graph, (size_t)n * (max_degree + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, idx->stream));
+  PANN_CUDA(cudaStreamSynchronize(idx->stream));
+  *out = idx;
+  return 0;
+}
+
+extern "C" int pann_index_create_synthetic(pann_index** out, int device, int dtype, int metric, uint64_t n, uint32_t dims,
+                                           uint32_t max_degree, int gen_kind, uint64_t seed, uint64_t stream,
+                                           uint32_t latent_r, uint32_t n_clusters) {
+  if (!out) PANN_FAIL("pann_index_create_synthetic: null argument");
+  int want = gen_kind == PANN_GEN_KIND_U8 ? PANN_U8 : (gen_kind == PANN_GEN_KIND_I8 ? PANN_I8 : PANN_F32);
+  if (want != dtype) PANN_FAIL("pann_index_create_synthetic: generator kind does not match dtype");
+  pann_index* idx = nullptr;
+  if (index_alloc(&idx, device, dtype, metric, n, dims, max_degree)) return 1;
+  if (pann_gen_rows_device(gen_kind, seed, stream, 0, n, dims, latent_r, n_clusters, idx->points, idx->geom.stride, idx->stream)) {
+    pann_index_destroy(idx);
+    return 1;
+  }
+  *out = idx;
+  return 0;
+}
+
+extern "C" void pann_index_destroy(pann_index* idx) {
+  if (!idx) return;
+  cudaSetDevice(idx->device);
+  if (idx->stream) cudaStreamSynchronize(idx->stream);
+  if (idx->points) cudaFree(idx->points);
+  if (idx->graph) cudaFree(idx->graph);
+  idx->queries.release(); idx->results.release(); idx->scratch_hash.release(); idx->scratch_vis.release();
+  idx->starts.release(); idx->flag.release(); idx->qmap.release(); idx->misc.release();
+  idx->gt_ids.release(); idx->gt_dists.release();
+  if (idx->pinned) cudaFreeHost(idx->pinned);
+  if (idx->ev0) cudaEventDestroy(idx->ev0);
+  if (idx->ev1) cudaEventDestroy(idx->ev1);
+  if (idx->stream) cudaStreamDestroy(idx->stream);
+  delete idx;
+}
+
+extern "C" int pann_index_set_graph(pann_index* idx, const uint32_t* host_graph) {
+  if (!idx || !host_graph) PANN_FAIL("pann_index_set_graph: null argument");
+  PANN_CUDA(cudaSetDevice(idx->device));
+  PANN_CUDA(cudaMemcpyAsync(idx->graph, host_graph, (size_t)idx->n * (idx->maxdeg + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, idx->stream));
+  PANN_CUDA(cudaStreamSynchronize(idx->stream));
+  return 0;
+}
+extern "C" int pann_index_get_graph(pann_index* idx, uint32_t* host_graph_out) {
+  if (!idx || !host_graph_out) PANN_FAIL("pann_index_get_graph: null argument");
+  PANN_CUDA(cudaSetDevice(idx->device));
+  PANN_CUDA(cudaMemcpyAsync(host_graph_out, idx->graph, (size_t)idx->n * (idx->maxdeg + 1) * sizeof(uint32_t), cudaMemcpyDeviceToHost, idx->stream));
+  PANN_CUDA(cudaStreamSynchronize(idx->stream));
+  return 0;
+}
+extern "C" int pann_index_get_points(pann_index* idx, uint64_t row0, uint64_t nrows, void* host_out, uint64_t out_stride_bytes) {
+  if (!idx || !host_out) PANN_FAIL("pann_index_get_points: null argument");
+  if (row0 + nrows > idx->n) PANN_FAIL("pann_index_get_points: row range out of bounds");
+  PANN_CUDA(cudaSetDevice(idx->device));
+  const size_t rowb = (size_t)idx->dims * idx->geom.elt;
+  PANN_CUDA(cudaMemcpy2DAsync(host_out, out_stride_bytes, idx->points + row0 * idx->geom.stride, idx->geom.stride, rowb, nrows, cudaMemcpyDeviceToHost, idx->stream));
+  PANN_CUDA(cudaStreamSynchronize(idx->stream));
+  return 0;
+}
+extern "C" int pann_index_info(pann_index* idx, uint64_t* n, uint32_t* dims, uint32_t* max_degree, int* dtype, int* metric) {
+  if (!idx) PANN_FAIL("pann_index_info: null index");
+  if (n) *n = idx->n;
+  if (dims) *dims = idx->dims;
+  if (max_degree) *max_degree = idx->maxdeg;
+  if (dtype) *dtype = idx->dtype;
+  if (metric) *metric = idx->metric;
+  return 0;
+}
+extern "C" int pann_index_last_timing(pann_index* idx, float* kernel_ms, int* launches) {
+  if (!idx) PANN_FAIL("pann_index_last_timing: null index");
+  if (kernel_ms) *kernel_ms = idx->last_ms;
+  if (launches) *launches = idx->last_launches;
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K1 planning and launch
+static inline uint32_t al16(size_t x) { return (uint32_t)((x + 15) / 16 * 16); }
+
+static const void* beam_kernel(int dtype, int metric, int cpl, bool gs) {
+  switch (dtype) {
+    case PANN_DT_F32: return pann_beam_kernel_dt0(metric, cpl, gs);
+    case PANN_DT_U8: return pann_beam_kernel_dt1(metric, cpl, gs);
+    default: return pann_beam_kernel_dt2(metric, cpl, gs);
+  }
+}
+
+static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap) {
+  const PannRowGeom& g = idx->geom;
+  const int cplT = g.cpl <= 3 ? (int)g.cpl : 0;
+  const uint32_t B = (uint32_t)A.beam;
+  A.ccap = std::max<uint32_t>(A.maxdeg + B / 8 + 1, A.nstarts);
+  A.vcap = vcap;
+  A.off_frontB = al16((size_t)B * 8);
+  A.off_cand = A.off_frontB + al16((size_t)B * 8);
+  A.off_scand = A.off_cand + al16((size_t)A.ccap * 8);
+  A.off_nbr = A.off_scand + al16((size_t)A.ccap * 8);
+  A.off_q = A.off_nbr + al16((size_t)std::max<uint32_t>(A.maxdeg, 1) * 4);
+  A.off_vis = A.off_q + (cplT == 0 ? g.stride : 0);
+  A.off_hash = A.off_vis + (gs ? 0 : al16((size_t)vcap * 8));
+  A.warp_bytes = A.off_hash + (gs ? 0 : (4u << A.bits));
+  const size_t cta_bytes = (size_t)A.warp_bytes * PANN_WARPS_PER_CTA;
+  if (cta_bytes > idx->smem_optin) PANN_FAIL("beam search: per-CTA shared memory exceeds the device limit (beam too wide for this max degree)");
+  const void* fn = beam_kernel(idx->dtype, idx->metric, cplT, gs);
+  PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
+  int per_sm = 0;
+  PANN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, PANN_WARPS_PER_CTA * 32, cta_bytes));
+  if (per_sm < 1) PANN_FAIL("beam search: kernel does not fit on an SM");
+  long long want = ((long long)A.nq + PANN_WARPS_PER_CTA - 1) / PANN_WARPS_PER_CTA;
+  int grid = (int)std::min<long long>(want, (long long)per_sm * idx->sms);
+  if (grid < 1) grid = 1;
+  if (gs) {
+    size_t warps = (size_t)grid * PANN_WARPS_PER_CTA;
+    if (idx->scratch_hash.reserve(warps * (4ull << A.bits))) return 1;
+    if (idx->scratch_vis.reserve(warps * (size_t)vcap * 8)) return 1;
+    A.g_hash = idx->scratch_hash.as<uint32_t>();
+    A.g_vis = idx->scratch_vis.as<u64>();
+  }
+  void* args[] = {(void*)&A};
+  PANN_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(PANN_WARPS_PER_CTA * 32), args, cta_bytes, idx->stream));
+  idx->last_launches++;
+  return 0;
+}
+
+int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint32_t qstride, const uint32_t* d_self_ids,
+                    const uint32_t* h_starts, uint32_t nstarts, const pann_query_params* qp, const SearchOutputs& out,
+                    int* status_or) {
+  if (nstarts == 0 || !h_starts) PANN_FAIL("beam search expects at least one start point");  // beamSearch.h:38-41
+  if (qp->beam < 1 || qp->beam > 65536) PANN_FAIL("beam search: beam width out of range");
+  if (qp->k < 0) PANN_FAIL("beam search: k must be non-negative");
+  for (uint32_t i = 0; i < nstarts; i++)
+    if (h_starts[i] >= idx->n) PANN_FAIL("beam search: start point out of range");
+  *status_or = 0;
+  if (nq == 0) return 0;
+  if (idx->starts.reserve(sizeof(uint32_t) * nstarts) || idx->flag.reserve(sizeof(int))) return 1;
+  PANN_CUDA(cudaMemcpyAsync(idx->starts.p, h_starts, sizeof(uint32_t) * nstarts, cudaMemcpyHostToDevice, idx->stream));
+  PANN_CUDA(cudaMemsetAsync(idx->flag.p, 0, sizeof(int), idx->stream));
+
+  BeamArgs A;
+  memset(&A, 0, sizeof(A));
+  A.points = idx->points; A.n = idx->n; A.stride = idx->geom.stride; A.nch = idx->geom.nch; A.lpr = idx->geom.lpr;
+  A.graph = idx->graph; A.maxdeg = idx->maxdeg;
+  A.queries = d_queries; A.nq = nq; A.qstride = qstride; A.self_ids = d_self_ids;
+  A.starts = idx->starts.as<uint32_t>(); A.nstarts = nstarts;
+  const long long beam = qp->beam;
+  A.k = (int)qp->k; A.beam = (int)beam;
+  A.bits = std::max<int>(10, (int)std::ceil(std::log2((double)(int)(beam * beam))) - 2);  // beamSearch.h:52
+  A.limit = qp->limit < 0 ? (long long)idx->n : qp->limit;
+  A.degree_limit = qp->degree_limit < 0 ? (int)idx->maxdeg : (int)std::min<int64_t>(qp->degree_limit, idx->maxdeg);
+  A.cut = qp->cut;
+  A.cut_rule = (qp->k > 0 && idx->metric == PANN_M_L2) ? 1 : 0;
+  A.out_ids = out.ids; A.out_dists = out.dists; A.out_visited = out.visited; A.out_cmps = out.cmps;
+  A.fr_ids = out.fr_ids; A.fr_dists = out.fr_dists; A.n_frontier = out.n_frontier; A.fcap = out.fcap;
+  A.vis_ids = out.vis_ids; A.vis_dists = out.vis_dists; A.n_visited = out.n_visited; A.vout = out.vout;
+  A.status = out.status; A.any_status = idx->flag.as<int>();
+
+  // shared-memory variant while the hash filter is <= 16 KB per warp; visited-list capacity is a guess
+  // that the retry below makes safe
+  const char* force = getenv("PANN_FORCE_GLOBAL_SCRATCH");
+  bool gs = A.bits > 12 || (force && force[0] == '1');
+  const long long vbig = std::min<long long>(A.limit, std::max<long long>(8 * beam + 4096, 16384));
+  uint32_t vcap = gs ? (uint32_t)vbig : (uint32_t)std::min<long long>(A.limit, std::max<long long>(2 * beam, beam + 64));
+  if (vcap < 1) vcap = 1;
+  if (launch_beam(idx, A, gs, vcap)) return 1;
+  int flag = 0;
+  PANN_CUDA(cudaMemcpyAsync(&flag, idx->flag.p, sizeof(int), cudaMemcpyDeviceToHost, idx->stream));
+  PANN_CUDA(cudaStreamSynchronize(idx->stream));
+  if ((flag & (1 << 1)) && !gs) {
+    // some visited lists outgrew shared memory: redo exactly those queries with the global-scratch variant
+    std::vector<int> st(nq);
+    PANN_CUDA(cudaMemcpy(st.data(), out.status, sizeof(int) * nq, cudaMemcpyDeviceToHost));
+    std::vector<uint32_t> redo;
+    for (uint64_t i = 0; i < nq; i++) if (st[i] == 1) redo.push_back((uint32_t)i);
+    if (idx->qmap.reserve(sizeof(uint32_t) * redo.size())) return 1;
+    PANN_CUDA(cudaMemcpyAsync(idx->qmap.p, redo.data(), sizeof(uint32_t) * redo.size(), cudaMemcpyHostToDevice, idx->stream));
+    PANN_CUDA(cudaMemsetAsync(idx->flag.p, 0, sizeof(int), idx->stream));
+    A.qmap = idx->qmap.as<uint32_t>();
+    A.nq = redo.size();
+    if (launch_beam(idx, A, true, (uint32_t)vbig)) return 1;
+    int flag2 = 0;
+    PANN_CUDA(cudaMemcpyAsync(&flag2, idx->flag.p, sizeof(int), cudaMemcpyDeviceToHost, idx->stream));
+    PANN_CUDA(cudaStreamSynchronize(idx->stream));
+    flag = (flag & ~(1 << 1)) | flag2;
+  }
+  *status_or = flag;
+  return 0;
+}
+
+static int check_status(int flag) {
+  if (flag & (1 << 3)) PANN_FAIL("beam search: more start points than the beam width (the reference overflows here, beamSearch.h:74-76)");
+  if (flag & (1 << 1)) PANN_FAIL("beam search: visited list exceeded the scratch capacity");
+  if (flag & (1 << 2)) PANN_FAIL("Error: beam search does not return enough candidates");  // beamSearch.h:416-419
+  return 0;
+}
+
+static int validate_qp(const pann_query_params* qp) {
+  if (!qp) PANN_FAIL("null query params");
+  if (qp->k > qp->beam) PANN_FAIL("Error: beam search parameter Q = " + std::to_string(qp->beam) + " same size or smaller than k = " + std::to_string(qp->k));  // beamSearch.h:549-553
+  return 0;
+}
+
+// packed result block: ids | dists | visited | cmps | status
+struct ResLayout { size_t ids, dists, visited, cmps, status, total; };
+static ResLayout res_layout(uint64_t nq, uint32_t k) {
+  ResLayout L;
+  L.ids = 0; L.dists = L.ids + 4ull * nq * k; L.visited = L.dists + 4ull * nq * k; L.cmps = L.visited + 4ull * nq;
+  L.status = L.cmps + 4ull * nq; L.total = L.status + 4ull * nq;
+  return L;
+}
+
+static int search_common(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t qstride, const uint32_t* starts,
+                         uint32_t nstarts, const pann_query_params* qp) {
+  ResLayout L = res_layout(nq, (uint32_t)qp->k);
+  if (idx->results.reserve(L.total + 16)) return 1;
+  idx->res_nq = nq; idx->res_k = (uint32_t)qp->k;
+  uint8_t* r = idx->results.as<uint8_t>();
+  SearchOutputs o;
+  o.ids = (uint32_t*)(r + L.ids); o.dists = (float*)(r + L.dists); o.visited = (uint32_t*)(r + L.visited);
+  o.cmps = (uint32_t*)(r + L.cmps); o.status = (int*)(r + L.status);
+  int flag = 0;
+  idx->last_launches = 0;
+  PANN_CUDA(cudaEventRecord(idx->ev0, idx->stream));
+  if (pann_run_search(idx, d_q, nq, qstride, nullptr, starts, nstarts, qp, o, &flag)) return 1;
+  PANN_CUDA(cudaEventRecord(idx->ev1, idx->stream));
+  PANN_CUDA(cudaEventSynchronize(idx->ev1));
+  PANN_CUDA(cudaEventElapsedTime(&idx->last_ms, idx->ev0, idx->ev1));
+  return check_status(flag);
+}
+
+static int upload_queries(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes) {
+  const size_t rowb = (size_t)idx->dims * idx->geom.elt;
+  if (q_stride_bytes < rowb) PANN_FAIL("query stride smaller than a row");
+  if (idx->queries.reserve((size_t)nq * idx->geom.stride + 16)) return 1;
+  if (idx->geom.stride != rowb) PANN_CUDA(cudaMemsetAsync(idx->queries.p, 0, (size_t)nq * idx->geom.stride, idx->stream));
+  if (q_stride_bytes == rowb && idx->geom.stride == rowb)
+    PANN_CUDA(cudaMemcpyAsync(idx->queries.p, host_queries, (size_t)nq * rowb, cudaMemcpyHostToDevice, idx->stream));
+  else
+    PANN_CUDA(cudaMemcpy2DAsync(idx->queries.p, idx->geom.stride, host_queries, q_stride_bytes, rowb, nq, cudaMemcpyHostToDevice, idx->stream));
+  idx->nq = nq;
+  return 0;
+}
+
+extern "C" int pann_queries_upload(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes) {
+  if (!idx || !host_queries) PANN_FAIL("pann_queries_upload: null argument");
+  PANN_CUDA(cudaSetDevice(idx->device));
+  if (upload_queries(idx, host_queries, nq, q_stride_bytes)) return 1;
+  PANN_CUDA(cudaStreamSynchronize(idx->stream));
+  return 0;
+}
+extern "C" int pann_queries_synthetic(pann_index* idx, uint64_t nq, int gen_kind, uint64_t seed, uint64_t stream,
+                                      uint32_t latent_r, uint32_t n_clusters) {
+  if (!idx) PANN_FAIL("pann_queries_synthetic: null index");
+  PANN_CUDA(cudaSetDevice(idx->device));
+  if (idx->queries.reserve((size_t)nq * idx->geom.stride + 16)) return 1;
+  if (pann_gen_rows_device(gen_kind, seed, stream, 0, nq, idx->dims, latent_r, n_clusters, idx->queries.p, idx->geom.stride, idx->stream)) return 1;
+  idx->nq = nq;
+  return 0;
+}
+extern "C" int pann_queries_download(pann_index* idx, void* host_out, uint64_t out_stride_bytes) {
+  if (!idx || !host_out) PANN_FAIL("pann_queries_download: null argument");
+  PANN_CUDA(cudaSetDevice(idx->device));
+  const size_t rowb = (size_t)idx->dims * idx->geom.elt;
+  PANN_CUDA(cudaMemcpy2DAsync(host_out, out_stride_bytes, idx->queries.p, idx->geom.stride, rowb, idx->nq, cudaMemcpyDeviceToHost, idx->stream));
+  PANN_CUDA(cudaStreamSynchronize(idx->stream));
+  return 0;
+}
+
+extern "C" int pann_search_resident(pann_index* idx, const uint32_t* starts, uint32_t nstarts, const pann_query_params* qp) {
+  if (!idx) PANN_FAIL("pann_search_resident: null index");
+  if (validate_qp(qp)) return 1;
+  if (idx->nq == 0) PANN_FAIL("pann_search_resident: no resident query set");
+  PANN_CUDA(cudaSetDevice(idx->device));
+  return search_common(idx, idx->queries.as<uint8_t>(), idx->nq, idx->geom.stride, starts, nstarts, qp);
+}
+
+static int fetch_results(pann_index* idx, uint32_t* out_ids, float* out_dists, uint32_t* out_visited, uint32_t* out_cmps) {
+  const uint64_t nq = idx->res_nq; const uint32_t k = idx->res_k;
+  ResLayout L = res_layout(nq, k);
+  void* pin = nullptr;
+  if (pann_pinned(idx, L.status, &pin)) return 1;
+  PANN_CUDA(cudaMemcpyAsync(pin, idx->results.p, L.status, cudaMemcpyDeviceToHost, idx->stream));
+  PANN_CUDA(cudaStreamSynchronize(idx->stream));
+  const uint8_t* h = (const uint8_t*)pin;
+  if (out_ids) memcpy(out_ids, h + L.ids, 4ull * nq * k);
+  if (out_dists) memcpy(out_dists, h + L.dists, 4ull * nq * k);
+  if (out_visited) memcpy(out_visited, h + L.visited, 4ull * nq);
+  if (out_cmps) memcpy(out_cmps, h + L.cmps, 4ull * nq);
+  return 0;
+}
+
+extern "C" int pann_search_fetch(pann_index* idx, uint32_t* out_ids, float* out_dists, uint32_t* out_visited, uint32_t* out_cmps) {
+  if (!idx) PANN_FAIL("pann_search_fetch: null index");
+  PANN_CUDA(cudaSetDevice(idx->device));
+  return fetch_results(idx, out_ids, out_dists, out_visited, out_cmps);
+}
+
+extern "C" int pann_search_batch(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes,
+                                 const uint32_t* starts, uint32_t nstarts, const pann_query_params* qp,
+                                 uint32_t* out_ids, float* out_dists, uint32_t* out_visited, uint32_t* out_cmps) {
+  if (!idx || (!host_queries && nq)) PANN_FAIL("pann_search_batch: null argument");
+  if (validate_qp(qp)) return 1;
+  PANN_CUDA(cudaSetDevice(idx->device));
+  if (nq == 0) return 0;
+  if (upload_queries(idx, host_queries, nq, q_stride_bytes)) return 1;
+  if (search_common(idx, idx->queries.as<uint8_t>(), nq, idx->geom.stride, starts, nstarts, qp)) return 1;
+  return fetch_results(idx, out_ids, out_dists, out_visited, out_cmps);
+}
+
+extern "C" int pann_search_full(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes,
+                                const uint32_t* self_ids, const uint32_t* starts, uint32_t nstarts,
+                                const pann_query_params* qp, uint32_t fcap, uint32_t* fr_ids, float* fr_dists,
+                                uint32_t* n_frontier, uint32_t vcap, uint32_t* vis_ids, float* vis_dists,
+                                uint32_t* n_visited, uint32_t* out_cmps) {
+  if (!idx || !qp) PANN_FAIL("pann_search_full: null argument");
+  if (!self_ids && !host_queries) PANN_FAIL("pann_search_full: need queries or self ids");
+  PANN_CUDA(cudaSetDevice(idx->device));
+  if (nq == 0) return 0;
+  const uint8_t* d_q = nullptr;
+  uint32_t* d_self = nullptr;
+  size_t need = 4ull * nq * fcap * 2 + 4ull * nq * vcap * 2 + 4ull * nq * 4 + (self_ids ? 4ull * nq : 0) + 256;
+  if (idx->misc.reserve(need)) return 1;
+  uint8_t* m = idx->misc.as<uint8_t>();
+  SearchOutputs o;
+  o.fcap = fcap; o.vout = vcap;
+  o.fr_ids = (uint32_t*)m; m += 4ull * nq * fcap;
+  o.fr_dists = (float*)m; m += 4ull * nq * fcap;
+  o.vis_ids = (uint32_t*)m; m += 4ull * nq * vcap;
+  o.vis_dists = (float*)m; m += 4ull * nq * vcap;
+  o.n_frontier = (uint32_t*)m; m += 4ull * nq;
+  o.n_visited = (uint32_t*)m; m += 4ull * nq;
+  o.cmps = (uint32_t*)m; m += 4ull * nq;
+  o.status = (int*)m; m += 4ull * nq;
+  if (self_ids) {
+    for (uint64_t i = 0; i < nq; i++) if (self_ids[i] >= idx->n) PANN_FAIL("pann_search_full: self id out of range");
+    d_self = (uint32_t*)m;
+    PANN_CUDA(cudaMemcpyAsync(d_self, self_ids, 4ull * nq, cudaMemcpyHostToDevice, idx->stream));
+  } else {
+    if (upload_queries(idx, host_queries, nq, q_stride_bytes)) return 1;
+    d_q = idx->queries.as<uint8_t>();
+  }
+  int flag = 0;
+  idx->last_launches = 0;
+  if (pann_run_search(idx, d_q, nq, idx->geom.stride, d_self, starts, nstarts, qp, o, &flag)) return 1;
+  if (check_status(flag & ~(1 << 2))) return 1;
+  if (fr_ids) PANN_CUDA(cudaMemcpy(fr_ids, o.fr_ids, 4ull * nq * fcap, cudaMemcpyDeviceToHost));
+  if (fr_dists) PANN_CUDA(cudaMemcpy(fr_dists, o.fr_dists, 4ull * nq * fcap, cudaMemcpyDeviceToHost));
+  if (vis_ids) PANN_CUDA(cudaMemcpy(vis_ids, o.vis_ids, 4ull * nq * vcap, cudaMemcpyDeviceToHost));
+  if (vis_dists) PANN_CUDA(cudaMemcpy(vis_dists, o.vis_dists, 4ull * nq * vcap, cudaMemcpyDeviceToHost));
+  if (n_frontier) PANN_CUDA(cudaMemcpy(n_frontier, o.n_frontier, 4ull * nq, cudaMemcpyDeviceToHost));
+  if (n_visited) PANN_CUDA(cudaMemcpy(n_visited, o.n_visited, 4ull * nq, cudaMemcpyDeviceToHost));
+  if (out_cmps) PANN_CUDA(cudaMemcpy(out_cmps, o.cmps, 4ull * nq, cudaMemcpyDeviceToHost));
+  return 0;
+}
+
+extern "C" int pann_random_permutation(int64_t n, int32_t* out) {
+  if (n < 0 || !out) PANN_FAIL("pann_random_permutation: bad argument");
+  pann_host_random_permutation(n, out);
+  return 0;
+}
+extern "C" int64_t pann_batch_schedule(uint64_t n, uint64_t m, int64_t* lo, int64_t* hi, int64_t cap) {
+  return pann_host_batch_schedule(n, m, lo, hi, cap);
+}

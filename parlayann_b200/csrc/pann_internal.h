@@ -1,0 +1,68 @@
+// pann_internal.h — host-side state behind the C ABI (include/pann.h).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <vector>
+
+#include "../../include/pann.h"
+#include "beam_search.cuh"
+#include "pann_common.cuh"
+
+// grow-only device buffer
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int reserve(size_t bytes) {
+    if (bytes <= cap) return 0;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = bytes + bytes / 4 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) { pann_set_error(std::string("cudaMalloc failed: ") + cudaGetErrorString(e)); return 1; }
+    cap = want;
+    return 0;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <class T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct pann_index {
+  int device = 0, dtype = 0, metric = 0;
+  int sms = 148;
+  size_t smem_optin = 0;
+  uint64_t n = 0;
+  uint32_t dims = 0, maxdeg = 0;
+  PannRowGeom geom{};
+  uint8_t* points = nullptr;   // n x geom.stride
+  uint32_t* graph = nullptr;   // n x (maxdeg+1)
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  float last_ms = 0.f;
+  int last_launches = 0;
+  // resident query set and results
+  DevBuf queries;  uint64_t nq = 0;
+  DevBuf results;  // packed: ids[nq*k] dists[nq*k] visited[nq] cmps[nq] status[nq]
+  uint64_t res_nq = 0; uint32_t res_k = 0;
+  DevBuf scratch_hash, scratch_vis, starts, flag, qmap, misc;
+  void* pinned = nullptr; size_t pinned_cap = 0;
+  // ground truth results (resident)
+  DevBuf gt_ids, gt_dists; uint64_t gt_nq = 0; uint32_t gt_k = 0;
+};
+
+struct SearchOutputs {  // device pointers (any may be null)
+  uint32_t* ids = nullptr; float* dists = nullptr; uint32_t* visited = nullptr; uint32_t* cmps = nullptr;
+  uint32_t* fr_ids = nullptr; float* fr_dists = nullptr; uint32_t* n_frontier = nullptr; uint32_t fcap = 0;
+  uint32_t* vis_ids = nullptr; float* vis_dists = nullptr; uint32_t* n_visited = nullptr; uint32_t vout = 0;
+  int* status = nullptr;  // nq ints, required
+};
+
+// Runs K1 over nq queries (device rows, or base rows self_ids) and retries visited-list overflows with the
+// global-scratch variant.  Does not synchronise the host unless a retry is needed; returns the OR of statuses.
+int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint32_t qstride, const uint32_t* d_self_ids,
+                    const uint32_t* h_starts, uint32_t nstarts, const pann_query_params* qp, const SearchOutputs& out,
+                    int* status_or);
+int pann_pinned(pann_index* idx, size_t bytes, void** p);
+int pann_gen_rows_device(int kind, uint64_t seed, uint64_t stream, uint64_t row0, uint64_t nrows, uint32_t d, uint32_t r,
+                         uint32_t nc, void* dev_out, uint64_t stride, cudaStream_t s);
+void pann_host_random_permutation(int64_t n, int32_t* out);
+int64_t pann_host_batch_schedule(uint64_t n, uint64_t m, int64_t* lo, int64_t* hi, int64_t cap);

@@ -1,0 +1,262 @@
+"""Host-side mirror of the reference's Python surface for the hot path, on top of the C ABI.
+
+Reference names kept (python/wrapper.py:3-116, python/module.cpp:59-76, python/graph_index.cpp:48-337):
+``build_vamana_index``, ``load_index``, and index objects with ``batch_search``, ``single_search``,
+``batch_search_from_string``, ``check_recall``.  All compute happens in libpann_cuda.so on the GPU.
+"""
+import ctypes as C
+import numpy as np
+
+from . import _lib, fileio
+from ._lib import QueryParams, PannError, check
+
+
+def _vp(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class GraphIndex:
+    """PointRange + Graph resident on one B200 (reference: python/graph_index.cpp:48-118)."""
+
+    def __init__(self, points=None, graph=None, data_type="uint8", metric="Euclidian", max_degree=None, device=0,
+                 synthetic=None):
+        self.data_type, self.metric = data_type, metric
+        self._h = C.c_void_p()
+        L = _lib.lib()
+        if synthetic is not None:  # dict(n, d, kind, seed, stream, r, nc): points generated on the device
+            s = synthetic
+            self.n, self.d = int(s["n"]), int(s["d"])
+            self.max_degree = int(max_degree)
+            check(L.pann_index_create_synthetic(C.byref(self._h), device, _lib.DTYPE[data_type], _lib.METRIC[metric],
+                                                C.c_uint64(self.n), C.c_uint32(self.d), C.c_uint32(self.max_degree),
+                                                _lib.GEN_KIND[s.get("kind", data_type)], C.c_uint64(s.get("seed", 1234)),
+                                                C.c_uint64(s.get("stream", 0)), C.c_uint32(s.get("r", 24)),
+                                                C.c_uint32(s.get("nc", 256))))
+        else:
+            points = np.ascontiguousarray(points, dtype=fileio.np_dtype(data_type))
+            self.n, self.d = points.shape
+            if graph is not None:
+                graph = np.ascontiguousarray(graph, dtype=np.uint32)
+                if graph.shape[0] != self.n:
+                    raise ValueError("graph and points disagree on n")
+                max_degree = graph.shape[1] - 1
+            self.max_degree = int(max_degree)
+            check(L.pann_index_create(C.byref(self._h), device, _lib.DTYPE[data_type], _lib.METRIC[metric],
+                                      C.c_uint64(self.n), C.c_uint32(self.d), C.c_uint64(points.strides[0]), _vp(points),
+                                      C.c_uint32(self.max_degree), _vp(graph)))
+        self.start_point = 0  # knn_index::set_start (vamana/index.h:148)
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            _lib.lib().pann_index_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- graph / points access
+    def set_graph(self, graph):
+        graph = np.ascontiguousarray(graph, dtype=np.uint32)
+        assert graph.shape == (self.n, self.max_degree + 1)
+        check(_lib.lib().pann_index_set_graph(self._h, _vp(graph)))
+
+    def graph(self):
+        g = np.empty((self.n, self.max_degree + 1), dtype=np.uint32)
+        check(_lib.lib().pann_index_get_graph(self._h, _vp(g)))
+        return g
+
+    def points(self, row0=0, nrows=None):
+        nrows = self.n - row0 if nrows is None else nrows
+        out = np.empty((nrows, self.d), dtype=fileio.np_dtype(self.data_type))
+        check(_lib.lib().pann_index_get_points(self._h, C.c_uint64(row0), C.c_uint64(nrows), _vp(out), C.c_uint64(out.strides[0])))
+        return out
+
+    def last_timing(self):
+        ms, nl = C.c_float(0), C.c_int(0)
+        check(_lib.lib().pann_index_last_timing(self._h, C.byref(ms), C.byref(nl)))
+        return ms.value, nl.value
+
+    # ---- search (qsearchAll, beamSearch.h:537-565)
+    def _qp(self, k, beam, cut, limit, degree_limit):
+        return QueryParams(int(k), int(beam), float(cut), -1 if limit is None else int(limit),
+                           -1 if degree_limit is None else int(degree_limit))
+
+    def search(self, queries, k=10, beam=10, cut=1.35, limit=None, degree_limit=None, starts=None, out=None):
+        """One beam search per row of `queries` (host array).  Returns ids, dists, visited, cmps."""
+        queries = np.ascontiguousarray(queries, dtype=fileio.np_dtype(self.data_type))
+        nq = queries.shape[0]
+        st = np.asarray([self.start_point] if starts is None else starts, dtype=np.uint32)
+        if out is None:
+            out = (np.empty((nq, k), np.uint32), np.empty((nq, k), np.float32), np.empty(nq, np.uint32), np.empty(nq, np.uint32))
+        qp = self._qp(k, beam, cut, limit, degree_limit)
+        check(_lib.lib().pann_search_batch(self._h, _vp(queries), C.c_uint64(nq), C.c_uint64(queries.strides[0]), _vp(st),
+                                           C.c_uint32(len(st)), C.byref(qp), _vp(out[0]), _vp(out[1]), _vp(out[2]), _vp(out[3])))
+        return out
+
+    def upload_queries(self, queries):
+        queries = np.ascontiguousarray(queries, dtype=fileio.np_dtype(self.data_type))
+        check(_lib.lib().pann_queries_upload(self._h, _vp(queries), C.c_uint64(queries.shape[0]), C.c_uint64(queries.strides[0])))
+        self.nq = queries.shape[0]
+
+    def synthetic_queries(self, nq, kind=None, seed=1234, stream=1, r=24, nc=256):
+        check(_lib.lib().pann_queries_synthetic(self._h, C.c_uint64(nq), _lib.GEN_KIND[kind or self.data_type], C.c_uint64(seed),
+                                                C.c_uint64(stream), C.c_uint32(r), C.c_uint32(nc)))
+        self.nq = nq
+
+    def download_queries(self):
+        out = np.empty((self.nq, self.d), dtype=fileio.np_dtype(self.data_type))
+        check(_lib.lib().pann_queries_download(self._h, _vp(out), C.c_uint64(out.strides[0])))
+        return out
+
+    def search_resident(self, k=10, beam=10, cut=1.35, limit=None, degree_limit=None, starts=None):
+        """Search the resident query set; results stay on the device (fetch_results)."""
+        st = np.asarray([self.start_point] if starts is None else starts, dtype=np.uint32)
+        qp = self._qp(k, beam, cut, limit, degree_limit)
+        check(_lib.lib().pann_search_resident(self._h, _vp(st), C.c_uint32(len(st)), C.byref(qp)))
+        self._res_k = k
+
+    def fetch_results(self):
+        nq, k = self.nq, self._res_k
+        out = (np.empty((nq, k), np.uint32), np.empty((nq, k), np.float32), np.empty(nq, np.uint32), np.empty(nq, np.uint32))
+        check(_lib.lib().pann_search_fetch(self._h, _vp(out[0]), _vp(out[1]), _vp(out[2]), _vp(out[3])))
+        return out
+
+    def search_full(self, queries=None, self_ids=None, k=0, beam=10, cut=1.35, limit=None, degree_limit=None, starts=None,
+                    vcap=1024):
+        """beam_search (beamSearch.h:217-223): whole frontier + whole visited list per query."""
+        if self_ids is not None:
+            self_ids = np.ascontiguousarray(self_ids, dtype=np.uint32)
+            nq = len(self_ids)
+            qptr, qstride = None, 0
+        else:
+            queries = np.ascontiguousarray(queries, dtype=fileio.np_dtype(self.data_type))
+            nq = queries.shape[0]
+            qptr, qstride = _vp(queries), queries.strides[0]
+        st = np.asarray([self.start_point] if starts is None else starts, dtype=np.uint32)
+        qp = self._qp(k, beam, cut, limit, degree_limit)
+        fcap = int(beam)
+        r = dict(fr_ids=np.zeros((nq, fcap), np.uint32), fr_dists=np.zeros((nq, fcap), np.float32), nfr=np.zeros(nq, np.uint32),
+                 vis_ids=np.zeros((nq, vcap), np.uint32), vis_dists=np.zeros((nq, vcap), np.float32), nvis=np.zeros(nq, np.uint32),
+                 cmps=np.zeros(nq, np.uint32))
+        check(_lib.lib().pann_search_full(self._h, qptr, C.c_uint64(nq), C.c_uint64(qstride), _vp(self_ids), _vp(st),
+                                          C.c_uint32(len(st)), C.byref(qp), C.c_uint32(fcap), _vp(r["fr_ids"]), _vp(r["fr_dists"]),
+                                          _vp(r["nfr"]), C.c_uint32(vcap), _vp(r["vis_ids"]), _vp(r["vis_dists"]), _vp(r["nvis"]),
+                                          _vp(r["cmps"])))
+        return r
+
+    # ---- build (knn_index::build_index, vamana/index.h:150-186)
+    def build(self, R=None, L=128, alpha=1.2, num_passes=1, sort_neighbors=True, stats=False):
+        R = self.max_degree if R is None else R
+        if R != self.max_degree:
+            raise ValueError("R must equal the index's max degree (BuildParams::max_degree, types.h:210-214)")
+        sv = np.zeros(self.n, np.uint32) if stats else None
+        sd = np.zeros(self.n, np.uint32) if stats else None
+        ph = (C.c_double * 3)()
+        check(_lib.lib().pann_vamana_build(self._h, C.c_uint32(R), C.c_uint32(L), C.c_double(alpha), int(num_passes),
+                                           int(bool(sort_neighbors)), _vp(sv), _vp(sd), ph))
+        self.build_phase_seconds = tuple(ph)
+        return (sv, sd) if stats else None
+
+    # ---- ground truth (compute_groundtruth.cpp:22-100)
+    def groundtruth(self, queries, k=100, id_offset=0):
+        queries = np.ascontiguousarray(queries, dtype=fileio.np_dtype(self.data_type))
+        nq = queries.shape[0]
+        ids = np.empty((nq, k), np.int32)
+        dists = np.empty((nq, k), np.float32)
+        check(_lib.lib().pann_groundtruth(self._h, _vp(queries), C.c_uint64(nq), C.c_uint64(queries.strides[0]), C.c_uint32(k),
+                                          C.c_int64(id_offset), _vp(ids), _vp(dists)))
+        return ids, dists
+
+    def groundtruth_resident(self, k=100, id_offset=0):
+        check(_lib.lib().pann_groundtruth_resident(self._h, C.c_uint32(k), C.c_int64(id_offset)))
+        self._gt_k = k
+
+    def fetch_groundtruth(self):
+        ids = np.empty((self.nq, self._gt_k), np.int32)
+        dists = np.empty((self.nq, self._gt_k), np.float32)
+        check(_lib.lib().pann_groundtruth_fetch(self._h, _vp(ids), _vp(dists)))
+        return ids, dists
+
+    # ---- the reference's Python methods (python/graph_index.cpp:192-305)
+    def batch_search(self, queries, knn, beam_width, quant=False, visit_limit=-1):
+        if quant:
+            raise NotImplementedError("quantized search + re-rank is a 'next' row (SURVEY.md §8f.2)")
+        dl = min(self.max_degree, 3 * visit_limit)  # graph_index.cpp:198
+        # the reference passes visit_limit straight into QueryParams: -1 means "visit nothing"
+        ids, dists, _, _ = self.search(queries, k=knn, beam=beam_width, cut=1.35, limit=max(visit_limit, 0), degree_limit=max(dl, 0))
+        return ids, dists
+
+    def single_search(self, q, knn, beam_width, quant=False, visit_limit=-1):
+        return self.batch_search(np.asarray(q)[None, :], knn, beam_width, quant, visit_limit)[0][0]
+
+    def batch_search_from_string(self, queries_file, knn, beam_width, quant=False, visit_limit=-1):
+        return self.batch_search(fileio.read_bin(queries_file, self.data_type), knn, beam_width, quant, visit_limit)
+
+    def check_recall(self, queries_file, gt_file, neighbors, k):
+        from .harness import recall_with_ties
+        gt_ids, gt_dists = fileio.read_ibin(gt_file)
+        r = recall_with_ties(neighbors, gt_ids, gt_dists, k)
+        print(f"Recall: {r:.6g}")
+        return r
+
+
+def groundtruth_merge(ids_list, dists_list, device=0):
+    """k-way merge of per-shard ground truth ([nq,k] each) under the (dist,id) order."""
+    ids = np.ascontiguousarray(np.stack(ids_list), dtype=np.int32)
+    dists = np.ascontiguousarray(np.stack(dists_list), dtype=np.float32)
+    s, nq, k = ids.shape
+    oi = np.empty((nq, k), np.int32)
+    od = np.empty((nq, k), np.float32)
+    check(_lib.lib().pann_groundtruth_merge(device, C.c_uint32(s), C.c_uint64(nq), C.c_uint32(k), _vp(ids), _vp(dists), _vp(oi), _vp(od)))
+    return oi, od
+
+
+def random_permutation(n):
+    out = np.empty(n, np.int32)
+    check(_lib.lib().pann_random_permutation(C.c_int64(n), _vp(out)))
+    return out
+
+
+def batch_schedule(n, m=None):
+    m = n if m is None else m
+    lo = np.zeros(8192, np.int64)
+    hi = np.zeros(8192, np.int64)
+    nb = _lib.lib().pann_batch_schedule(C.c_uint64(n), C.c_uint64(m), _vp(lo), _vp(hi), C.c_int64(8192))
+    return [(int(lo[i]), int(hi[i])) for i in range(nb)]
+
+
+# ---- module-level names of the reference's wrapper (python/wrapper.py)
+class defaults:  # python/module.cpp:142-148
+    METRIC = "Euclidian"
+    ALPHA = 1.2
+    GRAPH_DEGREE = 64
+    BEAMWIDTH = 128
+
+
+def build_vamana_index(metric, dtype, data_dir, index_dir, R, L, alpha, two_pass, device=0):
+    """python/wrapper.py:3-24 -> builder.cpp:36-95.  1-byte types and Euclidian floats build directly on the
+    points; the reference's MIPS normalisation/alpha override and its quantised float build (builder.cpp:45-87)
+    are 'next' rows and raise here rather than silently differing."""
+    if metric not in _lib.METRIC:
+        raise Exception("Invalid metric " + str(metric))
+    if dtype not in _lib.DTYPE:
+        raise Exception("Invalid data type " + str(dtype))
+    pts = fileio.read_bin(data_dir, dtype)
+    idx = GraphIndex(pts, None, dtype, metric, max_degree=R, device=device)
+    idx.build(R=R, L=L, alpha=alpha, num_passes=2 if two_pass else 1)
+    fileio.write_graph(index_dir, idx.graph())
+    return idx
+
+
+def load_index(metric, dtype, data_dir, index_dir, hnsw=False, device=0):
+    """python/wrapper.py:96-116."""
+    if hnsw:
+        raise NotImplementedError("HNSW model files are a 'next' row (SURVEY.md §8f.1)")
+    if metric not in _lib.METRIC:
+        raise Exception("Invalid metric")
+    if dtype not in _lib.DTYPE:
+        raise Exception("Invalid data type")
+    return GraphIndex(fileio.read_bin(data_dir, dtype), fileio.read_graph(index_dir), dtype, metric, device=device)

@@ -1,0 +1,157 @@
+"""K1 parity: the CUDA beam search (through the C ABI) against the CPU oracle on the same graph.
+Integer element types must match bit for bit: ids, distances, visited count, distance-comparison count
+(SURVEY.md §8c).  Floats: distances within 1e-5 relative and ids equal except where the oracle's own
+candidates tie within that tolerance."""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+
+pytestmark = pytest.mark.gpu
+
+
+def _index(ds):
+    import parlayann_b200 as P
+    return P.GraphIndex(ds.base, ds.graph, ds.data_type, ds.metric)
+
+
+def _check_exact(ds, idx, **qp):
+    ids, dists, vis, cmps = idx.search(ds.queries, **qp)
+    ref = O.search(ds.base, ds.graph, ds.queries, ds.data_type, ds.metric, **qp)
+    assert np.array_equal(ids, ref["ids"]), f"ids differ for {qp}: {(ids != ref['ids']).any(axis=1).sum()} queries"
+    assert np.array_equal(dists, ref["dists"]), f"dists differ for {qp}"
+    assert np.array_equal(vis, ref["visited"]), f"visited counts differ for {qp}"
+    assert np.array_equal(cmps, ref["cmps"]), f"distance-comparison counts differ for {qp}"
+
+
+@pytest.mark.parametrize("beam", [10, 13, 20, 32, 33, 50, 64, 100, 128])
+def test_u8_l2_beam_sweep(dataset, beam):
+    ds = dataset("uint8")
+    _check_exact(ds, _index(ds), k=10, beam=beam)
+
+
+@pytest.mark.parametrize("beam", [150, 200, 300, 500])
+def test_u8_l2_wide_beams_global_scratch(dataset, beam):
+    ds = dataset("uint8")
+    _check_exact(ds, _index(ds), k=10, beam=beam)
+
+
+@pytest.mark.parametrize("beam,limit", [(10, 10), (15, 12), (20, 15), (40, 30), (100, 50), (10, 1), (64, 200)])
+def test_u8_l2_visit_limits(dataset, beam, limit):
+    # the reference sweep's visit-limit settings (check_nn_recall.h:243-254): limit < 2*beam disables the skip rule
+    ds = dataset("uint8")
+    _check_exact(ds, _index(ds), k=10, beam=beam, limit=limit)
+
+
+@pytest.mark.parametrize("k,beam,cut", [(1, 10, 1.35), (10, 10, 1.35), (10, 100, 1.0), (10, 64, 1.1), (50, 100, 1.35), (100, 100, 1.35), (10, 1000, 10.0)])
+def test_u8_l2_k_and_cut(dataset, k, beam, cut):
+    ds = dataset("uint8")
+    _check_exact(ds, _index(ds), k=k, beam=beam, cut=cut)
+
+
+def test_u8_l2_degree_limit(dataset):
+    ds = dataset("uint8")
+    idx = _index(ds)
+    for dl in (5, 16, 31, 32):
+        _check_exact(ds, idx, k=10, beam=30, degree_limit=dl)
+    # degree 1 walks a path and ends with fewer than k results: both sides refuse (beamSearch.h:416-419)
+    import parlayann_b200 as P
+    with pytest.raises(RuntimeError):
+        O.search(ds.base, ds.graph, ds.queries, "uint8", k=10, beam=30, degree_limit=1)
+    with pytest.raises(P.PannError):
+        idx.search(ds.queries, k=10, beam=30, degree_limit=1)
+
+
+@pytest.mark.parametrize("data_type,metric", [("int8", "Euclidian"), ("uint8", "mips"), ("int8", "mips")])
+def test_other_integer_types_exact(dataset, data_type, metric):
+    ds = dataset(data_type, metric, n=8000, nq=300)
+    idx = _index(ds)
+    for beam in (10, 40, 128):
+        _check_exact(ds, idx, k=10, beam=beam)
+
+
+@pytest.mark.parametrize("d", [100, 96, 200, 17, 2048])
+def test_u8_odd_dimensions(dataset, d):
+    # rows that are not a multiple of 16 bytes are zero padded on the device; d=2048 takes the generic (CPL=0) path
+    ds = dataset("uint8", n=4000, d=d, nq=100)
+    idx = _index(ds)
+    _check_exact(ds, idx, k=10, beam=25)
+
+
+def test_multi_start(dataset):
+    # beam_search with several start points (HNSW layer search, beamSearch.h:217-223)
+    ds = dataset("uint8")
+    idx = _index(ds)
+    _check_exact(ds, idx, k=10, beam=20, starts=(0, 17, 4242, 9))
+
+
+def test_build_mode_visited_lists(dataset):
+    # the build's search (vamana/index.h:249-259): k=0, beam=L, cut=0, limit=n, the query is a base row
+    ds = dataset("uint8")
+    idx = _index(ds)
+    self_ids = np.arange(0, 2000, 7, dtype=np.uint32)
+    got = idx.search_full(self_ids=self_ids, k=0, beam=64, cut=0.0, vcap=512)
+    ref = O.search(ds.base, ds.graph, ds.base[self_ids], "uint8", k=0, beam=64, cut=0.0, selfs=self_ids, full=True, vcap=512)
+    assert np.array_equal(got["nvis"], ref["nvis"]) and np.array_equal(got["nfr"], ref["nfr"])
+    assert np.array_equal(got["cmps"], ref["cmps"])
+    for i in range(len(self_ids)):
+        nv, nf = ref["nvis"][i], ref["nfr"][i]
+        assert np.array_equal(got["vis_ids"][i, :nv], ref["vis_ids"][i, :nv])
+        assert np.array_equal(got["vis_dists"][i, :nv], ref["vis_dists"][i, :nv])
+        assert np.array_equal(got["fr_ids"][i, :nf], ref["fr_ids"][i, :nf])
+
+
+@pytest.mark.parametrize("metric,d", [("Euclidian", 128), ("mips", 200), ("Euclidian", 96)])
+def test_float_tolerance(dataset, metric, d):
+    ds = dataset("float", metric, n=8000, d=d, nq=300)
+    idx = _index(ds)
+    for beam in (10, 40, 100):
+        ids, dists, vis, cmps = idx.search(ds.queries, k=10, beam=beam)
+        ref = O.search(ds.base, ds.graph, ds.queries, "float", metric, k=10, beam=beam)
+        same = (ids == ref["ids"]).all(axis=1)
+        assert same.mean() >= 0.97, f"only {same.mean():.3f} of float queries have identical ids"
+        rel = np.abs(dists[same] - ref["dists"][same]) / np.maximum(np.abs(ref["dists"][same]), 1e-30)
+        assert rel.max() <= 1e-5, f"float distance error {rel.max()}"
+        # recall against exact ground truth within 0.2 % of the oracle's
+        gi, gd = O.groundtruth(ds.base, ds.queries, "float", metric, k=10)
+        from parlayann_b200.harness import recall_with_ties
+        r_gpu, r_ref = recall_with_ties(ids, gi, gd, 10), recall_with_ties(ref["ids"], gi, gd, 10)
+        assert abs(r_gpu - r_ref) <= 0.002
+
+
+def test_errors(dataset):
+    import parlayann_b200 as P
+    ds = dataset("uint8")
+    idx = _index(ds)
+    with pytest.raises(P.PannError):  # k > beam (beamSearch.h:549-553)
+        idx.search(ds.queries, k=20, beam=10)
+    with pytest.raises(P.PannError):  # no start point (beamSearch.h:38-41)
+        idx.search(ds.queries, k=10, beam=10, starts=())
+    with pytest.raises(P.PannError):  # fewer than k results (beamSearch.h:416-419): limit 0 visits nothing
+        idx.search(ds.queries, k=10, beam=10, limit=0)
+    ids, _, vis, _ = idx.search(ds.queries[:0], k=10, beam=10)  # empty batch
+    assert ids.shape == (0, 10)
+
+
+def test_resident_queries_match_host_path(dataset):
+    ds = dataset("uint8")
+    idx = _index(ds)
+    idx.upload_queries(ds.queries)
+    idx.search_resident(k=10, beam=13)
+    a = idx.fetch_results()
+    b = idx.search(ds.queries, k=10, beam=13)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+    ms, launches = idx.last_timing()
+    assert launches >= 1 and ms > 0
+
+
+def test_synthetic_device_generator_matches_cpu(dataset):
+    import parlayann_b200 as P
+    for dt, kind, d, r, nc in (("uint8", "uint8", 128, 24, 256), ("int8", "int8", 64, 24, 256), ("float", "float", 128, 24, 256),
+                               ("float", "float_norm", 96, 24, 256), ("float", "float", 200, 32, 0)):
+        idx = P.GraphIndex(data_type=dt, max_degree=8, synthetic=dict(n=3000, d=d, kind=kind, seed=99, r=r, nc=nc))
+        cpu = O.gen_points(kind, 3000, d, seed=99, r=r, nc=nc)
+        assert np.array_equal(idx.points(), cpu), (dt, kind, d)
+        idx.synthetic_queries(200, kind=kind, seed=99, stream=1, r=r, nc=nc)
+        assert np.array_equal(idx.download_queries(), O.gen_points(kind, 200, d, seed=99, stream=1, r=r, nc=nc))
