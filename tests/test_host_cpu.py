@@ -1,0 +1,76 @@
+"""CPU-only checks of the product's host side: the C-ABI library loads and exports every symbol
+include/pann.h declares, its host logic (insertion order, batch schedule) equals the reference's, file
+formats round-trip, and compute calls fail loudly without a GPU (no CPU fallback)."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from golden_util import GOLDEN
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_library_exports_every_declared_symbol():
+    from parlayann_b200 import _lib
+    hdr = open(os.path.join(ROOT, "include", "pann.h")).read()
+    declared = set(re.findall(r"\b(pann_[a-z0-9_]+)\s*\(", hdr))
+    assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
+    L = _lib.lib()
+    for s in declared:
+        assert hasattr(L, s), s
+
+
+def test_permutation_and_schedule_match_reference():
+    import parlayann_b200 as P
+    z = np.load(os.path.join(GOLDEN, "perms.npz"))
+    for key in z.files:
+        n = int(key.split("_")[1])
+        assert np.array_equal(P.random_permutation(n), z[key]), n
+    for n in (1, 5, 49, 50, 1000, 100000, 1000000, 60000000):
+        assert P.batch_schedule(n) == O.batch_schedule(n), n
+    s = P.batch_schedule(100000)
+    assert len(s) == 60 and s[10] == (1023, 2047) and s[11] == (2047, 4047)
+
+
+def test_no_cpu_fallback():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    import parlayann_b200 as P
+    pts = np.zeros((10, 16), np.uint8)
+    with pytest.raises(P.PannError):
+        P.GraphIndex(pts, None, "uint8", "Euclidian", max_degree=4)
+
+
+def test_file_formats_roundtrip(tmp_path):
+    from parlayann_b200 import fileio
+    rng = np.random.default_rng(0)
+    for dt, npdt in (("uint8", np.uint8), ("int8", np.int8), ("float", np.float32)):
+        a = rng.integers(-100, 100, size=(37, 19)).astype(npdt)
+        fileio.write_bin(tmp_path / "p.bin", a)
+        assert np.array_equal(fileio.read_bin(tmp_path / "p.bin", dt), a)
+    g = np.zeros((50, 9), np.uint32)
+    g[:, 0] = rng.integers(0, 9, size=50)
+    for i in range(50):
+        g[i, 1:1 + g[i, 0]] = rng.integers(0, 50, size=g[i, 0])
+    fileio.write_graph(tmp_path / "g", g)
+    assert np.array_equal(fileio.read_graph(tmp_path / "g"), g)
+    # header layout of graph.h:206-231: n, maxDeg, degrees, then edges
+    raw = np.fromfile(tmp_path / "g", dtype=np.uint32)
+    assert raw[0] == 50 and raw[1] == 8 and np.array_equal(raw[2:52], g[:, 0]) and raw.size == 52 + g[:, 0].sum()
+    ids = rng.integers(0, 1000, size=(7, 5)).astype(np.int32)
+    ds = rng.random((7, 5)).astype(np.float32)
+    fileio.write_ibin(tmp_path / "gt", ids, ds)
+    i2, d2 = fileio.read_ibin(tmp_path / "gt")
+    assert np.array_equal(i2, ids) and np.array_equal(d2, ds)
+
+
+def test_recall_with_ties():
+    from parlayann_b200.harness import recall_with_ties
+    gt_ids = np.array([[1, 2, 3, 4]], np.int32)
+    gt_d = np.array([[0.0, 1.0, 1.0, 2.0]], np.float32)
+    assert recall_with_ties(np.array([[1, 3]]), gt_ids, gt_d, 2) == 1.0   # 3 ties with the 2nd
+    assert recall_with_ties(np.array([[1, 4]]), gt_ids, gt_d, 2) == 0.5
