@@ -157,6 +157,15 @@ void beam_search(const PointSet& P, const uint32_t* graph, uint32_t maxdeg, cons
   out.cmps = cmps;
 }
 
+// instrumentation for DESIGN.md (not part of the algorithm): log2 histogram of prune candidate counts
+std::atomic<long> g_prune_hist[40];
+std::atomic<long> g_prune_max(0);
+inline void prune_hist_add(size_t c) {
+  int b = 0; while (((size_t)1 << b) < c) b++;
+  g_prune_hist[b]++;
+  long m = g_prune_max.load(); while ((long)c > m && !g_prune_max.compare_exchange_weak(m, (long)c)) {}
+}
+
 // algorithms/vamana/index.h:63-120.  cand already carries d(c,p).
 long robust_prune(const PointSet& P, const uint32_t* graph, uint32_t maxdeg, uint32_t R, uint32_t p,
                   std::vector<idd> cand, double alpha, bool add, std::vector<uint32_t>& out) {
@@ -167,6 +176,7 @@ long robust_prune(const PointSet& P, const uint32_t* graph, uint32_t maxdeg, uin
       comps++;
       cand.push_back(idd(row[1 + i], dist_rows(P.dtype, P.metric, P.row(row[1 + i]), P.row(p), P.d)));
     }
+  prune_hist_add(cand.size());
   std::sort(cand.begin(), cand.end(), less_idd);  // :80-83
   cand.erase(std::unique(cand.begin(), cand.end(), [](const idd& a, const idd& b) { return a.first == b.first; }), cand.end());
   std::vector<int> ids(cand.size());
@@ -226,6 +236,9 @@ void par_for(size_t lo, size_t hi, int nthreads, F f) {
 }  // namespace
 
 extern "C" {
+
+// out[0..40) = #prunes with candidate count in (2^(b-1), 2^b]; out[40] = max count; resets the counters
+void oracle_prune_hist(long* out) { for (int i = 0; i < 40; i++) out[i] = g_prune_hist[i].exchange(0); out[40] = g_prune_max.exchange(0); }
 
 int oracle_num_threads() { unsigned h = std::thread::hardware_concurrency(); return h ? (int)h : 1; }
 

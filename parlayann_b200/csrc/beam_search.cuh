@@ -61,23 +61,25 @@ __device__ __forceinline__ int pann_upper_bound(const u64* a, int n, u64 k1) {  
   return lo;
 }
 
-// Distances from the query to `cnt` rows listed in ids[] (shared memory); calls emit(id, dist, valid)
-// warp-uniformly once per pass with one row per lane group (valid only on the group's lane 0).
-template <int DT, int METRIC, int CPL, class Emit>
-__device__ __forceinline__ void pann_row_distances(const BeamArgs& A, const uint32_t* ids, int cnt, const uint4* qreg,
-                                                   const uint4* qsm, int lane, Emit emit) {
+// Distances from the query to `cnt` rows; row r is pann_key_id(keyOf(r)) (a 64-bit tag whose id field names
+// the row, so callers can carry a (dist,id) key through).  Calls emit(tag, dist, valid) warp-uniformly once per
+// pass with one row per lane group (valid only on the group's lane 0), rows in ascending r.
+// RG: anything with points / stride / nch / lpr (BeamArgs, PruneArgs).
+template <int DT, int METRIC, int CPL, class RG, class KeyOf, class Emit>
+__device__ __forceinline__ void pann_row_distances_g(const RG& A, KeyOf keyOf, int cnt, const uint4* qreg,
+                                                     const uint4* qsm, int lane, Emit emit) {
   const int lpr = A.lpr, G = 32 / lpr, grp = lane / lpr, sub = lane % lpr;
   constexpr int U = (CPL == 1) ? 4 : ((CPL == 2) ? 2 : 1);  // row groups in flight per lane
   for (int base = 0; base < cnt; base += G * U) {
-    uint32_t rid[U];
+    u64 rkey[U];
     DistAcc<DT, METRIC> acc[U];
     if constexpr (CPL > 0) {
       uint4 v[U][CPL];
 #pragma unroll
       for (int u = 0; u < U; u++) {
         int r = base + u * G + grp;
-        rid[u] = ids[r < cnt ? r : cnt - 1];
-        const uint8_t* row = A.points + (u64)rid[u] * A.stride;
+        rkey[u] = keyOf(r < cnt ? r : cnt - 1);
+        const uint8_t* row = A.points + (u64)pann_key_id(rkey[u]) * A.stride;
 #pragma unroll
         for (int c = 0; c < CPL; c++) {
           int ch = sub + c * lpr;
@@ -92,8 +94,8 @@ __device__ __forceinline__ void pann_row_distances(const BeamArgs& A, const uint
 #pragma unroll
       for (int u = 0; u < U; u++) {
         int r = base + u * G + grp;
-        rid[u] = ids[r < cnt ? r : cnt - 1];
-        const uint8_t* row = A.points + (u64)rid[u] * A.stride;
+        rkey[u] = keyOf(r < cnt ? r : cnt - 1);
+        const uint8_t* row = A.points + (u64)pann_key_id(rkey[u]) * A.stride;
         for (int ch = sub; ch < (int)A.nch; ch += lpr) acc[u].add(pann_ldg16(row + ch * 16), qsm[ch]);
       }
     }
@@ -101,9 +103,17 @@ __device__ __forceinline__ void pann_row_distances(const BeamArgs& A, const uint
     for (int u = 0; u < U; u++) {
       acc[u].reduce(lpr);
       int r = base + u * G + grp;
-      emit(rid[u], acc[u].result(), (sub == 0) && (r < cnt));
+      emit(rkey[u], acc[u].result(), (sub == 0) && (r < cnt));
     }
   }
+}
+// the same over a plain id list (shared memory): emit(id, dist, valid)
+template <int DT, int METRIC, int CPL, class RG, class Emit>
+__device__ __forceinline__ void pann_row_distances(const RG& A, const uint32_t* ids, int cnt, const uint4* qreg,
+                                                   const uint4* qsm, int lane, Emit emit) {
+  pann_row_distances_g<DT, METRIC, CPL>(
+      A, [&](int r) { return (u64)ids[r] << 1; }, cnt, qreg, qsm, lane,
+      [&](u64 tag, float d, bool ok) { emit(pann_key_id(tag), d, ok); });
 }
 
 template <int DT, int METRIC, int CPL, bool GS>

@@ -74,3 +74,31 @@ int64_t pann_host_batch_schedule(uint64_t n, uint64_t m, int64_t* lo, int64_t* h
   }
   return nb;
 }
+
+// build_index's final step (algorithms/vamana/index.h:180-185, graph.h:111-113): std::sort of every adjacency
+// list with a comparator on the distance to the owner ONLY.  The distances come from the device (K6); the
+// sort runs here with the same std::sort, so equal-distance neighbours end up where the reference leaves them.
+#include <thread>
+void pann_host_sort_rows(uint32_t* graph, const float* dists, uint64_t n, uint32_t maxdeg) {
+  unsigned nt = std::thread::hardware_concurrency();
+  if (nt == 0) nt = 1;
+  if (nt > 64) nt = 64;
+  auto work = [&](uint64_t lo, uint64_t hi) {
+    std::vector<std::pair<uint32_t, float>> tmp(maxdeg);
+    for (uint64_t i = lo; i < hi; i++) {
+      uint32_t* row = graph + i * (maxdeg + 1);
+      const float* d = dists + i * maxdeg;
+      uint32_t deg = row[0];
+      for (uint32_t j = 0; j < deg; j++) tmp[j] = {row[1 + j], d[j]};
+      std::sort(tmp.begin(), tmp.begin() + deg, [](const std::pair<uint32_t, float>& a, const std::pair<uint32_t, float>& b) { return a.second < b.second; });
+      for (uint32_t j = 0; j < deg; j++) row[1 + j] = tmp[j].first;
+    }
+  };
+  std::vector<std::thread> ts;
+  uint64_t chunk = (n + nt - 1) / nt;
+  for (unsigned t = 0; t < nt; t++) {
+    uint64_t lo = t * chunk, hi = std::min<uint64_t>(n, lo + chunk);
+    if (lo < hi) ts.emplace_back(work, lo, hi);
+  }
+  for (auto& t : ts) t.join();
+}

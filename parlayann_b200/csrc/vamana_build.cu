@@ -1,2 +1,261 @@
+// vamana_build.cu — knn_index::build_index / batch_insert on one B200 (algorithms/vamana/index.h:150-316).
+//
+// Per batch (the schedule and the insertion order are the reference's, computed on the host, host_util.cpp):
+//   phase 1   K1 in build mode (k=0, beam=L, query = base row, returns the visited list)      beam_search.cuh
+//             K3 robustPrune of every visited list -> new_out                                 vamana_prune.cuh
+//   phase 2   rows written + one (target << 32 | seq) key per new edge                        pann_write_rows_kernel
+//   phase 3   radix sort of the keys (= parlay::group_by_key with values in batch order),
+//             group heads, then K3 per group: append if it fits, else robustPrune             pann_find_heads_kernel
+// All reads of phase 1 see the pre-batch graph; phase 3 touches one row per group.  One GPU.
+#include <cub/device/device_radix_sort.cuh>
+
+#include <chrono>
+
 #include "pann_internal.h"
-extern "C" int pann_vamana_build(pann_index*, uint32_t, uint32_t, double, int, int, uint32_t*, uint32_t*, double*) { PANN_FAIL("pann_vamana_build: not built yet"); }
+#include "vamana_prune.cuh"
+
+__global__ void pann_write_rows_kernel(uint32_t* graph, uint32_t maxdeg, uint32_t R, uint64_t n, const uint32_t* perm_lo,
+                                       const uint32_t* new_out, const uint32_t* new_deg, uint32_t bs, u64* keys) {
+  uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= (uint64_t)bs * R) return;
+  uint32_t i = (uint32_t)(t / R), pos = (uint32_t)(t % R);
+  uint32_t p = perm_lo[i], deg = new_deg[i];
+  uint32_t* row = graph + (uint64_t)p * (maxdeg + 1);
+  if (pos == 0) row[0] = deg;
+  if (pos < deg) {
+    uint32_t nb = new_out[t];
+    row[1 + pos] = nb;
+    keys[t] = ((u64)nb << 32) | t;
+  } else {
+    keys[t] = ((u64)n << 32) | t;  // padding: sorts behind every real target
+  }
+}
+
+__global__ void pann_find_heads_kernel(const u64* sorted, uint32_t ns, uint64_t n, uint32_t* gstart, uint32_t* ngroups) {
+  uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= ns) return;
+  uint32_t t = (uint32_t)(sorted[j] >> 32);
+  if (t >= n) return;
+  if (j == 0 || (uint32_t)(sorted[j - 1] >> 32) != t) gstart[atomicAdd(ngroups, 1u)] = j;
+}
+
+static const void* prune_kernel(int dtype, int metric, int cpl, bool gs) {
+  switch (dtype) {
+    case PANN_DT_F32: return pann_prune_kernel_dt0(metric, cpl, gs);
+    case PANN_DT_U8: return pann_prune_kernel_dt1(metric, cpl, gs);
+    default: return pann_prune_kernel_dt2(metric, cpl, gs);
+  }
+}
+static const void* edge_kernel(int dtype, int metric, int cpl) {
+  switch (dtype) {
+    case PANN_DT_F32: return pann_edge_kernel_dt0(metric, cpl);
+    case PANN_DT_U8: return pann_edge_kernel_dt1(metric, cpl);
+    default: return pann_edge_kernel_dt2(metric, cpl);
+  }
+}
+static inline uint32_t al16(size_t x) { return (uint32_t)((x + 15) / 16 * 16); }
+
+// launches K3 over A's tasks (shared-memory variant), then the global-scratch variant over whatever it deferred
+static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevBuf& big, DevBuf& gscratch) {
+  const PannRowGeom& g = idx->geom;
+  const int cplT = g.cpl <= 3 ? (int)g.cpl : 0;
+  if (ntasks_bound == 0) return 0;
+  if (big.reserve(8 + 4ull * ntasks_bound)) return 1;
+  A.big_count = big.as<uint32_t>();
+  A.big_list = big.as<uint32_t>() + 2;
+  PANN_CUDA(cudaMemsetAsync(A.big_count, 0, 8, idx->stream));
+  A.cap = 512;
+  A.off_b = al16((size_t)A.cap * 8);
+  A.off_q = 2 * A.off_b;
+  A.warp_bytes = A.off_q + (cplT == 0 ? g.stride : 0);
+  A.task_map = nullptr; A.ntask_map = 0; A.g_scratch = nullptr;
+  {
+    const void* fn = prune_kernel(idx->dtype, idx->metric, cplT, false);
+    size_t cta_bytes = (size_t)A.warp_bytes * PANN_PRUNE_WARPS;
+    PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
+    int per_sm = 0;
+    PANN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, PANN_PRUNE_WARPS * 32, cta_bytes));
+    if (per_sm < 1) PANN_FAIL("robustPrune: kernel does not fit on an SM");
+    long long want = ((long long)ntasks_bound + PANN_PRUNE_WARPS - 1) / PANN_PRUNE_WARPS;
+    int grid = (int)std::max<long long>(1, std::min<long long>(want, (long long)per_sm * idx->sms));
+    void* args[] = {(void*)&A};
+    PANN_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(PANN_PRUNE_WARPS * 32), args, cta_bytes, idx->stream));
+    idx->last_launches++;
+  }
+  uint32_t bc[2] = {0, 0};
+  PANN_CUDA(cudaMemcpyAsync(bc, A.big_count, 8, cudaMemcpyDeviceToHost, idx->stream));
+  PANN_CUDA(cudaStreamSynchronize(idx->stream));
+  if (bc[0] == 0) return 0;
+  // rare: candidate lists beyond the shared-memory capacity — same kernel, lists in a global scratch slab
+  A.cap = bc[1];
+  A.task_map = A.big_list; A.ntask_map = bc[0];
+  A.off_b = 0; A.off_q = 0;
+  A.warp_bytes = (cplT == 0 ? g.stride : 0);
+  const void* fn = prune_kernel(idx->dtype, idx->metric, cplT, true);
+  size_t cta_bytes = (size_t)A.warp_bytes * PANN_PRUNE_WARPS;
+  PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
+  int grid = (int)std::min<uint32_t>((bc[0] + PANN_PRUNE_WARPS - 1) / PANN_PRUNE_WARPS, 4u * idx->sms);
+  if (gscratch.reserve((size_t)grid * PANN_PRUNE_WARPS * 2 * A.cap * 8)) return 1;
+  A.g_scratch = gscratch.as<u64>();
+  void* args[] = {(void*)&A};
+  PANN_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(PANN_PRUNE_WARPS * 32), args, cta_bytes, idx->stream));
+  idx->last_launches++;
+  return 0;
+}
+
+void pann_host_sort_rows(uint32_t* graph, const float* dists, uint64_t n, uint32_t maxdeg);
+
+extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double alpha, int num_passes, int sort_neighbors,
+                                 uint32_t* out_visited, uint32_t* out_cmps, double phase_seconds[3]) {
+  if (!idx) PANN_FAIL("pann_vamana_build: null index");
+  if (R == 0 || R != idx->maxdeg) PANN_FAIL("pann_vamana_build: R must equal the graph's max degree (BuildParams::max_degree, types.h:210-214)");
+  if (L < 1 || L > 65536) PANN_FAIL("pann_vamana_build: L out of range");
+  if (num_passes < 1) PANN_FAIL("pann_vamana_build: num_passes must be >= 1");
+  PANN_CUDA(cudaSetDevice(idx->device));
+  const uint64_t n = idx->n;
+  const uint32_t md = idx->maxdeg;
+  cudaStream_t s = idx->stream;
+  idx->last_launches = 0;
+
+  // insertion order and batch schedule: the reference's, bit for bit (index.h:206-234)
+  std::vector<int32_t> perm(n);
+  pann_host_random_permutation((int64_t)n, perm.data());
+  const int64_t nb = pann_host_batch_schedule(n, n, nullptr, nullptr, 0);
+  std::vector<int64_t> blo(nb), bhi(nb);
+  pann_host_batch_schedule(n, n, blo.data(), bhi.data(), nb);
+  uint64_t max_bs = 0;
+  for (int64_t b = 0; b < nb; b++) max_bs = std::max<uint64_t>(max_bs, (uint64_t)(bhi[b] - blo[b]));
+
+  DevBuf d_perm, d_vis_ids, d_vis_dists, d_cnt, d_new_out, d_keys, d_keys2, d_gstart, d_sort_tmp, d_big, d_gscr, d_stats;
+  auto release_all = [&]() {
+    d_perm.release(); d_vis_ids.release(); d_vis_dists.release(); d_cnt.release(); d_new_out.release(); d_keys.release();
+    d_keys2.release(); d_gstart.release(); d_sort_tmp.release(); d_big.release(); d_gscr.release(); d_stats.release();
+  };
+  struct Guard { decltype(release_all)& f; ~Guard() { f(); } } guard{release_all};
+
+  if (d_perm.reserve(4 * n)) return 1;
+  PANN_CUDA(cudaMemcpyAsync(d_perm.p, perm.data(), 4 * n, cudaMemcpyHostToDevice, s));
+  // a fresh build starts from the empty graph (Graph(maxDeg, n), graph.h:134-145)
+  PANN_CUDA(cudaMemsetAsync(idx->graph, 0, (size_t)n * (md + 1) * 4, s));
+  uint32_t* st_vis = nullptr; uint32_t* st_cmp = nullptr;
+  if (out_visited || out_cmps) {
+    if (d_stats.reserve(8 * n)) return 1;
+    PANN_CUDA(cudaMemsetAsync(d_stats.p, 0, 8 * n, s));
+    st_vis = d_stats.as<uint32_t>(); st_cmp = st_vis + n;
+  }
+  uint32_t vout = std::max<uint32_t>(2 * L, L + 64);
+  // per batch: nvis | cmps | status | new_deg | ngroups(1)
+  if (d_cnt.reserve(4 * (4 * max_bs + 4)) || d_new_out.reserve(4 * max_bs * R) || d_keys.reserve(8 * max_bs * R) ||
+      d_keys2.reserve(8 * max_bs * R) || d_gstart.reserve(4 * max_bs * R))
+    return 1;
+  int key_bits = 33; while (key_bits < 64 && (n >> (key_bits - 32)) != 0) key_bits++;  // targets 0..n inclusive
+  size_t sort_tmp_bytes = 0;
+  cub::DeviceRadixSort::SortKeys(nullptr, sort_tmp_bytes, d_keys.as<u64>(), d_keys2.as<u64>(), (int64_t)(max_bs * R), 0, key_bits, s);
+  if (d_sort_tmp.reserve(sort_tmp_bytes + 16)) return 1;
+
+  cudaEvent_t ev[4];
+  for (auto& e : ev) PANN_CUDA(cudaEventCreate(&e));
+  double ph[3] = {0, 0, 0};
+  const uint32_t start = 0;  // knn_index::set_start (index.h:148)
+  pann_query_params qp; qp.k = 0; qp.beam = L; qp.cut = 0.0; qp.limit = (int64_t)n; qp.degree_limit = md;  // index.h:250
+  int rc = 0;
+  for (int pass = 0; pass < num_passes && !rc; pass++) {
+    const double a = (pass == num_passes - 1) ? alpha : 1.0;  // index.h:173-178
+    for (int64_t b = 0; b < nb && !rc; b++) {
+      const uint32_t bs = (uint32_t)(bhi[b] - blo[b]);
+      const uint32_t* perm_lo = d_perm.as<uint32_t>() + blo[b];
+      uint32_t* c_nvis = d_cnt.as<uint32_t>();
+      uint32_t* c_cmps = c_nvis + max_bs;
+      int* c_status = (int*)(c_cmps + max_bs);
+      uint32_t* c_newdeg = (uint32_t*)(c_status + max_bs);
+      uint32_t* c_ngroups = c_newdeg + max_bs;
+      cudaEventRecord(ev[0], s);
+      // ---- phase 1: build-mode beam search from the start point, then robustPrune of the visited list
+      for (;;) {
+        if (d_vis_ids.reserve(4ull * max_bs * vout) || d_vis_dists.reserve(4ull * max_bs * vout)) { rc = 1; break; }
+        SearchOutputs o;
+        o.vis_ids = d_vis_ids.as<uint32_t>(); o.vis_dists = d_vis_dists.as<float>(); o.n_visited = c_nvis; o.vout = vout;
+        o.cmps = c_cmps; o.status = c_status;
+        int flag = 0;
+        if (pann_run_search(idx, nullptr, bs, idx->geom.stride, perm_lo, &start, 1, &qp, o, &flag)) { rc = 1; break; }
+        if (flag & (1 << 1)) {  // a visited list outgrew `vout`: redo the batch's searches with more room (nothing was written)
+          if (vout >= (1u << 20)) { pann_set_error("pann_vamana_build: visited list beyond 2^20 entries"); rc = 1; break; }
+          vout *= 2;
+          continue;
+        }
+        if (flag) { pann_set_error("pann_vamana_build: beam search failed (status " + std::to_string(flag) + ")"); rc = 1; }
+        break;
+      }
+      if (rc) break;
+      PruneArgs A;
+      memset(&A, 0, sizeof(A));
+      A.points = idx->points; A.stride = idx->geom.stride; A.nch = idx->geom.nch; A.lpr = idx->geom.lpr;
+      A.graph = idx->graph; A.maxdeg = md; A.R = R; A.n = n; A.alpha = a;
+      A.perm_lo = perm_lo; A.st_visited = st_vis; A.st_cmps = st_cmp;
+      A.mode = 0; A.ntasks = bs;
+      A.vis_ids = d_vis_ids.as<uint32_t>(); A.vis_dists = d_vis_dists.as<float>(); A.nvis = c_nvis; A.search_cmps = c_cmps; A.vout = vout;
+      A.new_out = d_new_out.as<uint32_t>(); A.new_deg = c_newdeg;
+      if (launch_prune(idx, A, bs, d_big, d_gscr)) { rc = 1; break; }
+      // ---- phase 2: rows of the inserted points + reverse-edge keys
+      const uint64_t nk = (uint64_t)bs * R;
+      pann_write_rows_kernel<<<(unsigned)((nk + 255) / 256), 256, 0, s>>>(idx->graph, md, R, n, perm_lo, d_new_out.as<uint32_t>(),
+                                                                       c_newdeg, bs, d_keys.as<u64>());
+      idx->last_launches++;
+      cudaEventRecord(ev[1], s);
+      // ---- phase 3a: group the reverse edges by target, values in batch order (index.h:278-282)
+      size_t tb = sort_tmp_bytes;
+      if (cub::DeviceRadixSort::SortKeys(d_sort_tmp.p, tb, d_keys.as<u64>(), d_keys2.as<u64>(), (int64_t)nk, 0, key_bits, s) != cudaSuccess) {
+        pann_set_error("pann_vamana_build: radix sort failed"); rc = 1; break;
+      }
+      idx->last_launches += (key_bits + 7) / 8 + 1;
+      PANN_CUDA(cudaMemsetAsync(c_ngroups, 0, 4, s));
+      pann_find_heads_kernel<<<(unsigned)((nk + 255) / 256), 256, 0, s>>>(d_keys2.as<u64>(), (uint32_t)nk, n, d_gstart.as<uint32_t>(), c_ngroups);
+      idx->last_launches++;
+      cudaEventRecord(ev[2], s);
+      // ---- phase 3b: per target, append or prune (index.h:289-300)
+      A.mode = 1; A.ntasks = (uint32_t)nk;
+      A.sorted = d_keys2.as<u64>(); A.nsorted = (uint32_t)nk; A.gstart = d_gstart.as<uint32_t>(); A.ngroups = c_ngroups;
+      if (launch_prune(idx, A, (uint32_t)std::min<uint64_t>(nk, n), d_big, d_gscr)) { rc = 1; break; }
+      cudaEventRecord(ev[3], s);
+      PANN_CUDA(cudaEventSynchronize(ev[3]));
+      for (int i = 0; i < 3; i++) { float ms = 0; cudaEventElapsedTime(&ms, ev[i], ev[i + 1]); ph[i] += ms * 1e-3; }
+    }
+  }
+  for (auto& e : ev) cudaEventDestroy(e);
+  if (rc) return 1;
+  PANN_CUDA(cudaGetLastError());
+
+  if (sort_neighbors) {  // index.h:180-185: per row, by distance to the owner only; the sort itself is std::sort on the
+    // host so that ties land exactly where the reference's libstdc++ introsort leaves them
+    DevBuf d_ed;
+    if (d_ed.reserve(4ull * n * md)) return 1;
+    EdgeDistArgs E;
+    memset(&E, 0, sizeof(E));
+    E.points = idx->points; E.stride = idx->geom.stride; E.nch = idx->geom.nch; E.lpr = idx->geom.lpr;
+    E.graph = idx->graph; E.maxdeg = md; E.n = n; E.out = d_ed.as<float>();
+    const int cplT = idx->geom.cpl <= 3 ? (int)idx->geom.cpl : 0;
+    E.off_q = al16((size_t)md * 4);
+    E.warp_bytes = E.off_q + (cplT == 0 ? idx->geom.stride : 0);
+    const void* fn = edge_kernel(idx->dtype, idx->metric, cplT);
+    size_t cta_bytes = (size_t)E.warp_bytes * PANN_PRUNE_WARPS;
+    PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
+    int grid = (int)std::min<uint64_t>((n + PANN_PRUNE_WARPS - 1) / PANN_PRUNE_WARPS, (uint64_t)idx->sms * 16);
+    void* args[] = {(void*)&E};
+    PANN_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(PANN_PRUNE_WARPS * 32), args, cta_bytes, s));
+    idx->last_launches++;
+    std::vector<uint32_t> hg((size_t)n * (md + 1));
+    std::vector<float> hd((size_t)n * md);
+    PANN_CUDA(cudaMemcpyAsync(hg.data(), idx->graph, hg.size() * 4, cudaMemcpyDeviceToHost, s));
+    PANN_CUDA(cudaMemcpyAsync(hd.data(), d_ed.p, hd.size() * 4, cudaMemcpyDeviceToHost, s));
+    PANN_CUDA(cudaStreamSynchronize(s));
+    d_ed.release();
+    pann_host_sort_rows(hg.data(), hd.data(), n, md);
+    PANN_CUDA(cudaMemcpyAsync(idx->graph, hg.data(), hg.size() * 4, cudaMemcpyHostToDevice, s));
+    PANN_CUDA(cudaStreamSynchronize(s));
+  }
+  if (out_visited) PANN_CUDA(cudaMemcpy(out_visited, st_vis, 4 * n, cudaMemcpyDeviceToHost));
+  if (out_cmps) PANN_CUDA(cudaMemcpy(out_cmps, st_cmp, 4 * n, cudaMemcpyDeviceToHost));
+  PANN_CUDA(cudaStreamSynchronize(s));
+  if (phase_seconds) { phase_seconds[0] = ph[0]; phase_seconds[1] = ph[1]; phase_seconds[2] = ph[2]; }
+  return 0;
+}

@@ -1,0 +1,264 @@
+// vamana_prune.cuh — K3: robustPrune, one warp per pruned vertex.
+//
+// Behavioural contract: knn_index::robustPrune (algorithms/vamana/index.h:63-120 and the ids-only overload
+// :124-137) and the reverse-edge step of batch_insert (:289-300) including add_neighbors_without_repeats
+// (:140-146): same candidate order ((dist,id) total order, adjacent duplicate ids dropped), same greedy
+// alpha-occlusion scan with the test  alpha * (double)d(p*,p') <= (double)d(p,p')  evaluated in double, same
+// distance-comparison counts.
+//
+// GPU layout (not a translation of the CPU loop): the candidate list is one array of 64-bit (dist,id) keys
+// in shared memory; the list is kept COMPACT — after each pick the survivors are rewritten in place by
+// ballot-ranked stores, so every pass of the occlusion scan is a dense batch of 128-bit row gathers
+// (same lane geometry and accumulation order as K1, so float distances are bit-identical between the two
+// kernels and duplicate ids always sort next to each other).
+#pragma once
+#include "beam_search.cuh"
+
+#define PANN_PRUNE_WARPS 4
+
+struct PruneArgs {
+  // row geometry (same member names as BeamArgs: pann_row_distances_g reads them)
+  const uint8_t* points; uint32_t stride, nch, lpr;
+  uint32_t* graph; uint32_t maxdeg, R;
+  uint64_t n;
+  double alpha;
+  int mode;                 // 0: phase 1 (visited lists -> new_out), 1: phase 3 (reverse-edge groups -> graph rows)
+  uint32_t ntasks;          // mode 0: batch size; mode 1: upper bound (real count read from *ngroups)
+  const uint32_t* perm_lo;  // insertion order, already offset to the batch: task i inserts perm_lo[i]
+  // mode 0 inputs: K1 build-mode outputs
+  const uint32_t* vis_ids; const float* vis_dists; const uint32_t* nvis; const uint32_t* search_cmps; uint32_t vout;
+  uint32_t* new_out; uint32_t* new_deg;  // ntasks x R, ntasks
+  // mode 1 inputs: sorted (target << 32 | seq) keys, group heads
+  const u64* sorted; uint32_t nsorted; const uint32_t* gstart; const uint32_t* ngroups;
+  // statistics (stats<indexType>, may be null)
+  uint32_t* st_visited; uint32_t* st_cmps;
+  // tasks whose candidate list exceeds `cap` are deferred to the global-scratch launch
+  uint32_t cap; uint32_t* big_list; uint32_t* big_count;  // big_count[0] = #deferred, [1] = their largest candidate count
+  const uint32_t* task_map; uint32_t ntask_map;  // GS launch: the deferred tasks
+  u64* g_scratch;                                 // GS launch: per warp 2 x cap keys
+  uint32_t off_b, off_q, warp_bytes;
+};
+
+template <int DT, int METRIC, int CPL, bool GS>
+__global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const PruneArgs A) {
+  extern __shared__ __align__(16) uint8_t pann_smem[];
+  const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  uint8_t* ws = pann_smem + (size_t)wic * A.warp_bytes;
+  const long long wglobal = (long long)blockIdx.x * PANN_PRUNE_WARPS + wic;
+  const long long wstride = (long long)gridDim.x * PANN_PRUNE_WARPS;
+  u64 *bufA, *bufB;
+  if constexpr (GS) {
+    bufA = A.g_scratch + (u64)wglobal * 2 * A.cap;
+    bufB = bufA + A.cap;
+  } else {
+    bufA = reinterpret_cast<u64*>(ws);
+    bufB = reinterpret_cast<u64*>(ws + A.off_b);
+  }
+  uint4* qsm = reinterpret_cast<uint4*>(ws + A.off_q);
+  uint32_t* cid = reinterpret_cast<uint32_t*>(bufB);  // candidate ids before they get their distances
+  const uint32_t ntasks = GS ? A.ntask_map : (A.mode == 1 ? *A.ngroups : A.ntasks);
+
+  for (long long tl = wglobal; tl < (long long)ntasks; tl += wstride) {
+    const uint32_t task = GS ? A.task_map[tl] : (uint32_t)tl;
+    // ---- who is pruned, and its candidates
+    uint32_t p, nc, g0 = 0;
+    if (A.mode == 0) {
+      p = A.perm_lo[task];
+      nc = A.nvis[task];
+    } else {
+      g0 = A.gstart[task];
+      p = (uint32_t)(A.sorted[g0] >> 32);
+      // group end = first key of a larger target (keys are sorted)
+      uint32_t lo = g0 + 1, hi = A.nsorted;
+      while (lo < hi) { uint32_t mid = (lo + hi) >> 1; if ((uint32_t)(A.sorted[mid] >> 32) <= p) lo = mid + 1; else hi = mid; }
+      nc = lo - g0;
+    }
+    uint32_t* grow = A.graph + (u64)p * (A.maxdeg + 1);
+    const uint32_t deg = grow[0];
+    const uint32_t C0 = nc + deg;
+    if (C0 > A.cap) {  // defer to the global-scratch launch (only GS == false can get here: its cap is exact)
+      if (lane == 0) { A.big_list[atomicAdd(A.big_count, 1u)] = task; atomicMax(A.big_count + 1, C0); }
+      continue;
+    }
+    // ---- reverse edges that fit: new ones first, then the old ones not among them (index.h:291-294, :140-146)
+    if (A.mode == 1 && C0 <= A.R) {
+      for (uint32_t i = lane; i < nc; i += 32) cid[i] = A.perm_lo[(uint32_t)A.sorted[g0 + i] / A.R];
+      __syncwarp();
+      uint32_t m = nc;
+      for (uint32_t base = 0; base < deg; base += 32) {
+        uint32_t i = base + lane;
+        uint32_t x = i < deg ? grow[1 + i] : 0u;
+        bool keep = i < deg;
+        if (keep) for (uint32_t j = 0; j < nc; j++) if (cid[j] == x) { keep = false; break; }
+        unsigned km = __ballot_sync(PANN_FULL, keep);
+        __syncwarp();
+        if (keep) cid[m + __popc(km & lt_mask)] = x;
+        m += __popc(km);
+      }
+      __syncwarp();
+      // the row is rewritten only after all of it has been read
+      for (uint32_t i = lane; i < m; i += 32) grow[1 + i] = cid[i];
+      if (lane == 0) grow[0] = m;
+      __syncwarp();
+      continue;
+    }
+    // ---- query row = the pruned vertex
+    const uint8_t* prow = A.points + (u64)p * A.stride;
+    uint4 qreg[CPL > 0 ? CPL : 1];
+    auto load_q = [&](const uint8_t* row) {
+      if constexpr (CPL > 0) {
+#pragma unroll
+        for (int c = 0; c < CPL; c++) {
+          int ch = (lane % A.lpr) + c * A.lpr;
+          qreg[c] = (ch < (int)A.nch) ? pann_ldg16(row + ch * 16) : make_uint4(0, 0, 0, 0);
+        }
+      } else {
+        __syncwarp();
+        for (int ch = lane; ch < (int)A.nch; ch += 32) qsm[ch] = pann_ldg16(row + ch * 16);
+        __syncwarp();
+      }
+    };
+    load_q(prow);
+    unsigned comps = 0;
+    int C = 0;  // keys in bufA
+    // candidates that already carry a distance (mode 0: the visited list, sorted by K1)
+    if (A.mode == 0) {
+      const uint32_t* vi = A.vis_ids + (u64)task * A.vout;
+      const float* vd = A.vis_dists + (u64)task * A.vout;
+      for (uint32_t i = lane; i < nc; i += 32) bufA[i] = pann_key(vd[i], vi[i]);
+      C = (int)nc;
+    }
+    // candidates that need one: mode 1 group members (:131-134), then the current out-neighbours (:72-77)
+    {
+      uint32_t m = 0;
+      if (A.mode == 1) { for (uint32_t i = lane; i < nc; i += 32) cid[i] = A.perm_lo[(uint32_t)A.sorted[g0 + i] / A.R]; m = nc; }
+      for (uint32_t i = lane; i < deg; i += 32) cid[m + i] = grow[1 + i];
+      m += deg;
+      __syncwarp();
+      comps += m;
+      pann_row_distances_g<DT, METRIC, CPL>(
+          A, [&](int r) { return (u64)cid[r] << 1; }, (int)m, qreg, qsm, lane, [&](u64 tag, float d, bool ok) {
+            unsigned bm = __ballot_sync(PANN_FULL, ok);
+            if (ok) bufA[C + __popc(bm & lt_mask)] = pann_key(d, pann_key_id(tag));
+            C += __popc(bm);
+          });
+      __syncwarp();
+    }
+    // ---- sort by (dist,id) (:80-83).  Mode 0 without out-neighbours is sorted already.
+    u64* S = bufB;
+    if (A.mode == 0 && deg == 0) {
+      S = bufA;
+    } else {
+      for (int i = lane; i < C; i += 32) {
+        u64 ci = bufA[i];
+        int r = 0;
+        for (int j = 0; j < C; j++) { u64 cj = bufA[j]; r += (cj < ci) || (cj == ci && j < i); }
+        bufB[r] = ci;
+      }
+      __syncwarp();
+      // std::unique on ids (:86-88): the same id has the same distance, so duplicates are adjacent
+      int w = 0;
+      for (int base = 0; base < C; base += 32) {
+        int i = base + lane;
+        u64 c = i < C ? bufB[i] : 0;
+        bool keep = i < C && (i == 0 || pann_key_id(bufB[i - 1]) != pann_key_id(c));
+        unsigned km = __ballot_sync(PANN_FULL, keep);
+        __syncwarp();
+        if (keep) bufB[w + __popc(km & lt_mask)] = c;
+        w += __popc(km);
+        __syncwarp();
+      }
+      C = w;
+    }
+    // ---- greedy occlusion scan (:95-116); S[start, n) = live candidates in order
+    uint32_t* outp = A.mode == 0 ? A.new_out + (u64)task * A.R : grow + 1;
+    int start = 0, n = C;
+    uint32_t m = 0;
+    while (m < A.R && start < n) {
+      const u64 ps = S[start];
+      start++;
+      const uint32_t ps_id = pann_key_id(ps);
+      if (ps_id == p) continue;
+      if (lane == 0) outp[m] = ps_id;
+      m++;
+      const int cnt = n - start;
+      if (cnt == 0) break;
+      comps += cnt;  // one distance per live later candidate (:108)
+      load_q(A.points + (u64)ps_id * A.stride);
+      int w = start;
+      pann_row_distances_g<DT, METRIC, CPL>(
+          A, [&](int r) { return S[start + r]; }, cnt, qreg, qsm, lane, [&](u64 key, float d, bool ok) {
+            bool keep = ok && !(A.alpha * (double)d <= (double)pann_key_dist(key));  // :111
+            unsigned km = __ballot_sync(PANN_FULL, keep);
+            if (keep) S[w + __popc(km & lt_mask)] = key;
+            w += __popc(km);
+          });
+      __syncwarp();
+      n = w;
+    }
+    if (lane == 0) {
+      if (A.mode == 0) {
+        A.new_deg[task] = m;
+        if (A.st_cmps) A.st_cmps[p] += A.search_cmps[task] + comps;
+        if (A.st_visited) A.st_visited[p] += nc;
+      } else {
+        grow[0] = m;
+        if (A.st_cmps) A.st_cmps[p] += comps;
+      }
+    }
+    __syncwarp();
+  }
+}
+
+// K6: distance of every edge to its owner, one warp per graph row (build_index's final per-row sort,
+// algorithms/vamana/index.h:180-185, compares exactly these values).  out: n x maxdeg floats.
+struct EdgeDistArgs {
+  const uint8_t* points; uint32_t stride, nch, lpr;
+  const uint32_t* graph; uint32_t maxdeg; uint64_t n;
+  float* out;
+  uint32_t off_q, warp_bytes;
+};
+template <int DT, int METRIC, int CPL>
+__global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_edge_dist_kernel(const EdgeDistArgs A) {
+  extern __shared__ __align__(16) uint8_t pann_smem[];
+  const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+  uint8_t* ws = pann_smem + (size_t)wic * A.warp_bytes;
+  uint32_t* ids = reinterpret_cast<uint32_t*>(ws);
+  uint4* qsm = reinterpret_cast<uint4*>(ws + A.off_q);
+  const long long wglobal = (long long)blockIdx.x * PANN_PRUNE_WARPS + wic;
+  const long long wstride = (long long)gridDim.x * PANN_PRUNE_WARPS;
+  for (long long i = wglobal; i < (long long)A.n; i += wstride) {
+    const uint32_t* grow = A.graph + (u64)i * (A.maxdeg + 1);
+    const int deg = (int)grow[0];
+    const uint8_t* row = A.points + (u64)i * A.stride;
+    uint4 qreg[CPL > 0 ? CPL : 1];
+    if constexpr (CPL > 0) {
+#pragma unroll
+      for (int c = 0; c < CPL; c++) {
+        int ch = (lane % A.lpr) + c * A.lpr;
+        qreg[c] = (ch < (int)A.nch) ? pann_ldg16(row + ch * 16) : make_uint4(0, 0, 0, 0);
+      }
+    } else {
+      for (int ch = lane; ch < (int)A.nch; ch += 32) qsm[ch] = pann_ldg16(row + ch * 16);
+    }
+    for (int j = lane; j < deg; j += 32) ids[j] = grow[1 + j];
+    __syncwarp();
+    float* o = A.out + (u64)i * A.maxdeg;
+    int w = 0;
+    pann_row_distances_g<DT, METRIC, CPL>(
+        A, [&](int r) { return (u64)ids[r] << 1; }, deg, qreg, qsm, lane, [&](u64, float d, bool ok) {
+          unsigned bm = __ballot_sync(PANN_FULL, ok);
+          if (ok) o[w + __popc(bm & ((1u << lane) - 1u))] = d;
+          w += __popc(bm);
+        });
+    __syncwarp();
+  }
+}
+
+const void* pann_prune_kernel_dt0(int metric, int cpl, bool gs);
+const void* pann_prune_kernel_dt1(int metric, int cpl, bool gs);
+const void* pann_prune_kernel_dt2(int metric, int cpl, bool gs);
+const void* pann_edge_kernel_dt0(int metric, int cpl);
+const void* pann_edge_kernel_dt1(int metric, int cpl);
+const void* pann_edge_kernel_dt2(int metric, int cpl);

@@ -155,3 +155,29 @@ def test_synthetic_device_generator_matches_cpu(dataset):
         assert np.array_equal(idx.points(), cpu), (dt, kind, d)
         idx.synthetic_queries(200, kind=kind, seed=99, stream=1, r=r, nc=nc)
         assert np.array_equal(idx.download_queries(), O.gen_points(kind, 200, d, seed=99, stream=1, r=r, nc=nc))
+
+
+def test_search_matches_reference_golden():
+    # the CUDA path against outputs of the UNMODIFIED reference (tests/golden, made by oracle/_ref/ref_driver)
+    import parlayann_b200 as P
+    from golden_util import INT_CASES, SEARCHES, golden
+    for name in INT_CASES:
+        g = golden(name)
+        idx = P.GraphIndex(g.base, g.graph, g.data_type, g.metric)
+        ran = 0
+        for si, s in enumerate(SEARCHES):
+            if f"s{si}_ids" not in g.z:
+                continue
+            ids, _, vis, cmps = idx.search(g.queries, **s)
+            assert np.array_equal(ids, g.z[f"s{si}_ids"]), (name, s)
+            assert np.array_equal(vis, g.z[f"s{si}_visited"]) and np.array_equal(cmps, g.z[f"s{si}_distances"]), (name, s)
+            ran += 1
+        assert ran >= 4
+        # build-mode visited lists
+        cnt = g.z["self_counts"]
+        got = idx.search_full(self_ids=np.arange(g.nq, dtype=np.uint32), k=0, beam=g.L, cut=0.0, vcap=2048)
+        assert np.array_equal(got["nvis"], cnt[:, 1]) and np.array_equal(got["cmps"], cnt[:, 2])
+        vi = g.split_lists(cnt[:, 1], g.z["self_visited"])
+        for i in range(g.nq):
+            assert np.array_equal(got["vis_ids"][i, :cnt[i, 1]], vi[i][:, 0])
+            assert np.array_equal(got["vis_dists"][i, :cnt[i, 1]].view(np.uint32), vi[i][:, 1])
