@@ -1,0 +1,383 @@
+#!/usr/bin/env python
+"""bench.py — QPS at recall@10 >= 0.95 of the batched beam search (BASELINE.json metric), one JSON line.
+
+Workload (config.workload): Vamana search over a synthetic BIGANN-shaped set (default 1M x 128 uint8, BASELINE.json
+configs[1]), 10 000 queries per GPU per step, graph R=64 L=128 alpha=1.2 built ON THE GPU by pann_vamana_build (the
+build time is reported too), exact ground truth from K4, QueryParams chosen by the reference's own sweep
+(check_nn_recall.h:214-257) as the cheapest setting whose tie-aware recall@10 is >= 0.95.
+
+  value   whole-job QPS with queries resident in HBM (device time from CUDA events on the library's stream)
+  e2e     the same through pann_search_batch with pinned HOST buffers: H2D queries + search + D2H ids/dists/counters
+  roofline  algorithmic bytes of the batch (counted on the device) / K1's device time, vs measured HBM
+  cpu_baseline  the unmodified reference (oracle/_ref/ref_driver -> qsearchAll) on this box's cores, same graph
+
+`--impl reference` runs only the reference's CPU path (it builds its own graph and ground truth with its own code).
+Multi-GPU (torchrun): one rank per GPU, replicated index, every rank searches its own 10 000-query batch
+(weak scaling, no data-path collective); time = max over ranks.
+"""
+import argparse
+import json
+import os
+import re
+import shutil
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+K = 10
+CUT_F = float(np.float32(1.35))   # the sweep passes the cut through a float (check_nn_recall.h:231)
+BEAMS = [10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 20, 22, 24, 26, 28, 30, 32, 34, 36, 38, 40, 45, 50, 55, 60, 65, 70, 80, 90, 100,
+         120, 140, 160, 180, 200, 225, 250, 275, 300, 375, 500, 750, 1000]
+LIMITS = [10, 11, 12, 13, 14, 15, 16, 17, 18, 19, 20, 21, 22, 23, 24, 25, 26, 28, 30, 35]
+
+
+def sweep_settings(maxdeg):
+    """(kind, k, beam, cut, limit, degree_limit) in the order of search_and_parse (check_nn_recall.h:214-254)."""
+    out = [("beam", K, b, CUT_F, -1, -1) for b in BEAMS if b >= K]
+    out += [("limit", K, max(l, K), 1.35, l, min(maxdeg, 5 * l)) for l in LIMITS]
+    return out
+
+
+def recall_with_ties(ids, gt_ids, gt_d, k):
+    """check_nn_recall.h:83-109, vectorised."""
+    kk = gt_ids.shape[1]
+    col = np.arange(kk)[None, :]
+    truth = (col < k) | (gt_d == gt_d[:, k - 1:k])
+    hit = ((ids[:, :k, None] == gt_ids[:, None, :]) & truth[:, None, :]).any(axis=2)
+    return float(np.float32(hit.sum()) / np.float32(k * ids.shape[0]))
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu):
+        self.gpu, self.lines, self.p = gpu, [], None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(self.gpu)],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=lambda: [self.lines.append(l) for l in self.p.stdout], daemon=True).start()
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.p.terminate()
+        sm, mx, reasons = [], [], set()
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# the reference's CPU path (oracle/_ref/ref_driver = the unmodified reference headers); used for cpu_baseline and
+# for --impl reference.  The only place bench.py touches oracle/.
+def ref_tools():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_lib as O
+    drv = O.ref_driver_path()
+    if drv is None:
+        raise RuntimeError("oracle/_ref/ref_driver missing or not runnable on this CPU (build it where /root/reference exists)")
+    return O, drv
+
+
+def ref_recall_runs(O, files, settings, reps):
+    """runs checkRecall (timed qsearchAll + tie-aware recall) for each setting; returns list of dict per (setting, rep)"""
+    st = ";".join(f"{k}:{b}:{c!r}:{l}:{d}" for (_, k, b, c, l, d) in settings)
+    out = O.ref_run(["recall", "-data_type", "uint8", "-dist_func", "Euclidian", "-base", files["base"], "-graph", files["graph"],
+                     "-query", files["query"], "-gt", files["gt"], "-settings", st, "-reps", reps])
+    rows = []
+    for m in re.finditer(r"REF_RECALL (\S+) QPS (\S+) avg_cmps (\d+) tail_cmps (\d+) avg_visited (\d+) tail_visited (\d+) k (\d+) beam (\d+) limit (\d+) dl (\d+)", out):
+        rows.append(dict(recall=float(m.group(1)), qps=float(m.group(2)), avg_cmps=int(m.group(3)), avg_visited=int(m.group(5)),
+                         beam=int(m.group(8)), limit=int(m.group(9)), dl=int(m.group(10))))
+    assert len(rows) == len(settings) * reps, out[-2000:]
+    return rows
+
+
+def choose_setting(settings, evaluate):
+    """first beam setting and first limit setting with recall >= 0.95 (both lists ascend in cost); the cheaper one
+    by average distance comparisons wins.  evaluate(setting) -> (recall, avg_cmps)."""
+    best = None
+    for kind in ("beam", "limit"):
+        for s in [x for x in settings if x[0] == kind]:
+            r, c = evaluate(s)
+            if r >= 0.95:
+                if best is None or c < best[2]:
+                    best = (s, r, c)
+                break
+    if best is None:
+        raise RuntimeError("no sweep setting reaches recall 0.95")
+    return best
+
+
+def run_reference(args, rank, world):
+    """--impl reference: everything through the reference's own code on the host cores."""
+    if rank != 0:
+        return
+    O, drv = ref_tools()
+    from parlayann_b200 import fileio
+    tmp = tempfile.mkdtemp(prefix="pann_ref_")
+    try:
+        t0 = time.time()
+        base = O.gen_points("uint8", args.n, 128)
+        qs = O.gen_points("uint8", args.nq, 128, stream=1)
+        files = {k: os.path.join(tmp, k) for k in ("base", "query", "graph", "gt")}
+        fileio.write_bin(files["base"], base); fileio.write_bin(files["query"], qs)
+        common = ["-data_type", "uint8", "-dist_func", "Euclidian", "-base", files["base"]]
+        out = O.ref_run(["build"] + common + ["-R", 64, "-L", 128, "-alpha", 1.2, "-out", os.path.join(tmp, "b")])
+        build_s = float(re.search(r"REF_BUILD_SECONDS (\S+)", out).group(1))
+        os.replace(os.path.join(tmp, "b.graph"), files["graph"])
+        out = O.ref_run(["gt"] + common + ["-query", files["query"], "-k", 100, "-out", os.path.join(tmp, "g")])
+        gt_s = float(re.search(r"REF_GT_SECONDS (\S+)", out).group(1))
+        os.replace(os.path.join(tmp, "g.ibin"), files["gt"])
+        settings = sweep_settings(64)
+        cache = {}
+
+        def ev(s):
+            if s not in cache:
+                r = ref_recall_runs(O, files, [s], 1)[0]
+                cache[s] = (r["recall"], r["avg_cmps"])
+            return cache[s]
+        (s, rec, cm) = choose_setting(settings, ev)
+        rows = ref_recall_runs(O, files, [s], args.warmup + args.steps)[args.warmup:]
+        ms = [1e3 * args.nq / r["qps"] for r in rows]
+        ms_per_step = float(np.mean(ms))
+        qps = args.nq / (ms_per_step * 1e-3)
+        cores = os.cpu_count()
+        line = {"impl": "reference", "metric": "QPS@recall10>=0.95", "value": qps, "unit": "queries/s", "n_gpus": args.gpus,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+                "config": workload_config(args, s, rec, cm),
+                "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": "reference",
+                                 "sample": f"all {args.nq} queries per step, {args.steps} steps, qsearchAll via checkRecall"},
+                "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                "gpu_launches": 0,
+                "reference_build_seconds": build_s, "reference_groundtruth_seconds": gt_s, "setup_seconds": time.time() - t0}
+        print(json.dumps(line), flush=True)
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+def workload_config(args, s, rec, cm):
+    kind, k, beam, cut, limit, dl = s
+    return {"workload": f"vamana_search_{args.n}x128_u8_{args.nq}q_per_gpu", "n": args.n, "dims": 128, "queries_per_gpu_per_step": args.nq,
+            "graph": "Vamana R=64 L=128 alpha=1.2 1 pass", "k": k, "beam": beam, "cut": cut,
+            "visit_limit": limit if limit >= 0 else args.n, "degree_limit": dl if dl >= 0 else 64, "recall10": rec, "avg_cmps": cm,
+            "parallelism": f"replicated index, queries sharded x{args.gpus}", "l2": "index 388 MB > L2; 256 MiB flush between steps"}
+
+
+# ----------------------------------------------------------------------------------------------------------------
+def run_ours(args, rank, local_rank, world):
+    import torch
+    import parlayann_b200 as P
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (parlayann_b200 has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def allmax(x):
+        t = torch.tensor([x], dtype=torch.float64, device="cuda")
+        if dist is not None:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    n, nq, R, L = args.n, args.nq, 64, 128
+    # ---- setup (untimed): replicated index, points synthesised on the device, graph built on the device
+    t_setup = time.time()
+    idx = P.GraphIndex(data_type="uint8", metric="Euclidian", max_degree=R, device=local_rank,
+                       synthetic=dict(n=n, d=128, kind="uint8", seed=1234, stream=0, r=24, nc=256))
+    t0 = time.time()
+    idx.build(R=R, L=L, alpha=1.2, num_passes=1, sort_neighbors=True)
+    build_s = time.time() - t0
+    build_launches = idx.last_timing()[1]
+    phases = idx.build_phase_seconds
+    # rank r searches its own query batch (generator stream 1 + r); rank 0's is the parity / recall batch
+    idx.synthetic_queries(nq, kind="uint8", seed=1234, stream=1 + rank)
+    queries = idx.download_queries()
+    t0 = time.time()
+    idx.groundtruth_resident(k=100)
+    gt_ms = idx.last_timing()[0]
+    gt_ids, gt_d = idx.fetch_groundtruth()
+    gt_s = time.time() - t0
+
+    settings = sweep_settings(R)
+    cache = {}
+
+    def qp_of(s):
+        kind, k, beam, cut, limit, dl = s
+        return dict(k=k, beam=beam, cut=cut, limit=None if limit < 0 else limit, degree_limit=None if dl < 0 else dl)
+
+    def ev(s):
+        if s not in cache:
+            idx.search_resident(**qp_of(s))
+            ids, _, vis, cmps = idx.fetch_results()
+            cache[s] = (recall_with_ties(ids, gt_ids, gt_d, K), int(cmps.astype(np.int64).sum() // nq))
+        return cache[s]
+    # every rank must time the same QueryParams: rank 0's batch decides
+    s, rec, cm = choose_setting(settings, ev)
+    if dist is not None:
+        obj = [s]
+        dist.broadcast_object_list(obj, src=0)
+        s = tuple(obj[0])
+        rec, cm = ev(s)
+    qp = qp_of(s)
+    setup_s = time.time() - t_setup
+
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+
+    def l2_flush():
+        flush.zero_()
+        torch.cuda.synchronize()
+
+    # pinned host buffers for the end-to-end path
+    hq = torch.from_numpy(queries).pin_memory()
+    out = (torch.empty((nq, K), dtype=torch.int32).pin_memory().numpy().view(np.uint32), torch.empty((nq, K), dtype=torch.float32).pin_memory().numpy(),
+           torch.empty(nq, dtype=torch.int32).pin_memory().numpy().view(np.uint32), torch.empty(nq, dtype=torch.int32).pin_memory().numpy().view(np.uint32))
+    hq_np = hq.numpy()
+
+    # ---- device-resident arm: W warm-up steps, then exactly K timed steps
+    for _ in range(args.warmup):
+        l2_flush(); idx.search_resident(**qp)
+    sampler = ClockSampler(local_rank)
+    barrier()
+    sampler.start()
+    dev_ms, launches, abytes = 0.0, 0, 0
+    t_wall0 = time.perf_counter()
+    if args.profile:
+        torch.cuda.profiler.start()        # ncu --profile-from-start off: only the timed steps are captured
+    for _ in range(args.steps):
+        l2_flush()
+        idx.search_resident(**qp)          # synchronous; device time from CUDA events on the library's stream
+        ms, nl = idx.last_timing()
+        dev_ms += ms; launches += nl; abytes += idx.last_bytes()
+    if args.profile:
+        torch.cuda.profiler.stop()
+    barrier()
+    wall_ms = (time.perf_counter() - t_wall0) * 1e3
+    # ---- end-to-end arm: host queries in, host results out, through the public batch call
+    for _ in range(args.warmup):
+        l2_flush(); idx.search(hq_np, out=out, **qp)
+    barrier()
+    e2e_ms = 0.0
+    for _ in range(args.steps):
+        l2_flush()
+        t0 = time.perf_counter()
+        idx.search(hq_np, out=out, **qp)   # H2D + K1 + D2H, returns when the results are in host memory
+        e2e_ms += (time.perf_counter() - t0) * 1e3
+    barrier()
+    clocks = sampler.stop()
+    ms_per_step = allmax(dev_ms / args.steps)
+    e2e_ms_per_step = allmax(e2e_ms / args.steps)
+    launches_all = int(allmax(launches))  # per rank (identical on every rank)
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        achieved = (abytes / args.steps) / (dev_ms / args.steps * 1e-3) / 1e9
+        traffic = None
+        try:
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get("k1_dram_bytes_per_launch")
+        except Exception:
+            pass
+        line = {"metric": "QPS@recall10>=0.95", "value": world * nq / (ms_per_step * 1e-3), "unit": "queries/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": workload_config(args, s, rec, cm),
+                "e2e": {"value": world * nq / (e2e_ms_per_step * 1e-3), "unit": "queries/s", "ms_per_step": e2e_ms_per_step,
+                        "h2d_bytes_per_step": int(hq_np.nbytes), "d2h_bytes_per_step": int(sum(o.nbytes for o in out))},
+                "gpu_launches": launches_all,
+                "clocks": clocks,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": traffic, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
+                             "algorithmic_bytes_per_launch": abytes / args.steps, "kernel": "pann_beam_search_kernel<u8,L2>"},
+                "wall_ms_per_step_incl_l2_flush": wall_ms / args.steps,
+                "build": {"seconds": build_s, "phase_seconds": {"beam_search+prune": phases[0], "bidirect": phases[1], "reverse_prune": phases[2]},
+                          "launches": build_launches, "what": f"pann_vamana_build {n}x128 u8 R=64 L=128 alpha=1.2, final sort incl."},
+                "groundtruth": {"seconds": gt_s, "device_ms": gt_ms, "what": f"{nq} x {n} x 128 u8, k=100"},
+                "setup_seconds": setup_s}
+        if world == 1 and not args.no_cpu_baseline:
+            try:
+                line["cpu_baseline"] = cpu_baseline(args, idx, queries, gt_ids, gt_d, s)
+            except Exception as e:  # the reference binary may be missing on a box that never saw /root/reference
+                line["cpu_baseline"] = {"value": None, "unit": "queries/s", "cores": os.cpu_count(), "kind": "reference", "sample": f"failed: {e}"}
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def cpu_baseline(args, idx, queries, gt_ids, gt_d, s):
+    """the unmodified reference's qsearchAll on the host cores, same points / graph / queries / QueryParams"""
+    O, drv = ref_tools()
+    from parlayann_b200 import fileio
+    tmp = tempfile.mkdtemp(prefix="pann_cpu_")
+    try:
+        files = {k: os.path.join(tmp, k) for k in ("base", "query", "graph", "gt")}
+        fileio.write_bin(files["base"], idx.points()); fileio.write_bin(files["query"], queries)
+        fileio.write_graph(files["graph"], idx.graph()); fileio.write_ibin(files["gt"], gt_ids, gt_d)
+        rows = ref_recall_runs(O, files, [s], 4)[1:]
+        qps = float(np.mean([r["qps"] for r in rows]))
+        return {"value": qps, "unit": "queries/s", "cores": os.cpu_count(), "kind": "reference", "recall10": rows[0]["recall"],
+                "avg_cmps": rows[0]["avg_cmps"],
+                "sample": f"all {args.nq} queries x 3 timed runs (1 warm-up) of the reference's checkRecall/qsearchAll on the GPU-built graph"}
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=1000000)
+    ap.add_argument("--nq", type=int, default=10000)
+    ap.add_argument("--profile", action="store_true", help="cudaProfilerStart/Stop around the timed device-resident steps")
+    ap.add_argument("--no-cpu-baseline", dest="no_cpu_baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, local_rank, world)
+
+
+if __name__ == "__main__":
+    main()

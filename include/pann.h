@@ -60,6 +60,9 @@ int pann_index_get_points(pann_index* idx, uint64_t row0, uint64_t nrows, void* 
 int pann_index_info(pann_index* idx, uint64_t* n, uint32_t* dims, uint32_t* max_degree, int* dtype, int* metric);
 /* device time (ms, CUDA events on the index's stream) and kernel-launch count of the last compute call */
 int pann_index_last_timing(pann_index* idx, float* kernel_ms, int* launches);
+/* algorithmic bytes of the last beam-search call (per query cmps*row_bytes + 4*(ids read from graph rows
+ * + rows visited) + row_bytes + 4k), summed on the device — the numerator of the HBM-gather roofline */
+int pann_index_last_bytes(pann_index* idx, uint64_t* algorithmic_bytes);
 
 /* qsearchAll / searchAll (algorithms/utils/beamSearch.h:537-565, :353-387): one beam search per query
  * (filtered_beam_search, beamSearch.h:22-214) from the given start points; writes the first k ids of each

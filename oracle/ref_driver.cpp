@@ -167,13 +167,31 @@ static int run(const std::string& cmd, int argc, char** argv) {
   }
 
   if (cmd == "recall") {
+    // -settings "k:beam:cut:limit:degree_limit;..." runs several QueryParams in one process (limit/degree_limit < 0 = n / maxDeg)
     groundTruth<uint> GT((char*)need(argc, argv, "-gt"));
     int reps = atoi(arg(argc, argv, "-reps", "1"));
-    for (int r = 0; r < reps; r++) {
-      nn_result N = checkRecall<PR, PR, PR, uint>(G, Points, Q, Points, Q, Points, Q, GT, false, start, k, QP, false);
-      printf("REF_RECALL %.9f QPS %.3f avg_cmps %u tail_cmps %u avg_visited %u tail_visited %u\n",
-             N.recall, (double)N.QPS, N.avg_cmps, N.tail_cmps, N.avg_visited, N.tail_visited);
+    std::vector<QueryParams> qps;
+    if (const char* st = arg(argc, argv, "-settings")) {
+      std::string all = st;
+      size_t pos = 0;
+      while (pos < all.size()) {
+        size_t e = all.find(';', pos);
+        if (e == std::string::npos) e = all.size();
+        long a, b, l, d; double c;
+        if (sscanf(all.substr(pos, e - pos).c_str(), "%ld:%ld:%lf:%ld:%ld", &a, &b, &c, &l, &d) != 5) { fprintf(stderr, "bad -settings\n"); return 2; }
+        qps.push_back(QueryParams(a, b, c, l < 0 ? (long)G.size() : l, d < 0 ? (long)G.max_degree() : d));
+        pos = e + 1;
+      }
+    } else {
+      qps.push_back(QP);
     }
+    for (auto& qp : qps)
+      for (int r = 0; r < reps; r++) {
+        nn_result N = checkRecall<PR, PR, PR, uint>(G, Points, Q, Points, Q, Points, Q, GT, false, start, qp.k, qp, false);
+        printf("REF_RECALL %.9f QPS %.3f avg_cmps %u tail_cmps %u avg_visited %u tail_visited %u k %ld beam %ld limit %ld dl %ld\n",
+               N.recall, (double)N.QPS, N.avg_cmps, N.tail_cmps, N.avg_visited, N.tail_visited, qp.k, qp.beamSize, qp.limit, qp.degree_limit);
+        fflush(stdout);
+      }
     return 0;
   }
   fprintf(stderr, "ref_driver: unknown command %s\n", cmd.c_str());

@@ -46,6 +46,8 @@ struct BeamArgs {
   int* status;                               // nq: 0 ok, 1 visited overflow, 2 fewer than k results, 3 too many starts
   int* any_status;                           // OR of all non-zero statuses (one word)
   const uint32_t* qmap;                      // optional: launch index -> query index (retries of a subset)
+  // algorithmic bytes of the batch (B_q = cmps*row + sum_hops 4*(1+nbrs read) + row + 4k), one atomic per query
+  u64* bytes_total; uint32_t rowbytes;
   // global scratch (GS variant): per resident warp
   uint32_t* g_hash; u64* g_vis;
 };
@@ -168,6 +170,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
     u64* nf = bufB;
     int F = 0, V = 0, C = 0, status = 0;
     unsigned cmps = A.nstarts;  // beamSearch.h:84
+    unsigned nread = 0;        // neighbour ids read from graph rows
 
     // ---- starting points (:64-70): distances, hash-filter insertion in list order, sort
     if ((int)A.nstarts > B || A.nstarts > A.ccap) {
@@ -231,6 +234,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
       const uint32_t* grow = A.graph + (u64)pann_key_id(cur) * (A.maxdeg + 1);
       const int deg = (int)__ldg(grow);
       const int ne = min(deg, A.degree_limit);
+      nread += ne;
       int S = 0;
       __syncwarp();
       for (int base = 0; base < ne; base += 32) {
@@ -356,6 +360,8 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
       if (A.n_visited) A.n_visited[q] = V;
       if (A.status) A.status[q] = status;
       if (status && A.any_status) atomicOr(A.any_status, 1 << status);
+      if (A.bytes_total)
+        atomicAdd(A.bytes_total, (u64)cmps * A.rowbytes + 4ull * (nread + (unsigned)V) + A.rowbytes + 4ull * (unsigned)A.k);
     }
     __syncwarp();
   }

@@ -1,5 +1,281 @@
+// groundtruth.cu — K4: brute-force exact k-NN (data_tools/compute_groundtruth.cpp:22-60 + write_ibin's per-row
+// sort :68-73), and K5: the k-way merge of per-shard results.
+//
+// v1 layout: the base set is walked in chunks; per chunk
+//   pann_gt_dist_kernel    64 queries x 64 base rows per CTA, 4x4 register tile per thread, operands staged
+//                          k-major in shared memory; 8-bit types accumulate exactly in int32 (dp4a), floats with
+//                          one rounded multiply and one rounded add per dimension in ascending order — the same
+//                          operation sequence the reference's scalar loop performs (euclidian_point.h:83-90,
+//                          mips_point.h:59-65), so float distances are bit-identical to the CPU's;
+//   pann_gt_select_kernel  one CTA per query: threshold-filtered scan of its distance row into a shared-memory
+//                          candidate buffer, bitonic shrink to the best k when the buffer fills and at chunk end.
+// Results are rows sorted by (distance, id).
 #include "pann_internal.h"
-extern "C" int pann_groundtruth(pann_index*, const void*, uint64_t, uint64_t, uint32_t, int64_t, int32_t*, float*) { PANN_FAIL("pann_groundtruth: not built yet"); }
-extern "C" int pann_groundtruth_resident(pann_index*, uint32_t, int64_t) { PANN_FAIL("not built yet"); }
-extern "C" int pann_groundtruth_fetch(pann_index*, int32_t*, float*) { PANN_FAIL("not built yet"); }
-extern "C" int pann_groundtruth_merge(int, uint32_t, uint64_t, uint32_t, const int32_t*, const float*, int32_t*, float*) { PANN_FAIL("not built yet"); }
+
+#define GT_TQ 64
+#define GT_TB 64
+#define GT_KW 32        // 32-bit words of each row staged per step (128 bytes)
+#define GT_SEL_THREADS 256
+#define GT_SEL_CAP 2048  // candidate buffer (keys) per query CTA
+
+template <int DT, int METRIC>
+__global__ void __launch_bounds__(256) pann_gt_dist_kernel(const uint8_t* __restrict__ base, uint64_t b0, uint32_t nbc,
+                                                           const uint8_t* __restrict__ queries, uint32_t nq, uint32_t stride,
+                                                           uint32_t nwords, float* __restrict__ D, uint32_t ldD) {
+  __shared__ __align__(16) uint32_t Qs[GT_KW][GT_TQ];
+  __shared__ __align__(16) uint32_t Bs[GT_KW][GT_TB];
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+  const uint32_t q0 = blockIdx.y * GT_TQ, r0 = blockIdx.x * GT_TB;
+  float facc[4][4];
+  int iacc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+#pragma unroll
+    for (int j = 0; j < 4; j++) { facc[i][j] = 0.f; iacc[i][j] = 0; }
+  // loader mapping: thread t stages 16 bytes: row (t & 63), 16-byte chunk (t >> 6) and (t >> 6) + 4 of the step
+  const int lrow = threadIdx.x & 63, lch = threadIdx.x >> 6;
+  const uint32_t qrow = min(q0 + lrow, nq - 1), brow = min(r0 + lrow, nbc - 1);
+  const uint8_t* qp = queries + (uint64_t)qrow * stride;
+  const uint8_t* bp = base + (b0 + brow) * (uint64_t)stride;
+  for (uint32_t w0 = 0; w0 < nwords; w0 += GT_KW) {
+#pragma unroll
+    for (int h = 0; h < 2; h++) {
+      int c = lch + 4 * h;  // chunk within the step: words 4c .. 4c+3
+      uint32_t w = w0 + 4 * c;
+      uint4 qv = make_uint4(0, 0, 0, 0), bv = make_uint4(0, 0, 0, 0);
+      if (w < nwords) { qv = __ldg(reinterpret_cast<const uint4*>(qp + 4ull * w)); bv = __ldg(reinterpret_cast<const uint4*>(bp + 4ull * w)); }
+      Qs[4 * c + 0][lrow] = qv.x; Qs[4 * c + 1][lrow] = qv.y; Qs[4 * c + 2][lrow] = qv.z; Qs[4 * c + 3][lrow] = qv.w;
+      Bs[4 * c + 0][lrow] = bv.x; Bs[4 * c + 1][lrow] = bv.y; Bs[4 * c + 2][lrow] = bv.z; Bs[4 * c + 3][lrow] = bv.w;
+    }
+    __syncthreads();
+    const int kw_end = min((uint32_t)GT_KW, nwords - w0);
+#pragma unroll 4
+    for (int kw = 0; kw < kw_end; kw++) {
+      const uint4 q4 = *reinterpret_cast<const uint4*>(&Qs[kw][ty * 4]);
+      const uint4 b4 = *reinterpret_cast<const uint4*>(&Bs[kw][tx * 4]);
+      const uint32_t qa[4] = {q4.x, q4.y, q4.z, q4.w}, ba[4] = {b4.x, b4.y, b4.z, b4.w};
+#pragma unroll
+      for (int i = 0; i < 4; i++)
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+          if constexpr (DT == PANN_DT_F32) {
+            const float qf = __uint_as_float(qa[i]), bf = __uint_as_float(ba[j]);
+            if constexpr (METRIC == PANN_M_L2) {
+              const float t = __fsub_rn(qf, bf);
+              facc[i][j] = __fadd_rn(facc[i][j], __fmul_rn(t, t));
+            } else {
+              facc[i][j] = __fadd_rn(facc[i][j], __fmul_rn(qf, bf));
+            }
+          } else if constexpr (DT == PANN_DT_U8) {
+            if constexpr (METRIC == PANN_M_L2) { unsigned x = __vabsdiffu4(qa[i], ba[j]); iacc[i][j] = (int)__dp4a(x, x, (unsigned)iacc[i][j]); }
+            else iacc[i][j] = (int)__dp4a(qa[i], ba[j], (unsigned)iacc[i][j]);
+          } else {
+            if constexpr (METRIC == PANN_M_L2) { unsigned x = __vabsdiffs4(qa[i], ba[j]); iacc[i][j] = (int)__dp4a(x, x, (unsigned)iacc[i][j]); }
+            else iacc[i][j] = __dp4a((int)qa[i], (int)ba[j], iacc[i][j]);
+          }
+        }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    const uint32_t q = q0 + ty * 4 + i;
+    if (q >= nq) continue;
+    float o[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      float v = (DT == PANN_DT_F32) ? facc[i][j] : (float)iacc[i][j];
+      o[j] = (METRIC == PANN_M_MIPS) ? -v : v;
+    }
+    float* dst = D + (uint64_t)q * ldD + r0 + tx * 4;
+    if (r0 + tx * 4 + 3 < nbc && (ldD & 3) == 0) *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+    else
+      for (int j = 0; j < 4; j++) if (r0 + tx * 4 + j < nbc) dst[j] = o[j];
+  }
+}
+
+// in-place ascending bitonic sort of `m` (power of two) keys in shared memory by the whole CTA
+__device__ __forceinline__ void gt_bitonic(u64* a, int m) {
+  for (int k = 2; k <= m; k <<= 1)
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = threadIdx.x; t < m; t += blockDim.x) {
+        int p = t ^ j;
+        if (p > t) {
+          u64 x = a[t], y = a[p];
+          bool up = (t & k) == 0;
+          if ((x > y) == up) { a[t] = y; a[p] = x; }
+        }
+      }
+      __syncthreads();
+    }
+}
+
+// state per query: K keys (sorted, unused slots = ~0) in `state`; D row of this chunk: nbc distances of base rows b0..
+__global__ void __launch_bounds__(GT_SEL_THREADS) pann_gt_select_kernel(const float* __restrict__ D, uint32_t ldD, uint32_t nbc,
+                                                                        uint64_t b0, uint32_t k, u64* __restrict__ state) {
+  __shared__ u64 buf[GT_SEL_CAP];
+  __shared__ int s_count;
+  __shared__ u64 s_tau;
+  const uint32_t q = blockIdx.x;
+  u64* st = state + (uint64_t)q * k;
+  for (int i = threadIdx.x; i < GT_SEL_CAP; i += blockDim.x) buf[i] = i < (int)k ? st[i] : ~0ull;
+  if (threadIdx.x == 0) { s_count = (int)k; s_tau = st[k - 1]; }
+  __syncthreads();
+  const float* row = D + (uint64_t)q * ldD;
+  const int SEG = GT_SEL_THREADS * 4;  // at most SEG appends between capacity checks
+  for (uint32_t s0 = 0; s0 < nbc; s0 += SEG) {
+    const u64 tau = s_tau;
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+      uint32_t j = s0 + u * GT_SEL_THREADS + threadIdx.x;
+      if (j < nbc) {
+        u64 key = pann_key(row[j], (uint32_t)(b0 + j));
+        if (key < tau) buf[atomicAdd(&s_count, 1)] = key;
+      }
+    }
+    __syncthreads();
+    const int cnt = s_count;  // read once between two barriers: the next segment's appends must not be seen by some threads only
+    __syncthreads();
+    if (cnt > GT_SEL_CAP - SEG) {  // shrink: keep the best k, tighten the threshold
+      for (int i = cnt + threadIdx.x; i < GT_SEL_CAP; i += blockDim.x) buf[i] = ~0ull;
+      __syncthreads();
+      gt_bitonic(buf, GT_SEL_CAP);
+      if (threadIdx.x == 0) { s_count = (int)k; s_tau = buf[k - 1]; }
+      __syncthreads();
+    }
+  }
+  {
+    int cnt = s_count;
+    for (int i = cnt + threadIdx.x; i < GT_SEL_CAP; i += blockDim.x) buf[i] = ~0ull;
+    __syncthreads();
+    int m = 2; while (m < cnt) m <<= 1;
+    gt_bitonic(buf, m);
+    for (int i = threadIdx.x; i < (int)k; i += blockDim.x) st[i] = buf[i];
+  }
+}
+
+__global__ void pann_gt_init_kernel(u64* state, uint64_t total) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < total) state[i] = ~0ull;
+}
+__global__ void pann_gt_finish_kernel(const u64* state, uint64_t total, int64_t id_offset, int32_t* ids, float* dists) {
+  uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  u64 key = state[i];
+  ids[i] = (int32_t)((int64_t)pann_key_id(key) + id_offset);
+  dists[i] = pann_key_dist(key);
+}
+
+// K5: one CTA per query, the union of S sorted shard rows -> best k under (dist, id).  ids are global here.
+__global__ void __launch_bounds__(GT_SEL_THREADS) pann_gt_merge_kernel(const int32_t* ids, const float* dists, uint32_t S, uint64_t nq,
+                                                                       uint32_t k, int32_t* out_ids, float* out_dists) {
+  __shared__ u64 buf[GT_SEL_CAP];
+  const uint64_t q = blockIdx.x;
+  const int tot = (int)(S * k);
+  int m = 2; while (m < tot) m <<= 1;
+  for (int i = threadIdx.x; i < m; i += blockDim.x) {
+    u64 key = ~0ull;
+    if (i < tot) { uint64_t src = ((uint64_t)(i / k) * nq + q) * k + (i % k); key = pann_key(dists[src], (uint32_t)ids[src]); }
+    buf[i] = key;
+  }
+  __syncthreads();
+  gt_bitonic(buf, m);
+  for (int i = threadIdx.x; i < (int)k; i += blockDim.x) { out_ids[q * k + i] = (int32_t)pann_key_id(buf[i]); out_dists[q * k + i] = pann_key_dist(buf[i]); }
+}
+
+// ---------------------------------------------------------------------------------------------
+template <int DT>
+static void launch_dist(int metric, dim3 grid, cudaStream_t s, const uint8_t* base, uint64_t b0, uint32_t nbc, const uint8_t* q,
+                        uint32_t nq, uint32_t stride, uint32_t nwords, float* D, uint32_t ldD) {
+  if (metric == PANN_M_L2) pann_gt_dist_kernel<DT, PANN_M_L2><<<grid, 256, 0, s>>>(base, b0, nbc, q, nq, stride, nwords, D, ldD);
+  else pann_gt_dist_kernel<DT, PANN_M_MIPS><<<grid, 256, 0, s>>>(base, b0, nbc, q, nq, stride, nwords, D, ldD);
+}
+
+// ground truth of the device-resident query rows d_q against the index's base rows; results stay in idx->gt_*
+static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, int64_t id_offset) {
+  if (k == 0 || k > GT_SEL_CAP / 2) PANN_FAIL("pann_groundtruth: k must be in 1.." + std::to_string(GT_SEL_CAP / 2));
+  if (idx->n < k) PANN_FAIL("pann_groundtruth: fewer base points than k");
+  if (nq == 0) { idx->gt_nq = 0; idx->gt_k = k; return 0; }
+  if ((int64_t)idx->n + id_offset > (int64_t)INT32_MAX) PANN_FAIL("pann_groundtruth: ids do not fit the .ibin format's int32");
+  cudaStream_t s = idx->stream;
+  const uint64_t nb = idx->n;
+  // chunk of base rows whose distance rows fit ~1 GiB
+  uint64_t cb = ((1ull << 28) / nq) / GT_TB * GT_TB;
+  cb = std::max<uint64_t>(cb, 4096);
+  cb = std::min<uint64_t>(cb, (nb + GT_TB - 1) / GT_TB * GT_TB);
+  DevBuf D, state;
+  auto fail = [&]() { D.release(); state.release(); return 1; };
+  if (D.reserve(4ull * nq * cb) || state.reserve(8ull * nq * k)) return fail();
+  if (idx->gt_ids.reserve(4ull * nq * k) || idx->gt_dists.reserve(4ull * nq * k)) return fail();
+  const uint64_t tot = nq * k;
+  idx->last_launches = 0;
+  cudaEventRecord(idx->ev0, s);
+  pann_gt_init_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(state.as<u64>(), tot);
+  idx->last_launches++;
+  const uint32_t nwords = idx->geom.stride / 4;
+  for (uint64_t b0 = 0; b0 < nb; b0 += cb) {
+    const uint32_t nbc = (uint32_t)std::min<uint64_t>(cb, nb - b0);
+    dim3 grid((nbc + GT_TB - 1) / GT_TB, (unsigned)((nq + GT_TQ - 1) / GT_TQ));
+    if (idx->dtype == PANN_DT_F32) launch_dist<PANN_DT_F32>(idx->metric, grid, s, idx->points, b0, nbc, d_q, (uint32_t)nq, idx->geom.stride, nwords, D.as<float>(), (uint32_t)cb);
+    else if (idx->dtype == PANN_DT_U8) launch_dist<PANN_DT_U8>(idx->metric, grid, s, idx->points, b0, nbc, d_q, (uint32_t)nq, idx->geom.stride, nwords, D.as<float>(), (uint32_t)cb);
+    else launch_dist<PANN_DT_I8>(idx->metric, grid, s, idx->points, b0, nbc, d_q, (uint32_t)nq, idx->geom.stride, nwords, D.as<float>(), (uint32_t)cb);
+    pann_gt_select_kernel<<<(unsigned)nq, GT_SEL_THREADS, 0, s>>>(D.as<float>(), (uint32_t)cb, nbc, b0, k, state.as<u64>());
+    idx->last_launches += 2;
+  }
+  pann_gt_finish_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(state.as<u64>(), tot, id_offset, idx->gt_ids.as<int32_t>(), idx->gt_dists.as<float>());
+  idx->last_launches++;
+  cudaEventRecord(idx->ev1, s);
+  cudaError_t e = cudaEventSynchronize(idx->ev1);
+  if (e == cudaSuccess) e = cudaGetLastError();
+  D.release(); state.release();
+  if (e != cudaSuccess) PANN_FAIL(std::string("pann_groundtruth: ") + cudaGetErrorString(e));
+  cudaEventElapsedTime(&idx->last_ms, idx->ev0, idx->ev1);
+  idx->gt_nq = nq; idx->gt_k = k;
+  return 0;
+}
+
+extern "C" int pann_groundtruth_resident(pann_index* idx, uint32_t k, int64_t id_offset) {
+  if (!idx) PANN_FAIL("pann_groundtruth_resident: null index");
+  if (idx->nq == 0) PANN_FAIL("pann_groundtruth_resident: no resident query set");
+  PANN_CUDA(cudaSetDevice(idx->device));
+  return gt_run(idx, idx->queries.as<uint8_t>(), idx->nq, k, id_offset);
+}
+extern "C" int pann_groundtruth_fetch(pann_index* idx, int32_t* out_ids, float* out_dists) {
+  if (!idx) PANN_FAIL("pann_groundtruth_fetch: null index");
+  PANN_CUDA(cudaSetDevice(idx->device));
+  const size_t b = 4ull * idx->gt_nq * idx->gt_k;
+  if (out_ids) PANN_CUDA(cudaMemcpyAsync(out_ids, idx->gt_ids.p, b, cudaMemcpyDeviceToHost, idx->stream));
+  if (out_dists) PANN_CUDA(cudaMemcpyAsync(out_dists, idx->gt_dists.p, b, cudaMemcpyDeviceToHost, idx->stream));
+  PANN_CUDA(cudaStreamSynchronize(idx->stream));
+  return 0;
+}
+extern "C" int pann_groundtruth(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes, uint32_t k,
+                                int64_t id_offset, int32_t* out_ids, float* out_dists) {
+  if (!idx || (!host_queries && nq)) PANN_FAIL("pann_groundtruth: null argument");
+  PANN_CUDA(cudaSetDevice(idx->device));
+  if (nq) {
+    if (pann_queries_upload(idx, host_queries, nq, q_stride_bytes)) return 1;
+  }
+  if (gt_run(idx, idx->queries.as<uint8_t>(), nq, k, id_offset)) return 1;
+  if (nq == 0) return 0;
+  return pann_groundtruth_fetch(idx, out_ids, out_dists);
+}
+
+extern "C" int pann_groundtruth_merge(int device, uint32_t nshards, uint64_t nq, uint32_t k, const int32_t* ids, const float* dists,
+                                      int32_t* out_ids, float* out_dists) {
+  if (!ids || !dists || !out_ids || !out_dists) PANN_FAIL("pann_groundtruth_merge: null argument");
+  if (nshards == 0 || k == 0 || (uint64_t)nshards * k > GT_SEL_CAP) PANN_FAIL("pann_groundtruth_merge: nshards * k must be in 1.." + std::to_string(GT_SEL_CAP));
+  if (nq == 0) return 0;
+  PANN_CUDA(cudaSetDevice(device));
+  const size_t in_b = 4ull * nshards * nq * k, out_b = 4ull * nq * k;
+  int32_t *d_ids = nullptr, *d_oi = nullptr; float *d_d = nullptr, *d_od = nullptr;
+  PANN_CUDA(cudaMalloc(&d_ids, in_b)); PANN_CUDA(cudaMalloc(&d_d, in_b)); PANN_CUDA(cudaMalloc(&d_oi, out_b)); PANN_CUDA(cudaMalloc(&d_od, out_b));
+  PANN_CUDA(cudaMemcpy(d_ids, ids, in_b, cudaMemcpyHostToDevice));
+  PANN_CUDA(cudaMemcpy(d_d, dists, in_b, cudaMemcpyHostToDevice));
+  pann_gt_merge_kernel<<<(unsigned)nq, GT_SEL_THREADS>>>(d_ids, d_d, nshards, nq, k, d_oi, d_od);
+  PANN_CUDA(cudaGetLastError());
+  PANN_CUDA(cudaMemcpy(out_ids, d_oi, out_b, cudaMemcpyDeviceToHost));
+  PANN_CUDA(cudaMemcpy(out_dists, d_od, out_b, cudaMemcpyDeviceToHost));
+  cudaFree(d_ids); cudaFree(d_d); cudaFree(d_oi); cudaFree(d_od);
+  return 0;
+}

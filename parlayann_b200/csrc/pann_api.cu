@@ -104,7 +104,7 @@ extern "C" void pann_index_destroy(pann_index* idx) {
   if (idx->points) cudaFree(idx->points);
   if (idx->graph) cudaFree(idx->graph);
   idx->queries.release(); idx->results.release(); idx->scratch_hash.release(); idx->scratch_vis.release();
-  idx->starts.release(); idx->flag.release(); idx->qmap.release(); idx->misc.release();
+  idx->bytes_ctr.release(); idx->starts.release(); idx->flag.release(); idx->qmap.release(); idx->misc.release();
   idx->gt_ids.release(); idx->gt_dists.release();
   if (idx->pinned) cudaFreeHost(idx->pinned);
   if (idx->ev0) cudaEventDestroy(idx->ev0);
@@ -143,6 +143,11 @@ extern "C" int pann_index_info(pann_index* idx, uint64_t* n, uint32_t* dims, uin
   if (max_degree) *max_degree = idx->maxdeg;
   if (dtype) *dtype = idx->dtype;
   if (metric) *metric = idx->metric;
+  return 0;
+}
+extern "C" int pann_index_last_bytes(pann_index* idx, uint64_t* algorithmic_bytes) {
+  if (!idx || !algorithmic_bytes) PANN_FAIL("pann_index_last_bytes: null argument");
+  *algorithmic_bytes = idx->last_bytes;
   return 0;
 }
 extern "C" int pann_index_last_timing(pann_index* idx, float* kernel_ms, int* launches) {
@@ -211,7 +216,8 @@ int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint
     if (h_starts[i] >= idx->n) PANN_FAIL("beam search: start point out of range");
   *status_or = 0;
   if (nq == 0) return 0;
-  if (idx->starts.reserve(sizeof(uint32_t) * nstarts) || idx->flag.reserve(sizeof(int))) return 1;
+  if (idx->starts.reserve(sizeof(uint32_t) * nstarts) || idx->flag.reserve(sizeof(int)) || idx->bytes_ctr.reserve(8)) return 1;
+  PANN_CUDA(cudaMemsetAsync(idx->bytes_ctr.p, 0, 8, idx->stream));
   PANN_CUDA(cudaMemcpyAsync(idx->starts.p, h_starts, sizeof(uint32_t) * nstarts, cudaMemcpyHostToDevice, idx->stream));
   PANN_CUDA(cudaMemsetAsync(idx->flag.p, 0, sizeof(int), idx->stream));
 
@@ -232,6 +238,7 @@ int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint
   A.fr_ids = out.fr_ids; A.fr_dists = out.fr_dists; A.n_frontier = out.n_frontier; A.fcap = out.fcap;
   A.vis_ids = out.vis_ids; A.vis_dists = out.vis_dists; A.n_visited = out.n_visited; A.vout = out.vout;
   A.status = out.status; A.any_status = idx->flag.as<int>();
+  A.bytes_total = idx->bytes_ctr.as<u64>(); A.rowbytes = idx->dims * idx->geom.elt;
 
   // shared-memory variant while the hash filter is <= 16 KB per warp; visited-list capacity is a guess
   // that the retry below makes safe
@@ -243,6 +250,7 @@ int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint
   if (launch_beam(idx, A, gs, vcap)) return 1;
   int flag = 0;
   PANN_CUDA(cudaMemcpyAsync(&flag, idx->flag.p, sizeof(int), cudaMemcpyDeviceToHost, idx->stream));
+  PANN_CUDA(cudaMemcpyAsync(&idx->last_bytes, idx->bytes_ctr.p, 8, cudaMemcpyDeviceToHost, idx->stream));
   PANN_CUDA(cudaStreamSynchronize(idx->stream));
   if ((flag & (1 << 1)) && !gs) {
     // some visited lists outgrew shared memory: redo exactly those queries with the global-scratch variant

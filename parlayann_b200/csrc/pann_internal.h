@@ -38,6 +38,7 @@ struct pann_index {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   float last_ms = 0.f;
+  DevBuf bytes_ctr; uint64_t last_bytes = 0;  // algorithmic bytes of the last search (device counter + host copy)
   int last_launches = 0;
   // resident query set and results
   DevBuf queries;  uint64_t nq = 0;

@@ -79,6 +79,11 @@ class GraphIndex:
         check(_lib.lib().pann_index_last_timing(self._h, C.byref(ms), C.byref(nl)))
         return ms.value, nl.value
 
+    def last_bytes(self):
+        b = C.c_uint64(0)
+        check(_lib.lib().pann_index_last_bytes(self._h, C.byref(b)))
+        return b.value
+
     # ---- search (qsearchAll, beamSearch.h:537-565)
     def _qp(self, k, beam, cut, limit, degree_limit):
         return QueryParams(int(k), int(beam), float(cut), -1 if limit is None else int(limit),
