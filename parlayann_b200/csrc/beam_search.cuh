@@ -11,7 +11,9 @@
 //    unflagged entry, and offset+1 < remain <=> another unflagged entry exists;
 //  * a hop reads the graph row with one coalesced warp load, runs the hash filter for 32 neighbours at
 //    once (__match_any resolves same-slot collisions in list order), compacts the survivors and gathers
-//    their vectors with 128-bit loads, LPR lanes per row, several rows in flight per lane;
+//    their vectors ONE ROW PER LANE: 32 rows per pass, every lane streams its own row with back-to-back
+//    128-bit loads (all of a row's sectors are requested at once) and accumulates in the reference's own
+//    dimension order — no cross-lane reduction, so float distances are bit-identical to the CPU's;
 //  * the merge is rank based: candidates are rank-sorted, de-duplicated, and each element's slot in the
 //    union is (its rank) + (lower_bound in the other list) — no serial set_union;
 //  * frontier, candidates, the visited list and the hash filter live in shared memory per warp; for
@@ -25,7 +27,7 @@
 
 struct BeamArgs {
   // index
-  const uint8_t* points; uint64_t n; uint32_t stride, nch, lpr;
+  const uint8_t* points; uint64_t n; uint32_t stride, nch;
   const uint32_t* graph; uint32_t maxdeg;
   // queries: either rows of `queries` (qstride bytes apart, 16-byte padded) or base rows self_ids[i]
   const uint8_t* queries; uint64_t nq; uint32_t qstride;
@@ -63,62 +65,64 @@ __device__ __forceinline__ int pann_upper_bound(const u64* a, int n, u64 k1) {  
   return lo;
 }
 
-// Distances from the query to `cnt` rows; row r is pann_key_id(keyOf(r)) (a 64-bit tag whose id field names
-// the row, so callers can carry a (dist,id) key through).  Calls emit(tag, dist, valid) warp-uniformly once per
-// pass with one row per lane group (valid only on the group's lane 0), rows in ascending r.
-// RG: anything with points / stride / nch / lpr (BeamArgs, PruneArgs).
-template <int DT, int METRIC, int CPL, class RG, class KeyOf, class Emit>
+// Distances from the query to `cnt` rows, one row per lane, 32 rows per pass; row r is pann_key_id(keyOf(r))
+// (a 64-bit tag whose id field names the row, so callers can carry a (dist,id) key through).  Calls
+// emit(tag, dist, valid) warp-uniformly once per pass; lane l carries row base + l, so ballot-ranked stores in
+// emit keep the rows in order.  QR > 0: the query's QR chunks are in registers (qreg); QR == 0: in shared
+// memory (qsm, read as broadcasts).  RG: anything with points / stride / nch (BeamArgs, PruneArgs, ...).
+template <int DT, int METRIC, int QR, class RG, class KeyOf, class Emit>
 __device__ __forceinline__ void pann_row_distances_g(const RG& A, KeyOf keyOf, int cnt, const uint4* qreg,
                                                      const uint4* qsm, int lane, Emit emit) {
-  const int lpr = A.lpr, G = 32 / lpr, grp = lane / lpr, sub = lane % lpr;
-  constexpr int U = (CPL == 1) ? 4 : ((CPL == 2) ? 2 : 1);  // row groups in flight per lane
-  for (int base = 0; base < cnt; base += G * U) {
-    u64 rkey[U];
-    DistAcc<DT, METRIC> acc[U];
-    if constexpr (CPL > 0) {
-      uint4 v[U][CPL];
+  for (int base = 0; base < cnt; base += 32) {
+    const int r = base + lane;
+    const bool ok = r < cnt;
+    u64 tag = 0;
+    DistAcc<DT, METRIC> acc;
+    if (ok) {
+      tag = keyOf(r);
+      const uint8_t* row = A.points + (u64)pann_key_id(tag) * A.stride;
+      if constexpr (QR > 0) {
+        uint4 v[QR];
 #pragma unroll
-      for (int u = 0; u < U; u++) {
-        int r = base + u * G + grp;
-        rkey[u] = keyOf(r < cnt ? r : cnt - 1);
-        const uint8_t* row = A.points + (u64)pann_key_id(rkey[u]) * A.stride;
+        for (int c = 0; c < QR; c++) v[c] = pann_ldg16(row + c * 16);
 #pragma unroll
-        for (int c = 0; c < CPL; c++) {
-          int ch = sub + c * lpr;
-          v[u][c] = (ch < (int)A.nch) ? pann_ldg16(row + ch * 16) : make_uint4(0, 0, 0, 0);
+        for (int c = 0; c < QR; c++) acc.add(v[c], qreg[c]);
+      } else {
+        const int nch = (int)A.nch;
+        for (int c0 = 0; c0 < nch; c0 += 8) {
+          uint4 v[8];
+#pragma unroll
+          for (int j = 0; j < 8; j++) if (c0 + j < nch) v[j] = pann_ldg16(row + (c0 + j) * 16);
+#pragma unroll
+          for (int j = 0; j < 8; j++) if (c0 + j < nch) acc.add(v[j], qsm[c0 + j]);
         }
       }
-#pragma unroll
-      for (int u = 0; u < U; u++)
-#pragma unroll
-        for (int c = 0; c < CPL; c++) acc[u].add(v[u][c], qreg[c]);
-    } else {
-#pragma unroll
-      for (int u = 0; u < U; u++) {
-        int r = base + u * G + grp;
-        rkey[u] = keyOf(r < cnt ? r : cnt - 1);
-        const uint8_t* row = A.points + (u64)pann_key_id(rkey[u]) * A.stride;
-        for (int ch = sub; ch < (int)A.nch; ch += lpr) acc[u].add(pann_ldg16(row + ch * 16), qsm[ch]);
-      }
     }
-#pragma unroll
-    for (int u = 0; u < U; u++) {
-      acc[u].reduce(lpr);
-      int r = base + u * G + grp;
-      emit(rkey[u], acc[u].result(), (sub == 0) && (r < cnt));
-    }
+    emit(tag, acc.result(), ok);
   }
 }
 // the same over a plain id list (shared memory): emit(id, dist, valid)
-template <int DT, int METRIC, int CPL, class RG, class Emit>
+template <int DT, int METRIC, int QR, class RG, class Emit>
 __device__ __forceinline__ void pann_row_distances(const RG& A, const uint32_t* ids, int cnt, const uint4* qreg,
                                                    const uint4* qsm, int lane, Emit emit) {
-  pann_row_distances_g<DT, METRIC, CPL>(
+  pann_row_distances_g<DT, METRIC, QR>(
       A, [&](int r) { return (u64)ids[r] << 1; }, cnt, qreg, qsm, lane,
       [&](u64 tag, float d, bool ok) { emit(pann_key_id(tag), d, ok); });
 }
+// the query row into registers (QR > 0, every lane holds all of it) or shared memory (QR == 0)
+template <int QR>
+__device__ __forceinline__ void pann_load_query(const uint8_t* qrow, uint32_t nch, uint4* qreg, uint4* qsm, int lane) {
+  if constexpr (QR > 0) {
+#pragma unroll
+    for (int c = 0; c < QR; c++) qreg[c] = pann_ldg16(qrow + c * 16);
+  } else {
+    __syncwarp();
+    for (int ch = lane; ch < (int)nch; ch += 32) qsm[ch] = pann_ldg16(qrow + ch * 16);
+    __syncwarp();
+  }
+}
 
-template <int DT, int METRIC, int CPL, bool GS>
+template <int DT, int METRIC, int QR, bool GS>
 __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kernel(const BeamArgs A) {
   extern __shared__ __align__(16) uint8_t pann_smem[];
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
@@ -154,16 +158,8 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
     }
     const long long self = A.self_ids ? (long long)A.self_ids[q] : -1;
     const uint8_t* qrow = A.self_ids ? A.points + (u64)self * A.stride : A.queries + (u64)q * A.qstride;
-    uint4 qreg[CPL > 0 ? CPL : 1];
-    if constexpr (CPL > 0) {
-#pragma unroll
-      for (int c = 0; c < CPL; c++) {
-        int ch = (lane % A.lpr) + c * A.lpr;
-        qreg[c] = (ch < (int)A.nch) ? pann_ldg16(qrow + ch * 16) : make_uint4(0, 0, 0, 0);
-      }
-    } else {
-      for (int ch = lane; ch < (int)A.nch; ch += 32) qsm[ch] = pann_ldg16(qrow + ch * 16);
-    }
+    uint4 qreg[QR > 0 ? QR : 1];
+    pann_load_query<QR>(qrow, A.nch, qreg, qsm, lane);
     __syncwarp();
 
     u64* front = bufA;
@@ -180,7 +176,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
         int cnt = min((int)A.maxdeg, (int)(A.nstarts - s0));
         for (int i = lane; i < cnt; i += 32) nbr[i] = A.starts[s0 + i];
         __syncwarp();
-        pann_row_distances<DT, METRIC, CPL>(A, nbr, cnt, qreg, qsm, lane, [&](uint32_t id, float d, bool ok) {
+        pann_row_distances<DT, METRIC, QR>(A, nbr, cnt, qreg, qsm, lane, [&](uint32_t id, float d, bool ok) {
           unsigned m = __ballot_sync(PANN_FULL, ok);
           if (ok) cand[C + __popc(m & lt_mask)] = pann_key(d, id);
           C += __popc(m);
@@ -211,19 +207,28 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
       }
       if (pos < 0 || (long long)V >= A.limit) break;  // remain <= offset, or visit limit reached (:107)
       const u64 cur = front[pos];
+      // the graph row is requested now (degree + the first 64 slots; slots past the degree are stale but in-row)
+      // so that its latency overlaps the visited-list insertion below
+      const uint32_t* grow = A.graph + (u64)pann_key_id(cur) * (A.maxdeg + 1);
+      const int deg = (int)__ldg(grow);
+      const uint32_t a0 = (lane < (int)A.maxdeg) ? __ldg(grow + 1 + lane) : 0u;
+      const uint32_t a1 = (32 + lane < (int)A.maxdeg) ? __ldg(grow + 33 + lane) : 0u;
       __syncwarp();
       if (lane == 0) front[pos] = cur | 1ull;
-      // visited.insert(upper_bound(cur)) (:112-113)
+      // visited.insert(upper_bound(cur)) (:112-113): one pass from the top, entries above cur move up by one
       if (V >= (int)A.vcap) { status = 1; break; }
       {
-        int ip = pann_upper_bound(vis, V, cur >> 1);
-        for (int top = V; top > ip; top -= 32) {  // shift [ip, V) up by one, highest block first
-          int i = top - 1 - lane;
-          u64 x = 0;
-          if (i >= ip) x = vis[i];
+        const u64 kc = cur >> 1;
+        int ip = V;
+        for (int top = V; top > 0; top -= 32) {
+          const int i = top - 1 - lane;
+          const u64 x = (i >= 0) ? vis[i] : 0ull;
+          const bool gt = (i >= 0) && ((x >> 1) > kc);
+          const unsigned m = __ballot_sync(PANN_FULL, gt);
+          if (gt) vis[i + 1] = x;  // every lane read its entry before the ballot; targets are this block's own slots + 1
+          ip -= __popc(m);
           __syncwarp();
-          if (i >= ip) vis[i + 1] = x;
-          __syncwarp();
+          if (__popc(m) < min(32, top)) break;
         }
         if (lane == 0) vis[ip] = cur & ~1ull;
         V++;
@@ -231,8 +236,6 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
       const bool full = (F == B);  // :115
       const float cutoff = full ? pann_key_dist(front[F - 1]) : 2147483648.0f;  // (float)INT_MAX (:150-152)
       // neighbours that pass the hash filter, in list order (:130-136)
-      const uint32_t* grow = A.graph + (u64)pann_key_id(cur) * (A.maxdeg + 1);
-      const int deg = (int)__ldg(grow);
       const int ne = min(deg, A.degree_limit);
       nread += ne;
       int S = 0;
@@ -240,7 +243,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
       for (int base = 0; base < ne; base += 32) {
         int i = base + lane;
         bool act = i < ne;
-        uint32_t a = act ? __ldg(grow + 1 + i) : 0u;
+        uint32_t a = base == 0 ? a0 : (base == 32 ? a1 : (act ? __ldg(grow + 1 + i) : 0u));
         uint32_t loc = act ? ((uint32_t)pann_hash64_2(a) & hmask) : (0x80000000u | lane);  // inactive lanes never match
         unsigned peers = __match_any_sync(PANN_FULL, loc);
         unsigned prev = peers & lt_mask;
@@ -260,7 +263,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
       }
       cmps += S;  // :155
       if (S + C > (int)A.ccap) { status = 1; break; }  // cannot happen (ccap >= maxdeg + beam/8); guards memory
-      pann_row_distances<DT, METRIC, CPL>(A, nbr, S, qreg, qsm, lane, [&](uint32_t id, float d, bool ok) {
+      pann_row_distances<DT, METRIC, QR>(A, nbr, S, qreg, qsm, lane, [&](uint32_t id, float d, bool ok) {
         bool take = ok && (d < cutoff);  // :153-158
         unsigned m = __ballot_sync(PANN_FULL, take);
         if (take) cand[C + __popc(m & lt_mask)] = pann_key(d, id);
@@ -277,15 +280,18 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
         }
         if (more) continue;
       }
-      // ---- merge (:173-208).  (a) stable rank sort of the candidates
+      // ---- merge (:173-208).  (a) rank sort of the candidates by strict "less": equal keys (the same vertex reached
+      //      twice, :174's std::unique) land in the same slot, and the slot they leave empty keeps the sentinel
+      for (int i = lane; i < C; i += 32) scand[i] = ~0ull;
+      __syncwarp();
       for (int i = lane; i < C; i += 32) {
-        u64 ci = cand[i];
+        const u64 ci = cand[i];
         int r = 0;
-        for (int j = 0; j < C; j++) { u64 cj = cand[j]; r += (cj < ci) || (cj == ci && j < i); }
+        for (int j = 0; j < C; j++) r += (cand[j] < ci) ? 1 : 0;
         scand[r] = ci;
       }
       __syncwarp();
-      // (b) drop duplicates (std::unique, :174) and entries already in the frontier (set_union keeps one),
+      // (b) drop the empty slots and entries already in the frontier (set_union keeps one),
       //     place the rest: slot = rank among kept candidates + #frontier entries below it
       int Cv = 0;
       for (int base = 0; base < C; base += 32) {
@@ -295,10 +301,10 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
         u64 c = 0;
         if (i < C) {
           c = scand[i];
-          bool dup = i > 0 && scand[i - 1] == c;
-          lbf = pann_lower_bound(front, F, c >> 1);
-          bool infr = lbf < F && (front[lbf] >> 1) == (c >> 1);
-          valid = !dup && !infr;
+          if (c != ~0ull) {
+            lbf = pann_lower_bound(front, F, c >> 1);
+            valid = !(lbf < F && (front[lbf] >> 1) == (c >> 1));
+          }
         }
         unsigned m = __ballot_sync(PANN_FULL, valid);
         int vr = Cv + __popc(m & lt_mask);
@@ -368,6 +374,6 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
 }
 
 // kernel lookup, one translation unit per element type (beam_search_{f32,u8,i8}.cu)
-const void* pann_beam_kernel_dt0(int metric, int cpl, bool gs);
-const void* pann_beam_kernel_dt1(int metric, int cpl, bool gs);
-const void* pann_beam_kernel_dt2(int metric, int cpl, bool gs);
+const void* pann_beam_kernel_dt0(int metric, int qr, bool gs);
+const void* pann_beam_kernel_dt1(int metric, int qr, bool gs);
+const void* pann_beam_kernel_dt2(int metric, int qr, bool gs);

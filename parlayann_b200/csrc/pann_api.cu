@@ -161,17 +161,17 @@ extern "C" int pann_index_last_timing(pann_index* idx, float* kernel_ms, int* la
 // K1 planning and launch
 static inline uint32_t al16(size_t x) { return (uint32_t)((x + 15) / 16 * 16); }
 
-static const void* beam_kernel(int dtype, int metric, int cpl, bool gs) {
+static const void* beam_kernel(int dtype, int metric, int qr, bool gs) {
   switch (dtype) {
-    case PANN_DT_F32: return pann_beam_kernel_dt0(metric, cpl, gs);
-    case PANN_DT_U8: return pann_beam_kernel_dt1(metric, cpl, gs);
-    default: return pann_beam_kernel_dt2(metric, cpl, gs);
+    case PANN_DT_F32: return pann_beam_kernel_dt0(metric, qr, gs);
+    case PANN_DT_U8: return pann_beam_kernel_dt1(metric, qr, gs);
+    default: return pann_beam_kernel_dt2(metric, qr, gs);
   }
 }
 
 static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap) {
   const PannRowGeom& g = idx->geom;
-  const int cplT = g.cpl <= 3 ? (int)g.cpl : 0;
+  const int qrT = pann_qr_of(g);
   const uint32_t B = (uint32_t)A.beam;
   A.ccap = std::max<uint32_t>(A.maxdeg + B / 8 + 1, A.nstarts);
   A.vcap = vcap;
@@ -180,12 +180,12 @@ static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap) {
   A.off_scand = A.off_cand + al16((size_t)A.ccap * 8);
   A.off_nbr = A.off_scand + al16((size_t)A.ccap * 8);
   A.off_q = A.off_nbr + al16((size_t)std::max<uint32_t>(A.maxdeg, 1) * 4);
-  A.off_vis = A.off_q + (cplT == 0 ? g.stride : 0);
+  A.off_vis = A.off_q + (qrT == 0 ? g.stride : 0);
   A.off_hash = A.off_vis + (gs ? 0 : al16((size_t)vcap * 8));
   A.warp_bytes = A.off_hash + (gs ? 0 : (4u << A.bits));
   const size_t cta_bytes = (size_t)A.warp_bytes * PANN_WARPS_PER_CTA;
   if (cta_bytes > idx->smem_optin) PANN_FAIL("beam search: per-CTA shared memory exceeds the device limit (beam too wide for this max degree)");
-  const void* fn = beam_kernel(idx->dtype, idx->metric, cplT, gs);
+  const void* fn = beam_kernel(idx->dtype, idx->metric, qrT, gs);
   PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
   int per_sm = 0;
   PANN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, PANN_WARPS_PER_CTA * 32, cta_bytes));
@@ -223,7 +223,7 @@ int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint
 
   BeamArgs A;
   memset(&A, 0, sizeof(A));
-  A.points = idx->points; A.n = idx->n; A.stride = idx->geom.stride; A.nch = idx->geom.nch; A.lpr = idx->geom.lpr;
+  A.points = idx->points; A.n = idx->n; A.stride = idx->geom.stride; A.nch = idx->geom.nch;
   A.graph = idx->graph; A.maxdeg = idx->maxdeg;
   A.queries = d_queries; A.nq = nq; A.qstride = qstride; A.self_ids = d_self_ids;
   A.starts = idx->starts.as<uint32_t>(); A.nstarts = nstarts;

@@ -66,8 +66,11 @@ __host__ __device__ __forceinline__ u64 pann_hash64_2(u64 x) {
 
 #ifdef __CUDACC__
 // ---------------------------------------------------------------------------------------------
-// Fused distance accumulators over 16-byte chunks (euclidian_point.h:45-90, mips_point.h:43-65).
-// 8-bit types accumulate exactly in int32 (dp4a), floats in fp32.
+// Fused distance accumulators over 16-byte chunks of ONE row, fed in ascending chunk order by one thread
+// (euclidian_point.h:45-90, mips_point.h:43-65).  8-bit types accumulate exactly in int32 (dp4a).  Floats do
+// exactly what the reference's scalar loop does — per dimension one rounded subtract, one rounded multiply and
+// one rounded add, in ascending order, never contracted to an FMA — so float distances are bit-identical to the
+// CPU's (the reference's compiler keeps that loop sequential: SURVEY.md §7 "Float parity").
 template <int DT, int METRIC> struct DistAcc;
 
 template <> struct DistAcc<PANN_DT_U8, PANN_M_L2> {
@@ -79,7 +82,6 @@ template <> struct DistAcc<PANN_DT_U8, PANN_M_L2> {
     x = __vabsdiffu4(p.z, q.z); acc = __dp4a(x, x, acc);
     x = __vabsdiffu4(p.w, q.w); acc = __dp4a(x, x, acc);
   }
-  __device__ __forceinline__ void reduce(int lpr) { for (int o = lpr >> 1; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o); }
   __device__ __forceinline__ float result() const { return (float)(int)acc; }
 };
 template <> struct DistAcc<PANN_DT_I8, PANN_M_L2> {
@@ -91,7 +93,6 @@ template <> struct DistAcc<PANN_DT_I8, PANN_M_L2> {
     x = __vabsdiffs4(p.z, q.z); acc = __dp4a(x, x, acc);
     x = __vabsdiffs4(p.w, q.w); acc = __dp4a(x, x, acc);
   }
-  __device__ __forceinline__ void reduce(int lpr) { for (int o = lpr >> 1; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o); }
   __device__ __forceinline__ float result() const { return (float)(int)acc; }
 };
 template <> struct DistAcc<PANN_DT_U8, PANN_M_MIPS> {
@@ -99,7 +100,6 @@ template <> struct DistAcc<PANN_DT_U8, PANN_M_MIPS> {
   __device__ __forceinline__ void add(const uint4& p, const uint4& q) {
     acc = __dp4a(p.x, q.x, acc); acc = __dp4a(p.y, q.y, acc); acc = __dp4a(p.z, q.z, acc); acc = __dp4a(p.w, q.w, acc);
   }
-  __device__ __forceinline__ void reduce(int lpr) { for (int o = lpr >> 1; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o); }
   __device__ __forceinline__ float result() const { return -((float)(int)acc); }
 };
 template <> struct DistAcc<PANN_DT_I8, PANN_M_MIPS> {
@@ -108,30 +108,21 @@ template <> struct DistAcc<PANN_DT_I8, PANN_M_MIPS> {
     acc = __dp4a((int)p.x, (int)q.x, acc); acc = __dp4a((int)p.y, (int)q.y, acc);
     acc = __dp4a((int)p.z, (int)q.z, acc); acc = __dp4a((int)p.w, (int)q.w, acc);
   }
-  __device__ __forceinline__ void reduce(int lpr) { for (int o = lpr >> 1; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o); }
   __device__ __forceinline__ float result() const { return -((float)acc); }
 };
 template <> struct DistAcc<PANN_DT_F32, PANN_M_L2> {
   float acc = 0.f;
-  __device__ __forceinline__ void add(const uint4& p, const uint4& q) {
-    float t;
-    t = __uint_as_float(q.x) - __uint_as_float(p.x); acc = fmaf(t, t, acc);
-    t = __uint_as_float(q.y) - __uint_as_float(p.y); acc = fmaf(t, t, acc);
-    t = __uint_as_float(q.z) - __uint_as_float(p.z); acc = fmaf(t, t, acc);
-    t = __uint_as_float(q.w) - __uint_as_float(p.w); acc = fmaf(t, t, acc);
+  __device__ __forceinline__ void add1(unsigned p, unsigned q) {
+    float t = __fsub_rn(__uint_as_float(q), __uint_as_float(p));
+    acc = __fadd_rn(acc, __fmul_rn(t, t));
   }
-  __device__ __forceinline__ void reduce(int lpr) { for (int o = lpr >> 1; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o); }
+  __device__ __forceinline__ void add(const uint4& p, const uint4& q) { add1(p.x, q.x); add1(p.y, q.y); add1(p.z, q.z); add1(p.w, q.w); }
   __device__ __forceinline__ float result() const { return acc; }
 };
 template <> struct DistAcc<PANN_DT_F32, PANN_M_MIPS> {
   float acc = 0.f;
-  __device__ __forceinline__ void add(const uint4& p, const uint4& q) {
-    acc = fmaf(__uint_as_float(q.x), __uint_as_float(p.x), acc);
-    acc = fmaf(__uint_as_float(q.y), __uint_as_float(p.y), acc);
-    acc = fmaf(__uint_as_float(q.z), __uint_as_float(p.z), acc);
-    acc = fmaf(__uint_as_float(q.w), __uint_as_float(p.w), acc);
-  }
-  __device__ __forceinline__ void reduce(int lpr) { for (int o = lpr >> 1; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o); }
+  __device__ __forceinline__ void add1(unsigned p, unsigned q) { acc = __fadd_rn(acc, __fmul_rn(__uint_as_float(q), __uint_as_float(p))); }
+  __device__ __forceinline__ void add(const uint4& p, const uint4& q) { add1(p.x, q.x); add1(p.y, q.y); add1(p.z, q.z); add1(p.w, q.w); }
   __device__ __forceinline__ float result() const { return -acc; }
 };
 
@@ -145,8 +136,6 @@ struct PannRowGeom {
   uint32_t elt;     // bytes per element
   uint32_t stride;  // bytes per device row, multiple of 16
   uint32_t nch;     // 16-byte chunks per row
-  uint32_t lpr;     // lanes cooperating on one row (power of two <= 32)
-  uint32_t cpl;     // chunks per lane = ceil(nch / lpr)
 };
 inline PannRowGeom pann_row_geom(uint32_t dims, int dtype) {
   PannRowGeom g;
@@ -154,15 +143,9 @@ inline PannRowGeom pann_row_geom(uint32_t dims, int dtype) {
   g.elt = dtype == PANN_DT_F32 ? 4 : 1;
   g.stride = (dims * g.elt + 15) / 16 * 16;
   g.nch = g.stride / 16;
-  // lanes per row: the power of two (<= 32) that wastes the fewest lane-slots, preferring more lanes
-  uint32_t best = 32, best_waste = ~0u;
-  for (uint32_t l = 32; l >= 1; l >>= 1) {
-    uint32_t c = (g.nch + l - 1) / l;
-    if (c > 4 && l < 32) break;  // keep per-lane register footprint bounded
-    uint32_t waste = c * l - g.nch;
-    if (waste < best_waste) { best_waste = waste; best = l; }
-  }
-  g.lpr = best;
-  g.cpl = (g.nch + g.lpr - 1) / g.lpr;
   return g;
 }
+// kernels are specialised for rows of exactly PANN_QR chunks (128 bytes: 128-d uint8/int8), whose query lives in
+// registers; every other shape takes the generic variant (QR = 0) with the query in shared memory
+#define PANN_QR 8
+inline int pann_qr_of(const PannRowGeom& g) { return g.nch == PANN_QR ? PANN_QR : 0; }

@@ -39,18 +39,18 @@ __global__ void pann_find_heads_kernel(const u64* sorted, uint32_t ns, uint64_t 
   if (j == 0 || (uint32_t)(sorted[j - 1] >> 32) != t) gstart[atomicAdd(ngroups, 1u)] = j;
 }
 
-static const void* prune_kernel(int dtype, int metric, int cpl, bool gs) {
+static const void* prune_kernel(int dtype, int metric, int qr, bool gs) {
   switch (dtype) {
-    case PANN_DT_F32: return pann_prune_kernel_dt0(metric, cpl, gs);
-    case PANN_DT_U8: return pann_prune_kernel_dt1(metric, cpl, gs);
-    default: return pann_prune_kernel_dt2(metric, cpl, gs);
+    case PANN_DT_F32: return pann_prune_kernel_dt0(metric, qr, gs);
+    case PANN_DT_U8: return pann_prune_kernel_dt1(metric, qr, gs);
+    default: return pann_prune_kernel_dt2(metric, qr, gs);
   }
 }
-static const void* edge_kernel(int dtype, int metric, int cpl) {
+static const void* edge_kernel(int dtype, int metric, int qr) {
   switch (dtype) {
-    case PANN_DT_F32: return pann_edge_kernel_dt0(metric, cpl);
-    case PANN_DT_U8: return pann_edge_kernel_dt1(metric, cpl);
-    default: return pann_edge_kernel_dt2(metric, cpl);
+    case PANN_DT_F32: return pann_edge_kernel_dt0(metric, qr);
+    case PANN_DT_U8: return pann_edge_kernel_dt1(metric, qr);
+    default: return pann_edge_kernel_dt2(metric, qr);
   }
 }
 static inline uint32_t al16(size_t x) { return (uint32_t)((x + 15) / 16 * 16); }
@@ -58,7 +58,7 @@ static inline uint32_t al16(size_t x) { return (uint32_t)((x + 15) / 16 * 16); }
 // launches K3 over A's tasks (shared-memory variant), then the global-scratch variant over whatever it deferred
 static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevBuf& big, DevBuf& gscratch) {
   const PannRowGeom& g = idx->geom;
-  const int cplT = g.cpl <= 3 ? (int)g.cpl : 0;
+  const int qrT = pann_qr_of(g);
   if (ntasks_bound == 0) return 0;
   if (big.reserve(8 + 4ull * ntasks_bound)) return 1;
   A.big_count = big.as<uint32_t>();
@@ -67,10 +67,10 @@ static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, De
   A.cap = 512;
   A.off_b = al16((size_t)A.cap * 8);
   A.off_q = 2 * A.off_b;
-  A.warp_bytes = A.off_q + (cplT == 0 ? g.stride : 0);
+  A.warp_bytes = A.off_q + (qrT == 0 ? g.stride : 0);
   A.task_map = nullptr; A.ntask_map = 0; A.g_scratch = nullptr;
   {
-    const void* fn = prune_kernel(idx->dtype, idx->metric, cplT, false);
+    const void* fn = prune_kernel(idx->dtype, idx->metric, qrT, false);
     size_t cta_bytes = (size_t)A.warp_bytes * PANN_PRUNE_WARPS;
     PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
     int per_sm = 0;
@@ -90,8 +90,8 @@ static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, De
   A.cap = bc[1];
   A.task_map = A.big_list; A.ntask_map = bc[0];
   A.off_b = 0; A.off_q = 0;
-  A.warp_bytes = (cplT == 0 ? g.stride : 0);
-  const void* fn = prune_kernel(idx->dtype, idx->metric, cplT, true);
+  A.warp_bytes = (qrT == 0 ? g.stride : 0);
+  const void* fn = prune_kernel(idx->dtype, idx->metric, qrT, true);
   size_t cta_bytes = (size_t)A.warp_bytes * PANN_PRUNE_WARPS;
   PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
   int grid = (int)std::min<uint32_t>((bc[0] + PANN_PRUNE_WARPS - 1) / PANN_PRUNE_WARPS, 4u * idx->sms);
@@ -189,7 +189,7 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
       if (rc) break;
       PruneArgs A;
       memset(&A, 0, sizeof(A));
-      A.points = idx->points; A.stride = idx->geom.stride; A.nch = idx->geom.nch; A.lpr = idx->geom.lpr;
+      A.points = idx->points; A.stride = idx->geom.stride; A.nch = idx->geom.nch;
       A.graph = idx->graph; A.maxdeg = md; A.R = R; A.n = n; A.alpha = a;
       A.perm_lo = perm_lo; A.st_visited = st_vis; A.st_cmps = st_cmp;
       A.mode = 0; A.ntasks = bs;
@@ -231,12 +231,12 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
     if (d_ed.reserve(4ull * n * md)) return 1;
     EdgeDistArgs E;
     memset(&E, 0, sizeof(E));
-    E.points = idx->points; E.stride = idx->geom.stride; E.nch = idx->geom.nch; E.lpr = idx->geom.lpr;
+    E.points = idx->points; E.stride = idx->geom.stride; E.nch = idx->geom.nch;
     E.graph = idx->graph; E.maxdeg = md; E.n = n; E.out = d_ed.as<float>();
-    const int cplT = idx->geom.cpl <= 3 ? (int)idx->geom.cpl : 0;
+    const int qrT = pann_qr_of(idx->geom);
     E.off_q = al16((size_t)md * 4);
-    E.warp_bytes = E.off_q + (cplT == 0 ? idx->geom.stride : 0);
-    const void* fn = edge_kernel(idx->dtype, idx->metric, cplT);
+    E.warp_bytes = E.off_q + (qrT == 0 ? idx->geom.stride : 0);
+    const void* fn = edge_kernel(idx->dtype, idx->metric, qrT);
     size_t cta_bytes = (size_t)E.warp_bytes * PANN_PRUNE_WARPS;
     PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
     int grid = (int)std::min<uint64_t>((n + PANN_PRUNE_WARPS - 1) / PANN_PRUNE_WARPS, (uint64_t)idx->sms * 16);

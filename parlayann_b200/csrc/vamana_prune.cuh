@@ -9,8 +9,8 @@
 // GPU layout (not a translation of the CPU loop): the candidate list is one array of 64-bit (dist,id) keys
 // in shared memory; the list is kept COMPACT — after each pick the survivors are rewritten in place by
 // ballot-ranked stores, so every pass of the occlusion scan is a dense batch of 128-bit row gathers
-// (same lane geometry and accumulation order as K1, so float distances are bit-identical between the two
-// kernels and duplicate ids always sort next to each other).
+// (same per-lane row accumulation as K1, so float distances are bit-identical between the kernels — and to
+// the CPU's — and duplicate ids always sort next to each other).
 #pragma once
 #include "beam_search.cuh"
 
@@ -18,7 +18,7 @@
 
 struct PruneArgs {
   // row geometry (same member names as BeamArgs: pann_row_distances_g reads them)
-  const uint8_t* points; uint32_t stride, nch, lpr;
+  const uint8_t* points; uint32_t stride, nch;
   uint32_t* graph; uint32_t maxdeg, R;
   uint64_t n;
   double alpha;
@@ -39,7 +39,7 @@ struct PruneArgs {
   uint32_t off_b, off_q, warp_bytes;
 };
 
-template <int DT, int METRIC, int CPL, bool GS>
+template <int DT, int METRIC, int QR, bool GS>
 __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const PruneArgs A) {
   extern __shared__ __align__(16) uint8_t pann_smem[];
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
@@ -105,20 +105,8 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
     }
     // ---- query row = the pruned vertex
     const uint8_t* prow = A.points + (u64)p * A.stride;
-    uint4 qreg[CPL > 0 ? CPL : 1];
-    auto load_q = [&](const uint8_t* row) {
-      if constexpr (CPL > 0) {
-#pragma unroll
-        for (int c = 0; c < CPL; c++) {
-          int ch = (lane % A.lpr) + c * A.lpr;
-          qreg[c] = (ch < (int)A.nch) ? pann_ldg16(row + ch * 16) : make_uint4(0, 0, 0, 0);
-        }
-      } else {
-        __syncwarp();
-        for (int ch = lane; ch < (int)A.nch; ch += 32) qsm[ch] = pann_ldg16(row + ch * 16);
-        __syncwarp();
-      }
-    };
+    uint4 qreg[QR > 0 ? QR : 1];
+    auto load_q = [&](const uint8_t* row) { pann_load_query<QR>(row, A.nch, qreg, qsm, lane); };
     load_q(prow);
     unsigned comps = 0;
     int C = 0;  // keys in bufA
@@ -137,7 +125,7 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
       m += deg;
       __syncwarp();
       comps += m;
-      pann_row_distances_g<DT, METRIC, CPL>(
+      pann_row_distances_g<DT, METRIC, QR>(
           A, [&](int r) { return (u64)cid[r] << 1; }, (int)m, qreg, qsm, lane, [&](u64 tag, float d, bool ok) {
             unsigned bm = __ballot_sync(PANN_FULL, ok);
             if (ok) bufA[C + __popc(bm & lt_mask)] = pann_key(d, pann_key_id(tag));
@@ -187,7 +175,7 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
       comps += cnt;  // one distance per live later candidate (:108)
       load_q(A.points + (u64)ps_id * A.stride);
       int w = start;
-      pann_row_distances_g<DT, METRIC, CPL>(
+      pann_row_distances_g<DT, METRIC, QR>(
           A, [&](int r) { return S[start + r]; }, cnt, qreg, qsm, lane, [&](u64 key, float d, bool ok) {
             bool keep = ok && !(A.alpha * (double)d <= (double)pann_key_dist(key));  // :111
             unsigned km = __ballot_sync(PANN_FULL, keep);
@@ -214,12 +202,12 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
 // K6: distance of every edge to its owner, one warp per graph row (build_index's final per-row sort,
 // algorithms/vamana/index.h:180-185, compares exactly these values).  out: n x maxdeg floats.
 struct EdgeDistArgs {
-  const uint8_t* points; uint32_t stride, nch, lpr;
+  const uint8_t* points; uint32_t stride, nch;
   const uint32_t* graph; uint32_t maxdeg; uint64_t n;
   float* out;
   uint32_t off_q, warp_bytes;
 };
-template <int DT, int METRIC, int CPL>
+template <int DT, int METRIC, int QR>
 __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_edge_dist_kernel(const EdgeDistArgs A) {
   extern __shared__ __align__(16) uint8_t pann_smem[];
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
@@ -232,21 +220,13 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_edge_dist_kernel(c
     const uint32_t* grow = A.graph + (u64)i * (A.maxdeg + 1);
     const int deg = (int)grow[0];
     const uint8_t* row = A.points + (u64)i * A.stride;
-    uint4 qreg[CPL > 0 ? CPL : 1];
-    if constexpr (CPL > 0) {
-#pragma unroll
-      for (int c = 0; c < CPL; c++) {
-        int ch = (lane % A.lpr) + c * A.lpr;
-        qreg[c] = (ch < (int)A.nch) ? pann_ldg16(row + ch * 16) : make_uint4(0, 0, 0, 0);
-      }
-    } else {
-      for (int ch = lane; ch < (int)A.nch; ch += 32) qsm[ch] = pann_ldg16(row + ch * 16);
-    }
+    uint4 qreg[QR > 0 ? QR : 1];
+    pann_load_query<QR>(row, A.nch, qreg, qsm, lane);
     for (int j = lane; j < deg; j += 32) ids[j] = grow[1 + j];
     __syncwarp();
     float* o = A.out + (u64)i * A.maxdeg;
     int w = 0;
-    pann_row_distances_g<DT, METRIC, CPL>(
+    pann_row_distances_g<DT, METRIC, QR>(
         A, [&](int r) { return (u64)ids[r] << 1; }, deg, qreg, qsm, lane, [&](u64, float d, bool ok) {
           unsigned bm = __ballot_sync(PANN_FULL, ok);
           if (ok) o[w + __popc(bm & ((1u << lane) - 1u))] = d;
@@ -256,9 +236,9 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_edge_dist_kernel(c
   }
 }
 
-const void* pann_prune_kernel_dt0(int metric, int cpl, bool gs);
-const void* pann_prune_kernel_dt1(int metric, int cpl, bool gs);
-const void* pann_prune_kernel_dt2(int metric, int cpl, bool gs);
-const void* pann_edge_kernel_dt0(int metric, int cpl);
-const void* pann_edge_kernel_dt1(int metric, int cpl);
-const void* pann_edge_kernel_dt2(int metric, int cpl);
+const void* pann_prune_kernel_dt0(int metric, int qr, bool gs);
+const void* pann_prune_kernel_dt1(int metric, int qr, bool gs);
+const void* pann_prune_kernel_dt2(int metric, int qr, bool gs);
+const void* pann_edge_kernel_dt0(int metric, int qr);
+const void* pann_edge_kernel_dt1(int metric, int qr);
+const void* pann_edge_kernel_dt2(int metric, int qr);

@@ -18,7 +18,7 @@ def _build(base, data_type, metric, R, L, alpha=1.2, passes=1, sort_neighbors=Fa
     return idx, idx.graph(), st
 
 
-@pytest.mark.parametrize("name", INT_CASES)
+@pytest.mark.parametrize("name", list(CASES))
 def test_build_matches_reference_golden(name):
     g = golden(name)
     idx, got, (sv, sd) = _build(g.base, g.data_type, g.metric, g.R, g.L, passes=g.passes)
@@ -29,23 +29,13 @@ def test_build_matches_reference_golden(name):
     assert np.array_equal(valid_graph(got_s), valid_graph(g.z["graph_sorted"])), "sorted graph differs from the reference's"
 
 
-@pytest.mark.parametrize("name", [c for c in CASES if c not in INT_CASES])
-def test_float_build_close_to_reference(name):
-    # float distances differ in the last bits (lane-parallel sum vs the CPU's sequential sum), so a prune decision
-    # can flip; the graphs must still be nearly identical and search as well
-    g = golden(name)
-    idx, got, _ = _build(g.base, g.data_type, g.metric, g.R, g.L, passes=g.passes)
-    ref = valid_graph(g.z["graph_unsorted"])
-    same_rows = (valid_graph(got) == ref).all(axis=1).mean()
-    assert same_rows >= 0.95, f"only {same_rows:.3f} of float rows identical"
-    assert abs(int(got[:, 0].sum()) - int(ref[:, 0].sum())) <= 0.01 * ref[:, 0].sum()
-
-
 @pytest.mark.parametrize("data_type,metric,n,d,R,L,passes", [
     ("uint8", "Euclidian", 20000, 128, 32, 64, 1),
     ("uint8", "Euclidian", 6000, 128, 64, 128, 1),
     ("int8", "Euclidian", 6000, 100, 24, 48, 2),
     ("uint8", "mips", 5000, 64, 16, 40, 1),
+    ("float", "Euclidian", 5000, 96, 24, 48, 1),
+    ("float", "mips", 4000, 200, 16, 32, 1),
 ])
 def test_build_matches_oracle(dataset, data_type, metric, n, d, R, L, passes):
     ds = dataset(data_type, metric, n=n, d=d, nq=10, R=R, L=L)
