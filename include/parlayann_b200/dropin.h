@@ -1,0 +1,215 @@
+// parlayann_b200/dropin.h — the reference-side C++ binding of libpann_cuda.so (include/pann.h).
+//
+// Header-only; compile it INSIDE the reference tree (it uses the reference's own types, nothing is re-declared):
+//     #include "utils/beamSearch.h"   #include "vamana/index.h"   #include "parlayann_b200/dropin.h"
+//     g++ ... -I<reference>/algorithms -I<reference>/parlaylib/include -I<this repo>/include \
+//         -L<this repo>/parlayann_b200 -lpann_cuda -Wl,-rpath,<this repo>/parlayann_b200
+// It gives the batch-level entry points of the hot path the same names, template parameters, argument order, return
+// types and error behaviour (message on std::cout, then abort()) as the reference, in namespace parlayANN::b200:
+//     qsearchAll   (algorithms/utils/beamSearch.h:537-565)      searchAll (:353-387)
+//     knn_index<PR,QPR,idx>::build_index (algorithms/vamana/index.h:150-186)
+//     compute_groundtruth (data_tools/compute_groundtruth.cpp:22-60)
+// A maintainer switches a call site by adding `b200::`.  The index (points + graph) is kept
+// resident on the GPU in a DeviceIndex; the reference-signature overloads look it up in a small cache keyed by the
+// PointRange's buffer address, so repeated calls (the search sweep of check_nn_recall.h:214-257) upload once.
+#pragma once
+#include <cstdlib>
+#include <iostream>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <type_traits>
+#include <utility>
+#include <vector>
+
+#include "../pann.h"
+
+namespace parlayANN {
+namespace b200 {
+
+// element type / metric of the reference's point classes (euclidian_point.h:92-242, mips_point.h:67-139)
+template <typename Point> struct point_traits { static constexpr bool supported = false; };
+#define PANN_B200_TRAIT(P, T, DT, M)                                                     \
+  template <> struct point_traits<P<T>> {                                                \
+    static constexpr bool supported = true;                                              \
+    static constexpr int dtype = DT, metric = M;                                         \
+    using elt = T;                                                                       \
+  };
+PANN_B200_TRAIT(Euclidian_Point, float, PANN_F32, PANN_L2)
+PANN_B200_TRAIT(Euclidian_Point, uint8_t, PANN_U8, PANN_L2)
+PANN_B200_TRAIT(Euclidian_Point, int8_t, PANN_I8, PANN_L2)
+PANN_B200_TRAIT(Mips_Point, float, PANN_F32, PANN_MIPS)
+PANN_B200_TRAIT(Mips_Point, uint8_t, PANN_U8, PANN_MIPS)
+PANN_B200_TRAIT(Mips_Point, int8_t, PANN_I8, PANN_MIPS)
+#undef PANN_B200_TRAIT
+
+inline void check(int rc) {  // the reference's error convention: message, then abort()
+  if (rc != 0) { std::cout << pann_last_error() << std::endl; abort(); }
+}
+
+template <typename PointRange> inline size_t row_stride(const PointRange& P) {
+  return (size_t)(P.location(1) - P.location(0));  // PointRange::aligned_bytes is private (point_range.h:139)
+}
+template <typename indexType> inline indexType* graph_base(const Graph<indexType>& G) {
+  return G[0].begin() - 1;  // flat n x (maxDeg+1) array, slot 0 = degree (graph.h:134-141, :234-242)
+}
+
+// PointRange + Graph resident on one GPU (RAII around pann_index)
+template <typename PointRange, typename indexType = unsigned int>
+class DeviceIndex {
+  static_assert(point_traits<typename PointRange::Point>::supported,
+                "parlayann_b200 covers Euclidian_Point / Mips_Point over float, uint8_t, int8_t (SURVEY.md §8)");
+  static_assert(sizeof(indexType) == 4, "graph ids are 32-bit");
+  using T = point_traits<typename PointRange::Point>;
+
+ public:
+  DeviceIndex(const PointRange& Points, long max_degree, const Graph<indexType>* G = nullptr, int device = 0) {
+    check(pann_index_create(&h_, device, T::dtype, T::metric, Points.size(), Points.dimension(), row_stride(Points),
+                            Points.location(0), (uint32_t)max_degree, G ? (const uint32_t*)graph_base(*G) : nullptr));
+  }
+  DeviceIndex(const PointRange& Points, const Graph<indexType>& G, int device = 0)
+      : DeviceIndex(Points, G.max_degree(), &G, device) {}
+  DeviceIndex(const DeviceIndex&) = delete;
+  DeviceIndex& operator=(const DeviceIndex&) = delete;
+  ~DeviceIndex() { pann_index_destroy(h_); }
+  void upload_graph(const Graph<indexType>& G) { check(pann_index_set_graph(h_, (const uint32_t*)graph_base(G))); }
+  void download_graph(Graph<indexType>& G) { check(pann_index_get_graph(h_, (uint32_t*)graph_base(G))); }
+  pann_index* handle() const { return h_; }
+
+ private:
+  pann_index* h_ = nullptr;
+};
+
+inline pann_query_params to_pann(const QueryParams& QP) {  // types.h:218-231
+  pann_query_params q;
+  q.k = QP.k; q.beam = QP.beamSize; q.cut = QP.cut;
+  // the ABI reads a negative limit as "all"; the reference visits / reads nothing then (beamSearch.h:107, :130)
+  q.limit = QP.limit < 0 ? 0 : QP.limit; q.degree_limit = QP.degree_limit < 0 ? 0 : QP.degree_limit;
+  return q;
+}
+
+// ---- resident-index cache for the reference-signature overloads (keyed by the PointRange's buffer) ----------------
+template <typename PointRange, typename indexType>
+inline DeviceIndex<PointRange, indexType>& cached_index(const PointRange& Points, const Graph<indexType>& G, bool graph_dirty) {
+  using DI = DeviceIndex<PointRange, indexType>;
+  struct Entry { std::unique_ptr<DI> di; const void* graph; long maxdeg; };
+  static std::map<const void*, Entry> cache;
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  const void* key = Points.location(0);
+  auto it = cache.find(key);
+  if (it == cache.end() || it->second.maxdeg != G.max_degree()) {
+    cache[key] = Entry{std::make_unique<DI>(Points, G), graph_base(G), G.max_degree()};
+    return *cache[key].di;
+  }
+  if (graph_dirty || it->second.graph != graph_base(G)) { it->second.di->upload_graph(G); it->second.graph = graph_base(G); }
+  return *it->second.di;
+}
+
+// ---- searchAll (beamSearch.h:353-387) on a resident index -------------------------------------------------------
+template <typename PointRange, typename indexType>
+parlay::sequence<parlay::sequence<indexType>>
+searchAll(DeviceIndex<PointRange, indexType>& D, const PointRange& Query_Points, stats<indexType>& QueryStats,
+          const parlay::sequence<indexType>& starting_points, const QueryParams& QP) {
+  if (QP.k > QP.beamSize) {  // beamSearch.h:368-372 / :549-553
+    std::cout << "Error: beam search parameter Q = " << QP.beamSize << " same size or smaller than k = " << QP.k << std::endl;
+    abort();
+  }
+  const size_t nq = Query_Points.size();
+  const size_t k = (size_t)QP.k;
+  std::vector<uint32_t> ids(nq * k), visited(nq), cmps(nq);
+  pann_query_params q = to_pann(QP);
+  if (nq)
+    check(pann_search_batch(D.handle(), Query_Points.location(0), nq, row_stride(Query_Points), (const uint32_t*)starting_points.begin(),
+                            (uint32_t)starting_points.size(), &q, ids.data(), nullptr, visited.data(), cmps.data()));
+  parlay::sequence<parlay::sequence<indexType>> all_neighbors(nq);
+  parlay::parallel_for(0, nq, [&](size_t i) {
+    all_neighbors[i] = parlay::tabulate(k, [&](size_t j) { return (indexType)ids[i * k + j]; });
+    QueryStats.increment_visited(i, visited[i]);  // stats.h:70-73
+    QueryStats.increment_dist(i, cmps[i]);
+  });
+  return all_neighbors;
+}
+
+// reference signature (beamSearch.h:362-367)
+template <typename PointRange, typename indexType>
+parlay::sequence<parlay::sequence<indexType>>
+searchAll(PointRange& Query_Points, Graph<indexType>& G, PointRange& Base_Points, stats<indexType>& QueryStats,
+          parlay::sequence<indexType> starting_points, QueryParams& QP) {
+  return searchAll(cached_index(Base_Points, G, false), Query_Points, QueryStats, starting_points, QP);
+}
+template <typename PointRange, typename indexType>
+parlay::sequence<parlay::sequence<indexType>>
+searchAll(PointRange& Query_Points, Graph<indexType>& G, PointRange& Base_Points, stats<indexType>& QueryStats,
+          indexType starting_point, QueryParams& QP) {
+  parlay::sequence<indexType> start_points = {starting_point};
+  return searchAll(cached_index(Base_Points, G, false), Query_Points, QueryStats, start_points, QP);
+}
+
+// ---- qsearchAll (beamSearch.h:537-565), reference signature.  The quantised ranges must be the same type as the
+// exact ones (no quantisation: beam_search_rerank then reduces to filtered_beam_search, :409-410, :445-452);
+// quantised search + re-rank is a "next" row.
+template <typename PointRange, typename QPointRange, typename QQPointRange, typename indexType>
+parlay::sequence<parlay::sequence<indexType>>
+qsearchAll(const PointRange& Query_Points, const QPointRange&, const QQPointRange&, const Graph<indexType>& G,
+           const PointRange& Base_Points, const QPointRange&, const QQPointRange&, stats<indexType>& QueryStats,
+           const indexType starting_point, const QueryParams& QP) {
+  static_assert(std::is_same<PointRange, QPointRange>::value && std::is_same<PointRange, QQPointRange>::value,
+                "parlayann_b200: quantised search + re-rank is not on the GPU path yet (SURVEY.md §8f.2)");
+  parlay::sequence<indexType> starting_points = {starting_point};
+  return searchAll(cached_index(Base_Points, G, false), Query_Points, QueryStats, starting_points, QP);
+}
+
+// ---- knn_index::build_index (vamana/index.h:150-186) -------------------------------------------------------------
+// Same class shape as the reference's knn_index: construct with BuildParams, call build_index(G, Points, QPoints,
+// BuildStats, sort_neighbors).  The graph is built on the GPU and copied into G; BuildStats receives the same
+// per-point counters the reference accumulates (index.h:260-265, :298).
+template <typename PointRange, typename QPointRange, typename indexType>
+struct knn_index {
+  using GraphI = Graph<indexType>;
+  BuildParams BP;
+  indexType start_point = 0;
+  double phase_seconds[3] = {0, 0, 0};  // beam search + prune / bidirect / reverse-edge prune (index.h:313-315)
+  knn_index(BuildParams& BP) : BP(BP) {}
+  indexType get_start() { return start_point; }
+  void set_start() { start_point = 0; }
+
+  void build_index(GraphI& G, PointRange& Points, QPointRange&, stats<indexType>& BuildStats, bool sort_neighbors = true) {
+    static_assert(std::is_same<PointRange, QPointRange>::value,
+                  "parlayann_b200: building on a quantised copy is not on the GPU path yet (SURVEY.md §8f.2)");
+    if (BP.single_batch != 0) { std::cout << "parlayann_b200: single_batch builds are not supported" << std::endl; abort(); }
+    std::cout << "Building graph..." << std::endl;
+    set_start();
+    const size_t n = Points.size();
+    DeviceIndex<PointRange, indexType> D(Points, G.max_degree());
+    std::vector<uint32_t> vis(n), cmp(n);
+    std::cout << "number of passes = " << BP.num_passes << std::endl;
+    check(pann_vamana_build(D.handle(), (uint32_t)BP.R, (uint32_t)BP.L, BP.alpha, BP.num_passes, sort_neighbors ? 1 : 0,
+                            vis.data(), cmp.data(), phase_seconds));
+    D.download_graph(G);
+    parlay::parallel_for(0, n, [&](size_t i) { BuildStats.increment_visited(i, vis[i]); BuildStats.increment_dist(i, cmp[i]); });
+    std::cout << "beam search time: " << phase_seconds[0] << std::endl;
+    std::cout << "bidirect time: " << phase_seconds[1] << std::endl;
+    std::cout << "prune time: " << phase_seconds[2] << std::endl;
+  }
+};
+
+// ---- compute_groundtruth (data_tools/compute_groundtruth.cpp:22-60) -----------------------------------------------
+// Returns the same structure (per query k pairs (int id, float dist)), already sorted by (distance, id), so the
+// reference's write_ibin (:64-100) can be applied to it unchanged.
+template <typename PointRange>
+parlay::sequence<parlay::sequence<std::pair<int, float>>> compute_groundtruth(PointRange& B, PointRange& Q, int k) {
+  const size_t nq = Q.size();
+  DeviceIndex<PointRange, unsigned int> D(B, 1);
+  std::vector<int32_t> ids(nq * (size_t)k);
+  std::vector<float> ds(nq * (size_t)k);
+  if (nq) check(pann_groundtruth(D.handle(), Q.location(0), nq, row_stride(Q), (uint32_t)k, 0, ids.data(), ds.data()));
+  auto answers = parlay::tabulate(nq, [&](size_t i) {
+    return parlay::tabulate((size_t)k, [&](size_t j) { return std::make_pair((int)ids[i * k + j], ds[i * k + j]); });
+  });
+  std::cout << "Done computing groundtruth" << std::endl;
+  return answers;
+}
+
+}  // namespace b200
+}  // namespace parlayANN

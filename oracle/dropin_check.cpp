@@ -1,0 +1,98 @@
+// oracle/dropin_check.cpp — TEST INFRASTRUCTURE.  Compiles the drop-in header (include/parlayann_b200/dropin.h) inside
+// the UNMODIFIED reference (headers included by path) and checks, in ONE process, that switching a call site from
+// parlayANN::X to parlayANN::b200::X gives the same bytes: the built graph and build statistics, qsearchAll's ids and
+// per-query counters, and the ground truth.  Built by oracle/Makefile into oracle/_ref/ (needs /root/reference);
+// run by tests/test_dropin_gpu.py on the GPU box.
+#include <algorithm>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "utils/beamSearch.h"
+#include "utils/euclidian_point.h"
+#include "utils/graph.h"
+#include "utils/mips_point.h"
+#include "utils/point_range.h"
+#include "utils/stats.h"
+#include "utils/types.h"
+#include "vamana/index.h"
+
+#define main ref_compute_groundtruth_main
+#define pid gt_pid
+#include "../data_tools/compute_groundtruth.cpp"
+#undef pid
+#undef main
+
+#include "parlayann_b200/dropin.h"
+
+using namespace parlayANN;
+using uint = unsigned int;
+
+static const char* arg(int argc, char** argv, const char* name, const char* dflt) {
+  for (int i = 1; i + 1 < argc; i++) if (!strcmp(argv[i], name)) return argv[i + 1];
+  return dflt;
+}
+
+template <typename PR>
+static int run(int argc, char** argv) {
+  PR Points((char*)arg(argc, argv, "-base", ""));
+  PR Q((char*)arg(argc, argv, "-query", ""));
+  long R = atol(arg(argc, argv, "-R", "32")), L = atol(arg(argc, argv, "-L", "64")), k = atol(arg(argc, argv, "-k", "10"));
+  int passes = atoi(arg(argc, argv, "-passes", "1"));
+  int bad = 0;
+  BuildParams BP(R, L, 1.2, passes, false);
+  // --- build: reference on the CPU, drop-in on the GPU
+  Graph<uint> Gc(BP.max_degree(), Points.size()), Gg(BP.max_degree(), Points.size());
+  stats<uint> Sc(Points.size()), Sg(Points.size());
+  { knn_index<PR, PR, uint> I(BP); I.build_index(Gc, Points, Points, Sc, true); }
+  { b200::knn_index<PR, PR, uint> I(BP); I.build_index(Gg, Points, Points, Sg, true); }
+  size_t diff_rows = 0;
+  for (size_t i = 0; i < Points.size(); i++) {
+    bool same = Gc[i].size() == Gg[i].size();
+    for (size_t j = 0; same && j < Gc[i].size(); j++) same = Gc[i][j] == Gg[i][j];
+    diff_rows += !same;
+  }
+  bool st_same = std::equal(Sc.visited.begin(), Sc.visited.end(), Sg.visited.begin()) && std::equal(Sc.distances.begin(), Sc.distances.end(), Sg.distances.begin());
+  printf("DROPIN build: %zu of %zu rows differ, stats %s\n", diff_rows, Points.size(), st_same ? "identical" : "DIFFER");
+  bad += diff_rows != 0 || !st_same;
+  // --- qsearchAll over the reference's sweep of beams, same graph on both sides
+  for (long beam : {10L, 13L, 20L, 40L, 100L, 300L}) {
+    if (beam < k) continue;
+    QueryParams QP(k, beam, 1.35, (long)Gc.size(), (long)Gc.max_degree());
+    stats<uint> qc(Q.size()), qg(Q.size());
+    auto rc = qsearchAll<PR, PR, PR, uint>(Q, Q, Q, Gc, Points, Points, Points, qc, 0u, QP);
+    auto rg = b200::qsearchAll<PR, PR, PR, uint>(Q, Q, Q, Gc, Points, Points, Points, qg, 0u, QP);
+    size_t dq = 0;
+    for (size_t i = 0; i < Q.size(); i++) dq += !(rc[i] == rg[i]);
+    bool s2 = std::equal(qc.visited.begin(), qc.visited.end(), qg.visited.begin()) && std::equal(qc.distances.begin(), qc.distances.end(), qg.distances.begin());
+    printf("DROPIN qsearchAll beam %ld: %zu of %zu queries differ, stats %s\n", beam, dq, Q.size(), s2 ? "identical" : "DIFFER");
+    bad += dq != 0 || !s2;
+  }
+  // --- ground truth: sorted distance rows must be identical
+  {
+    int gk = 20;
+    auto ac = compute_groundtruth<PR>(Points, Q, gk);
+    auto ag = b200::compute_groundtruth<PR>(Points, Q, gk);
+    size_t dr = 0;
+    for (size_t i = 0; i < Q.size(); i++) {
+      std::vector<float> a, b;
+      for (auto& e : ac[i]) a.push_back(e.second);
+      for (auto& e : ag[i]) b.push_back(e.second);
+      std::sort(a.begin(), a.end());
+      dr += !(a == b);
+    }
+    printf("DROPIN compute_groundtruth: %zu of %zu rows differ\n", dr, Q.size());
+    bad += dr != 0;
+  }
+  printf(bad ? "DROPIN_FAIL\n" : "DROPIN_OK\n");
+  return bad ? 1 : 0;
+}
+
+int main(int argc, char** argv) {
+  std::string dt = arg(argc, argv, "-data_type", "uint8"), df = arg(argc, argv, "-dist_func", "Euclidian");
+  bool l2 = df == "Euclidian";
+  if (dt == "uint8") return l2 ? run<PointRange<Euclidian_Point<uint8_t>>>(argc, argv) : run<PointRange<Mips_Point<uint8_t>>>(argc, argv);
+  if (dt == "int8") return l2 ? run<PointRange<Euclidian_Point<int8_t>>>(argc, argv) : run<PointRange<Mips_Point<int8_t>>>(argc, argv);
+  if (dt == "float") return l2 ? run<PointRange<Euclidian_Point<float>>>(argc, argv) : run<PointRange<Mips_Point<float>>>(argc, argv);
+  return 2;
+}

@@ -54,12 +54,26 @@ struct BeamArgs {
   uint32_t* g_hash; u64* g_vis;
 };
 
+// Both searches count instead of bisecting when the list is short (n is warp-uniform at every call site): the loads
+// are independent, so a handful of resident warps is not left waiting on a chain of dependent shared-memory reads.
 __device__ __forceinline__ int pann_lower_bound(const u64* a, int n, u64 k1) {  // #{x : x>>1 < k1}
+  if (n <= 32) {
+    int r = 0;
+#pragma unroll 4
+    for (int j = 0; j < n; j++) r += ((a[j] >> 1) < k1) ? 1 : 0;
+    return r;
+  }
   int lo = 0, hi = n;
   while (lo < hi) { int mid = (lo + hi) >> 1; if ((a[mid] >> 1) < k1) lo = mid + 1; else hi = mid; }
   return lo;
 }
 __device__ __forceinline__ int pann_upper_bound(const u64* a, int n, u64 k1) {  // #{x : x>>1 <= k1}
+  if (n <= 32) {
+    int r = 0;
+#pragma unroll 4
+    for (int j = 0; j < n; j++) r += ((a[j] >> 1) <= k1) ? 1 : 0;
+    return r;
+  }
   int lo = 0, hi = n;
   while (lo < hi) { int mid = (lo + hi) >> 1; if ((a[mid] >> 1) <= k1) lo = mid + 1; else hi = mid; }
   return lo;
@@ -68,11 +82,12 @@ __device__ __forceinline__ int pann_upper_bound(const u64* a, int n, u64 k1) {  
 // Distances from the query to `cnt` rows, one row per lane, 32 rows per pass; row r is pann_key_id(keyOf(r))
 // (a 64-bit tag whose id field names the row, so callers can carry a (dist,id) key through).  Calls
 // emit(tag, dist, valid) warp-uniformly once per pass; lane l carries row base + l, so ballot-ranked stores in
-// emit keep the rows in order.  QR > 0: the query's QR chunks are in registers (qreg); QR == 0: in shared
-// memory (qsm, read as broadcasts).  RG: anything with points / stride / nch (BeamArgs, PruneArgs, ...).
+// emit keep the rows in order.  The query is read from shared memory (qsm, broadcast reads).  QR > 0: rows have
+// exactly QR chunks and the loop is unrolled with all QR loads in flight; QR == 0: any row length, 8 loads in flight.
+// RG: anything with points / stride / nch (BeamArgs, PruneArgs, ...).
 template <int DT, int METRIC, int QR, class RG, class KeyOf, class Emit>
-__device__ __forceinline__ void pann_row_distances_g(const RG& A, KeyOf keyOf, int cnt, const uint4* qreg,
-                                                     const uint4* qsm, int lane, Emit emit) {
+__device__ __forceinline__ void pann_row_distances_g(const RG& A, KeyOf keyOf, int cnt, const uint4* qsm, int lane,
+                                                     Emit emit) {
   for (int base = 0; base < cnt; base += 32) {
     const int r = base + lane;
     const bool ok = r < cnt;
@@ -86,7 +101,7 @@ __device__ __forceinline__ void pann_row_distances_g(const RG& A, KeyOf keyOf, i
 #pragma unroll
         for (int c = 0; c < QR; c++) v[c] = pann_ldg16(row + c * 16);
 #pragma unroll
-        for (int c = 0; c < QR; c++) acc.add(v[c], qreg[c]);
+        for (int c = 0; c < QR; c++) acc.add(v[c], qsm[c]);
       } else {
         const int nch = (int)A.nch;
         for (int c0 = 0; c0 < nch; c0 += 8) {
@@ -103,27 +118,21 @@ __device__ __forceinline__ void pann_row_distances_g(const RG& A, KeyOf keyOf, i
 }
 // the same over a plain id list (shared memory): emit(id, dist, valid)
 template <int DT, int METRIC, int QR, class RG, class Emit>
-__device__ __forceinline__ void pann_row_distances(const RG& A, const uint32_t* ids, int cnt, const uint4* qreg,
-                                                   const uint4* qsm, int lane, Emit emit) {
+__device__ __forceinline__ void pann_row_distances(const RG& A, const uint32_t* ids, int cnt, const uint4* qsm, int lane,
+                                                   Emit emit) {
   pann_row_distances_g<DT, METRIC, QR>(
-      A, [&](int r) { return (u64)ids[r] << 1; }, cnt, qreg, qsm, lane,
+      A, [&](int r) { return (u64)ids[r] << 1; }, cnt, qsm, lane,
       [&](u64 tag, float d, bool ok) { emit(pann_key_id(tag), d, ok); });
 }
-// the query row into registers (QR > 0, every lane holds all of it) or shared memory (QR == 0)
-template <int QR>
-__device__ __forceinline__ void pann_load_query(const uint8_t* qrow, uint32_t nch, uint4* qreg, uint4* qsm, int lane) {
-  if constexpr (QR > 0) {
-#pragma unroll
-    for (int c = 0; c < QR; c++) qreg[c] = pann_ldg16(qrow + c * 16);
-  } else {
-    __syncwarp();
-    for (int ch = lane; ch < (int)nch; ch += 32) qsm[ch] = pann_ldg16(qrow + ch * 16);
-    __syncwarp();
-  }
+// the query row into shared memory
+__device__ __forceinline__ void pann_load_query(const uint8_t* qrow, uint32_t nch, uint4* qsm, int lane) {
+  __syncwarp();
+  for (int ch = lane; ch < (int)nch; ch += 32) qsm[ch] = pann_ldg16(qrow + ch * 16);
+  __syncwarp();
 }
 
 template <int DT, int METRIC, int QR, bool GS>
-__global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kernel(const BeamArgs A) {
+__global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_beam_search_kernel(const BeamArgs A) {
   extern __shared__ __align__(16) uint8_t pann_smem[];
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
   const unsigned lt_mask = (1u << lane) - 1u;
@@ -158,9 +167,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
     }
     const long long self = A.self_ids ? (long long)A.self_ids[q] : -1;
     const uint8_t* qrow = A.self_ids ? A.points + (u64)self * A.stride : A.queries + (u64)q * A.qstride;
-    uint4 qreg[QR > 0 ? QR : 1];
-    pann_load_query<QR>(qrow, A.nch, qreg, qsm, lane);
-    __syncwarp();
+    pann_load_query(qrow, A.nch, qsm, lane);
 
     u64* front = bufA;
     u64* nf = bufB;
@@ -176,7 +183,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
         int cnt = min((int)A.maxdeg, (int)(A.nstarts - s0));
         for (int i = lane; i < cnt; i += 32) nbr[i] = A.starts[s0 + i];
         __syncwarp();
-        pann_row_distances<DT, METRIC, QR>(A, nbr, cnt, qreg, qsm, lane, [&](uint32_t id, float d, bool ok) {
+        pann_row_distances<DT, METRIC, QR>(A, nbr, cnt, qsm, lane, [&](uint32_t id, float d, bool ok) {
           unsigned m = __ballot_sync(PANN_FULL, ok);
           if (ok) cand[C + __popc(m & lt_mask)] = pann_key(d, id);
           C += __popc(m);
@@ -263,7 +270,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
       }
       cmps += S;  // :155
       if (S + C > (int)A.ccap) { status = 1; break; }  // cannot happen (ccap >= maxdeg + beam/8); guards memory
-      pann_row_distances<DT, METRIC, QR>(A, nbr, S, qreg, qsm, lane, [&](uint32_t id, float d, bool ok) {
+      pann_row_distances<DT, METRIC, QR>(A, nbr, S, qsm, lane, [&](uint32_t id, float d, bool ok) {
         bool take = ok && (d < cutoff);  // :153-158
         unsigned m = __ballot_sync(PANN_FULL, take);
         if (take) cand[C + __popc(m & lt_mask)] = pann_key(d, id);
@@ -332,7 +339,14 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_beam_search_kern
       // (d) cut rule (:190-195): threshold (float)(cut * (double)dist[k]), never below the old size
       if (A.cut_rule && nfs > A.k) {
         float thr = (float)(A.cut * (double)pann_key_dist(nf[A.k]));
-        int c = pann_upper_bound(nf, nfs, (u64)pann_fsort(thr) << 31);
+        const u64 tk = (u64)pann_fsort(thr) << 31;  // (thr, id 0) >> 1
+        int c = 0;
+        for (int base = 0; base < nfs; base += 32) {  // warp-uniform key: count by ballot
+          const int i = base + lane;
+          const int pc = __popc(__ballot_sync(PANN_FULL, i < nfs && (nf[i] >> 1) <= tk));
+          c += pc;
+          if (pc < 32) break;
+        }
         nfs = max(c, F);
       }
       u64* t = front; front = nf; nf = t;

@@ -180,7 +180,7 @@ static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap) {
   A.off_scand = A.off_cand + al16((size_t)A.ccap * 8);
   A.off_nbr = A.off_scand + al16((size_t)A.ccap * 8);
   A.off_q = A.off_nbr + al16((size_t)std::max<uint32_t>(A.maxdeg, 1) * 4);
-  A.off_vis = A.off_q + (qrT == 0 ? g.stride : 0);
+  A.off_vis = A.off_q + g.stride;
   A.off_hash = A.off_vis + (gs ? 0 : al16((size_t)vcap * 8));
   A.warp_bytes = A.off_hash + (gs ? 0 : (4u << A.bits));
   const size_t cta_bytes = (size_t)A.warp_bytes * PANN_WARPS_PER_CTA;

@@ -67,7 +67,7 @@ static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, De
   A.cap = 512;
   A.off_b = al16((size_t)A.cap * 8);
   A.off_q = 2 * A.off_b;
-  A.warp_bytes = A.off_q + (qrT == 0 ? g.stride : 0);
+  A.warp_bytes = A.off_q + g.stride;
   A.task_map = nullptr; A.ntask_map = 0; A.g_scratch = nullptr;
   {
     const void* fn = prune_kernel(idx->dtype, idx->metric, qrT, false);
@@ -90,7 +90,7 @@ static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, De
   A.cap = bc[1];
   A.task_map = A.big_list; A.ntask_map = bc[0];
   A.off_b = 0; A.off_q = 0;
-  A.warp_bytes = (qrT == 0 ? g.stride : 0);
+  A.warp_bytes = g.stride;
   const void* fn = prune_kernel(idx->dtype, idx->metric, qrT, true);
   size_t cta_bytes = (size_t)A.warp_bytes * PANN_PRUNE_WARPS;
   PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
@@ -235,7 +235,7 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
     E.graph = idx->graph; E.maxdeg = md; E.n = n; E.out = d_ed.as<float>();
     const int qrT = pann_qr_of(idx->geom);
     E.off_q = al16((size_t)md * 4);
-    E.warp_bytes = E.off_q + (qrT == 0 ? idx->geom.stride : 0);
+    E.warp_bytes = E.off_q + idx->geom.stride;
     const void* fn = edge_kernel(idx->dtype, idx->metric, qrT);
     size_t cta_bytes = (size_t)E.warp_bytes * PANN_PRUNE_WARPS;
     PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));

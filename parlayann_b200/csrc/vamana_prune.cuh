@@ -105,8 +105,7 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
     }
     // ---- query row = the pruned vertex
     const uint8_t* prow = A.points + (u64)p * A.stride;
-    uint4 qreg[QR > 0 ? QR : 1];
-    auto load_q = [&](const uint8_t* row) { pann_load_query<QR>(row, A.nch, qreg, qsm, lane); };
+    auto load_q = [&](const uint8_t* row) { pann_load_query(row, A.nch, qsm, lane); };
     load_q(prow);
     unsigned comps = 0;
     int C = 0;  // keys in bufA
@@ -126,7 +125,7 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
       __syncwarp();
       comps += m;
       pann_row_distances_g<DT, METRIC, QR>(
-          A, [&](int r) { return (u64)cid[r] << 1; }, (int)m, qreg, qsm, lane, [&](u64 tag, float d, bool ok) {
+          A, [&](int r) { return (u64)cid[r] << 1; }, (int)m, qsm, lane, [&](u64 tag, float d, bool ok) {
             unsigned bm = __ballot_sync(PANN_FULL, ok);
             if (ok) bufA[C + __popc(bm & lt_mask)] = pann_key(d, pann_key_id(tag));
             C += __popc(bm);
@@ -176,7 +175,7 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
       load_q(A.points + (u64)ps_id * A.stride);
       int w = start;
       pann_row_distances_g<DT, METRIC, QR>(
-          A, [&](int r) { return S[start + r]; }, cnt, qreg, qsm, lane, [&](u64 key, float d, bool ok) {
+          A, [&](int r) { return S[start + r]; }, cnt, qsm, lane, [&](u64 key, float d, bool ok) {
             bool keep = ok && !(A.alpha * (double)d <= (double)pann_key_dist(key));  // :111
             unsigned km = __ballot_sync(PANN_FULL, keep);
             if (keep) S[w + __popc(km & lt_mask)] = key;
@@ -220,14 +219,13 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_edge_dist_kernel(c
     const uint32_t* grow = A.graph + (u64)i * (A.maxdeg + 1);
     const int deg = (int)grow[0];
     const uint8_t* row = A.points + (u64)i * A.stride;
-    uint4 qreg[QR > 0 ? QR : 1];
-    pann_load_query<QR>(row, A.nch, qreg, qsm, lane);
+    pann_load_query(row, A.nch, qsm, lane);
     for (int j = lane; j < deg; j += 32) ids[j] = grow[1 + j];
     __syncwarp();
     float* o = A.out + (u64)i * A.maxdeg;
     int w = 0;
     pann_row_distances_g<DT, METRIC, QR>(
-        A, [&](int r) { return (u64)ids[r] << 1; }, deg, qreg, qsm, lane, [&](u64, float d, bool ok) {
+        A, [&](int r) { return (u64)ids[r] << 1; }, deg, qsm, lane, [&](u64, float d, bool ok) {
           unsigned bm = __ballot_sync(PANN_FULL, ok);
           if (ok) o[w + __popc(bm & ((1u << lane) - 1u))] = d;
           w += __popc(bm);
