@@ -50,34 +50,40 @@ struct BeamArgs {
   const uint32_t* qmap;                      // optional: launch index -> query index (retries of a subset)
   // algorithmic bytes of the batch (B_q = cmps*row + sum_hops 4*(1+nbrs read) + row + 4k), one atomic per query
   u64* bytes_total; uint32_t rowbytes;
+  uint32_t* qcounter;                        // optional: dynamic query distribution (zeroed before the launch)
   // global scratch (GS variant): per resident warp
   uint32_t* g_hash; u64* g_vis;
 };
 
-// Both searches count instead of bisecting when the list is short (n is warp-uniform at every call site): the loads
-// are independent, so a handful of resident warps is not left waiting on a chain of dependent shared-memory reads.
-__device__ __forceinline__ int pann_lower_bound(const u64* a, int n, u64 k1) {  // #{x : x>>1 < k1}
-  if (n <= 32) {
-    int r = 0;
-#pragma unroll 4
-    for (int j = 0; j < n; j++) r += ((a[j] >> 1) < k1) ? 1 : 0;
-    return r;
+// Counting and bisecting on RAW keys (flag bit included): for a threshold key t with bit 0 clear,
+//   x < t        <=>  (x >> 1) <  (t >> 1)          and          x <= (t | 1)  <=>  (x >> 1) <= (t >> 1),
+// so no shifts are needed.  Short lists are counted, not bisected (n is warp-uniform at every call site): the loads are
+// independent and each element costs one subtract-with-borrow chain (3 integer adds), two accumulators deep.
+__device__ __forceinline__ void pann_borrow_count(int& neg, u64 x, u64 t) {  // neg -= (x < t)
+  const unsigned xl = (unsigned)x, xh = (unsigned)(x >> 32), tl = (unsigned)t, th = (unsigned)(t >> 32);
+  asm("{\n\t.reg .u32 tt;\n\tsub.cc.u32 tt, %1, %3;\n\tsubc.cc.u32 tt, %2, %4;\n\tsubc.u32 %0, %0, 0;\n\t}"
+      : "+r"(neg) : "r"(xl), "r"(xh), "r"(tl), "r"(th));
+}
+__device__ __forceinline__ int pann_count_below_any(const u64* a, int n, u64 t) {  // #{j < n : a[j] < t}, any order
+  int n0 = 0, n1 = 0, j = 0;
+#pragma unroll 1   // lists are short (about one beam): a deeper unroll only bloats the code and runs its remainder loops
+  for (; j + 4 <= n; j += 4) {
+    const u64 x0 = a[j], x1 = a[j + 1], x2 = a[j + 2], x3 = a[j + 3];
+    pann_borrow_count(n0, x0, t); pann_borrow_count(n1, x1, t); pann_borrow_count(n0, x2, t); pann_borrow_count(n1, x3, t);
   }
+#pragma unroll 1
+  for (; j < n; j++) pann_borrow_count(n0, a[j], t);
+  return -(n0 + n1);
+}
+__device__ __forceinline__ int pann_count_below(const u64* a, int n, u64 t) {  // the same for a SORTED list
+  if (n <= 40) return pann_count_below_any(a, n, t);
   int lo = 0, hi = n;
-  while (lo < hi) { int mid = (lo + hi) >> 1; if ((a[mid] >> 1) < k1) lo = mid + 1; else hi = mid; }
+  while (lo < hi) { int mid = (lo + hi) >> 1; if (a[mid] < t) lo = mid + 1; else hi = mid; }
   return lo;
 }
-__device__ __forceinline__ int pann_upper_bound(const u64* a, int n, u64 k1) {  // #{x : x>>1 <= k1}
-  if (n <= 32) {
-    int r = 0;
-#pragma unroll 4
-    for (int j = 0; j < n; j++) r += ((a[j] >> 1) <= k1) ? 1 : 0;
-    return r;
-  }
-  int lo = 0, hi = n;
-  while (lo < hi) { int mid = (lo + hi) >> 1; if ((a[mid] >> 1) <= k1) lo = mid + 1; else hi = mid; }
-  return lo;
-}
+// t = a (dist,id) key with bit 0 clear
+__device__ __forceinline__ int pann_lower_bound(const u64* a, int n, u64 t) { return pann_count_below(a, n, t); }       // #{x>>1 <  t>>1}
+__device__ __forceinline__ int pann_upper_bound(const u64* a, int n, u64 t) { return pann_count_below(a, n, t + 2); }   // #{x>>1 <= t>>1}
 
 // Distances from the query to `cnt` rows, one row per lane, 32 rows per pass; row r is pann_key_id(keyOf(r))
 // (a 64-bit tag whose id field names the row, so callers can carry a (dist,id) key through).  Calls
@@ -157,7 +163,15 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
   const int B = A.beam;
   const long long wstride = (long long)gridDim.x * PANN_WARPS_PER_CTA;
 
-  for (long long ql = wglobal; ql < (long long)A.nq; ql += wstride) {
+  // the first query of a warp is its own index; further ones come from a shared counter, so a warp that drew short
+  // searches takes more of them (query lengths vary by 2-3x)
+  auto next_query = [&](long long ql) -> long long {
+    if (!A.qcounter) return ql + wstride;
+    unsigned nx = 0;
+    if (lane == 0) nx = atomicAdd(A.qcounter, 1u);
+    return wstride + (long long)__shfl_sync(PANN_FULL, nx, 0);
+  };
+  for (long long ql = wglobal; ql < (long long)A.nq; ql = next_query(ql)) {
     const long long q = A.qmap ? (long long)A.qmap[ql] : ql;
     // ---- per-query init: hash filter := -1 (beamSearch.h:53), query chunks into registers / shared memory
     {
@@ -206,14 +220,18 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
     // ---- main loop (:107-209)
     while (status == 0) {
       // next to visit = first unflagged frontier entry  (unvisited_frontier[offset], :109)
-      int pos = -1;
-      for (int base = 0; base < F && pos < 0; base += 32) {
-        int i = base + lane;
-        unsigned m = __ballot_sync(PANN_FULL, i < F && !(front[i] & 1ull));
-        if (m) pos = base + __ffs(m) - 1;
+      int pos = -1, nflag = 0;  // nflag = #frontier entries already visited
+      for (int base = 0; base < F; base += 32) {
+        const int i = base + lane;
+        const unsigned m = __ballot_sync(PANN_FULL, i < F && !(front[i] & 1ull));
+        nflag += min(32, F - base) - __popc(m);
+        if (m && pos < 0) pos = base + __ffs(m) - 1;
       }
       if (pos < 0 || (long long)V >= A.limit) break;  // remain <= offset, or visit limit reached (:107)
       const u64 cur = front[pos];
+      // every visited vertex still sits in the frontier (flagged entries are distinct members of `visited`): then a
+      // candidate that is not in the frontier cannot be in `visited`, and the merge skips that lookup
+      const bool vis_in_front = (nflag == V);
       // the graph row is requested now (degree + the first 64 slots; slots past the degree are stale but in-row)
       // so that its latency overlaps the visited-list insertion below
       const uint32_t* grow = A.graph + (u64)pann_key_id(cur) * (A.maxdeg + 1);
@@ -225,12 +243,12 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
       // visited.insert(upper_bound(cur)) (:112-113): one pass from the top, entries above cur move up by one
       if (V >= (int)A.vcap) { status = 1; break; }
       {
-        const u64 kc = cur >> 1;
+        const u64 kc = cur | 1ull;  // x > kc  <=>  (x >> 1) > (cur >> 1)   (entries of vis have bit 0 clear)
         int ip = V;
         for (int top = V; top > 0; top -= 32) {
           const int i = top - 1 - lane;
           const u64 x = (i >= 0) ? vis[i] : 0ull;
-          const bool gt = (i >= 0) && ((x >> 1) > kc);
+          const bool gt = (i >= 0) && (x > kc);
           const unsigned m = __ballot_sync(PANN_FULL, gt);
           if (gt) vis[i + 1] = x;  // every lane read its entry before the ballot; targets are this block's own slots + 1
           ip -= __popc(m);
@@ -293,14 +311,13 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
       __syncwarp();
       for (int i = lane; i < C; i += 32) {
         const u64 ci = cand[i];
-        int r = 0;
-        for (int j = 0; j < C; j++) r += (cand[j] < ci) ? 1 : 0;
-        scand[r] = ci;
+        scand[pann_count_below_any(cand, C, ci)] = ci;
       }
       __syncwarp();
       // (b) drop the empty slots and entries already in the frontier (set_union keeps one),
       //     place the rest: slot = rank among kept candidates + #frontier entries below it
       int Cv = 0;
+      unsigned occ = 0;  // B <= 32: slots of the new frontier taken by candidates
       for (int base = 0; base < C; base += 32) {
         int i = base + lane;
         bool valid = false;
@@ -309,29 +326,41 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
         if (i < C) {
           c = scand[i];
           if (c != ~0ull) {
-            lbf = pann_lower_bound(front, F, c >> 1);
-            valid = !(lbf < F && (front[lbf] >> 1) == (c >> 1));
+            lbf = pann_count_below(front, F, c);
+            valid = !(lbf < F && (front[lbf] & ~1ull) == c);
           }
         }
         unsigned m = __ballot_sync(PANN_FULL, valid);
         int vr = Cv + __popc(m & lt_mask);
+        bool placed = false;
         if (valid) {
           cand[vr] = c;
           int np = vr + lbf;
           if (np < B) {
-            int vp = pann_lower_bound(vis, V, c >> 1);  // re-entering an already visited vertex keeps it visited
-            u64 fl = (vp < V && (vis[vp] >> 1) == (c >> 1)) ? 1ull : 0ull;
+            u64 fl = 0ull;
+            if (!vis_in_front) {  // re-entering an already visited vertex keeps it visited
+              int vp = pann_count_below(vis, V, c);
+              fl = (vp < V && vis[vp] == c) ? 1ull : 0ull;
+            }
             nf[np] = c | fl;
+            placed = true;
+            lbf = np;
           }
         }
+        if (B <= 32) occ |= __reduce_or_sync(PANN_FULL, placed ? (1u << lbf) : 0u);
         Cv += __popc(m);
       }
       __syncwarp();
-      // (c) frontier entries move up by the number of kept candidates below them
-      for (int i = lane; i < F; i += 32) {
-        u64 f = front[i];
-        int np = i + pann_lower_bound(cand, Cv, f >> 1);
-        if (np < B) nf[np] = f;
+      // (c) the frontier entries fill the remaining slots in order
+      if (B <= 32) {
+        const int nfs0 = min(B, F + Cv);
+        if (lane < nfs0 && !((occ >> lane) & 1u)) nf[lane] = front[__popc(~occ & lt_mask)];
+      } else {
+        for (int i = lane; i < F; i += 32) {
+          u64 f = front[i];
+          int np = i + pann_count_below(cand, Cv, f & ~1ull);
+          if (np < B) nf[np] = f;
+        }
       }
       int nfs = min(B, F + Cv);  // :185
       C = 0;
@@ -339,11 +368,11 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
       // (d) cut rule (:190-195): threshold (float)(cut * (double)dist[k]), never below the old size
       if (A.cut_rule && nfs > A.k) {
         float thr = (float)(A.cut * (double)pann_key_dist(nf[A.k]));
-        const u64 tk = (u64)pann_fsort(thr) << 31;  // (thr, id 0) >> 1
+        const u64 tk = ((u64)pann_fsort(thr) << 32) | 1ull;  // x <= tk  <=>  (x >> 1) <= ((thr, id 0) >> 1)
         int c = 0;
         for (int base = 0; base < nfs; base += 32) {  // warp-uniform key: count by ballot
           const int i = base + lane;
-          const int pc = __popc(__ballot_sync(PANN_FULL, i < nfs && (nf[i] >> 1) <= tk));
+          const int pc = __popc(__ballot_sync(PANN_FULL, i < nfs && nf[i] <= tk));
           c += pc;
           if (pc < 32) break;
         }

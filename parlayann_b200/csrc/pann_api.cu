@@ -216,8 +216,8 @@ int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint
     if (h_starts[i] >= idx->n) PANN_FAIL("beam search: start point out of range");
   *status_or = 0;
   if (nq == 0) return 0;
-  if (idx->starts.reserve(sizeof(uint32_t) * nstarts) || idx->flag.reserve(sizeof(int)) || idx->bytes_ctr.reserve(8)) return 1;
-  PANN_CUDA(cudaMemsetAsync(idx->bytes_ctr.p, 0, 8, idx->stream));
+  if (idx->starts.reserve(sizeof(uint32_t) * nstarts) || idx->flag.reserve(sizeof(int)) || idx->bytes_ctr.reserve(16)) return 1;
+  PANN_CUDA(cudaMemsetAsync(idx->bytes_ctr.p, 0, 16, idx->stream));
   PANN_CUDA(cudaMemcpyAsync(idx->starts.p, h_starts, sizeof(uint32_t) * nstarts, cudaMemcpyHostToDevice, idx->stream));
   PANN_CUDA(cudaMemsetAsync(idx->flag.p, 0, sizeof(int), idx->stream));
 
@@ -239,6 +239,8 @@ int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint
   A.vis_ids = out.vis_ids; A.vis_dists = out.vis_dists; A.n_visited = out.n_visited; A.vout = out.vout;
   A.status = out.status; A.any_status = idx->flag.as<int>();
   A.bytes_total = idx->bytes_ctr.as<u64>(); A.rowbytes = idx->dims * idx->geom.elt;
+  A.qcounter = reinterpret_cast<uint32_t*>(idx->bytes_ctr.as<u64>() + 1);
+  { const char* sq = getenv("PANN_STATIC_QUERIES"); if (sq && sq[0] == '1') A.qcounter = nullptr; }
 
   // shared-memory variant while the hash filter is <= 16 KB per warp; visited-list capacity is a guess
   // that the retry below makes safe
@@ -262,6 +264,7 @@ int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint
     PANN_CUDA(cudaMemcpyAsync(idx->qmap.p, redo.data(), sizeof(uint32_t) * redo.size(), cudaMemcpyHostToDevice, idx->stream));
     PANN_CUDA(cudaMemsetAsync(idx->flag.p, 0, sizeof(int), idx->stream));
     A.qmap = idx->qmap.as<uint32_t>();
+    A.qcounter = nullptr;  // the counter was used by the first launch
     A.nq = redo.size();
     if (launch_beam(idx, A, true, (uint32_t)vbig)) return 1;
     int flag2 = 0;
