@@ -116,6 +116,12 @@ int pann_groundtruth_fetch(pann_index* idx, int32_t* out_ids, float* out_dists);
 int pann_groundtruth_merge(int device, uint32_t nshards, uint64_t nq, uint32_t k, const int32_t* ids, const float* dists,
                            int32_t* out_ids, float* out_dists);
 
+/* device-pointer variants for the multi-GPU path (base rows sharded over ranks, one NCCL all-gather of the local
+ * top-k, then the same merge on the device): nothing touches the host.  stream = cudaStream_t (NULL = default). */
+int pann_groundtruth_device_result(pann_index* idx, const int32_t** d_ids, const float** d_dists, uint64_t* nq, uint32_t* k);
+int pann_groundtruth_merge_device(int device, uint32_t nshards, uint64_t nq, uint32_t k, const int32_t* d_ids, const float* d_dists,
+                                  int32_t* d_out_ids, float* d_out_dists, void* stream);
+
 /* pinned host memory for callers that want asynchronous copies */
 int pann_host_alloc(void** p, size_t bytes);
 int pann_host_free(void* p);

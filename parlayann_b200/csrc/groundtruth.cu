@@ -279,3 +279,27 @@ extern "C" int pann_groundtruth_merge(int device, uint32_t nshards, uint64_t nq,
   cudaFree(d_ids); cudaFree(d_d); cudaFree(d_oi); cudaFree(d_od);
   return 0;
 }
+
+// Device-pointer variants for the multi-GPU path (base rows sharded over ranks): the local top-k stays
+// on the device, the ranks exchange it with an NCCL all-gather into one [nshards, nq, k] block, and K5 merges that
+// block in place on every rank.  `stream` is a cudaStream_t (0 = the legacy default stream).
+extern "C" int pann_groundtruth_device_result(pann_index* idx, const int32_t** d_ids, const float** d_dists, uint64_t* nq, uint32_t* k) {
+  if (!idx) PANN_FAIL("pann_groundtruth_device_result: null index");
+  if (idx->gt_nq == 0) PANN_FAIL("pann_groundtruth_device_result: no ground truth on the device");
+  if (d_ids) *d_ids = idx->gt_ids.as<int32_t>();
+  if (d_dists) *d_dists = idx->gt_dists.as<float>();
+  if (nq) *nq = idx->gt_nq;
+  if (k) *k = idx->gt_k;
+  return 0;
+}
+extern "C" int pann_groundtruth_merge_device(int device, uint32_t nshards, uint64_t nq, uint32_t k, const int32_t* d_ids, const float* d_dists,
+                                             int32_t* d_out_ids, float* d_out_dists, void* stream) {
+  if (!d_ids || !d_dists || !d_out_ids || !d_out_dists) PANN_FAIL("pann_groundtruth_merge_device: null argument");
+  if (nshards == 0 || k == 0 || (uint64_t)nshards * k > GT_SEL_CAP) PANN_FAIL("pann_groundtruth_merge: nshards * k must be in 1.." + std::to_string(GT_SEL_CAP));
+  if (nq == 0) return 0;
+  PANN_CUDA(cudaSetDevice(device));
+  pann_gt_merge_kernel<<<(unsigned)nq, GT_SEL_THREADS, 0, (cudaStream_t)stream>>>(d_ids, d_dists, nshards, nq, k, d_out_ids, d_out_dists);
+  PANN_CUDA(cudaGetLastError());
+  return 0;
+}
+

@@ -1,0 +1,137 @@
+"""Multi-GPU layer: one process per GPU (torch.distributed), only where the path shards.
+
+* search       — queries are independent (beamSearch.h:556): the index is replicated, the query batch is cut into
+                 `world` contiguous slices, every rank searches its slice; no data-path collective.  The slices are
+                 put back together with one all-gather of nq*k ids (400 KB at 10 000 x 10) when the caller wants the
+                 whole answer on every rank.
+* ground truth — the BASE rows are sharded (compute_groundtruth.cpp:22-60 scans all of them per query): every rank
+                 computes the top-k of all queries against its shard with global ids (id_offset), the ranks exchange
+                 the [nq, k] blocks with one all-gather (NCCL over NVLink on GPUs) and each merges the `world` sorted
+                 rows per query with K5 under the (dist, id) order.
+* Vamana build — does not shard (each batch reads the graph the previous batch wrote): one GPU, replicas only.
+
+The partition helpers are pure functions (tested on CPU with world_size-2 gloo groups); the compute callbacks default
+to the CUDA library and can be replaced by a checker in tests.
+"""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import check
+
+
+def shard_bounds(n, rank, world):
+    """Contiguous slice [lo, hi) of n items for `rank`: the first n % world ranks get one more."""
+    if not (0 <= rank < world):
+        raise ValueError("rank out of range")
+    q, r = divmod(int(n), int(world))
+    lo = rank * q + min(rank, r)
+    return lo, lo + q + (1 if rank < r else 0)
+
+
+def _dist():
+    import torch.distributed as dist
+    return dist
+
+
+def _world(group=None):
+    dist = _dist()
+    if not dist.is_available() or not dist.is_initialized():
+        return 0, 1
+    return dist.get_rank(group), dist.get_world_size(group)
+
+
+def _comm_device(group=None):
+    import torch
+    dist = _dist()
+    return torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(group) == "nccl" else torch.device("cpu")
+
+
+def all_gather_rows(local, counts, group=None):
+    """Concatenation over ranks of `local` (rows of rank r: counts[r]); ragged slices are padded for the collective."""
+    import torch
+    dist = _dist()
+    rank, world = _world(group)
+    if world == 1:
+        return local
+    dev = _comm_device(group)
+    m = max(counts)
+    pad = np.zeros((m,) + local.shape[1:], dtype=local.dtype)
+    pad[:local.shape[0]] = local
+    view = pad.view(np.int32) if pad.dtype == np.uint32 else pad   # torch has no uint32 collectives
+    t = torch.from_numpy(view).to(dev)
+    outs = [torch.empty_like(t) for _ in range(world)]
+    dist.all_gather(outs, t, group=group)
+    parts = [o.cpu().numpy().view(local.dtype)[:counts[r]] for r, o in enumerate(outs)]
+    return np.concatenate(parts, axis=0)
+
+
+def search_sharded(index, queries, gather=True, group=None, **qp):
+    """qsearchAll over a query batch cut across the ranks of `group`.  `index` is this rank's replica
+    (GraphIndex).  Returns (ids, dists, visited, cmps) for all queries when gather=True, else this rank's slice."""
+    rank, world = _world(group)
+    nq = queries.shape[0]
+    lo, hi = shard_bounds(nq, rank, world)
+    k = int(qp.get("k", 10))
+    if hi > lo:
+        ids, dists, vis, cmps = index.search(queries[lo:hi], **qp)
+    else:  # more ranks than queries
+        ids, dists = np.empty((0, k), np.uint32), np.empty((0, k), np.float32)
+        vis, cmps = np.empty(0, np.uint32), np.empty(0, np.uint32)
+    if not gather or world == 1:
+        return ids, dists, vis, cmps
+    counts = [shard_bounds(nq, r, world)[1] - shard_bounds(nq, r, world)[0] for r in range(world)]
+    return tuple(all_gather_rows(a, counts, group) for a in (ids, dists, vis, cmps))
+
+
+class _DevView:
+    """a device pointer as a __cuda_array_interface__ object (read by torch.as_tensor without a copy)"""
+
+    def __init__(self, ptr, shape, typestr):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+def groundtruth_sharded(index, queries=None, k=100, base_offset=0, group=None, local_fn=None, merge_fn=None):
+    """compute_groundtruth with the base rows sharded over the ranks: `index` holds this rank's base shard whose
+    first row has global id `base_offset`.  Every rank returns the global (ids [nq,k] int32, dists [nq,k] float32).
+
+    Default path (GPU): local top-k stays on the device, NCCL all-gather of the [nq,k] id and distance blocks,
+    K5 merge on the device, one D2H copy of the result.  local_fn(queries, k, base_offset) -> (ids, dists) and
+    merge_fn(list_ids, list_dists) -> (ids, dists) replace the compute for host-logic tests."""
+    rank, world = _world(group)
+    if local_fn is not None or merge_fn is not None:
+        ids, dists = local_fn(queries, k, base_offset)
+        if world == 1:
+            return merge_fn([ids], [dists])
+        nq = ids.shape[0]
+        gi = all_gather_rows(ids, [nq] * world, group).reshape(world, nq, k)
+        gd = all_gather_rows(dists, [nq] * world, group).reshape(world, nq, k)
+        return merge_fn(list(gi), list(gd))
+    import torch
+    L = _lib.lib()
+    if queries is not None:
+        index.upload_queries(queries)
+    index.groundtruth_resident(k=k, id_offset=base_offset)
+    if world == 1:
+        return index.fetch_groundtruth()
+    dist = _dist()
+    if dist.get_backend(group) != "nccl":
+        raise RuntimeError("groundtruth_sharded: the GPU path needs an NCCL process group")
+    p_ids, p_d, nq, kk = C.c_void_p(), C.c_void_p(), C.c_uint64(), C.c_uint32()
+    check(L.pann_groundtruth_device_result(index._h, C.byref(p_ids), C.byref(p_d), C.byref(nq), C.byref(kk)))
+    nq = nq.value
+    dev = torch.device("cuda", torch.cuda.current_device())
+    loc_i = torch.as_tensor(_DevView(p_ids.value, (nq, k), "<i4"), device=dev)
+    loc_d = torch.as_tensor(_DevView(p_d.value, (nq, k), "<f4"), device=dev)
+    all_i = torch.empty((world, nq, k), dtype=torch.int32, device=dev)
+    all_d = torch.empty((world, nq, k), dtype=torch.float32, device=dev)
+    dist.all_gather_into_tensor(all_i, loc_i, group=group)
+    dist.all_gather_into_tensor(all_d, loc_d, group=group)
+    out_i = torch.empty((nq, k), dtype=torch.int32, device=dev)
+    out_d = torch.empty((nq, k), dtype=torch.float32, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    check(L.pann_groundtruth_merge_device(dev.index, C.c_uint32(world), C.c_uint64(nq), C.c_uint32(k), C.c_void_p(all_i.data_ptr()),
+                                          C.c_void_p(all_d.data_ptr()), C.c_void_p(out_i.data_ptr()), C.c_void_p(out_d.data_ptr()),
+                                          C.c_void_p(st)))
+    return out_i.cpu().numpy(), out_d.cpu().numpy()
