@@ -11,6 +11,8 @@
 //                          candidate buffer, bitonic shrink to the best k when the buffer fills and at chunk end.
 // Results are rows sorted by (distance, id).
 #include "pann_internal.h"
+#include "gt_mma.cuh"
+#include <algorithm>
 
 #define GT_TQ 64
 #define GT_TB 64
@@ -191,6 +193,66 @@ static void launch_dist(int metric, dim3 grid, cudaStream_t s, const uint8_t* ba
   else pann_gt_dist_kernel<DT, PANN_M_MIPS><<<grid, 256, 0, s>>>(base, b0, nbc, q, nq, stride, nwords, D, ldD);
 }
 
+// ---------------------------------------------------------------------------------------------
+// K4 v2 host side (gt_mma.cuh): TMA descriptors, chunk schedule, overflow fallback
+#include <cudaTypedefs.h>
+static PFN_cuTensorMapEncodeTiled_v12000 gt_encode_fn() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess && qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  }
+  return fn;
+}
+// rows of `stride` bytes seen as a 2-D byte tensor; boxes of 128 bytes x box_rows, 128-byte swizzle, zero fill outside
+static int gt_make_tmap(CUtensorMap* tm, const void* ptr, uint64_t rows, uint32_t stride, uint32_t box_rows) {
+  auto fn = gt_encode_fn();
+  if (!fn) PANN_FAIL("pann_groundtruth: cuTensorMapEncodeTiled is not available from this driver");
+  cuuint64_t dims[2] = {stride, rows};
+  cuuint64_t strides[1] = {stride};
+  cuuint32_t box[2] = {GTM_KB_BYTES, box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(tm, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<void*>(ptr), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) PANN_FAIL("pann_groundtruth: cuTensorMapEncodeTiled failed (" + std::to_string((int)r) + ")");
+  return 0;
+}
+
+template <int DT, int METRIC>
+static void gt_launch_shrink(pann_index* idx, cudaStream_t s, const uint8_t* d_q, uint32_t nq, uint32_t k, u64* state, const uint32_t* cand_ids,
+                             uint32_t* cand_cnt, const void* qnorm, const float* bnmax, void* thr, int* overflow) {
+  const size_t sm = 8ull * GTS_KEYS + idx->geom.stride;
+  cudaFuncSetAttribute(pann_gt_shrink_kernel<DT, METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
+  pann_gt_shrink_kernel<DT, METRIC><<<nq, 256, sm, s>>>(idx->points, idx->geom.stride, idx->geom.nch, d_q, k, state, cand_ids, cand_cnt, qnorm, bnmax, thr, overflow);
+}
+template <int DT, int METRIC>
+static void gt_launch_thr(cudaStream_t s, const u64* state, uint32_t nq, uint32_t k, const void* qnorm, const float* bnmax, void* thr) {
+  pann_gt_thr_kernel<DT, METRIC><<<(nq + 255) / 256, 256, 0, s>>>(state, nq, k, qnorm, bnmax, thr);
+}
+#define GT_DISPATCH(idx, CALL)                                                                              \
+  do {                                                                                                      \
+    const bool l2__ = (idx)->metric == PANN_M_L2;                                                           \
+    if ((idx)->dtype == PANN_DT_F32) { if (l2__) CALL(PANN_DT_F32, PANN_M_L2); else CALL(PANN_DT_F32, PANN_M_MIPS); } \
+    else if ((idx)->dtype == PANN_DT_U8) { if (l2__) CALL(PANN_DT_U8, PANN_M_L2); else CALL(PANN_DT_U8, PANN_M_MIPS); } \
+    else { if (l2__) CALL(PANN_DT_I8, PANN_M_L2); else CALL(PANN_DT_I8, PANN_M_MIPS); }                   \
+  } while (0)
+
+// v1 over base rows [lo, hi): distance chunks + select into `state`
+static void gt_v1_range(pann_index* idx, cudaStream_t s, const uint8_t* d_q, uint64_t nq, uint32_t k, u64* state, float* D, uint64_t cb,
+                        uint64_t lo, uint64_t hi) {
+  const uint32_t nwords = idx->geom.stride / 4;
+  for (uint64_t b0 = lo; b0 < hi; b0 += cb) {
+    const uint32_t nbc = (uint32_t)std::min<uint64_t>(cb, hi - b0);
+    dim3 grid((nbc + GT_TB - 1) / GT_TB, (unsigned)((nq + GT_TQ - 1) / GT_TQ));
+    if (idx->dtype == PANN_DT_F32) launch_dist<PANN_DT_F32>(idx->metric, grid, s, idx->points, b0, nbc, d_q, (uint32_t)nq, idx->geom.stride, nwords, D, (uint32_t)cb);
+    else if (idx->dtype == PANN_DT_U8) launch_dist<PANN_DT_U8>(idx->metric, grid, s, idx->points, b0, nbc, d_q, (uint32_t)nq, idx->geom.stride, nwords, D, (uint32_t)cb);
+    else launch_dist<PANN_DT_I8>(idx->metric, grid, s, idx->points, b0, nbc, d_q, (uint32_t)nq, idx->geom.stride, nwords, D, (uint32_t)cb);
+    pann_gt_select_kernel<<<(unsigned)nq, GT_SEL_THREADS, 0, s>>>(D, (uint32_t)cb, nbc, b0, k, state);
+    idx->last_launches += 2;
+  }
+}
 // ground truth of the device-resident query rows d_q against the index's base rows; results stay in idx->gt_*
 static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, int64_t id_offset) {
   if (k == 0 || k > GT_SEL_CAP / 2) PANN_FAIL("pann_groundtruth: k must be in 1.." + std::to_string(GT_SEL_CAP / 2));
@@ -199,35 +261,119 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
   if ((int64_t)idx->n + id_offset > (int64_t)INT32_MAX) PANN_FAIL("pann_groundtruth: ids do not fit the .ibin format's int32");
   cudaStream_t s = idx->stream;
   const uint64_t nb = idx->n;
-  // chunk of base rows whose distance rows fit ~1 GiB
+  const uint32_t stride = idx->geom.stride;
+  const bool isint = idx->dtype != PANN_DT_F32;
+
+  // ---- plan: tensor-core path (K4 v2) for everything after a seed chunk, CUDA-core path (v1) for the seed chunk,
+  //      for shapes the MMA kernel does not take, and for a chunk whose candidate lists overflowed
+  const uint32_t kb = (stride + GTM_KB_BYTES - 1) / GTM_KB_BYTES;
+  int nstages = (int)((220 * 1024 - (long long)kb * GTM_A_STAGE_BYTES) / GTM_B_STAGE_BYTES);
+  nstages = std::min(nstages, GTM_STAGES);
+  const uint64_t seed = std::max<uint64_t>(4096, ((4ull * k + GTM_N - 1) / GTM_N) * GTM_N);
+  const char* force_v1 = getenv("PANN_GT_V1");
+  bool use_mma = !(force_v1 && force_v1[0] == '1') && stride >= GTM_KB_BYTES && nstages >= 2 && nb >= 2 * seed && nq < (1ull << 31);
+  // growth of the MMA chunks: expected survivors of a chunk of c rows after s rows have been seen ~ k c / s
+  const double growth = std::min(8.0, 1.0 + (double)GTM_CAND_CAP / (3.0 * k));
+
+  // v1 distance chunk (~1 GiB for the whole job, only the seed rows when the MMA path runs)
   uint64_t cb = ((1ull << 28) / nq) / GT_TB * GT_TB;
   cb = std::max<uint64_t>(cb, 4096);
-  cb = std::min<uint64_t>(cb, (nb + GT_TB - 1) / GT_TB * GT_TB);
-  DevBuf D, state;
-  auto fail = [&]() { D.release(); state.release(); return 1; };
+  cb = std::min<uint64_t>(cb, ((use_mma ? seed : nb) + GT_TB - 1) / GT_TB * GT_TB);
+  DevBuf D, state, state_bak, bnorm, qnorm, thr, cand_ids, cand_cnt, misc;
+  auto fail = [&]() { D.release(); state.release(); state_bak.release(); bnorm.release(); qnorm.release(); thr.release(); cand_ids.release(); cand_cnt.release(); misc.release(); return 1; };
   if (D.reserve(4ull * nq * cb) || state.reserve(8ull * nq * k)) return fail();
   if (idx->gt_ids.reserve(4ull * nq * k) || idx->gt_dists.reserve(4ull * nq * k)) return fail();
+  const uint64_t nb_pad = (nb + GTM_N - 1) / GTM_N * GTM_N;
+  CUtensorMap tmQ, tmB;
+  if (use_mma) {
+    if (state_bak.reserve(8ull * nq * k) || bnorm.reserve(4ull * nb_pad) || qnorm.reserve(4ull * nq) || thr.reserve(4ull * nq) ||
+        cand_ids.reserve(4ull * nq * GTM_CAND_CAP) || cand_cnt.reserve(4ull * nq) || misc.reserve(16)) return fail();
+    if (gt_make_tmap(&tmQ, d_q, nq, stride, GTM_M) || gt_make_tmap(&tmB, idx->points, nb, stride, GTM_N)) return fail();
+  }
+  int* h_flag = nullptr;
+  if (use_mma && pann_pinned(idx, 64, (void**)&h_flag)) return fail();
   const uint64_t tot = nq * k;
   idx->last_launches = 0;
   cudaEventRecord(idx->ev0, s);
   pann_gt_init_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(state.as<u64>(), tot);
   idx->last_launches++;
-  const uint32_t nwords = idx->geom.stride / 4;
-  for (uint64_t b0 = 0; b0 < nb; b0 += cb) {
-    const uint32_t nbc = (uint32_t)std::min<uint64_t>(cb, nb - b0);
-    dim3 grid((nbc + GT_TB - 1) / GT_TB, (unsigned)((nq + GT_TQ - 1) / GT_TQ));
-    if (idx->dtype == PANN_DT_F32) launch_dist<PANN_DT_F32>(idx->metric, grid, s, idx->points, b0, nbc, d_q, (uint32_t)nq, idx->geom.stride, nwords, D.as<float>(), (uint32_t)cb);
-    else if (idx->dtype == PANN_DT_U8) launch_dist<PANN_DT_U8>(idx->metric, grid, s, idx->points, b0, nbc, d_q, (uint32_t)nq, idx->geom.stride, nwords, D.as<float>(), (uint32_t)cb);
-    else launch_dist<PANN_DT_I8>(idx->metric, grid, s, idx->points, b0, nbc, d_q, (uint32_t)nq, idx->geom.stride, nwords, D.as<float>(), (uint32_t)cb);
-    pann_gt_select_kernel<<<(unsigned)nq, GT_SEL_THREADS, 0, s>>>(D.as<float>(), (uint32_t)cb, nbc, b0, k, state.as<u64>());
+  if (!use_mma) {
+    gt_v1_range(idx, s, d_q, nq, k, state.as<u64>(), D.as<float>(), cb, 0, nb);
+  } else {
+    float* bnmax = misc.as<float>();
+    int* overflow = misc.as<int>() + 1;
+    cudaMemsetAsync(misc.p, 0, 16, s);
+    cudaMemsetAsync(cand_cnt.p, 0, 4ull * nq, s);
+    const int store_zero = idx->metric == PANN_M_MIPS ? 1 : 0;
+    if (idx->dtype == PANN_DT_F32) {
+      pann_gt_norm_kernel<PANN_DT_F32><<<(unsigned)((nb_pad + 255) / 256), 256, 0, s>>>(idx->points, nb, nb_pad, stride, idx->geom.nch, bnorm.p, store_zero, bnmax);
+      pann_gt_norm_kernel<PANN_DT_F32><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>(d_q, nq, nq, stride, idx->geom.nch, qnorm.p, 0, nullptr);
+    } else if (idx->dtype == PANN_DT_U8) {
+      pann_gt_norm_kernel<PANN_DT_U8><<<(unsigned)((nb_pad + 255) / 256), 256, 0, s>>>(idx->points, nb, nb_pad, stride, idx->geom.nch, bnorm.p, store_zero, nullptr);
+      pann_gt_norm_kernel<PANN_DT_U8><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>(d_q, nq, nq, stride, idx->geom.nch, qnorm.p, 0, nullptr);
+    } else {
+      pann_gt_norm_kernel<PANN_DT_I8><<<(unsigned)((nb_pad + 255) / 256), 256, 0, s>>>(idx->points, nb, nb_pad, stride, idx->geom.nch, bnorm.p, store_zero, nullptr);
+      pann_gt_norm_kernel<PANN_DT_I8><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>(d_q, nq, nq, stride, idx->geom.nch, qnorm.p, 0, nullptr);
+    }
     idx->last_launches += 2;
+    // seed: exact top-k of the first rows on the CUDA cores, then the first thresholds
+    gt_v1_range(idx, s, d_q, nq, k, state.as<u64>(), D.as<float>(), cb, 0, seed);
+#define GT_THR(DT, M) gt_launch_thr<DT, M>(s, state.as<u64>(), (uint32_t)nq, k, qnorm.p, bnmax, thr.p)
+    GT_DISPATCH(idx, GT_THR);
+    idx->last_launches++;
+    // instruction descriptor: D = s32 / f32, A and B = u8 / s8 / tf32, K-major both, N = 256, M = 128
+    uint32_t idesc = 0;
+    if (isint) { const uint32_t f = idx->dtype == PANN_DT_I8 ? 1u : 0u; idesc = (2u << 4) | (f << 7) | (f << 10); }
+    else idesc = (1u << 4) | (2u << 7) | (2u << 10);
+    idesc |= (uint32_t)(GTM_N >> 3) << 17;
+    idesc |= (uint32_t)(GTM_M >> 4) << 24;
+    const size_t smem = 1024 + (size_t)kb * GTM_A_STAGE_BYTES + (size_t)nstages * GTM_B_STAGE_BYTES + 256;
+    const void* kfn = isint ? (const void*)pann_gt_mma_kernel<true> : (const void*)pann_gt_mma_kernel<false>;
+    if (cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
+      fail(); PANN_FAIL("pann_groundtruth: cannot reserve shared memory for the MMA kernel");
+    }
+    const uint32_t nqb = (uint32_t)((nq + GTM_M - 1) / GTM_M);
+    uint64_t lo = seed;
+    while (lo < nb) {
+      uint64_t c = (uint64_t)((growth - 1.0) * (double)lo);
+      c = std::max<uint64_t>(c / GTM_N * GTM_N, GTM_N);
+      const uint64_t hi = std::min<uint64_t>(nb, lo + c);
+      const uint64_t tiles = (hi - lo + GTM_N - 1) / GTM_N;
+      uint64_t S = std::max<uint64_t>(1, std::min<uint64_t>(tiles, (4ull * idx->sms + nqb - 1) / nqb));
+      const uint32_t tps = (uint32_t)((tiles + S - 1) / S);
+      S = (tiles + tps - 1) / tps;
+      cudaMemcpyAsync(state_bak.p, state.p, 8ull * nq * k, cudaMemcpyDeviceToDevice, s);
+      GtMmaArgs A;
+      A.nq = (uint32_t)nq; A.kb = kb; A.nstages = (uint32_t)nstages; A.row_lo = lo; A.row_hi = hi; A.tiles_per_seg = tps;
+      A.bnorm = bnorm.p; A.thr = thr.p; A.cand_ids = cand_ids.as<uint32_t>(); A.cand_cnt = cand_cnt.as<uint32_t>();
+      if (isint) pann_gt_mma_kernel<true><<<dim3(nqb, (unsigned)S), GTM_THREADS, smem, s>>>(tmQ, tmB, A, idesc);
+      else pann_gt_mma_kernel<false><<<dim3(nqb, (unsigned)S), GTM_THREADS, smem, s>>>(tmQ, tmB, A, idesc);
+#define GT_SHRINK(DT, M) gt_launch_shrink<DT, M>(idx, s, d_q, (uint32_t)nq, k, state.as<u64>(), cand_ids.as<uint32_t>(), cand_cnt.as<uint32_t>(), qnorm.p, bnmax, thr.p, overflow)
+      GT_DISPATCH(idx, GT_SHRINK);
+      idx->last_launches += 2;
+      cudaMemcpyAsync(h_flag, overflow, sizeof(int), cudaMemcpyDeviceToHost, s);
+      cudaError_t e = cudaStreamSynchronize(s);
+      if (e != cudaSuccess) { fail(); PANN_FAIL(std::string("pann_groundtruth (MMA path): ") + cudaGetErrorString(e)); }
+      if (*h_flag) {
+        // some query passed more than GTM_CAND_CAP rows of this chunk (rows ordered so that the threshold stays loose):
+        // take the chunk again on the CUDA cores from the saved state
+        cudaMemcpyAsync(state.p, state_bak.p, 8ull * nq * k, cudaMemcpyDeviceToDevice, s);
+        cudaMemsetAsync(overflow, 0, sizeof(int), s);
+        cudaMemsetAsync(cand_cnt.p, 0, 4ull * nq, s);
+        gt_v1_range(idx, s, d_q, nq, k, state.as<u64>(), D.as<float>(), cb, lo, hi);
+        GT_DISPATCH(idx, GT_THR);
+        idx->last_launches++;
+        idx->gt_fallback_chunks++;
+      }
+      lo = hi;
+    }
   }
   pann_gt_finish_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(state.as<u64>(), tot, id_offset, idx->gt_ids.as<int32_t>(), idx->gt_dists.as<float>());
   idx->last_launches++;
   cudaEventRecord(idx->ev1, s);
   cudaError_t e = cudaEventSynchronize(idx->ev1);
   if (e == cudaSuccess) e = cudaGetLastError();
-  D.release(); state.release();
+  fail();
   if (e != cudaSuccess) PANN_FAIL(std::string("pann_groundtruth: ") + cudaGetErrorString(e));
   cudaEventElapsedTime(&idx->last_ms, idx->ev0, idx->ev1);
   idx->gt_nq = nq; idx->gt_k = k;

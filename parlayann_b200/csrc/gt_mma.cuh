@@ -1,0 +1,357 @@
+// gt_mma.cuh — K4 v2: brute-force ground truth as a tcgen05/TMA GEMM with a fused per-row threshold filter.
+//
+// compute_groundtruth (data_tools/compute_groundtruth.cpp:22-60) scans every base row per query.  Here a CTA owns 128
+// queries (the A operand, M = 128, loaded once by TMA) and streams 256-row tiles of the base set (B operand, N = 256)
+// through a 4-stage TMA pipeline; one elected thread issues tcgen05.mma (kind::i8 for uint8/int8 rows — exact int32 dot
+// products; kind::tf32 for float rows) into a double-buffered 2 x 256-column TMEM accumulator; eight epilogue warps read
+// the accumulators back with tcgen05.ld and keep only the rows that can still enter the query's top-k:
+//      |b|^2 - 2 q.b  <=  T_q          (L2;  T_q = tau_q + margin_q - |q|^2,  tau_q = current k-th distance)
+//            - 2 q.b  <=  T_q          (MIPS; T_q = 2 (tau_q + margin_q))
+// Survivors are appended (row id only) to a per-query candidate list.  pann_gt_shrink_kernel then recomputes the
+// EXACT distance of every candidate with the reference's own operation order (DistAcc, as K1), merges with the
+// running top-k and tightens tau_q.  The tensor-core pass therefore only has to be a superset filter: for 8-bit rows it
+// is exact (margin 0), for float rows margin_q bounds the tf32 truncation error (2^-10 per operand), so the final
+// result is bit-identical to the CUDA-core path and to the reference.  No distance matrix ever goes to HBM.
+#pragma once
+#include <cuda.h>
+#include <type_traits>
+
+#include "pann_internal.h"
+
+#define GTM_M 128          // queries per CTA (UMMA M)
+#define GTM_N 256          // base rows per tile (UMMA N)
+#define GTM_KB_BYTES 128   // bytes of K per smem stage = one 128B swizzle atom
+#define GTM_STAGES 4
+#define GTM_THREADS 320    // warp 0: TMA producer, warp 1: MMA issuer, warps 2-9: epilogue
+#define GTM_CAND_CAP 4096  // candidate ids per query per chunk
+#define GTM_A_STAGE_BYTES (GTM_M * GTM_KB_BYTES)   // 16 KB
+#define GTM_B_STAGE_BYTES (GTM_N * GTM_KB_BYTES)   // 32 KB
+#define GTS_KEYS 8192       // shrink kernel: key slots in shared memory (>= k + GTM_CAND_CAP, k <= 1024)
+
+// ---------------------------------------------------------------------------------------------------------------
+// PTX wrappers (sm_100a)
+__device__ __forceinline__ uint32_t gtm_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void gtm_mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(gtm_smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void gtm_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(gtm_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void gtm_mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(gtm_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void gtm_mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(gtm_smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void gtm_tma_load_2d(void* smem_dst, const CUtensorMap* tm, int c0, int c1, uint64_t* bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(gtm_smem_u32(smem_dst)),
+      "l"((uint64_t)tm), "r"(c0), "r"(c1), "r"(gtm_smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void gtm_tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void gtm_tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void gtm_tcgen05_commit(uint64_t* bar) {  // implies fence::before_thread_sync
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(gtm_smem_u32(bar)) : "memory");
+}
+// K-major operand tile in shared memory, 128-byte swizzle: rows of 128 bytes, 8-row groups 1024 bytes apart
+__device__ __forceinline__ uint64_t gtm_smem_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr & 0x3ffff) >> 4);        // start address, bits [0,14)
+  d |= (uint64_t)1 << 16;                             // leading byte offset (unused for swizzled K-major), bits [16,30)
+  d |= (uint64_t)(1024 >> 4) << 32;                   // stride byte offset = 1024, bits [32,46)
+  d |= (uint64_t)1 << 46;                             // descriptor version (sm_100), bits [46,48)
+  d |= (uint64_t)2 << 61;                             // SWIZZLE_128B, bits [61,64)
+  return d;
+}
+template <bool ISINT>
+__device__ __forceinline__ void gtm_mma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  const uint32_t z = 0;
+  if constexpr (ISINT) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(z), "r"(z), "r"(z), "r"(z)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(z), "r"(z), "r"(z), "r"(z)
+        : "memory");
+  }
+}
+// 32 consecutive accumulator columns of this thread's TMEM lane
+__device__ __forceinline__ void gtm_tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]),
+        "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]),
+        "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+        "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr));
+}
+__device__ __forceinline__ void gtm_tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// ---------------------------------------------------------------------------------------------------------------
+struct GtMmaArgs {
+  uint32_t nq, kb, nstages;    // queries; 128-byte k-blocks per row; B pipeline depth (<= GTM_STAGES)
+  uint64_t row_lo, row_hi;     // base rows of this chunk; row_lo is a multiple of GTM_N
+  uint32_t tiles_per_seg;      // blockIdx.y walks tiles [y * tiles_per_seg, (y+1) * tiles_per_seg) of the chunk
+  const void* bnorm;           // per base row: |b|^2 (L2) or 0 (MIPS); float or int32; padded with +inf / 2^30 to a tile multiple
+  const void* thr;             // per query: T_q (float or int32)
+  uint32_t* cand_ids;          // [nq][GTM_CAND_CAP]
+  uint32_t* cand_cnt;          // [nq]
+};
+
+template <bool ISINT>
+__global__ void __launch_bounds__(GTM_THREADS, 1)
+pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmB, const GtMmaArgs A, const uint32_t idesc) {
+  extern __shared__ __align__(1024) uint8_t gtm_smem_raw[];
+  // carve (1024-byte aligned tiles): A[kb] | B[STAGES] | barriers | tmem base
+  uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(gtm_smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* sA = base;
+  uint8_t* sB = sA + (size_t)A.kb * GTM_A_STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sB + (size_t)A.nstages * GTM_B_STAGE_BYTES);
+  uint64_t* full = bars;                       // [STAGES]  TMA -> MMA
+  uint64_t* empty = bars + GTM_STAGES;         // [STAGES]  MMA -> TMA
+  uint64_t* a_full = bars + 2 * GTM_STAGES;    // queries landed
+  uint64_t* t_full = a_full + 1;               // [2] accumulator ready (MMA -> epilogue)
+  uint64_t* t_empty = t_full + 2;              // [2] accumulator drained (epilogue -> MMA)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+
+  const int widx = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t q0 = blockIdx.x * GTM_M;
+  const uint64_t chunk_tiles = (A.row_hi - A.row_lo + GTM_N - 1) / GTM_N;
+  const uint64_t t_lo = (uint64_t)blockIdx.y * A.tiles_per_seg;
+  const uint64_t t_hi = min(chunk_tiles, t_lo + A.tiles_per_seg);
+  const uint32_t ntiles = t_lo < t_hi ? (uint32_t)(t_hi - t_lo) : 0u;
+  const uint64_t seg_row0 = A.row_lo + t_lo * GTM_N;
+
+  if (widx == 0 && lane == 0) {
+    for (int i = 0; i < GTM_STAGES; i++) { gtm_mbar_init(&full[i], 1); gtm_mbar_init(&empty[i], 1); }
+    gtm_mbar_init(a_full, 1);
+    for (int i = 0; i < 2; i++) { gtm_mbar_init(&t_full[i], 1); gtm_mbar_init(&t_empty[i], 8); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (widx == 1) {  // TMEM: all 512 columns (two 256-column accumulators); this warp also frees them
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(gtm_smem_u32(tmem_slot)) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  gtm_tcgen05_fence_before();
+  __syncthreads();
+  gtm_tcgen05_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (widx == 0) {
+    // ===== TMA producer =====
+    if (lane == 0 && ntiles > 0) {
+      gtm_mbar_expect_tx(a_full, A.kb * GTM_A_STAGE_BYTES);
+      for (uint32_t j = 0; j < A.kb; j++) gtm_tma_load_2d(sA + (size_t)j * GTM_A_STAGE_BYTES, &tmQ, (int)(j * GTM_KB_BYTES), (int)q0, a_full);
+      uint32_t stage = 0, phase = 0;
+      for (uint32_t t = 0; t < ntiles; t++) {
+        const int row0 = (int)(seg_row0 + (uint64_t)t * GTM_N);
+        for (uint32_t j = 0; j < A.kb; j++) {
+          gtm_mbar_wait(&empty[stage], phase ^ 1);
+          gtm_mbar_expect_tx(&full[stage], GTM_B_STAGE_BYTES);
+          gtm_tma_load_2d(sB + (size_t)stage * GTM_B_STAGE_BYTES, &tmB, (int)(j * GTM_KB_BYTES), row0, &full[stage]);
+          if (++stage == A.nstages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (widx == 1) {
+    // ===== MMA issuer (one thread) =====
+    if (lane == 0 && ntiles > 0) {
+      gtm_mbar_wait(a_full, 0);
+      uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
+      for (uint32_t t = 0; t < ntiles; t++) {
+        gtm_mbar_wait(&t_empty[as], aphase ^ 1);
+        gtm_tcgen05_fence_after();
+        const uint32_t tmem_d = tmem_base + as * GTM_N;
+        for (uint32_t j = 0; j < A.kb; j++) {
+          gtm_mbar_wait(&full[stage], phase);
+          gtm_tcgen05_fence_after();
+          const uint64_t adesc = gtm_smem_desc(gtm_smem_u32(sA + (size_t)j * GTM_A_STAGE_BYTES));
+          const uint64_t bdesc = gtm_smem_desc(gtm_smem_u32(sB + (size_t)stage * GTM_B_STAGE_BYTES));
+#pragma unroll
+          for (uint32_t k4 = 0; k4 < 4; k4++)  // UMMA K = 32 bytes: advance the start address inside the swizzle atom
+            gtm_mma<ISINT>(tmem_d, adesc + 2 * k4, bdesc + 2 * k4, idesc, (j | k4) != 0 ? 1u : 0u);
+          gtm_tcgen05_commit(&empty[stage]);
+          if (++stage == A.nstages) { stage = 0; phase ^= 1; }
+        }
+        gtm_tcgen05_commit(&t_full[as]);
+        as ^= 1;
+        if (as == 0) aphase ^= 1;
+      }
+    }
+  } else {
+    // ===== epilogue: 8 warps; warp w reads TMEM lanes 32*(w%4).., column half (w-2)/4 =====
+    const uint32_t quad = widx & 3, half = (uint32_t)(widx - 2) >> 2;
+    const uint32_t q = q0 + quad * 32 + lane;
+    const bool qok = q < A.nq;
+    typedef typename std::conditional<ISINT, int, float>::type acc_t;
+    acc_t T;
+    if constexpr (ISINT) T = qok ? reinterpret_cast<const int*>(A.thr)[q] : INT_MIN;
+    else T = qok ? reinterpret_cast<const float*>(A.thr)[q] : -INFINITY;
+    uint32_t* my_ids = A.cand_ids + (size_t)(qok ? q : 0) * GTM_CAND_CAP;
+    uint32_t* my_cnt = A.cand_cnt + (qok ? q : 0);
+    uint32_t as = 0, aphase = 0;
+    for (uint32_t t = 0; t < ntiles; t++) {
+      const uint64_t row0 = seg_row0 + (uint64_t)t * GTM_N;
+      gtm_mbar_wait(&t_full[as], aphase);
+      gtm_tcgen05_fence_after();
+#pragma unroll 1
+      for (uint32_t c = 0; c < 4; c++) {
+        const uint32_t col0 = half * 128 + c * 32;
+        uint32_t v[32];
+        gtm_tmem_ld32(tmem_base + ((quad * 32) << 16) + as * GTM_N + col0, v);
+        uint4 bn[8];
+        const uint4* bnp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint32_t*>(A.bnorm) + row0 + col0);
+#pragma unroll
+        for (int i = 0; i < 8; i++) bn[i] = __ldg(bnp + i);
+        gtm_tmem_ld_wait();
+        const uint32_t* bnw = reinterpret_cast<const uint32_t*>(bn);
+#pragma unroll
+        for (int j = 0; j < 32; j++) {
+          bool pass;
+          if constexpr (ISINT) pass = ((int)bnw[j] - 2 * (int)v[j]) <= T;
+          else pass = fmaf(-2.0f, __uint_as_float(v[j]), __uint_as_float(bnw[j])) <= T;
+          if (pass) {
+            const uint32_t pos = atomicAdd(my_cnt, 1u);
+            if (pos < GTM_CAND_CAP) my_ids[pos] = (uint32_t)(row0 + col0 + j);
+          }
+        }
+      }
+      gtm_tcgen05_fence_before();
+      __syncwarp();
+      if (lane == 0) gtm_mbar_arrive(&t_empty[as]);
+      as ^= 1;
+      if (as == 0) aphase ^= 1;
+    }
+  }
+  gtm_tcgen05_fence_before();
+  __syncthreads();
+  if (widx == 1) {
+    gtm_tcgen05_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem_base) : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// norms: |x|^2 per row (int32 exact for 8-bit rows, fp32 for floats).  store_zero: MIPS keeps 0 in the table (the test
+// has no |b|^2 term) but still reports the maximum norm for the float margin.  Rows n..n_pad get the pad value that
+// fails every test (+inf / 2^30).
+template <int DT>
+__global__ void pann_gt_norm_kernel(const uint8_t* __restrict__ rows, uint64_t n, uint64_t n_pad, uint32_t stride, uint32_t nch,
+                                    void* __restrict__ out, int store_zero, float* __restrict__ maxnorm) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_pad) return;
+  if (i >= n) {
+    if constexpr (DT == PANN_DT_F32) reinterpret_cast<float*>(out)[i] = INFINITY;
+    else reinterpret_cast<int*>(out)[i] = 1 << 30;
+    return;
+  }
+  const uint4* r = reinterpret_cast<const uint4*>(rows + i * stride);
+  if constexpr (DT == PANN_DT_F32) {
+    float s = 0.f;
+    for (uint32_t c = 0; c < nch; c++) {
+      const uint4 v = __ldg(r + c);
+      const float a = __uint_as_float(v.x), b = __uint_as_float(v.y), cc = __uint_as_float(v.z), d = __uint_as_float(v.w);
+      s += a * a + b * b + cc * cc + d * d;
+    }
+    reinterpret_cast<float*>(out)[i] = store_zero ? 0.f : s;
+    if (maxnorm) atomicMax(reinterpret_cast<int*>(maxnorm), __float_as_int(s));  // s >= 0: int order = float order
+  } else {
+    int s = 0;
+    for (uint32_t c = 0; c < nch; c++) {
+      const uint4 v = __ldg(r + c);
+      if constexpr (DT == PANN_DT_U8) { s = __dp4a(v.x, v.x, (unsigned)s); s = __dp4a(v.y, v.y, (unsigned)s); s = __dp4a(v.z, v.z, (unsigned)s); s = __dp4a(v.w, v.w, (unsigned)s); }
+      else { s = __dp4a((int)v.x, (int)v.x, s); s = __dp4a((int)v.y, (int)v.y, s); s = __dp4a((int)v.z, (int)v.z, s); s = __dp4a((int)v.w, (int)v.w, s); }
+    }
+    reinterpret_cast<int*>(out)[i] = store_zero ? 0 : s;
+  }
+}
+
+// T_q from the current k-th key of query q (see the header comment); conservative by construction
+template <int DT, int METRIC>
+__device__ __forceinline__ void gt_write_thr(u64 kth, uint32_t q, const void* qnorm, const float* bnmax, void* thr) {
+  if constexpr (DT == PANN_DT_F32) {
+    float T = 3.0e38f;
+    if (kth != ~0ull) {
+      const double tau = (double)pann_key_dist(kth);
+      const double qn = (double)reinterpret_cast<const float*>(qnorm)[q], bm = (double)*bnmax;
+      const double margin = 0.0078125 * sqrt(qn * bm) + 1e-4 * (qn + bm) + 1e-30;
+      const double t = (METRIC == PANN_M_L2) ? (tau + margin - qn) : 2.0 * (tau + margin);
+      T = __double2float_ru(t);
+    }
+    reinterpret_cast<float*>(thr)[q] = T;
+  } else {
+    int T = 1 << 29;
+    if (kth != ~0ull) {
+      const float tau = pann_key_dist(kth);
+      const int ti = (int)tau + (fabsf(tau) >= 16777216.f ? 64 : 0);  // distances are (float)(int): exact below 2^24
+      T = (METRIC == PANN_M_L2) ? ti - reinterpret_cast<const int*>(qnorm)[q] : 2 * ti;
+    }
+    reinterpret_cast<int*>(thr)[q] = T;
+  }
+}
+template <int DT, int METRIC>
+__global__ void pann_gt_thr_kernel(const u64* __restrict__ state, uint32_t nq, uint32_t k, const void* qnorm, const float* bnmax, void* thr) {
+  const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q < nq) gt_write_thr<DT, METRIC>(state[(uint64_t)q * k + k - 1], q, qnorm, bnmax, thr);
+}
+
+// One CTA per query: exact distances of the candidates (reference operation order), merge with the running top-k
+// (bitonic sort of k + candidates keys in shared memory), new threshold.  A list that overflowed sets *overflow.
+__device__ __forceinline__ void gtm_bitonic(u64* a, int m) {
+  for (int k = 2; k <= m; k <<= 1)
+    for (int j = k >> 1; j > 0; j >>= 1) {
+      for (int t = threadIdx.x; t < m; t += blockDim.x) {
+        const int p = t ^ j;
+        if (p > t) {
+          const u64 x = a[t], y = a[p];
+          const bool up = (t & k) == 0;
+          if ((x > y) == up) { a[t] = y; a[p] = x; }
+        }
+      }
+      __syncthreads();
+    }
+}
+template <int DT, int METRIC>
+__global__ void __launch_bounds__(256) pann_gt_shrink_kernel(const uint8_t* __restrict__ points, uint32_t stride, uint32_t nch,
+                                                             const uint8_t* __restrict__ queries, uint32_t k, u64* __restrict__ state,
+                                                             const uint32_t* __restrict__ cand_ids, uint32_t* __restrict__ cand_cnt,
+                                                             const void* qnorm, const float* bnmax, void* thr, int* overflow) {
+  extern __shared__ __align__(16) uint8_t gts_smem[];
+  u64* buf = reinterpret_cast<u64*>(gts_smem);                       // up to k + GTM_CAND_CAP keys, padded to a power of two
+  const uint32_t q = blockIdx.x;
+  const uint32_t cnt = cand_cnt[q];
+  __syncthreads();
+  if (threadIdx.x == 0) cand_cnt[q] = 0;
+  if (cnt > GTM_CAND_CAP) { if (threadIdx.x == 0) atomicOr(overflow, 1); return; }
+  if (cnt == 0) return;                                              // nothing can have changed
+  int m = 2; while (m < (int)(k + cnt)) m <<= 1;
+  uint4* qs = reinterpret_cast<uint4*>(gts_smem + 8ull * GTS_KEYS);
+  for (uint32_t c = threadIdx.x; c < nch; c += blockDim.x) qs[c] = __ldg(reinterpret_cast<const uint4*>(queries + (uint64_t)q * stride) + c);
+  for (int i = threadIdx.x; i < m; i += blockDim.x) buf[i] = i < (int)k ? state[(uint64_t)q * k + i] : ~0ull;
+  __syncthreads();
+  for (uint32_t i = threadIdx.x; i < cnt; i += blockDim.x) {
+    const uint32_t id = cand_ids[(uint64_t)q * GTM_CAND_CAP + i];
+    const uint4* row = reinterpret_cast<const uint4*>(points + (uint64_t)id * stride);
+    DistAcc<DT, METRIC> acc;
+    for (uint32_t c = 0; c < nch; c++) acc.add(__ldg(row + c), qs[c]);
+    buf[k + i] = pann_key(acc.result(), id);
+  }
+  __syncthreads();
+  gtm_bitonic(buf, m);
+  for (int i = threadIdx.x; i < (int)k; i += blockDim.x) state[(uint64_t)q * k + i] = buf[i];
+  if (threadIdx.x == 0) gt_write_thr<DT, METRIC>(buf[k - 1], q, qnorm, bnmax, thr);
+}

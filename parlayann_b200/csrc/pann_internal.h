@@ -48,6 +48,7 @@ struct pann_index {
   void* pinned = nullptr; size_t pinned_cap = 0;
   // ground truth results (resident)
   DevBuf gt_ids, gt_dists; uint64_t gt_nq = 0; uint32_t gt_k = 0;
+  int gt_fallback_chunks = 0;  // MMA chunks retaken on the CUDA cores (candidate-list overflow), cumulative
 };
 
 struct SearchOutputs {  // device pointers (any may be null)
