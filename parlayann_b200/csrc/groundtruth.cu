@@ -222,10 +222,10 @@ static int gt_make_tmap(CUtensorMap* tm, const void* ptr, uint64_t rows, uint32_
 
 template <int DT, int METRIC>
 static void gt_launch_shrink(pann_index* idx, cudaStream_t s, const uint8_t* d_q, uint32_t nq, uint32_t k, u64* state, const uint32_t* cand_ids,
-                             uint32_t* cand_cnt, const void* qnorm, const float* bnmax, void* thr, int* overflow) {
+                             uint32_t* cand_cnt, uint32_t nsub, uint32_t subcap, const void* qnorm, const float* bnmax, void* thr, int* overflow) {
   const size_t sm = 8ull * GTS_KEYS + idx->geom.stride;
   cudaFuncSetAttribute(pann_gt_shrink_kernel<DT, METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-  pann_gt_shrink_kernel<DT, METRIC><<<nq, 256, sm, s>>>(idx->points, idx->geom.stride, idx->geom.nch, d_q, k, state, cand_ids, cand_cnt, qnorm, bnmax, thr, overflow);
+  pann_gt_shrink_kernel<DT, METRIC><<<nq, 256, sm, s>>>(idx->points, idx->geom.stride, idx->geom.nch, d_q, k, state, cand_ids, cand_cnt, nsub, subcap, qnorm, bnmax, thr, overflow);
 }
 template <int DT, int METRIC>
 static void gt_launch_thr(cudaStream_t s, const u64* state, uint32_t nq, uint32_t k, const void* qnorm, const float* bnmax, void* thr) {
@@ -267,13 +267,15 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
   // ---- plan: tensor-core path (K4 v2) for everything after a seed chunk, CUDA-core path (v1) for the seed chunk,
   //      for shapes the MMA kernel does not take, and for a chunk whose candidate lists overflowed
   const uint32_t kb = (stride + GTM_KB_BYTES - 1) / GTM_KB_BYTES;
-  int nstages = (int)((220 * 1024 - (long long)kb * GTM_A_STAGE_BYTES) / GTM_B_STAGE_BYTES);
+  int nstages = (int)((212 * 1024 - (long long)kb * GTM_A_STAGE_BYTES) / GTM_B_STAGE_BYTES);
   nstages = std::min(nstages, GTM_STAGES);
-  const uint64_t seed = std::max<uint64_t>(4096, ((4ull * k + GTM_N - 1) / GTM_N) * GTM_N);
+  uint64_t seed = std::max<uint64_t>(512, ((2ull * k + GTM_N - 1) / GTM_N) * GTM_N);  // sample that sets the first thresholds
+  if (const char* e = getenv("PANN_GT_SEED")) seed = std::max<uint64_t>(((uint64_t)atoll(e) + GTM_N - 1) / GTM_N * GTM_N, ((2ull * k + GTM_N - 1) / GTM_N) * GTM_N);
   const char* force_v1 = getenv("PANN_GT_V1");
   bool use_mma = !(force_v1 && force_v1[0] == '1') && stride >= GTM_KB_BYTES && nstages >= 2 && nb >= 2 * seed && nq < (1ull << 31);
   // growth of the MMA chunks: expected survivors of a chunk of c rows after s rows have been seen ~ k c / s
-  const double growth = std::min(8.0, 1.0 + (double)GTM_CAND_CAP / (3.0 * k));
+  double growth = std::min(4.0, 1.0 + (double)GTM_CAND_CAP / (3.0 * k));
+  if (const char* e = getenv("PANN_GT_GROWTH")) growth = std::max(1.25, std::min(growth, atof(e)));
 
   // v1 distance chunk (~1 GiB for the whole job, only the seed rows when the MMA path runs)
   uint64_t cb = ((1ull << 28) / nq) / GT_TB * GT_TB;
@@ -287,7 +289,7 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
   CUtensorMap tmQ, tmB;
   if (use_mma) {
     if (state_bak.reserve(8ull * nq * k) || bnorm.reserve(4ull * nb_pad) || qnorm.reserve(4ull * nq) || thr.reserve(4ull * nq) ||
-        cand_ids.reserve(4ull * nq * GTM_CAND_CAP) || cand_cnt.reserve(4ull * nq) || misc.reserve(16)) return fail();
+        cand_ids.reserve(4ull * nq * GTM_CAND_CAP) || cand_cnt.reserve(4ull * nq * GTM_MAX_SUB) || misc.reserve(16)) return fail();
     if (gt_make_tmap(&tmQ, d_q, nq, stride, GTM_M) || gt_make_tmap(&tmB, idx->points, nb, stride, GTM_N)) return fail();
   }
   int* h_flag = nullptr;
@@ -303,7 +305,7 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
     float* bnmax = misc.as<float>();
     int* overflow = misc.as<int>() + 1;
     cudaMemsetAsync(misc.p, 0, 16, s);
-    cudaMemsetAsync(cand_cnt.p, 0, 4ull * nq, s);
+    cudaMemsetAsync(cand_cnt.p, 0, 4ull * nq * GTM_MAX_SUB, s);
     const int store_zero = idx->metric == PANN_M_MIPS ? 1 : 0;
     if (idx->dtype == PANN_DT_F32) {
       pann_gt_norm_kernel<PANN_DT_F32><<<(unsigned)((nb_pad + 255) / 256), 256, 0, s>>>(idx->points, nb, nb_pad, stride, idx->geom.nch, bnorm.p, store_zero, bnmax);
@@ -316,39 +318,42 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
       pann_gt_norm_kernel<PANN_DT_I8><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>(d_q, nq, nq, stride, idx->geom.nch, qnorm.p, 0, nullptr);
     }
     idx->last_launches += 2;
-    // seed: exact top-k of the first rows on the CUDA cores, then the first thresholds
+    // seed: the k-th distance within the first `seed` rows (CUDA cores) bounds the final k-th distance from above; it
+    // only sets the first thresholds — the state is cleared again and the MMA pass starts at row 0
     gt_v1_range(idx, s, d_q, nq, k, state.as<u64>(), D.as<float>(), cb, 0, seed);
 #define GT_THR(DT, M) gt_launch_thr<DT, M>(s, state.as<u64>(), (uint32_t)nq, k, qnorm.p, bnmax, thr.p)
     GT_DISPATCH(idx, GT_THR);
-    idx->last_launches++;
+    pann_gt_init_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(state.as<u64>(), tot);
+    idx->last_launches += 2;
     // instruction descriptor: D = s32 / f32, A and B = u8 / s8 / tf32, K-major both, N = 256, M = 128
     uint32_t idesc = 0;
     if (isint) { const uint32_t f = idx->dtype == PANN_DT_I8 ? 1u : 0u; idesc = (2u << 4) | (f << 7) | (f << 10); }
     else idesc = (1u << 4) | (2u << 7) | (2u << 10);
     idesc |= (uint32_t)(GTM_N >> 3) << 17;
     idesc |= (uint32_t)(GTM_M >> 4) << 24;
-    const size_t smem = 1024 + (size_t)kb * GTM_A_STAGE_BYTES + (size_t)nstages * GTM_B_STAGE_BYTES + 256;
+    const size_t smem = 1024 + (size_t)kb * GTM_A_STAGE_BYTES + (size_t)nstages * GTM_B_STAGE_BYTES + 256 + GTM_BN * GTM_N * 4;
     const void* kfn = isint ? (const void*)pann_gt_mma_kernel<true> : (const void*)pann_gt_mma_kernel<false>;
     if (cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) {
       fail(); PANN_FAIL("pann_groundtruth: cannot reserve shared memory for the MMA kernel");
     }
     const uint32_t nqb = (uint32_t)((nq + GTM_M - 1) / GTM_M);
-    uint64_t lo = seed;
+    uint64_t lo = 0;
     while (lo < nb) {
-      uint64_t c = (uint64_t)((growth - 1.0) * (double)lo);
+      uint64_t c = lo == 0 ? (uint64_t)(growth * (double)seed) : (uint64_t)((growth - 1.0) * (double)lo);
       c = std::max<uint64_t>(c / GTM_N * GTM_N, GTM_N);
       const uint64_t hi = std::min<uint64_t>(nb, lo + c);
       const uint64_t tiles = (hi - lo + GTM_N - 1) / GTM_N;
-      uint64_t S = std::max<uint64_t>(1, std::min<uint64_t>(tiles, (4ull * idx->sms + nqb - 1) / nqb));
+      uint64_t S = std::max<uint64_t>(1, std::min<uint64_t>(std::min<uint64_t>(tiles, GTM_MAX_SUB / 2), (4ull * idx->sms + nqb - 1) / nqb));
       const uint32_t tps = (uint32_t)((tiles + S - 1) / S);
       S = (tiles + tps - 1) / tps;
       cudaMemcpyAsync(state_bak.p, state.p, 8ull * nq * k, cudaMemcpyDeviceToDevice, s);
       GtMmaArgs A;
       A.nq = (uint32_t)nq; A.kb = kb; A.nstages = (uint32_t)nstages; A.row_lo = lo; A.row_hi = hi; A.tiles_per_seg = tps;
       A.bnorm = bnorm.p; A.thr = thr.p; A.cand_ids = cand_ids.as<uint32_t>(); A.cand_cnt = cand_cnt.as<uint32_t>();
+      A.subcap = (uint32_t)(GTM_CAND_CAP / (2 * S));
       if (isint) pann_gt_mma_kernel<true><<<dim3(nqb, (unsigned)S), GTM_THREADS, smem, s>>>(tmQ, tmB, A, idesc);
       else pann_gt_mma_kernel<false><<<dim3(nqb, (unsigned)S), GTM_THREADS, smem, s>>>(tmQ, tmB, A, idesc);
-#define GT_SHRINK(DT, M) gt_launch_shrink<DT, M>(idx, s, d_q, (uint32_t)nq, k, state.as<u64>(), cand_ids.as<uint32_t>(), cand_cnt.as<uint32_t>(), qnorm.p, bnmax, thr.p, overflow)
+#define GT_SHRINK(DT, M) gt_launch_shrink<DT, M>(idx, s, d_q, (uint32_t)nq, k, state.as<u64>(), cand_ids.as<uint32_t>(), cand_cnt.as<uint32_t>(), (uint32_t)(2 * S), A.subcap, qnorm.p, bnmax, thr.p, overflow)
       GT_DISPATCH(idx, GT_SHRINK);
       idx->last_launches += 2;
       cudaMemcpyAsync(h_flag, overflow, sizeof(int), cudaMemcpyDeviceToHost, s);
@@ -359,7 +364,7 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
         // take the chunk again on the CUDA cores from the saved state
         cudaMemcpyAsync(state.p, state_bak.p, 8ull * nq * k, cudaMemcpyDeviceToDevice, s);
         cudaMemsetAsync(overflow, 0, sizeof(int), s);
-        cudaMemsetAsync(cand_cnt.p, 0, 4ull * nq, s);
+        cudaMemsetAsync(cand_cnt.p, 0, 4ull * nq * GTM_MAX_SUB, s);
         gt_v1_range(idx, s, d_q, nq, k, state.as<u64>(), D.as<float>(), cb, lo, hi);
         GT_DISPATCH(idx, GT_THR);
         idx->last_launches++;

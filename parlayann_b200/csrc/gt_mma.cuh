@@ -22,8 +22,10 @@
 #define GTM_N 256          // base rows per tile (UMMA N)
 #define GTM_KB_BYTES 128   // bytes of K per smem stage = one 128B swizzle atom
 #define GTM_STAGES 4
+#define GTM_BN 8             // ring of per-tile |b|^2 rows (1 KB each)
 #define GTM_THREADS 320    // warp 0: TMA producer, warp 1: MMA issuer, warps 2-9: epilogue
-#define GTM_CAND_CAP 4096  // candidate ids per query per chunk
+#define GTM_CAND_CAP 4096  // candidate ids per query per chunk, split into private sub-lists (one per segment CTA and column half)
+#define GTM_MAX_SUB 64      // sub-lists per query (2 x segments): no atomics, every epilogue thread owns its list and counter
 #define GTM_A_STAGE_BYTES (GTM_M * GTM_KB_BYTES)   // 16 KB
 #define GTM_B_STAGE_BYTES (GTM_N * GTM_KB_BYTES)   // 32 KB
 #define GTS_KEYS 8192       // shrink kernel: key slots in shared memory (>= k + GTM_CAND_CAP, k <= 1024)
@@ -54,6 +56,12 @@ __device__ __forceinline__ void gtm_tma_load_2d(void* smem_dst, const CUtensorMa
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(gtm_smem_u32(smem_dst)),
       "l"((uint64_t)tm), "r"(c0), "r"(c1), "r"(gtm_smem_u32(bar))
       : "memory");
+}
+// 1-D bulk copy global -> shared (bytes % 16 == 0, both sides 16-byte aligned), completion counted on an mbarrier
+__device__ __forceinline__ void gtm_bulk_load(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(gtm_smem_u32(smem_dst)),
+               "l"((uint64_t)gsrc), "r"(bytes), "r"(gtm_smem_u32(bar))
+               : "memory");
 }
 __device__ __forceinline__ void gtm_tcgen05_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void gtm_tcgen05_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -108,8 +116,9 @@ struct GtMmaArgs {
   uint32_t tiles_per_seg;      // blockIdx.y walks tiles [y * tiles_per_seg, (y+1) * tiles_per_seg) of the chunk
   const void* bnorm;           // per base row: |b|^2 (L2) or 0 (MIPS); float or int32; padded with +inf / 2^30 to a tile multiple
   const void* thr;             // per query: T_q (float or int32)
-  uint32_t* cand_ids;          // [nq][GTM_CAND_CAP]
-  uint32_t* cand_cnt;          // [nq]
+  uint32_t* cand_ids;          // [nq][nsub][subcap]  (nsub = 2 * gridDim.y, nsub * subcap <= GTM_CAND_CAP)
+  uint32_t* cand_cnt;          // [nq][GTM_MAX_SUB]
+  uint32_t subcap;
 };
 
 template <bool ISINT>
@@ -126,7 +135,10 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   uint64_t* a_full = bars + 2 * GTM_STAGES;    // queries landed
   uint64_t* t_full = a_full + 1;               // [2] accumulator ready (MMA -> epilogue)
   uint64_t* t_empty = t_full + 2;              // [2] accumulator drained (epilogue -> MMA)
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(t_empty + 2);
+  uint64_t* bn_full = t_empty + 2;             // [GTM_BN] |b|^2 of a tile landed (bulk copy -> epilogue)
+  uint64_t* bn_empty = bn_full + GTM_BN;       // [GTM_BN] slot read by all epilogue warps (epilogue -> producer)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bn_empty + GTM_BN);
+  uint32_t* bn_s = reinterpret_cast<uint32_t*>(reinterpret_cast<uint8_t*>(bars) + 256);   // [GTM_BN][GTM_N] ring of per-tile |b|^2 rows
 
   const int widx = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t q0 = blockIdx.x * GTM_M;
@@ -140,6 +152,7 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     for (int i = 0; i < GTM_STAGES; i++) { gtm_mbar_init(&full[i], 1); gtm_mbar_init(&empty[i], 1); }
     gtm_mbar_init(a_full, 1);
     for (int i = 0; i < 2; i++) { gtm_mbar_init(&t_full[i], 1); gtm_mbar_init(&t_empty[i], 8); }
+    for (int i = 0; i < GTM_BN; i++) { gtm_mbar_init(&bn_full[i], 1); gtm_mbar_init(&bn_empty[i], 8); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (widx == 1) {  // TMEM: all 512 columns (two 256-column accumulators); this warp also frees them
@@ -156,9 +169,14 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     if (lane == 0 && ntiles > 0) {
       gtm_mbar_expect_tx(a_full, A.kb * GTM_A_STAGE_BYTES);
       for (uint32_t j = 0; j < A.kb; j++) gtm_tma_load_2d(sA + (size_t)j * GTM_A_STAGE_BYTES, &tmQ, (int)(j * GTM_KB_BYTES), (int)q0, a_full);
-      uint32_t stage = 0, phase = 0;
+      uint32_t stage = 0, phase = 0, bs = 0, bphase = 0;
       for (uint32_t t = 0; t < ntiles; t++) {
         const int row0 = (int)(seg_row0 + (uint64_t)t * GTM_N);
+        // the tile's |b|^2 row (1 KB) goes into its own small ring, so the operand pipeline never waits for the epilogue
+        gtm_mbar_wait(&bn_empty[bs], bphase ^ 1);
+        gtm_mbar_expect_tx(&bn_full[bs], GTM_N * 4);
+        gtm_bulk_load(bn_s + bs * GTM_N, reinterpret_cast<const uint32_t*>(A.bnorm) + (uint64_t)row0, GTM_N * 4, &bn_full[bs]);
+        if (++bs == GTM_BN) { bs = 0; bphase ^= 1; }
         for (uint32_t j = 0; j < A.kb; j++) {
           gtm_mbar_wait(&empty[stage], phase ^ 1);
           gtm_mbar_expect_tx(&full[stage], GTM_B_STAGE_BYTES);
@@ -201,11 +219,13 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     acc_t T;
     if constexpr (ISINT) T = qok ? reinterpret_cast<const int*>(A.thr)[q] : INT_MIN;
     else T = qok ? reinterpret_cast<const float*>(A.thr)[q] : -INFINITY;
-    uint32_t* my_ids = A.cand_ids + (size_t)(qok ? q : 0) * GTM_CAND_CAP;
-    uint32_t* my_cnt = A.cand_cnt + (qok ? q : 0);
-    uint32_t as = 0, aphase = 0;
+    const uint32_t sub = blockIdx.y * 2 + half;
+    uint32_t* my_ids = A.cand_ids + (size_t)(qok ? q : 0) * GTM_CAND_CAP + (size_t)sub * A.subcap;
+    uint32_t cnt = 0;   // appended so far (may run past subcap: the shrink kernel reports the overflow)
+    uint32_t as = 0, aphase = 0, bs = 0, bphase = 0;
     for (uint32_t t = 0; t < ntiles; t++) {
       const uint64_t row0 = seg_row0 + (uint64_t)t * GTM_N;
+      gtm_mbar_wait(&bn_full[bs], bphase);
       gtm_mbar_wait(&t_full[as], aphase);
       gtm_tcgen05_fence_after();
 #pragma unroll 1
@@ -214,28 +234,50 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         uint32_t v[32];
         gtm_tmem_ld32(tmem_base + ((quad * 32) << 16) + as * GTM_N + col0, v);
         uint4 bn[8];
-        const uint4* bnp = reinterpret_cast<const uint4*>(reinterpret_cast<const uint32_t*>(A.bnorm) + row0 + col0);
+        const uint4* bnp = reinterpret_cast<const uint4*>(bn_s + bs * GTM_N + col0);   // broadcast reads
 #pragma unroll
-        for (int i = 0; i < 8; i++) bn[i] = __ldg(bnp + i);
+        for (int i = 0; i < 8; i++) bn[i] = bnp[i];
         gtm_tmem_ld_wait();
         const uint32_t* bnw = reinterpret_cast<const uint32_t*>(bn);
+        // w_j = |b_j|^2 - 2 q.b_j ; almost never <= T_q once the threshold has tightened: test the minimum first
+        acc_t w[32], g4[8];
 #pragma unroll
         for (int j = 0; j < 32; j++) {
-          bool pass;
-          if constexpr (ISINT) pass = ((int)bnw[j] - 2 * (int)v[j]) <= T;
-          else pass = fmaf(-2.0f, __uint_as_float(v[j]), __uint_as_float(bnw[j])) <= T;
-          if (pass) {
-            const uint32_t pos = atomicAdd(my_cnt, 1u);
-            if (pos < GTM_CAND_CAP) my_ids[pos] = (uint32_t)(row0 + col0 + j);
+          if constexpr (ISINT) w[j] = (int)bnw[j] - 2 * (int)v[j];
+          else w[j] = fmaf(-2.0f, __uint_as_float(v[j]), __uint_as_float(bnw[j]));
+        }
+#pragma unroll
+        for (int g = 0; g < 8; g++) {   // minima of groups of four, then of the 32 (+inf pads, no NaNs: fminf is exact)
+          if constexpr (ISINT) g4[g] = min(min(w[4 * g], w[4 * g + 1]), min(w[4 * g + 2], w[4 * g + 3]));
+          else g4[g] = fminf(fminf(w[4 * g], w[4 * g + 1]), fminf(w[4 * g + 2], w[4 * g + 3]));
+        }
+        acc_t mn;
+        if constexpr (ISINT) mn = min(min(min(g4[0], g4[1]), min(g4[2], g4[3])), min(min(g4[4], g4[5]), min(g4[6], g4[7])));
+        else mn = fminf(fminf(fminf(g4[0], g4[1]), fminf(g4[2], g4[3])), fminf(fminf(g4[4], g4[5]), fminf(g4[6], g4[7])));
+        if (mn <= T) {
+#pragma unroll
+          for (int g = 0; g < 8; g++) {
+            if (g4[g] <= T) {
+#pragma unroll
+              for (int jj = 0; jj < 4; jj++) {
+                const int j = 4 * g + jj;
+                if (w[j] <= T) {
+                  if (cnt < A.subcap) my_ids[cnt] = (uint32_t)(row0 + col0 + j);
+                  cnt++;
+                }
+              }
+            }
           }
         }
       }
       gtm_tcgen05_fence_before();
       __syncwarp();
-      if (lane == 0) gtm_mbar_arrive(&t_empty[as]);
+      if (lane == 0) { gtm_mbar_arrive(&t_empty[as]); gtm_mbar_arrive(&bn_empty[bs]); }
       as ^= 1;
       if (as == 0) aphase ^= 1;
+      if (++bs == GTM_BN) { bs = 0; bphase ^= 1; }
     }
+    if (qok) A.cand_cnt[(size_t)q * GTM_MAX_SUB + sub] = cnt;
   }
   gtm_tcgen05_fence_before();
   __syncthreads();
@@ -314,13 +356,11 @@ __global__ void pann_gt_thr_kernel(const u64* __restrict__ state, uint32_t nq, u
 __device__ __forceinline__ void gtm_bitonic(u64* a, int m) {
   for (int k = 2; k <= m; k <<= 1)
     for (int j = k >> 1; j > 0; j >>= 1) {
-      for (int t = threadIdx.x; t < m; t += blockDim.x) {
-        const int p = t ^ j;
-        if (p > t) {
-          const u64 x = a[t], y = a[p];
-          const bool up = (t & k) == 0;
-          if ((x > y) == up) { a[t] = y; a[p] = x; }
-        }
+      for (int i = threadIdx.x; i < (m >> 1); i += blockDim.x) {   // one compare-exchange per thread and step
+        const int t = 2 * i - (i & (j - 1)), p = t + j;
+        const u64 x = a[t], y = a[p];
+        const bool up = (t & k) == 0;
+        if ((x > y) == up) { a[t] = y; a[p] = x; }
       }
       __syncthreads();
     }
@@ -329,26 +369,45 @@ template <int DT, int METRIC>
 __global__ void __launch_bounds__(256) pann_gt_shrink_kernel(const uint8_t* __restrict__ points, uint32_t stride, uint32_t nch,
                                                              const uint8_t* __restrict__ queries, uint32_t k, u64* __restrict__ state,
                                                              const uint32_t* __restrict__ cand_ids, uint32_t* __restrict__ cand_cnt,
+                                                             uint32_t nsub, uint32_t subcap,
                                                              const void* qnorm, const float* bnmax, void* thr, int* overflow) {
   extern __shared__ __align__(16) uint8_t gts_smem[];
+  __shared__ uint32_t s_off[GTM_MAX_SUB + 1];
+  __shared__ int s_over;
   u64* buf = reinterpret_cast<u64*>(gts_smem);                       // up to k + GTM_CAND_CAP keys, padded to a power of two
   const uint32_t q = blockIdx.x;
-  const uint32_t cnt = cand_cnt[q];
+  if (threadIdx.x == 0) s_over = 0;
   __syncthreads();
-  if (threadIdx.x == 0) cand_cnt[q] = 0;
-  if (cnt > GTM_CAND_CAP) { if (threadIdx.x == 0) atomicOr(overflow, 1); return; }
+  if (threadIdx.x < nsub) {
+    const uint32_t c = cand_cnt[(size_t)q * GTM_MAX_SUB + threadIdx.x];
+    if (c > subcap) s_over = 1;
+    s_off[threadIdx.x + 1] = min(c, subcap);
+  }
+  __syncthreads();
+  if (s_over) { if (threadIdx.x == 0) atomicOr(overflow, 1); return; }
+  if (threadIdx.x == 0) { s_off[0] = 0; for (uint32_t i = 0; i < nsub; i++) s_off[i + 1] += s_off[i]; }
+  __syncthreads();
+  const uint32_t cnt = s_off[nsub];
   if (cnt == 0) return;                                              // nothing can have changed
   int m = 2; while (m < (int)(k + cnt)) m <<= 1;
   uint4* qs = reinterpret_cast<uint4*>(gts_smem + 8ull * GTS_KEYS);
   for (uint32_t c = threadIdx.x; c < nch; c += blockDim.x) qs[c] = __ldg(reinterpret_cast<const uint4*>(queries + (uint64_t)q * stride) + c);
   for (int i = threadIdx.x; i < m; i += blockDim.x) buf[i] = i < (int)k ? state[(uint64_t)q * k + i] : ~0ull;
   __syncthreads();
-  for (uint32_t i = threadIdx.x; i < cnt; i += blockDim.x) {
-    const uint32_t id = cand_ids[(uint64_t)q * GTM_CAND_CAP + i];
+  // the sub-lists are mostly empty: gather the ids densely first (staged in the key slots), then one dense pass of
+  // exact distances
+  for (uint32_t sl = threadIdx.x >> 5; sl < nsub; sl += blockDim.x >> 5) {
+    const uint32_t o = s_off[sl], c = s_off[sl + 1] - o;
+    for (uint32_t i = threadIdx.x & 31; i < c; i += 32)
+      buf[k + o + i] = cand_ids[(uint64_t)q * GTM_CAND_CAP + (uint64_t)sl * subcap + i];
+  }
+  __syncthreads();
+  for (uint32_t ci = threadIdx.x; ci < cnt; ci += blockDim.x) {
+    const uint32_t id = (uint32_t)buf[k + ci];
     const uint4* row = reinterpret_cast<const uint4*>(points + (uint64_t)id * stride);
     DistAcc<DT, METRIC> acc;
     for (uint32_t c = 0; c < nch; c++) acc.add(__ldg(row + c), qs[c]);
-    buf[k + i] = pann_key(acc.result(), id);
+    buf[k + ci] = pann_key(acc.result(), id);
   }
   __syncthreads();
   gtm_bitonic(buf, m);
