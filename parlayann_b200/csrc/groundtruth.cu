@@ -343,17 +343,17 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
       c = std::max<uint64_t>(c / GTM_N * GTM_N, GTM_N);
       const uint64_t hi = std::min<uint64_t>(nb, lo + c);
       const uint64_t tiles = (hi - lo + GTM_N - 1) / GTM_N;
-      uint64_t S = std::max<uint64_t>(1, std::min<uint64_t>(std::min<uint64_t>(tiles, GTM_MAX_SUB / 2), (4ull * idx->sms + nqb - 1) / nqb));
+      uint64_t S = std::max<uint64_t>(1, std::min<uint64_t>(std::min<uint64_t>(tiles, GTM_MAX_SUB / (GTM_EPI_WARPS / 4)), (4ull * idx->sms + nqb - 1) / nqb));
       const uint32_t tps = (uint32_t)((tiles + S - 1) / S);
       S = (tiles + tps - 1) / tps;
       cudaMemcpyAsync(state_bak.p, state.p, 8ull * nq * k, cudaMemcpyDeviceToDevice, s);
       GtMmaArgs A;
       A.nq = (uint32_t)nq; A.kb = kb; A.nstages = (uint32_t)nstages; A.row_lo = lo; A.row_hi = hi; A.tiles_per_seg = tps;
       A.bnorm = bnorm.p; A.thr = thr.p; A.cand_ids = cand_ids.as<uint32_t>(); A.cand_cnt = cand_cnt.as<uint32_t>();
-      A.subcap = (uint32_t)(GTM_CAND_CAP / (2 * S));
+      A.subcap = (uint32_t)(GTM_CAND_CAP / ((GTM_EPI_WARPS / 4) * S));
       if (isint) pann_gt_mma_kernel<true><<<dim3(nqb, (unsigned)S), GTM_THREADS, smem, s>>>(tmQ, tmB, A, idesc);
       else pann_gt_mma_kernel<false><<<dim3(nqb, (unsigned)S), GTM_THREADS, smem, s>>>(tmQ, tmB, A, idesc);
-#define GT_SHRINK(DT, M) gt_launch_shrink<DT, M>(idx, s, d_q, (uint32_t)nq, k, state.as<u64>(), cand_ids.as<uint32_t>(), cand_cnt.as<uint32_t>(), (uint32_t)(2 * S), A.subcap, qnorm.p, bnmax, thr.p, overflow)
+#define GT_SHRINK(DT, M) gt_launch_shrink<DT, M>(idx, s, d_q, (uint32_t)nq, k, state.as<u64>(), cand_ids.as<uint32_t>(), cand_cnt.as<uint32_t>(), (uint32_t)((GTM_EPI_WARPS / 4) * S), A.subcap, qnorm.p, bnmax, thr.p, overflow)
       GT_DISPATCH(idx, GT_SHRINK);
       idx->last_launches += 2;
       cudaMemcpyAsync(h_flag, overflow, sizeof(int), cudaMemcpyDeviceToHost, s);

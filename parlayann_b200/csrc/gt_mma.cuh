@@ -23,8 +23,9 @@
 #define GTM_KB_BYTES 128   // bytes of K per smem stage = one 128B swizzle atom
 #define GTM_STAGES 4
 #define GTM_BN 8             // ring of per-tile |b|^2 rows (1 KB each)
-#define GTM_THREADS 320    // warp 0: TMA producer, warp 1: MMA issuer, warps 2-9: epilogue
-#define GTM_CAND_CAP 4096  // candidate ids per query per chunk, split into private sub-lists (one per segment CTA and column half)
+#define GTM_EPI_WARPS 16    // epilogue warps: 4 TMEM lane quadrants x 4 column quarters
+#define GTM_THREADS (64 + 32 * GTM_EPI_WARPS)   // warp 0: TMA producer, warp 1: MMA issuer, then the epilogue warps
+#define GTM_CAND_CAP 4096  // candidate ids per query per chunk, split into private sub-lists (one per segment CTA and column quarter)
 #define GTM_MAX_SUB 64      // sub-lists per query (2 x segments): no atomics, every epilogue thread owns its list and counter
 #define GTM_A_STAGE_BYTES (GTM_M * GTM_KB_BYTES)   // 16 KB
 #define GTM_B_STAGE_BYTES (GTM_N * GTM_KB_BYTES)   // 32 KB
@@ -116,7 +117,7 @@ struct GtMmaArgs {
   uint32_t tiles_per_seg;      // blockIdx.y walks tiles [y * tiles_per_seg, (y+1) * tiles_per_seg) of the chunk
   const void* bnorm;           // per base row: |b|^2 (L2) or 0 (MIPS); float or int32; padded with +inf / 2^30 to a tile multiple
   const void* thr;             // per query: T_q (float or int32)
-  uint32_t* cand_ids;          // [nq][nsub][subcap]  (nsub = 2 * gridDim.y, nsub * subcap <= GTM_CAND_CAP)
+  uint32_t* cand_ids;          // [nq][nsub][subcap]  (nsub = (GTM_EPI_WARPS / 4) * gridDim.y, nsub * subcap <= GTM_CAND_CAP)
   uint32_t* cand_cnt;          // [nq][GTM_MAX_SUB]
   uint32_t subcap;
 };
@@ -151,8 +152,8 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
   if (widx == 0 && lane == 0) {
     for (int i = 0; i < GTM_STAGES; i++) { gtm_mbar_init(&full[i], 1); gtm_mbar_init(&empty[i], 1); }
     gtm_mbar_init(a_full, 1);
-    for (int i = 0; i < 2; i++) { gtm_mbar_init(&t_full[i], 1); gtm_mbar_init(&t_empty[i], 8); }
-    for (int i = 0; i < GTM_BN; i++) { gtm_mbar_init(&bn_full[i], 1); gtm_mbar_init(&bn_empty[i], 8); }
+    for (int i = 0; i < 2; i++) { gtm_mbar_init(&t_full[i], 1); gtm_mbar_init(&t_empty[i], GTM_EPI_WARPS); }
+    for (int i = 0; i < GTM_BN; i++) { gtm_mbar_init(&bn_full[i], 1); gtm_mbar_init(&bn_empty[i], GTM_EPI_WARPS); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (widx == 1) {  // TMEM: all 512 columns (two 256-column accumulators); this warp also frees them
@@ -211,15 +212,15 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       }
     }
   } else {
-    // ===== epilogue: 8 warps; warp w reads TMEM lanes 32*(w%4).., column half (w-2)/4 =====
-    const uint32_t quad = widx & 3, half = (uint32_t)(widx - 2) >> 2;
+    // ===== epilogue: GTM_EPI_WARPS warps; warp w reads TMEM lanes 32*(w%4).. and one column quarter =====
+    const uint32_t quad = widx & 3, part = (uint32_t)(widx - 2) >> 2;   // TMEM lanes 32*quad.., columns 64*part..
     const uint32_t q = q0 + quad * 32 + lane;
     const bool qok = q < A.nq;
     typedef typename std::conditional<ISINT, int, float>::type acc_t;
     acc_t T;
     if constexpr (ISINT) T = qok ? reinterpret_cast<const int*>(A.thr)[q] : INT_MIN;
     else T = qok ? reinterpret_cast<const float*>(A.thr)[q] : -INFINITY;
-    const uint32_t sub = blockIdx.y * 2 + half;
+    const uint32_t sub = blockIdx.y * (GTM_EPI_WARPS / 4) + part;
     uint32_t* my_ids = A.cand_ids + (size_t)(qok ? q : 0) * GTM_CAND_CAP + (size_t)sub * A.subcap;
     uint32_t cnt = 0;   // appended so far (may run past subcap: the shrink kernel reports the overflow)
     uint32_t as = 0, aphase = 0, bs = 0, bphase = 0;
@@ -229,8 +230,8 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       gtm_mbar_wait(&t_full[as], aphase);
       gtm_tcgen05_fence_after();
 #pragma unroll 1
-      for (uint32_t c = 0; c < 4; c++) {
-        const uint32_t col0 = half * 128 + c * 32;
+      for (uint32_t c = 0; c < GTM_N / 32 / (GTM_EPI_WARPS / 4); c++) {
+        const uint32_t col0 = part * (GTM_N / (GTM_EPI_WARPS / 4)) + c * 32;
         uint32_t v[32];
         gtm_tmem_ld32(tmem_base + ((quad * 32) << 16) + as * GTM_N + col0, v);
         uint4 bn[8];

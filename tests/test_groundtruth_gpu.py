@@ -92,3 +92,48 @@ def test_groundtruth_errors():
         idx.groundtruth(base[:5], k=0)
     ids, dists = idx.groundtruth(base[:5], k=50)
     assert (ids[:, 0] == np.arange(5)).all() and (dists[:, 0] == 0).all()
+
+
+# ---- K4 v2 (tcgen05 / TMA GEMM with the fused threshold filter) against K4 v1 (CUDA cores, PANN_GT_V1=1)
+def _both_paths(idx, queries, k, monkeypatch):
+    monkeypatch.setenv("PANN_GT_V1", "0")
+    a = idx.groundtruth(queries, k=k)
+    n_mma = idx.last_timing()[1]
+    monkeypatch.setenv("PANN_GT_V1", "1")
+    b = idx.groundtruth(queries, k=k)
+    return a, b, n_mma
+
+
+@pytest.mark.parametrize("data_type,metric,kind,n,d,nq,k", [
+    ("uint8", "Euclidian", "uint8", 30000, 128, 300, 100), ("uint8", "mips", "uint8", 20000, 128, 130, 10),
+    ("int8", "Euclidian", "int8", 20000, 128, 129, 50), ("int8", "mips", "int8", 20011, 160, 100, 100),
+    ("float", "Euclidian", "float_norm", 40000, 96, 300, 100), ("float", "mips", "float", 20000, 200, 130, 20),
+    ("float", "Euclidian", "float", 20000, 100, 257, 1), ("uint8", "Euclidian", "uint8", 20000, 200, 64, 1000),
+])
+def test_mma_path_identical_to_cuda_core_path(data_type, metric, kind, n, d, nq, k, monkeypatch):
+    import parlayann_b200 as P
+    base = O.gen_points(kind, n, d)
+    qs = O.gen_points(kind, nq, d, stream=1)
+    idx = P.GraphIndex(base, None, data_type, metric, max_degree=4)
+    (gi, gd), (vi, vd), _ = _both_paths(idx, qs, k, monkeypatch)
+    assert np.array_equal(gd.view(np.uint32), vd.view(np.uint32))   # bit-identical floats
+    assert np.array_equal(gi, vi)                                   # both sorted by (dist, id): same ids, ties included
+    oi, od = O.groundtruth(base, qs, data_type, metric, k=k)
+    assert np.array_equal(gd, od)
+
+
+def test_mma_path_overflow_falls_back(monkeypatch):
+    """rows ordered so that every row is closer than all rows before it: the thresholds stay loose, the candidate
+    lists overflow, and the chunk is taken again on the CUDA cores — the result must not change"""
+    import parlayann_b200 as P
+    n, d, nq, k = 30000, 128, 64, 10
+    lvl = (255 - (np.arange(n) * 200 // n)).astype(np.uint8)            # 255 ... 56, non-increasing
+    base = np.repeat(lvl[:, None], d, axis=1)
+    base[:, 0] = (np.arange(n) % 7).astype(np.uint8)                    # break exact ties a little
+    qs = np.zeros((nq, d), np.uint8)
+    qs[:, 1] = np.arange(nq, dtype=np.uint8)
+    idx = P.GraphIndex(base, None, "uint8", "Euclidian", max_degree=4)
+    (gi, gd), (vi, vd), _ = _both_paths(idx, qs, k, monkeypatch)
+    assert np.array_equal(gd, vd) and np.array_equal(gi, vi)
+    oi, od = O.groundtruth(base, qs, "uint8", "Euclidian", k=k)
+    assert np.array_equal(gd, od)
