@@ -220,12 +220,13 @@ static int gt_make_tmap(CUtensorMap* tm, const void* ptr, uint64_t rows, uint32_
   return 0;
 }
 
+static int gt_shrink_threads() { const char* e = getenv("PANN_GT_SHRINK_THREADS"); return e ? atoi(e) : 128; }
 template <int DT, int METRIC>
 static void gt_launch_shrink(pann_index* idx, cudaStream_t s, const uint8_t* d_q, uint32_t nq, uint32_t k, u64* state, const uint32_t* cand_ids,
-                             uint32_t* cand_cnt, uint32_t nsub, uint32_t subcap, const void* qnorm, const float* bnmax, void* thr, int* overflow) {
-  const size_t sm = 8ull * GTS_KEYS + idx->geom.stride;
-  cudaFuncSetAttribute(pann_gt_shrink_kernel<DT, METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm);
-  pann_gt_shrink_kernel<DT, METRIC><<<nq, 256, sm, s>>>(idx->points, idx->geom.stride, idx->geom.nch, d_q, k, state, cand_ids, cand_cnt, nsub, subcap, qnorm, bnmax, thr, overflow);
+                             uint32_t* cand_cnt, uint32_t nsub, uint32_t subcap, uint32_t keys_cap, const void* qnorm, const float* bnmax, void* thr, int* overflow) {
+  const size_t sm = 8ull * keys_cap + idx->geom.stride;
+  cudaFuncSetAttribute(pann_gt_shrink_kernel<DT, METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(8ull * GTS_KEYS + idx->geom.stride));
+  pann_gt_shrink_kernel<DT, METRIC><<<nq, keys_cap == GTS_KEYS_SMALL ? gt_shrink_threads() : 256, sm, s>>>(idx->points, idx->geom.stride, idx->geom.nch, d_q, k, state, cand_ids, cand_cnt, nsub, subcap, keys_cap, qnorm, bnmax, thr, overflow);
 }
 template <int DT, int METRIC>
 static void gt_launch_thr(cudaStream_t s, const u64* state, uint32_t nq, uint32_t k, const void* qnorm, const float* bnmax, void* thr) {
@@ -280,10 +281,10 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
   // v1 distance chunk (~1 GiB for the whole job, only the seed rows when the MMA path runs)
   uint64_t cb = ((1ull << 28) / nq) / GT_TB * GT_TB;
   cb = std::max<uint64_t>(cb, 4096);
-  cb = std::min<uint64_t>(cb, ((use_mma ? seed : nb) + GT_TB - 1) / GT_TB * GT_TB);
+  cb = std::min<uint64_t>(cb, (nb + GT_TB - 1) / GT_TB * GT_TB);
   DevBuf D, state, state_bak, bnorm, qnorm, thr, cand_ids, cand_cnt, misc;
   auto fail = [&]() { D.release(); state.release(); state_bak.release(); bnorm.release(); qnorm.release(); thr.release(); cand_ids.release(); cand_cnt.release(); misc.release(); return 1; };
-  if (D.reserve(4ull * nq * cb) || state.reserve(8ull * nq * k)) return fail();
+  if ((!use_mma && D.reserve(4ull * nq * cb)) || state.reserve(8ull * nq * k)) return fail();   // the MMA path needs D only for a fallback
   if (idx->gt_ids.reserve(4ull * nq * k) || idx->gt_dists.reserve(4ull * nq * k)) return fail();
   const uint64_t nb_pad = (nb + GTM_N - 1) / GTM_N * GTM_N;
   CUtensorMap tmQ, tmB;
@@ -318,13 +319,12 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
       pann_gt_norm_kernel<PANN_DT_I8><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>(d_q, nq, nq, stride, idx->geom.nch, qnorm.p, 0, nullptr);
     }
     idx->last_launches += 2;
-    // seed: the k-th distance within the first `seed` rows (CUDA cores) bounds the final k-th distance from above; it
-    // only sets the first thresholds — the state is cleared again and the MMA pass starts at row 0
-    gt_v1_range(idx, s, d_q, nq, k, state.as<u64>(), D.as<float>(), cb, 0, seed);
+    // first thresholds: "everything passes" — the first chunk is just the first `seed` rows, all of which become
+    // candidates; from then on the chunks grow geometrically and the thresholds do the filtering
 #define GT_THR(DT, M) gt_launch_thr<DT, M>(s, state.as<u64>(), (uint32_t)nq, k, qnorm.p, bnmax, thr.p)
-    GT_DISPATCH(idx, GT_THR);
-    pann_gt_init_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(state.as<u64>(), tot);
-    idx->last_launches += 2;
+    if (isint) pann_gt_thr_init_kernel<PANN_DT_U8><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>((uint32_t)nq, thr.p);
+    else pann_gt_thr_init_kernel<PANN_DT_F32><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>((uint32_t)nq, thr.p);
+    idx->last_launches++;
     // instruction descriptor: D = s32 / f32, A and B = u8 / s8 / tf32, K-major both, N = 256, M = 128
     uint32_t idesc = 0;
     if (isint) { const uint32_t f = idx->dtype == PANN_DT_I8 ? 1u : 0u; idesc = (2u << 4) | (f << 7) | (f << 10); }
@@ -339,7 +339,7 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
     const uint32_t nqb = (uint32_t)((nq + GTM_M - 1) / GTM_M);
     uint64_t lo = 0;
     while (lo < nb) {
-      uint64_t c = lo == 0 ? (uint64_t)(growth * (double)seed) : (uint64_t)((growth - 1.0) * (double)lo);
+      uint64_t c = lo == 0 ? seed : (uint64_t)((growth - 1.0) * (double)lo);
       c = std::max<uint64_t>(c / GTM_N * GTM_N, GTM_N);
       const uint64_t hi = std::min<uint64_t>(nb, lo + c);
       const uint64_t tiles = (hi - lo + GTM_N - 1) / GTM_N;
@@ -350,21 +350,34 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
       GtMmaArgs A;
       A.nq = (uint32_t)nq; A.kb = kb; A.nstages = (uint32_t)nstages; A.row_lo = lo; A.row_hi = hi; A.tiles_per_seg = tps;
       A.bnorm = bnorm.p; A.thr = thr.p; A.cand_ids = cand_ids.as<uint32_t>(); A.cand_cnt = cand_cnt.as<uint32_t>();
+      { const char* e = getenv("PANN_GT_DBG"); A.dbg = e ? (uint32_t)atoi(e) : 0u; }
       A.subcap = (uint32_t)(GTM_CAND_CAP / ((GTM_EPI_WARPS / 4) * S));
       if (isint) pann_gt_mma_kernel<true><<<dim3(nqb, (unsigned)S), GTM_THREADS, smem, s>>>(tmQ, tmB, A, idesc);
       else pann_gt_mma_kernel<false><<<dim3(nqb, (unsigned)S), GTM_THREADS, smem, s>>>(tmQ, tmB, A, idesc);
-#define GT_SHRINK(DT, M) gt_launch_shrink<DT, M>(idx, s, d_q, (uint32_t)nq, k, state.as<u64>(), cand_ids.as<uint32_t>(), cand_cnt.as<uint32_t>(), (uint32_t)((GTM_EPI_WARPS / 4) * S), A.subcap, qnorm.p, bnmax, thr.p, overflow)
+#define GT_SHRINK(DT, M) gt_launch_shrink<DT, M>(idx, s, d_q, (uint32_t)nq, k, state.as<u64>(), cand_ids.as<uint32_t>(), cand_cnt.as<uint32_t>(), (uint32_t)((GTM_EPI_WARPS / 4) * S), A.subcap, keys_cap, qnorm.p, bnmax, thr.p, overflow)
+      // small tier first (8 KB of key slots, many CTAs per SM); queries with more keys raise bit 1 and get the large tier
+      uint32_t keys_cap = (k + (lo == 0 ? seed : 0) <= GTS_KEYS_SMALL / 2) ? GTS_KEYS_SMALL : GTS_KEYS;
       GT_DISPATCH(idx, GT_SHRINK);
       idx->last_launches += 2;
       cudaMemcpyAsync(h_flag, overflow, sizeof(int), cudaMemcpyDeviceToHost, s);
       cudaError_t e = cudaStreamSynchronize(s);
       if (e != cudaSuccess) { fail(); PANN_FAIL(std::string("pann_groundtruth (MMA path): ") + cudaGetErrorString(e)); }
+      if (*h_flag == 2 && keys_cap != GTS_KEYS) {
+        cudaMemsetAsync(overflow, 0, sizeof(int), s);
+        keys_cap = GTS_KEYS;
+        GT_DISPATCH(idx, GT_SHRINK);
+        idx->last_launches++;
+        cudaMemcpyAsync(h_flag, overflow, sizeof(int), cudaMemcpyDeviceToHost, s);
+        e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) { fail(); PANN_FAIL(std::string("pann_groundtruth (MMA path): ") + cudaGetErrorString(e)); }
+      }
       if (*h_flag) {
         // some query passed more than GTM_CAND_CAP rows of this chunk (rows ordered so that the threshold stays loose):
         // take the chunk again on the CUDA cores from the saved state
         cudaMemcpyAsync(state.p, state_bak.p, 8ull * nq * k, cudaMemcpyDeviceToDevice, s);
         cudaMemsetAsync(overflow, 0, sizeof(int), s);
         cudaMemsetAsync(cand_cnt.p, 0, 4ull * nq * GTM_MAX_SUB, s);
+        if (D.reserve(4ull * nq * cb)) return fail();
         gt_v1_range(idx, s, d_q, nq, k, state.as<u64>(), D.as<float>(), cb, lo, hi);
         GT_DISPATCH(idx, GT_THR);
         idx->last_launches++;

@@ -29,7 +29,8 @@
 #define GTM_MAX_SUB 64      // sub-lists per query (2 x segments): no atomics, every epilogue thread owns its list and counter
 #define GTM_A_STAGE_BYTES (GTM_M * GTM_KB_BYTES)   // 16 KB
 #define GTM_B_STAGE_BYTES (GTM_N * GTM_KB_BYTES)   // 32 KB
-#define GTS_KEYS 8192       // shrink kernel: key slots in shared memory (>= k + GTM_CAND_CAP, k <= 1024)
+#define GTS_KEYS 8192       // shrink kernel, large tier: key slots in shared memory (>= k + GTM_CAND_CAP, k <= 1024)
+#define GTS_KEYS_SMALL 1024 // small tier (8 KB: eight CTAs per SM); queries with more keys set flag bit 1 and wait for the large tier
 
 // ---------------------------------------------------------------------------------------------------------------
 // PTX wrappers (sm_100a)
@@ -108,6 +109,11 @@ __device__ __forceinline__ void gtm_tmem_ld32(uint32_t taddr, uint32_t (&v)[32])
         "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
       : "r"(taddr));
 }
+__device__ __forceinline__ uint4 gtm_lds128(uint32_t saddr) {
+  uint4 r;
+  asm volatile("ld.shared.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "r"(saddr));
+  return r;
+}
 __device__ __forceinline__ void gtm_tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -120,6 +126,7 @@ struct GtMmaArgs {
   uint32_t* cand_ids;          // [nq][nsub][subcap]  (nsub = (GTM_EPI_WARPS / 4) * gridDim.y, nsub * subcap <= GTM_CAND_CAP)
   uint32_t* cand_cnt;          // [nq][GTM_MAX_SUB]
   uint32_t subcap;
+  uint32_t dbg;                // experiments only (PANN_GT_DBG): 1 = skip the filter arithmetic, 2 = skip the TMEM loads as well
 };
 
 template <bool ISINT>
@@ -223,6 +230,7 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     const uint32_t sub = blockIdx.y * (GTM_EPI_WARPS / 4) + part;
     uint32_t* my_ids = A.cand_ids + (size_t)(qok ? q : 0) * GTM_CAND_CAP + (size_t)sub * A.subcap;
     uint32_t cnt = 0;   // appended so far (may run past subcap: the shrink kernel reports the overflow)
+    const uint32_t bn_s_addr = gtm_smem_u32(bn_s);
     uint32_t as = 0, aphase = 0, bs = 0, bphase = 0;
     for (uint32_t t = 0; t < ntiles; t++) {
       const uint64_t row0 = seg_row0 + (uint64_t)t * GTM_N;
@@ -233,12 +241,14 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       for (uint32_t c = 0; c < GTM_N / 32 / (GTM_EPI_WARPS / 4); c++) {
         const uint32_t col0 = part * (GTM_N / (GTM_EPI_WARPS / 4)) + c * 32;
         uint32_t v[32];
+        if (A.dbg & 2) continue;
         gtm_tmem_ld32(tmem_base + ((quad * 32) << 16) + as * GTM_N + col0, v);
         uint4 bn[8];
-        const uint4* bnp = reinterpret_cast<const uint4*>(bn_s + bs * GTM_N + col0);   // broadcast reads
+        const uint32_t bnp = bn_s_addr + (bs * GTM_N + col0) * 4;   // broadcast reads
 #pragma unroll
-        for (int i = 0; i < 8; i++) bn[i] = bnp[i];
+        for (int i = 0; i < 8; i++) bn[i] = gtm_lds128(bnp + 16 * i);
         gtm_tmem_ld_wait();
+        if (A.dbg & 1) { if (v[0] == 0x7fffffffu && v[31] == 0x7ffffffeu) cnt++; continue; }
         const uint32_t* bnw = reinterpret_cast<const uint32_t*>(bn);
         // w_j = |b_j|^2 - 2 q.b_j ; almost never <= T_q once the threshold has tightened: test the minimum first
         acc_t w[32], g4[8];
@@ -346,6 +356,13 @@ __device__ __forceinline__ void gt_write_thr(u64 kth, uint32_t q, const void* qn
     reinterpret_cast<int*>(thr)[q] = T;
   }
 }
+template <int DT>
+__global__ void pann_gt_thr_init_kernel(uint32_t nq, void* thr) {   // "everything passes" (pads still fail: +inf / 2^30)
+  const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= nq) return;
+  if constexpr (DT == PANN_DT_F32) reinterpret_cast<float*>(thr)[q] = 3.0e38f;
+  else reinterpret_cast<int*>(thr)[q] = 1 << 29;
+}
 template <int DT, int METRIC>
 __global__ void pann_gt_thr_kernel(const u64* __restrict__ state, uint32_t nq, uint32_t k, const void* qnorm, const float* bnmax, void* thr) {
   const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
@@ -370,7 +387,7 @@ template <int DT, int METRIC>
 __global__ void __launch_bounds__(256) pann_gt_shrink_kernel(const uint8_t* __restrict__ points, uint32_t stride, uint32_t nch,
                                                              const uint8_t* __restrict__ queries, uint32_t k, u64* __restrict__ state,
                                                              const uint32_t* __restrict__ cand_ids, uint32_t* __restrict__ cand_cnt,
-                                                             uint32_t nsub, uint32_t subcap,
+                                                             uint32_t nsub, uint32_t subcap, uint32_t keys_cap,
                                                              const void* qnorm, const float* bnmax, void* thr, int* overflow) {
   extern __shared__ __align__(16) uint8_t gts_smem[];
   __shared__ uint32_t s_off[GTM_MAX_SUB + 1];
@@ -389,9 +406,11 @@ __global__ void __launch_bounds__(256) pann_gt_shrink_kernel(const uint8_t* __re
   if (threadIdx.x == 0) { s_off[0] = 0; for (uint32_t i = 0; i < nsub; i++) s_off[i + 1] += s_off[i]; }
   __syncthreads();
   const uint32_t cnt = s_off[nsub];
-  if (cnt == 0) return;                                              // nothing can have changed
+  if (cnt == 0) return;                                              // nothing can have changed (or done by the small tier)
+  if (k + cnt > keys_cap) { if (threadIdx.x == 0) atomicOr(overflow, 2); return; }   // left for the launch with more key slots
+  if (threadIdx.x < nsub) cand_cnt[(size_t)q * GTM_MAX_SUB + threadIdx.x] = 0;        // done: a later tier skips this query
   int m = 2; while (m < (int)(k + cnt)) m <<= 1;
-  uint4* qs = reinterpret_cast<uint4*>(gts_smem + 8ull * GTS_KEYS);
+  uint4* qs = reinterpret_cast<uint4*>(gts_smem + 8ull * keys_cap);
   for (uint32_t c = threadIdx.x; c < nch; c += blockDim.x) qs[c] = __ldg(reinterpret_cast<const uint4*>(queries + (uint64_t)q * stride) + c);
   for (int i = threadIdx.x; i < m; i += blockDim.x) buf[i] = i < (int)k ? state[(uint64_t)q * k + i] : ~0ull;
   __syncthreads();
