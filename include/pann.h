@@ -53,6 +53,10 @@ int pann_index_create(pann_index** out, int device, int dtype, int metric, uint6
 int pann_index_create_synthetic(pann_index** out, int device, int dtype, int metric, uint64_t n, uint32_t dims,
                                 uint32_t max_degree, int gen_kind, uint64_t seed, uint64_t stream, uint32_t latent_r,
                                 uint32_t n_clusters);
+/* rows first_row .. first_row+n of the same (counter-based) stream: one base shard per GPU without any host traffic */
+int pann_index_create_synthetic_shard(pann_index** out, int device, int dtype, int metric, uint64_t first_row, uint64_t n,
+                                      uint32_t dims, uint32_t max_degree, int gen_kind, uint64_t seed, uint64_t stream,
+                                      uint32_t latent_r, uint32_t n_clusters);
 void pann_index_destroy(pann_index* idx);
 int pann_index_set_graph(pann_index* idx, const uint32_t* host_graph);        /* Graph(char* gFile) after load */
 int pann_index_get_graph(pann_index* idx, uint32_t* host_graph_out);          /* for Graph::save */

@@ -23,7 +23,7 @@ class PannError(RuntimeError):
 
 # every symbol include/pann.h declares (tests check that the library exports all of them)
 SYMBOLS = [
-    "pann_last_error", "pann_device_count", "pann_version", "pann_index_create", "pann_index_create_synthetic",
+    "pann_last_error", "pann_device_count", "pann_version", "pann_index_create", "pann_index_create_synthetic", "pann_index_create_synthetic_shard",
     "pann_index_destroy", "pann_index_set_graph", "pann_index_get_graph", "pann_index_get_points", "pann_index_info",
     "pann_index_last_timing", "pann_index_last_bytes", "pann_search_batch", "pann_queries_upload", "pann_queries_synthetic",
     "pann_queries_download", "pann_search_resident", "pann_search_fetch", "pann_search_full", "pann_vamana_build",

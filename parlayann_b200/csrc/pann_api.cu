@@ -84,12 +84,17 @@ extern "C" int pann_index_create(pann_index** out, int device, int dtype, int me
 extern "C" int pann_index_create_synthetic(pann_index** out, int device, int dtype, int metric, uint64_t n, uint32_t dims,
                                            uint32_t max_degree, int gen_kind, uint64_t seed, uint64_t stream,
                                            uint32_t latent_r, uint32_t n_clusters) {
+  return pann_index_create_synthetic_shard(out, device, dtype, metric, 0, n, dims, max_degree, gen_kind, seed, stream, latent_r, n_clusters);
+}
+extern "C" int pann_index_create_synthetic_shard(pann_index** out, int device, int dtype, int metric, uint64_t first_row, uint64_t n,
+                                                 uint32_t dims, uint32_t max_degree, int gen_kind, uint64_t seed, uint64_t stream,
+                                                 uint32_t latent_r, uint32_t n_clusters) {
   if (!out) PANN_FAIL("pann_index_create_synthetic: null argument");
   int want = gen_kind == PANN_GEN_KIND_U8 ? PANN_U8 : (gen_kind == PANN_GEN_KIND_I8 ? PANN_I8 : PANN_F32);
   if (want != dtype) PANN_FAIL("pann_index_create_synthetic: generator kind does not match dtype");
   pann_index* idx = nullptr;
   if (index_alloc(&idx, device, dtype, metric, n, dims, max_degree)) return 1;
-  if (pann_gen_rows_device(gen_kind, seed, stream, 0, n, dims, latent_r, n_clusters, idx->points, idx->geom.stride, idx->stream)) {
+  if (pann_gen_rows_device(gen_kind, seed, stream, first_row, n, dims, latent_r, n_clusters, idx->points, idx->geom.stride, idx->stream)) {
     pann_index_destroy(idx);
     return 1;
   }

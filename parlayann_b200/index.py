@@ -27,8 +27,8 @@ class GraphIndex:
             s = synthetic
             self.n, self.d = int(s["n"]), int(s["d"])
             self.max_degree = int(max_degree)
-            check(L.pann_index_create_synthetic(C.byref(self._h), device, _lib.DTYPE[data_type], _lib.METRIC[metric],
-                                                C.c_uint64(self.n), C.c_uint32(self.d), C.c_uint32(self.max_degree),
+            check(L.pann_index_create_synthetic_shard(C.byref(self._h), device, _lib.DTYPE[data_type], _lib.METRIC[metric],
+                                                C.c_uint64(s.get("row0", 0)), C.c_uint64(self.n), C.c_uint32(self.d), C.c_uint32(self.max_degree),
                                                 _lib.GEN_KIND[s.get("kind", data_type)], C.c_uint64(s.get("seed", 1234)),
                                                 C.c_uint64(s.get("stream", 0)), C.c_uint32(s.get("r", 24)),
                                                 C.c_uint32(s.get("nc", 256))))
