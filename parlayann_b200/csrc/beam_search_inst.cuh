@@ -1,6 +1,7 @@
 // beam_search_inst.cuh — instantiates K1 / K3 / K6 of one element type (PANN_INST_DT) so the three
 // element types compile in parallel translation units.  QR = PANN_QR (128-byte rows, query in registers) or 0.
 #include "beam_search.cuh"
+#include "beam_search_small.cuh"
 #include "vamana_prune.cuh"
 
 #define PANN_CAT_(a, b) a##b
@@ -15,6 +16,15 @@ static const void* pick_beam(int qr, bool gs) {
 }
 const void* PANN_CAT(pann_beam_kernel_dt, PANN_INST_DT)(int metric, int qr, bool gs) {
   return metric == PANN_M_L2 ? pick_beam<PANN_M_L2>(qr, gs) : pick_beam<PANN_M_MIPS>(qr, gs);
+}
+
+template <int METRIC>
+static const void* pick_beam_small(int qr) {
+  if (qr == PANN_QR) return (const void*)&pann_beam_search_small_kernel<PANN_INST_DT, METRIC, PANN_QR>;
+  return (const void*)&pann_beam_search_small_kernel<PANN_INST_DT, METRIC, 0>;
+}
+const void* PANN_CAT(pann_beam_small_kernel_dt, PANN_INST_DT)(int metric, int qr) {
+  return metric == PANN_M_L2 ? pick_beam_small<PANN_M_L2>(qr) : pick_beam_small<PANN_M_MIPS>(qr);
 }
 
 template <int METRIC>

@@ -1,0 +1,219 @@
+// beam_search_small.cuh — K1s: the beam search for narrow beams (beam <= 32, the regime of the recall-0.95 operating
+// points), one query per warp, with the whole frontier in REGISTERS: lane i holds frontier entry i.
+//
+// Same behavioural contract as pann_beam_search_kernel (beam_search.cuh; parlayANN::filtered_beam_search,
+// algorithms/utils/beamSearch.h:22-214) and bit-identical results; what differs is how a hop is executed:
+//  * next-to-visit, cutoff, cut rule and results are ballots / shuffles on the register frontier — no shared-memory
+//    round trips;
+//  * the neighbours are not compacted: lane l filters and scores neighbour l (then l+32) itself, so each round's row
+//    gathers are issued right after its filter step and overlap the next round's hashing;
+//  * the merge is a run of ballot-ranked insertions (one per surviving candidate, usually < beam of them): position =
+//    popc(ballot(entry < candidate)), duplicates found by ballot, entries above the position move up by one lane with
+//    a shuffle.  This equals set_union + truncate (:173-185) because both are "the beam smallest distinct keys";
+//  * the visited list is an unsorted id list (membership is all the search needs); callers that want the sorted
+//    visited list (the build) use the general kernel.
+// Shared memory per warp: hash filter (4 KB at beam <= 64), pending candidates, query row, visited ids.
+#pragma once
+#include "beam_search.cuh"
+
+// distance from the query (shared memory) to base row `a`, computed by this lane alone, chunks in ascending order
+template <int DT, int METRIC, int QR>
+__device__ __forceinline__ float pann_lane_distance(const BeamArgs& A, uint32_t a, bool on, const uint4* qsm) {
+  DistAcc<DT, METRIC> acc;
+  if (on) {
+    const uint8_t* row = A.points + (u64)a * A.stride;
+    if constexpr (QR > 0) {
+      uint4 v[QR];
+#pragma unroll
+      for (int c = 0; c < QR; c++) v[c] = pann_ldg16(row + c * 16);
+#pragma unroll
+      for (int c = 0; c < QR; c++) acc.add(v[c], qsm[c]);
+    } else {
+      const int nch = (int)A.nch;
+      for (int c0 = 0; c0 < nch; c0 += 8) {
+        uint4 v[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) if (c0 + j < nch) v[j] = pann_ldg16(row + (c0 + j) * 16);
+#pragma unroll
+        for (int j = 0; j < 8; j++) if (c0 + j < nch) acc.add(v[j], qsm[c0 + j]);
+      }
+    }
+  }
+  return acc.result();
+}
+__device__ __forceinline__ u64 pann_shfl64(u64 x, int src) {
+  const uint32_t lo = __shfl_sync(PANN_FULL, (uint32_t)x, src), hi = __shfl_sync(PANN_FULL, (uint32_t)(x >> 32), src);
+  return ((u64)hi << 32) | lo;
+}
+__device__ __forceinline__ u64 pann_shfl_up64(u64 x) {
+  const uint32_t lo = __shfl_up_sync(PANN_FULL, (uint32_t)x, 1), hi = __shfl_up_sync(PANN_FULL, (uint32_t)(x >> 32), 1);
+  return ((u64)hi << 32) | lo;
+}
+
+template <int DT, int METRIC, int QR>
+__global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_beam_search_small_kernel(const BeamArgs A) {
+  extern __shared__ __align__(16) uint8_t pann_smem[];
+  const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+  const unsigned lt_mask = (1u << lane) - 1u;
+  uint8_t* ws = pann_smem + (size_t)wic * A.warp_bytes;
+  u64* cand = reinterpret_cast<u64*>(ws + A.off_cand);
+  uint4* qsm = reinterpret_cast<uint4*>(ws + A.off_q);
+  uint32_t* visid = reinterpret_cast<uint32_t*>(ws + A.off_vis);
+  uint32_t* hashf = reinterpret_cast<uint32_t*>(ws + A.off_hash);
+  const uint32_t hmask = (1u << A.bits) - 1u;
+  const int B = A.beam;
+  const long long wglobal = (long long)blockIdx.x * PANN_WARPS_PER_CTA + wic;
+  const long long wstride = (long long)gridDim.x * PANN_WARPS_PER_CTA;
+  auto next_query = [&](long long ql) -> long long {
+    if (!A.qcounter) return ql + wstride;
+    unsigned nx = 0;
+    if (lane == 0) nx = atomicAdd(A.qcounter, 1u);
+    return wstride + (long long)__shfl_sync(PANN_FULL, nx, 0);
+  };
+  for (long long ql = wglobal; ql < (long long)A.nq; ql = next_query(ql)) {
+    const long long q = A.qmap ? (long long)A.qmap[ql] : ql;
+    {
+      const uint4 ones = make_uint4(~0u, ~0u, ~0u, ~0u);
+      uint4* h4 = reinterpret_cast<uint4*>(hashf);
+      for (int i = lane; i < (1 << A.bits) / 4; i += 32) h4[i] = ones;
+    }
+    const long long self = A.self_ids ? (long long)A.self_ids[q] : -1;
+    const uint8_t* qrow = A.self_ids ? A.points + (u64)self * A.stride : A.queries + (u64)q * A.qstride;
+    pann_load_query(qrow, A.nch, qsm, lane);
+
+    u64 fk = ~0ull;  // frontier entry `lane` ((dist,id) key, bit 0 = visited), ~0 beyond the frontier
+    int F = 0, V = 0, C = 0, status = 0;
+    unsigned cmps = A.nstarts, nread = 0;
+
+    // ---- starting points (:64-70)
+    if ((int)A.nstarts > B || A.nstarts > 32u) {
+      status = 3;
+    } else {
+      const bool on = lane < (int)A.nstarts;
+      const uint32_t a = on ? A.starts[lane] : 0u;
+      const float d = pann_lane_distance<DT, METRIC, QR>(A, a, on, qsm);
+      const u64 key = on ? pann_key(d, a) : ~0ull;
+      if (lane == 0)
+        for (uint32_t i = 0; i < A.nstarts; i++) { const uint32_t s = A.starts[i]; hashf[(uint32_t)pann_hash64_2(s) & hmask] = s; }
+      int r = 0;
+      for (int j = 0; j < (int)A.nstarts; j++) {
+        const u64 kj = pann_shfl64(key, j);
+        r += (kj < key) || (kj == key && j < lane);
+      }
+      if (on) cand[r] = key;
+      __syncwarp();
+      if (on) fk = cand[lane];
+      F = (int)A.nstarts;
+      __syncwarp();
+    }
+
+    // ---- main loop (:107-209)
+    while (status == 0) {
+      const unsigned unv = __ballot_sync(PANN_FULL, lane < F && !(fk & 1ull));
+      if (!unv || (long long)V >= A.limit) break;
+      const int pos = __ffs(unv) - 1;
+      const bool vis_in_front = (F - __popc(unv)) == V;  // every visited vertex is still a (flagged) frontier entry
+      const bool more_after = __popc(unv) > 1;           // offset + 1 < remain (:164)
+      const u64 cur = pann_shfl64(fk, pos);
+      const uint32_t* grow = A.graph + (u64)pann_key_id(cur) * (A.maxdeg + 1);
+      const int deg = (int)__ldg(grow);
+      const uint32_t a0 = (lane < (int)A.maxdeg) ? __ldg(grow + 1 + lane) : 0u;
+      const uint32_t a1 = (32 + lane < (int)A.maxdeg) ? __ldg(grow + 33 + lane) : 0u;
+      if (lane == pos) fk |= 1ull;
+      if (V >= (int)A.vcap) { status = 1; break; }
+      if (lane == 0) visid[V] = pann_key_id(cur);
+      V++;
+      const bool full = (F == B);
+      const float cutoff = full ? pann_key_dist(pann_shfl64(fk, F - 1)) : 2147483648.0f;  // (float)INT_MAX (:150-152)
+      const int ne = min(deg, A.degree_limit);
+      nread += ne;
+      for (int base = 0; base < ne; base += 32) {
+        const int i = base + lane;
+        const bool act = i < ne;
+        const uint32_t a = base == 0 ? a0 : (base == 32 ? a1 : (act ? __ldg(grow + 1 + i) : 0u));
+        const uint32_t loc = act ? ((uint32_t)pann_hash64_2(a) & hmask) : (0x80000000u | lane);
+        const unsigned peers = __match_any_sync(PANN_FULL, loc);
+        const unsigned prev = peers & lt_mask;
+        const uint32_t from_prev = __shfl_sync(PANN_FULL, a, prev ? (31 - __clz(prev)) : lane);
+        bool seen = false;
+        if (act) {
+          const uint32_t slot = prev ? from_prev : hashf[loc];
+          seen = (slot == a);
+        }
+        __syncwarp();
+        if (act && (peers >> lane) <= 1u) hashf[loc] = a;
+        const bool keep = act && !seen && ((long long)a != self);
+        cmps += __popc(__ballot_sync(PANN_FULL, keep));  // :155
+        const float d = pann_lane_distance<DT, METRIC, QR>(A, a, keep, qsm);
+        const bool take = keep && (d < cutoff);           // :153-158
+        const unsigned m = __ballot_sync(PANN_FULL, take);
+        if (C + __popc(m) > (int)A.ccap) { status = 1; break; }  // cannot happen (ccap >= maxdeg + beam/8); guards memory
+        if (take) cand[C + __popc(m & lt_mask)] = pann_key(d, a);
+        C += __popc(m);
+        __syncwarp();
+      }
+      if (status) break;
+      if (C == 0) continue;
+      if (A.limit >= 2ll * B && C < B / 8 && more_after) continue;  // :162-168, candidates are kept
+      // ---- merge (:173-208) as ballot-ranked insertions
+      const int F_old = F;
+      for (int j = 0; j < C; j++) {
+        const u64 c = cand[j];
+        const int lb = __popc(__ballot_sync(PANN_FULL, fk < c));  // raw compare: bit 0 of c is clear
+        const unsigned dup = __ballot_sync(PANN_FULL, (fk & ~1ull) == c);
+        if (dup || lb >= B) continue;
+        u64 fl = 0ull;
+        if (!vis_in_front) {  // a vertex that comes back after it was visited stays visited
+          const uint32_t id = pann_key_id(c);
+          bool found = false;
+          for (int b0 = 0; b0 < V; b0 += 32) found |= (b0 + lane < V) && (visid[b0 + lane] == id);
+          fl = __any_sync(PANN_FULL, found) ? 1ull : 0ull;
+        }
+        const u64 up = pann_shfl_up64(fk);
+        if (lane == lb) fk = c | fl;
+        else if (lane > lb) fk = up;
+        if (lane >= B) fk = ~0ull;
+        F = min(F + 1, B);
+      }
+      C = 0;
+      // cut rule (:190-195)
+      int nfs = F;
+      if (A.cut_rule && nfs > A.k) {
+        const float thr = (float)(A.cut * (double)pann_key_dist(pann_shfl64(fk, A.k)));
+        const u64 tk = ((u64)pann_fsort(thr) << 32) | 1ull;
+        const int c = __popc(__ballot_sync(PANN_FULL, lane < nfs && fk <= tk));
+        nfs = max(c, F_old);
+        if (lane >= nfs) fk = ~0ull;
+      }
+      F = nfs;
+      __syncwarp();
+    }
+
+    // ---- results
+    if (status == 0 && F < A.k) status = 2;  // beamSearch.h:416-419
+    if (A.out_ids && lane < A.k) {
+      const bool ok = lane < F;
+      A.out_ids[q * A.k + lane] = ok ? pann_key_id(fk) : 0xffffffffu;
+      if (A.out_dists) A.out_dists[q * A.k + lane] = ok ? pann_key_dist(fk) : 0.f;
+    }
+    if (A.fr_ids && lane < F && lane < (int)A.fcap) {
+      A.fr_ids[q * A.fcap + lane] = pann_key_id(fk);
+      A.fr_dists[q * A.fcap + lane] = pann_key_dist(fk);
+    }
+    if (lane == 0) {
+      if (A.out_visited) A.out_visited[q] = V;
+      if (A.out_cmps) A.out_cmps[q] = cmps;
+      if (A.n_frontier) A.n_frontier[q] = F;
+      if (A.n_visited) A.n_visited[q] = V;
+      if (A.status) A.status[q] = status;
+      if (status && A.any_status) atomicOr(A.any_status, 1 << status);
+      if (A.bytes_total)
+        atomicAdd(A.bytes_total, (u64)cmps * A.rowbytes + 4ull * (nread + (unsigned)V) + A.rowbytes + 4ull * (unsigned)A.k);
+    }
+    __syncwarp();
+  }
+}
+
+const void* pann_beam_small_kernel_dt0(int metric, int qr);
+const void* pann_beam_small_kernel_dt1(int metric, int qr);
+const void* pann_beam_small_kernel_dt2(int metric, int qr);

@@ -174,12 +174,43 @@ static const void* beam_kernel(int dtype, int metric, int qr, bool gs) {
   }
 }
 
+static const void* beam_small_kernel(int dtype, int metric, int qr) {
+  switch (dtype) {
+    case PANN_DT_F32: return pann_beam_small_kernel_dt0(metric, qr);
+    case PANN_DT_U8: return pann_beam_small_kernel_dt1(metric, qr);
+    default: return pann_beam_small_kernel_dt2(metric, qr);
+  }
+}
+
 static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap) {
   const PannRowGeom& g = idx->geom;
   const int qrT = pann_qr_of(g);
   const uint32_t B = (uint32_t)A.beam;
   A.ccap = std::max<uint32_t>(A.maxdeg + B / 8 + 1, A.nstarts);
   A.vcap = vcap;
+  // narrow beams without a visited-list output: K1s, frontier in registers (beam_search_small.cuh)
+  const char* force_general = getenv("PANN_K1_GENERAL");
+  const bool small = !gs && B <= 32 && A.nstarts <= 32 && !A.vis_ids && !(force_general && force_general[0] == '1');
+  if (small) {
+    A.off_cand = 0;
+    A.off_q = al16((size_t)A.ccap * 8);
+    A.off_vis = A.off_q + g.stride;
+    A.off_hash = A.off_vis + al16((size_t)vcap * 4);
+    A.warp_bytes = A.off_hash + (4u << A.bits);
+    const size_t cta_bytes = (size_t)A.warp_bytes * PANN_WARPS_PER_CTA;
+    const void* fn = beam_small_kernel(idx->dtype, idx->metric, qrT);
+    PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
+    int per_sm = 0;
+    PANN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, PANN_WARPS_PER_CTA * 32, cta_bytes));
+    if (per_sm < 1) PANN_FAIL("beam search: kernel does not fit on an SM");
+    long long want = ((long long)A.nq + PANN_WARPS_PER_CTA - 1) / PANN_WARPS_PER_CTA;
+    int grid = (int)std::min<long long>(want, (long long)per_sm * idx->sms);
+    if (grid < 1) grid = 1;
+    void* args[] = {(void*)&A};
+    PANN_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(PANN_WARPS_PER_CTA * 32), args, cta_bytes, idx->stream));
+    idx->last_launches++;
+    return 0;
+  }
   A.off_frontB = al16((size_t)B * 8);
   A.off_cand = A.off_frontB + al16((size_t)B * 8);
   A.off_scand = A.off_cand + al16((size_t)A.ccap * 8);

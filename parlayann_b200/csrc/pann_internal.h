@@ -6,6 +6,7 @@
 
 #include "../../include/pann.h"
 #include "beam_search.cuh"
+#include "beam_search_small.cuh"
 #include "pann_common.cuh"
 
 // grow-only device buffer
