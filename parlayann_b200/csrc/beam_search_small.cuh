@@ -83,6 +83,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
 
     u64 fk = ~0ull;  // frontier entry `lane` ((dist,id) key, bit 0 = visited), ~0 beyond the frontier
     int F = 0, V = 0, C = 0, status = 0;
+    uint32_t vis0 = 0xffffffffu, vis1 = 0xffffffffu;  // visited ids V = lane and lane + 32 (later ones: shared memory)
     unsigned cmps = A.nstarts, nread = 0;
 
     // ---- starting points (:64-70)
@@ -121,10 +122,22 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
       const uint32_t a1 = (32 + lane < (int)A.maxdeg) ? __ldg(grow + 33 + lane) : 0u;
       if (lane == pos) fk |= 1ull;
       if (V >= (int)A.vcap) { status = 1; break; }
-      if (lane == 0) visid[V] = pann_key_id(cur);
+      if (V < 32) { if (lane == V) vis0 = pann_key_id(cur); }
+      else if (V < 64) { if (lane == V - 32) vis1 = pann_key_id(cur); }
+      else if (lane == 0) visid[V] = pann_key_id(cur);
       V++;
       const bool full = (F == B);
       const float cutoff = full ? pann_key_dist(pann_shfl64(fk, F - 1)) : 2147483648.0f;  // (float)INT_MAX (:150-152)
+      // Early drop (beams < 16, where every hop with a candidate merges): with the cut rule on and more than k entries, a
+      // candidate that sorts after the whole frontier AND after the cut threshold of the CURRENT k-th entry is inserted
+      // and cut again by the very same merge (:190-195; the new threshold can only be lower), so it never matters.
+      u64 drop_above = ~0ull;
+      if (A.cut_rule && F > A.k && B < 16) {
+        const float thr0 = (float)(A.cut * (double)pann_key_dist(pann_shfl64(fk, A.k)));
+        const u64 tk0 = ((u64)pann_fsort(thr0) << 32) | 1ull;
+        const u64 worst = pann_shfl64(fk, F - 1) | 1ull;
+        drop_above = tk0 > worst ? tk0 : worst;
+      }
       const int ne = min(deg, A.degree_limit);
       nread += ne;
       for (int base = 0; base < ne; base += 32) {
@@ -145,10 +158,11 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
         const bool keep = act && !seen && ((long long)a != self);
         cmps += __popc(__ballot_sync(PANN_FULL, keep));  // :155
         const float d = pann_lane_distance<DT, METRIC, QR>(A, a, keep, qsm);
-        const bool take = keep && (d < cutoff);           // :153-158
+        const u64 key = pann_key(d, a);
+        const bool take = keep && (d < cutoff) && (key <= drop_above);  // :153-158
         const unsigned m = __ballot_sync(PANN_FULL, take);
         if (C + __popc(m) > (int)A.ccap) { status = 1; break; }  // cannot happen (ccap >= maxdeg + beam/8); guards memory
-        if (take) cand[C + __popc(m & lt_mask)] = pann_key(d, a);
+        if (take) cand[C + __popc(m & lt_mask)] = key;
         C += __popc(m);
         __syncwarp();
       }
@@ -165,8 +179,8 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
         u64 fl = 0ull;
         if (!vis_in_front) {  // a vertex that comes back after it was visited stays visited
           const uint32_t id = pann_key_id(c);
-          bool found = false;
-          for (int b0 = 0; b0 < V; b0 += 32) found |= (b0 + lane < V) && (visid[b0 + lane] == id);
+          bool found = (vis0 == id) || (vis1 == id);   // ids are < 2^31: the 0xffffffff fill never matches
+          for (int b0 = 64; b0 < V; b0 += 32) found |= (b0 + lane < V) && (visid[b0 + lane] == id);
           fl = __any_sync(PANN_FULL, found) ? 1ull : 0ull;
         }
         const u64 up = pann_shfl_up64(fk);
