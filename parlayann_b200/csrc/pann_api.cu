@@ -286,6 +286,9 @@ int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint
   uint32_t vcap = gs ? (uint32_t)vbig : (uint32_t)std::min<long long>(A.limit, std::max<long long>(2 * beam, beam + 64));
   if (vcap < 1) vcap = 1;
   if (launch_beam(idx, A, gs, vcap)) return 1;
+  if (out.after_kernel) PANN_CUDA(cudaEventRecord(out.after_kernel, idx->stream));
+  for (const auto& c : out.after)
+    if (c.dst && c.bytes) PANN_CUDA(cudaMemcpyAsync(c.dst, c.src, c.bytes, cudaMemcpyDeviceToHost, idx->stream));
   int flag = 0;
   PANN_CUDA(cudaMemcpyAsync(&flag, idx->flag.p, sizeof(int), cudaMemcpyDeviceToHost, idx->stream));
   PANN_CUDA(cudaMemcpyAsync(&idx->last_bytes, idx->bytes_ctr.p, 8, cudaMemcpyDeviceToHost, idx->stream));
@@ -304,6 +307,9 @@ int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint
     A.nq = redo.size();
     if (launch_beam(idx, A, true, (uint32_t)vbig)) return 1;
     int flag2 = 0;
+    if (out.after_kernel) PANN_CUDA(cudaEventRecord(out.after_kernel, idx->stream));
+    for (const auto& c : out.after)  // the retried queries changed the result block: copy it again
+      if (c.dst && c.bytes) PANN_CUDA(cudaMemcpyAsync(c.dst, c.src, c.bytes, cudaMemcpyDeviceToHost, idx->stream));
     PANN_CUDA(cudaMemcpyAsync(&flag2, idx->flag.p, sizeof(int), cudaMemcpyDeviceToHost, idx->stream));
     PANN_CUDA(cudaStreamSynchronize(idx->stream));
     flag = (flag & ~(1 << 1)) | flag2;
@@ -334,8 +340,17 @@ static ResLayout res_layout(uint64_t nq, uint32_t k) {
   return L;
 }
 
+static bool is_pinned_host(const void* p) {
+  if (!p) return true;
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return a.type == cudaMemoryTypeHost;
+}
+
+// host_out (may be null): {ids, dists, visited, cmps} host buffers of the batch call.  When all of them are pinned the
+// results go straight there behind the kernel and the call has ONE host synchronisation; otherwise the caller fetches.
 static int search_common(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t qstride, const uint32_t* starts,
-                         uint32_t nstarts, const pann_query_params* qp) {
+                         uint32_t nstarts, const pann_query_params* qp, void* const* host_out = nullptr, bool* delivered = nullptr) {
   ResLayout L = res_layout(nq, (uint32_t)qp->k);
   if (idx->results.reserve(L.total + 16)) return 1;
   idx->res_nq = nq; idx->res_k = (uint32_t)qp->k;
@@ -345,10 +360,16 @@ static int search_common(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint3
   o.cmps = (uint32_t*)(r + L.cmps); o.status = (int*)(r + L.status);
   int flag = 0;
   idx->last_launches = 0;
+  if (delivered) *delivered = false;
+  if (host_out && is_pinned_host(host_out[0]) && is_pinned_host(host_out[1]) && is_pinned_host(host_out[2]) && is_pinned_host(host_out[3])) {
+    const size_t kb = 4ull * nq * (uint32_t)qp->k;
+    o.after[0] = {host_out[0], o.ids, kb}; o.after[1] = {host_out[1], o.dists, kb};
+    o.after[2] = {host_out[2], o.visited, 4ull * nq}; o.after[3] = {host_out[3], o.cmps, 4ull * nq};
+    if (delivered) *delivered = true;
+  }
+  o.after_kernel = idx->ev1;
   PANN_CUDA(cudaEventRecord(idx->ev0, idx->stream));
-  if (pann_run_search(idx, d_q, nq, qstride, nullptr, starts, nstarts, qp, o, &flag)) return 1;
-  PANN_CUDA(cudaEventRecord(idx->ev1, idx->stream));
-  PANN_CUDA(cudaEventSynchronize(idx->ev1));
+  if (pann_run_search(idx, d_q, nq, qstride, nullptr, starts, nstarts, qp, o, &flag)) return 1;   // synchronises once
   PANN_CUDA(cudaEventElapsedTime(&idx->last_ms, idx->ev0, idx->ev1));
   return check_status(flag);
 }
@@ -428,8 +449,10 @@ extern "C" int pann_search_batch(pann_index* idx, const void* host_queries, uint
   PANN_CUDA(cudaSetDevice(idx->device));
   if (nq == 0) return 0;
   if (upload_queries(idx, host_queries, nq, q_stride_bytes)) return 1;
-  if (search_common(idx, idx->queries.as<uint8_t>(), nq, idx->geom.stride, starts, nstarts, qp)) return 1;
-  return fetch_results(idx, out_ids, out_dists, out_visited, out_cmps);
+  void* const host_out[4] = {out_ids, out_dists, out_visited, out_cmps};
+  bool delivered = false;
+  if (search_common(idx, idx->queries.as<uint8_t>(), nq, idx->geom.stride, starts, nstarts, qp, host_out, &delivered)) return 1;
+  return delivered ? 0 : fetch_results(idx, out_ids, out_dists, out_visited, out_cmps);
 }
 
 extern "C" int pann_search_full(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes,

@@ -57,6 +57,9 @@ struct SearchOutputs {  // device pointers (any may be null)
   uint32_t* fr_ids = nullptr; float* fr_dists = nullptr; uint32_t* n_frontier = nullptr; uint32_t fcap = 0;
   uint32_t* vis_ids = nullptr; float* vis_dists = nullptr; uint32_t* n_visited = nullptr; uint32_t vout = 0;
   int* status = nullptr;  // nq ints, required
+  // optional device->host copies enqueued right after the kernel, ahead of the one host synchronisation of the call
+  struct Copy { void* dst; const void* src; size_t bytes; } after[4] = {};
+  cudaEvent_t after_kernel = nullptr;  // recorded between the kernel and those copies
 };
 
 // Runs K1 over nq queries (device rows, or base rows self_ids) and retries visited-list overflows with the
