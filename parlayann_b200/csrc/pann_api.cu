@@ -192,6 +192,10 @@ static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap) {
   const char* force_general = getenv("PANN_K1_GENERAL");
   const bool small = !gs && B <= 32 && A.nstarts <= 32 && !A.vis_ids && !(force_general && force_general[0] == '1');
   if (small) {
+    // visited ids: 64 in registers, the rest 4 bytes each in shared memory — room for 256 costs 1 KB per warp and keeps
+    // the retry with the general kernel for truly long walks
+    vcap = (uint32_t)std::min<long long>(std::max<long long>(A.limit, 1), std::max<long long>(256, 4ll * B));
+    A.vcap = vcap;
     A.off_cand = 0;
     A.off_q = al16((size_t)A.ccap * 8);
     A.off_vis = A.off_q + g.stride;

@@ -11,6 +11,7 @@
 
 #include <chrono>
 
+#include <stdio.h>
 #include "pann_internal.h"
 #include "vamana_prune.cuh"
 
@@ -85,9 +86,10 @@ static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, De
   uint32_t bc[2] = {0, 0};
   PANN_CUDA(cudaMemcpyAsync(bc, A.big_count, 8, cudaMemcpyDeviceToHost, idx->stream));
   PANN_CUDA(cudaStreamSynchronize(idx->stream));
+  if (getenv("PANN_BUILD_VERBOSE")) fprintf(stderr, "    prune mode %d: %u tasks deferred to the long-list launch, longest %u\n", A.mode, bc[0], bc[1]);
   if (bc[0] == 0) return 0;
   // rare: candidate lists beyond the shared-memory capacity — same kernel, lists in a global scratch slab
-  A.cap = bc[1];
+  A.cap = 1024; while (A.cap < bc[1]) A.cap <<= 1;   // power of two: the long-list path sorts bitonically in place
   A.task_map = A.big_list; A.ntask_map = bc[0];
   A.off_b = 0; A.off_q = 0;
   A.warp_bytes = g.stride;
@@ -219,6 +221,10 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
       cudaEventRecord(ev[3], s);
       PANN_CUDA(cudaEventSynchronize(ev[3]));
       for (int i = 0; i < 3; i++) { float ms = 0; cudaEventElapsedTime(&ms, ev[i], ev[i + 1]); ph[i] += ms * 1e-3; }
+      if (getenv("PANN_BUILD_VERBOSE")) {
+        float m0, m1, m2; cudaEventElapsedTime(&m0, ev[0], ev[1]); cudaEventElapsedTime(&m1, ev[1], ev[2]); cudaEventElapsedTime(&m2, ev[2], ev[3]);
+        fprintf(stderr, "  batch %lld size %u: search+prune %.2f ms, group %.2f ms, reverse %.2f ms\n", (long long)b, bs, m0, m1, m2);
+      }
     }
   }
   for (auto& e : ev) cudaEventDestroy(e);

@@ -137,19 +137,38 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
     if (A.mode == 0 && deg == 0) {
       S = bufA;
     } else {
-      for (int i = lane; i < C; i += 32) {
-        u64 ci = bufA[i];
-        int r = 0;
-        for (int j = 0; j < C; j++) { u64 cj = bufA[j]; r += (cj < ci) || (cj == ci && j < i); }
-        bufB[r] = ci;
+      const u64* src = bufB;
+      if constexpr (GS) {
+        // long lists (a hub that collected thousands of reverse edges in one batch): bitonic sort in place, O(C log^2 C)
+        // instead of the rank sort's O(C^2).  Equal keys are identical (same vertex, same distance): order is moot.
+        int msz = 2; while (msz < C) msz <<= 1;   // <= cap: the host rounds the scratch slab up to a power of two
+        for (int i = C + lane; i < msz; i += 32) bufA[i] = ~0ull;
+        __syncwarp();
+        for (int k = 2; k <= msz; k <<= 1)
+          for (int j = k >> 1; j > 0; j >>= 1) {
+            for (int i = lane; i < (msz >> 1); i += 32) {
+              const int t = 2 * i - (i & (j - 1)), q = t + j;
+              const u64 x = bufA[t], y = bufA[q];
+              if ((x > y) == ((t & k) == 0)) { bufA[t] = y; bufA[q] = x; }
+            }
+            __syncwarp();
+          }
+        src = bufA;
+      } else {
+        for (int i = lane; i < C; i += 32) {
+          u64 ci = bufA[i];
+          int r = 0;
+          for (int j = 0; j < C; j++) { u64 cj = bufA[j]; r += (cj < ci) || (cj == ci && j < i); }
+          bufB[r] = ci;
+        }
+        __syncwarp();
       }
-      __syncwarp();
       // std::unique on ids (:86-88): the same id has the same distance, so duplicates are adjacent
       int w = 0;
       for (int base = 0; base < C; base += 32) {
         int i = base + lane;
-        u64 c = i < C ? bufB[i] : 0;
-        bool keep = i < C && (i == 0 || pann_key_id(bufB[i - 1]) != pann_key_id(c));
+        u64 c = i < C ? src[i] : 0;
+        bool keep = i < C && (i == 0 || pann_key_id(src[i - 1]) != pann_key_id(c));
         unsigned km = __ballot_sync(PANN_FULL, keep);
         __syncwarp();
         if (keep) bufB[w + __popc(km & lt_mask)] = c;
