@@ -297,6 +297,19 @@ def run_ours(args, rank, local_rank, world):
         e2e_ms += (time.perf_counter() - t0) * 1e3
     barrier()
     clocks = sampler.stop()
+    # ---- the same search over a 1 000 000-query batch of the same generator (10 000 queries are about
+    #      two waves of warps on one B200, so the steady-state rate of the kernel is reported next to the headline)
+    big = None
+    if args.big_batch > 0:
+        idx.synthetic_queries(args.big_batch, kind="uint8", seed=1234, stream=1000 + rank)
+        idx.search_resident(**qp)
+        bm, bb = 0.0, 0
+        for _ in range(3):
+            l2_flush(); idx.search_resident(**qp)
+            bm += idx.last_timing()[0]; bb += idx.last_bytes()
+        big_ms = allmax(bm / 3)
+        big = {"queries_per_gpu": args.big_batch, "value": world * args.big_batch / (big_ms * 1e-3), "unit": "queries/s", "ms_per_step": big_ms,
+               "roofline_frac": (bb / 3) / (bm / 3 * 1e-3) / 1e9 / float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0)) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else None}
     ms_per_step = allmax(dev_ms / args.steps)
     e2e_ms_per_step = allmax(e2e_ms / args.steps)
     launches_all = int(allmax(launches))  # per rank (identical on every rank)
@@ -323,12 +336,14 @@ def run_ours(args, rank, local_rank, world):
                 "clocks": clocks,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                              "traffic": traffic, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
-                             "algorithmic_bytes_per_launch": abytes / args.steps, "kernel": "pann_beam_search_kernel<u8,L2>"},
+                             "algorithmic_bytes_per_launch": abytes / args.steps, "kernel": "pann_beam_search_small_kernel<u8,L2> (beam <= 32) / pann_beam_search_kernel<u8,L2>"},
                 "wall_ms_per_step_incl_l2_flush": wall_ms / args.steps,
                 "build": {"seconds": build_s, "phase_seconds": {"beam_search+prune": phases[0], "bidirect": phases[1], "reverse_prune": phases[2]},
                           "launches": build_launches, "what": f"pann_vamana_build {n}x128 u8 R=64 L=128 alpha=1.2, final sort incl."},
                 "groundtruth": {"seconds": gt_s, "device_ms": gt_ms, "what": f"{nq} x {n} x 128 u8, k=100"},
                 "setup_seconds": setup_s}
+        if big is not None:
+            line["throughput_batch"] = big
         if world == 1 and not args.no_cpu_baseline:
             try:
                 line["cpu_baseline"] = cpu_baseline(args, idx, queries, gt_ids, gt_d, s)
@@ -368,6 +383,7 @@ def main():
     ap.add_argument("--nq", type=int, default=10000)
     ap.add_argument("--profile", action="store_true", help="cudaProfilerStart/Stop around the timed device-resident steps")
     ap.add_argument("--no-cpu-baseline", dest="no_cpu_baseline", action="store_true")
+    ap.add_argument("--big-batch", dest="big_batch", type=int, default=1000000, help="extra steady-state measurement over this many queries (0 = off)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

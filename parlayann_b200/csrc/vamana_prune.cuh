@@ -37,6 +37,8 @@ struct PruneArgs {
   const uint32_t* task_map; uint32_t ntask_map;  // GS launch: the deferred tasks
   u64* g_scratch;                                 // GS launch: per warp 2 x cap keys
   uint32_t off_b, off_q, warp_bytes;
+  // row cache (shared memory): the rows of up to rc_rows candidates, rc_pitch bytes apart, and their slot numbers
+  uint32_t rc_rows, rc_pitch, off_rc, off_pos;
 };
 
 template <int DT, int METRIC, int QR, bool GS>
@@ -45,8 +47,9 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
   const unsigned lt_mask = (1u << lane) - 1u;
   uint8_t* ws = pann_smem + (size_t)wic * A.warp_bytes;
-  const long long wglobal = (long long)blockIdx.x * PANN_PRUNE_WARPS + wic;
-  const long long wstride = (long long)gridDim.x * PANN_PRUNE_WARPS;
+  const int wpc = blockDim.x >> 5;  // warps per CTA: PANN_PRUNE_WARPS, fewer when the row cache needs the shared memory
+  const long long wglobal = (long long)blockIdx.x * wpc + wic;
+  const long long wstride = (long long)gridDim.x * wpc;
   u64 *bufA, *bufB;
   if constexpr (GS) {
     bufA = A.g_scratch + (u64)wglobal * 2 * A.cap;
@@ -181,6 +184,53 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
     uint32_t* outp = A.mode == 0 ? A.new_out + (u64)task * A.R : grow + 1;
     int start = 0, n = C;
     uint32_t m = 0;
+    if (!GS && A.rc_rows && C <= (int)A.rc_rows) {
+      // Row cache: every candidate row is fetched ONCE (all gathers in flight together) into shared memory; the scan
+      // below — up to R picks, each a pass over the live candidates — then never leaves the SM.  Without it each pick
+      // costs two dependent trips to L2/HBM (the picked row, then the live rows), ~130 per pruned vertex.
+      uint4* rc = reinterpret_cast<uint4*>(ws + A.off_rc);
+      uint16_t* P = reinterpret_cast<uint16_t*>(ws + A.off_pos);  // cache slot of S[i], compacted with S
+      const uint32_t pw = A.rc_pitch / 16;
+      for (int i = lane; i < C * (int)A.nch; i += 32) {
+        const int r = i / (int)A.nch, ch = i - r * (int)A.nch;
+        rc[r * pw + ch] = pann_ldg16(A.points + (u64)pann_key_id(S[r]) * A.stride + ch * 16);
+      }
+      for (int i = lane; i < C; i += 32) P[i] = (uint16_t)i;
+      __syncwarp();
+      while (m < A.R && start < n) {
+        const u64 ps = S[start];
+        const uint4* qrow = rc + (uint32_t)P[start] * pw;
+        start++;
+        const uint32_t ps_id = pann_key_id(ps);
+        if (ps_id == p) continue;
+        if (lane == 0) outp[m] = ps_id;
+        m++;
+        const int cnt = n - start;
+        if (cnt == 0) break;
+        comps += cnt;  // one distance per live later candidate (:108)
+        int w = start;
+        for (int base = 0; base < cnt; base += 32) {
+          const int r = base + lane;
+          const bool ok = r < cnt;
+          u64 key = 0;
+          uint16_t slot = 0;
+          DistAcc<DT, METRIC> acc;
+          if (ok) {
+            key = S[start + r];
+            slot = P[start + r];
+            const uint4* row = rc + (uint32_t)slot * pw;
+            for (int c = 0; c < (int)A.nch; c++) acc.add(row[c], qrow[c]);
+          }
+          const float d = acc.result();
+          const bool keep = ok && !(A.alpha * (double)d <= (double)pann_key_dist(key));  // :111
+          const unsigned km = __ballot_sync(PANN_FULL, keep);
+          if (keep) { const int o = w + __popc(km & lt_mask); S[o] = key; P[o] = slot; }
+          w += __popc(km);
+          __syncwarp();
+        }
+        n = w;
+      }
+    } else {
     while (m < A.R && start < n) {
       const u64 ps = S[start];
       start++;
@@ -202,6 +252,7 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
           });
       __syncwarp();
       n = w;
+    }
     }
     if (lane == 0) {
       if (A.mode == 0) {

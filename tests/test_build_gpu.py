@@ -74,3 +74,13 @@ def test_build_errors():
         idx.build(R=16, L=16)
     with pytest.raises(P.PannError):
         idx.build(R=8, L=0)
+
+
+@pytest.mark.parametrize("data_type,metric,n,d,R,L,passes", [
+    ("uint8", "Euclidian", 20000, 128, 32, 64, 1), ("uint8", "Euclidian", 6000, 128, 64, 128, 2),
+    ("int8", "mips", 6000, 100, 24, 48, 2), ("float", "Euclidian", 5000, 48, 24, 48, 1),
+])
+def test_build_with_row_cache_matches_oracle(dataset, data_type, metric, n, d, R, L, passes, monkeypatch):
+    """K3 with the candidate rows cached in shared memory (the path large builds take) writes the same graph"""
+    monkeypatch.setenv("PANN_PRUNE_ROW_CACHE", "1")
+    test_build_matches_oracle(dataset, data_type, metric, n, d, R, L, passes)
