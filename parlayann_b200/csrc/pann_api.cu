@@ -201,7 +201,8 @@ static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap) {
     A.off_vis = A.off_q + g.stride;
     A.off_hash = A.off_vis + al16((size_t)vcap * 4);
     A.warp_bytes = A.off_hash + (4u << A.bits);
-    const size_t cta_bytes = (size_t)A.warp_bytes * PANN_WARPS_PER_CTA;
+    size_t cta_bytes = (size_t)A.warp_bytes * PANN_WARPS_PER_CTA;
+    if (const char* e = getenv("PANN_K1_PAD_SMEM")) cta_bytes += (size_t)atoi(e);   // experiments: fewer CTAs per SM, more L1
     const void* fn = beam_small_kernel(idx->dtype, idx->metric, qrT);
     PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
     int per_sm = 0;
