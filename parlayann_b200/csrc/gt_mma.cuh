@@ -3,7 +3,7 @@
 // compute_groundtruth (data_tools/compute_groundtruth.cpp:22-60) scans every base row per query.  Here a CTA owns 128
 // queries (the A operand, M = 128, loaded once by TMA) and streams 256-row tiles of the base set (B operand, N = 256)
 // through a 4-stage TMA pipeline; one elected thread issues tcgen05.mma (kind::i8 for uint8/int8 rows — exact int32 dot
-// products; kind::tf32 for float rows) into a double-buffered 2 x 256-column TMEM accumulator; eight epilogue warps read
+// products; kind::tf32 for float rows) into a double-buffered 2 x 256-column TMEM accumulator; sixteen epilogue warps read
 // the accumulators back with tcgen05.ld and keep only the rows that can still enter the query's top-k:
 //      |b|^2 - 2 q.b  <=  T_q          (L2;  T_q = tau_q + margin_q - |q|^2,  tau_q = current k-th distance)
 //            - 2 q.b  <=  T_q          (MIPS; T_q = 2 (tau_q + margin_q))
