@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libpann_cuda.so")
+LIB_PATH = os.environ.get("PANN_LIB_PATH") or os.path.join(_HERE, "libpann_cuda.so")  # the override is for A/B builds of the same ABI
 
 DTYPE = {"float": 0, "uint8": 1, "int8": 2}
 METRIC = {"Euclidian": 0, "mips": 1}

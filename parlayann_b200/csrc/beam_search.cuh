@@ -51,6 +51,7 @@ struct BeamArgs {
   // algorithmic bytes of the batch (B_q = cmps*row + sum_hops 4*(1+nbrs read) + row + 4k), one atomic per query
   u64* bytes_total; uint32_t rowbytes;
   uint32_t* qcounter;                        // optional: dynamic query distribution (zeroed before the launch)
+  uint32_t tune;                             // K1s: bit 0 = always prefetch neighbour rows to L2, bit 1 = never (default: only while the launch drains)
   // global scratch (GS variant): per resident warp
   uint32_t* g_hash; u64* g_vis;
 };
@@ -85,19 +86,88 @@ __device__ __forceinline__ int pann_count_below(const u64* a, int n, u64 t) {  /
 __device__ __forceinline__ int pann_lower_bound(const u64* a, int n, u64 t) { return pann_count_below(a, n, t); }       // #{x>>1 <  t>>1}
 __device__ __forceinline__ int pann_upper_bound(const u64* a, int n, u64 t) { return pann_count_below(a, n, t + 2); }   // #{x>>1 <= t>>1}
 
+// Integer rows of exactly 128 bytes (QR == 8, uint8 / int8): FOUR lanes share a row.  `a` is this lane's row id and bit l
+// of keepmask says whether lane l has one.  Lane 4r + s loads chunks s and s + 4 of the rows of lanes 8g + r, g = 0..3
+// (two 128-bit loads 64 bytes apart: the four lanes of a row touch its 128-byte line with two requests instead of
+// eight, which is what the L1 data stage counts); the partial sums are folded across the quad by a transposing
+// reduction (3 shuffles for 32 rows) and one more shuffle hands every lane the sum of its own row.  qsm = the query
+// row in shared memory.  Integer sums are exact in any order, so the result is bit-identical to the
+// sequential loop; float rows keep that loop (their order is part of the result).
+__device__ __forceinline__ uint4 pann_lds16_volatile(const uint4* p) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"((unsigned)__cvta_generic_to_shared(p)));
+  return v;
+}
+// two 128-bit loads 64 bytes apart, issued only if `on` (the registers are left undefined otherwise: callers ignore them)
+__device__ __forceinline__ void pann_ldg16x2_if(const uint8_t* p, unsigned on, uint4& v0, uint4& v1) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.u32 p, %9, 0;\n\t"
+      "@p ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%8];\n\t"
+      "@p ld.global.nc.v4.u32 {%4,%5,%6,%7}, [%8+64];\n\t}"
+      : "=r"(v0.x), "=r"(v0.y), "=r"(v0.z), "=r"(v0.w), "=r"(v1.x), "=r"(v1.y), "=r"(v1.z), "=r"(v1.w)
+      : "l"(p), "r"(on));
+}
+template <int DT, int QR> __host__ __device__ constexpr bool pann_quad_rows() { return QR == 8 && DT != PANN_DT_F32; }
+template <int DT, int METRIC, class RG>
+__device__ __forceinline__ float pann_quad_distance(const RG& A, uint32_t a, unsigned keepmask, const uint4* qsm, int lane) {
+  const int sub = lane & 3, rowi = lane >> 2;
+  // all eight loads go out before anything is consumed (volatile asm keeps them in program order: left to itself the
+  // compiler, short of registers, interleaves loads and arithmetic and serialises the two halves of the rows)
+  uint4 v[4][2];
+#pragma unroll
+  for (int g = 0; g < 4; g++) {
+    const int src = g * 8 + rowi;
+    const uint32_t ag = __shfl_sync(PANN_FULL, a, src);
+#ifdef PANN_QUAD_ASM
+    pann_ldg16x2_if(A.points + (u64)ag * A.stride + sub * 16, (keepmask >> src) & 1u, v[g][0], v[g][1]);
+#else
+    v[g][0] = v[g][1] = make_uint4(0u, 0u, 0u, 0u);
+    if ((keepmask >> src) & 1u) {
+      const uint8_t* row = A.points + (u64)ag * A.stride + sub * 16;
+      v[g][0] = pann_ldg16(row);
+      v[g][1] = pann_ldg16(row + 64);
+    }
+#endif
+  }
+  const uint4 q0 = pann_lds16_volatile(qsm + sub), q1 = pann_lds16_volatile(qsm + sub + 4);
+  DistAcc<DT, METRIC> acc[4];
+#pragma unroll
+  for (int g = 0; g < 4; g++) { acc[g].add(v[g][0], q0); acc[g].add(v[g][1], q1); }
+  unsigned part[4];
+#pragma unroll
+  for (int g = 0; g < 4; g++) part[g] = (unsigned)acc[g].acc;
+  const bool b1 = (lane & 2) != 0, b0 = (lane & 1) != 0;
+  const unsigned r0 = (b1 ? part[2] : part[0]) + __shfl_xor_sync(PANN_FULL, b1 ? part[0] : part[2], 2);
+  const unsigned r1 = (b1 ? part[3] : part[1]) + __shfl_xor_sync(PANN_FULL, b1 ? part[1] : part[3], 2);
+  const unsigned tot = (b0 ? r1 : r0) + __shfl_xor_sync(PANN_FULL, b0 ? r0 : r1, 1);
+  // lane 4r + s now holds the sum of the row of lane 8s + r; the row of lane l = 8g + r sits in lane 4r + g
+  const unsigned mine = __shfl_sync(PANN_FULL, tot, (lane & 7) * 4 + (lane >> 3));
+  DistAcc<DT, METRIC> res;
+  res.acc = (decltype(res.acc))mine;
+  return res.result();
+}
+
 // Distances from the query to `cnt` rows, one row per lane, 32 rows per pass; row r is pann_key_id(keyOf(r))
 // (a 64-bit tag whose id field names the row, so callers can carry a (dist,id) key through).  Calls
 // emit(tag, dist, valid) warp-uniformly once per pass; lane l carries row base + l, so ballot-ranked stores in
 // emit keep the rows in order.  The query is read from shared memory (qsm, broadcast reads).  QR > 0: rows have
 // exactly QR chunks and the loop is unrolled with all QR loads in flight; QR == 0: any row length, 8 loads in flight.
 // RG: anything with points / stride / nch (BeamArgs, PruneArgs, ...).
-template <int DT, int METRIC, int QR, class RG, class KeyOf, class Emit>
+// QUAD: use pann_quad_distance where the row shape allows it (the beam search does; the prune kernel keeps the
+// one-row-per-lane loop, whose 40 registers buy it 48 resident warps per SM).
+template <int DT, int METRIC, int QR, bool QUAD = false, class RG, class KeyOf, class Emit>
 __device__ __forceinline__ void pann_row_distances_g(const RG& A, KeyOf keyOf, int cnt, const uint4* qsm, int lane,
                                                      Emit emit) {
   for (int base = 0; base < cnt; base += 32) {
     const int r = base + lane;
     const bool ok = r < cnt;
     u64 tag = 0;
+    if constexpr (QUAD && pann_quad_rows<DT, QR>()) {
+      if (ok) tag = keyOf(r);
+      const float d = pann_quad_distance<DT, METRIC>(A, pann_key_id(tag), __ballot_sync(PANN_FULL, ok), qsm, lane);
+      emit(tag, d, ok);
+      continue;
+    }
     DistAcc<DT, METRIC> acc;
     if (ok) {
       tag = keyOf(r);
@@ -126,7 +196,7 @@ __device__ __forceinline__ void pann_row_distances_g(const RG& A, KeyOf keyOf, i
 template <int DT, int METRIC, int QR, class RG, class Emit>
 __device__ __forceinline__ void pann_row_distances(const RG& A, const uint32_t* ids, int cnt, const uint4* qsm, int lane,
                                                    Emit emit) {
-  pann_row_distances_g<DT, METRIC, QR>(
+  pann_row_distances_g<DT, METRIC, QR, true>(
       A, [&](int r) { return (u64)ids[r] << 1; }, cnt, qsm, lane,
       [&](u64 tag, float d, bool ok) { emit(pann_key_id(tag), d, ok); });
 }

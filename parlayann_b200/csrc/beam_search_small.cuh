@@ -41,6 +41,7 @@ __device__ __forceinline__ float pann_lane_distance(const BeamArgs& A, uint32_t 
   }
   return acc.result();
 }
+__device__ __forceinline__ void pann_prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ u64 pann_shfl64(u64 x, int src) {
   const uint32_t lo = __shfl_sync(PANN_FULL, (uint32_t)x, src), hi = __shfl_sync(PANN_FULL, (uint32_t)(x >> 32), src);
   return ((u64)hi << 32) | lo;
@@ -51,7 +52,10 @@ __device__ __forceinline__ u64 pann_shfl_up64(u64 x) {
 }
 
 template <int DT, int METRIC, int QR>
-__global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_beam_search_small_kernel(const BeamArgs A) {
+#ifndef PANN_K1S_MINB
+#define PANN_K1S_MINB 7  // 72 registers: at 64 the compiler interleaves the row loads with arithmetic (fewer rows in flight per warp); measured 8 / 7 / 6 CTAs per SM: 55.0 / 51.6 / 57.8 ms per 1M queries at 10M points
+#endif
+__global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MINB : 4) pann_beam_search_small_kernel(const BeamArgs A) {
   extern __shared__ __align__(16) uint8_t pann_smem[];
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
   const unsigned lt_mask = (1u << lane) - 1u;
@@ -62,25 +66,36 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
   uint32_t* hashf = reinterpret_cast<uint32_t*>(ws + A.off_hash);
   const uint32_t hmask = (1u << A.bits) - 1u;
   const int B = A.beam;
-  const long long wglobal = (long long)blockIdx.x * PANN_WARPS_PER_CTA + wic;
-  const long long wstride = (long long)gridDim.x * PANN_WARPS_PER_CTA;
-  auto next_query = [&](long long ql) -> long long {
+  // query indices fit 32 bits (the host checks nq < 2^31): narrow scalars keep the register file for the gathers
+  const int wglobal = (int)blockIdx.x * PANN_WARPS_PER_CTA + wic;
+  const int wstride = (int)gridDim.x * PANN_WARPS_PER_CTA;
+  const int nq = (int)A.nq;
+  const int limit = (int)(A.limit < 0x7fffffffll ? A.limit : 0x7fffffffll);
+  auto next_query = [&](int ql) -> int {
     if (!A.qcounter) return ql + wstride;
     unsigned nx = 0;
     if (lane == 0) nx = atomicAdd(A.qcounter, 1u);
-    return wstride + (long long)__shfl_sync(PANN_FULL, nx, 0);
+    return (int)min((unsigned)wstride + __shfl_sync(PANN_FULL, nx, 0), 0x7fffffffu);
   };
-  for (long long ql = wglobal; ql < (long long)A.nq; ql = next_query(ql)) {
-    const long long q = A.qmap ? (long long)A.qmap[ql] : ql;
+  for (int ql = wglobal; ql < nq; ql = next_query(ql)) {
+    const int q = A.qmap ? (int)A.qmap[ql] : ql;
     {
       const uint4 ones = make_uint4(~0u, ~0u, ~0u, ~0u);
       uint4* h4 = reinterpret_cast<uint4*>(hashf);
       for (int i = lane; i < (1 << A.bits) / 4; i += 32) h4[i] = ones;
     }
-    const long long self = A.self_ids ? (long long)A.self_ids[q] : -1;
+    const uint32_t self = A.self_ids ? A.self_ids[q] : 0xffffffffu;  // ids are < 2^31
     const uint8_t* qrow = A.self_ids ? A.points + (u64)self * A.stride : A.queries + (u64)q * A.qstride;
     pann_load_query(qrow, A.nch, qsm, lane);
+    constexpr bool QUAD = pann_quad_rows<DT, QR>();
 
+    // row prefetch policy (see the main loop): always, or — for the queries handed out last — once half the warps retired
+    const bool always_pf = (A.tune & 1u) != 0;
+#ifdef PANN_NO_DRAIN
+    const bool drain_watch = false;
+#else
+    const bool drain_watch = !always_pf && A.qcounter && !(A.tune & 2u) && (ql + wstride >= nq);
+#endif
     u64 fk = ~0ull;  // frontier entry `lane` ((dist,id) key, bit 0 = visited), ~0 beyond the frontier
     int F = 0, V = 0, C = 0, status = 0;
     uint32_t vis0 = 0xffffffffu, vis1 = 0xffffffffu;  // visited ids V = lane and lane + 32 (later ones: shared memory)
@@ -92,7 +107,9 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
     } else {
       const bool on = lane < (int)A.nstarts;
       const uint32_t a = on ? A.starts[lane] : 0u;
-      const float d = pann_lane_distance<DT, METRIC, QR>(A, a, on, qsm);
+      float d;
+      if constexpr (QUAD) d = pann_quad_distance<DT, METRIC>(A, a, __ballot_sync(PANN_FULL, on), qsm, lane);
+      else d = pann_lane_distance<DT, METRIC, QR>(A, a, on, qsm);
       const u64 key = on ? pann_key(d, a) : ~0ull;
       if (lane == 0)
         for (uint32_t i = 0; i < A.nstarts; i++) { const uint32_t s = A.starts[i]; hashf[(uint32_t)pann_hash64_2(s) & hmask] = s; }
@@ -111,12 +128,14 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
     // ---- main loop (:107-209)
     while (status == 0) {
       const unsigned unv = __ballot_sync(PANN_FULL, lane < F && !(fk & 1ull));
-      if (!unv || (long long)V >= A.limit) break;
+      if (!unv || V >= limit) break;
       const int pos = __ffs(unv) - 1;
       const bool vis_in_front = (F - __popc(unv)) == V;  // every visited vertex is still a (flagged) frontier entry
       const bool more_after = __popc(unv) > 1;           // offset + 1 < remain (:164)
       const u64 cur = pann_shfl64(fk, pos);
       const uint32_t* grow = A.graph + (u64)pann_key_id(cur) * (A.maxdeg + 1);
+      uint32_t drain_cnt = 0;  // read next to the graph row, so its latency is hidden under that load
+      if (drain_watch) asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(drain_cnt) : "l"(A.qcounter));
       const int deg = (int)__ldg(grow);
       const uint32_t a0 = (lane < (int)A.maxdeg) ? __ldg(grow + 1 + lane) : 0u;
       const uint32_t a1 = (32 + lane < (int)A.maxdeg) ? __ldg(grow + 33 + lane) : 0u;
@@ -140,6 +159,16 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
       }
       const int ne = min(deg, A.degree_limit);
       nread += ne;
+      // L2 prefetch of every neighbour row, issued before the filter runs, takes one memory latency out of the hop.  It
+      // pays when the memory system has slack — rows mostly L2-resident (tune bit 0, set by the host for small point
+      // sets), or the launch is draining: every warp that runs out of queries still bumps the query counter, so
+      // counter - (nq - warps) = retired warps (only the last `warps` queries of a launch look at it).  Under a saturated gather stream (10M points, all warps busy) the extra
+      // requests cost more than the latency they hide (measured: -40 % throughput), so it stays off there.
+      const bool pf = always_pf || (drain_watch && ((long long)drain_cnt + wstride - nq) * 2 >= wstride);
+      if (pf) {
+        if (lane < ne) pann_prefetch_l2(A.points + (u64)a0 * A.stride);
+        if (32 + lane < ne) pann_prefetch_l2(A.points + (u64)a1 * A.stride);
+      }
       for (int base = 0; base < ne; base += 32) {
         const int i = base + lane;
         const bool act = i < ne;
@@ -155,9 +184,12 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
         }
         __syncwarp();
         if (act && (peers >> lane) <= 1u) hashf[loc] = a;
-        const bool keep = act && !seen && ((long long)a != self);
-        cmps += __popc(__ballot_sync(PANN_FULL, keep));  // :155
-        const float d = pann_lane_distance<DT, METRIC, QR>(A, a, keep, qsm);
+        const bool keep = act && !seen && (a != self);
+        const unsigned keepmask = __ballot_sync(PANN_FULL, keep);
+        cmps += __popc(keepmask);  // :155
+        float d;
+        if constexpr (QUAD) d = pann_quad_distance<DT, METRIC>(A, a, keepmask, qsm, lane);
+        else d = pann_lane_distance<DT, METRIC, QR>(A, a, keep, qsm);
         const u64 key = pann_key(d, a);
         const bool take = keep && (d < cutoff) && (key <= drop_above);  // :153-158
         const unsigned m = __ballot_sync(PANN_FULL, take);
@@ -207,12 +239,12 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? 8 : 4) pann_
     if (status == 0 && F < A.k) status = 2;  // beamSearch.h:416-419
     if (A.out_ids && lane < A.k) {
       const bool ok = lane < F;
-      A.out_ids[q * A.k + lane] = ok ? pann_key_id(fk) : 0xffffffffu;
-      if (A.out_dists) A.out_dists[q * A.k + lane] = ok ? pann_key_dist(fk) : 0.f;
+      A.out_ids[(u64)q * A.k + lane] = ok ? pann_key_id(fk) : 0xffffffffu;
+      if (A.out_dists) A.out_dists[(u64)q * A.k + lane] = ok ? pann_key_dist(fk) : 0.f;
     }
     if (A.fr_ids && lane < F && lane < (int)A.fcap) {
-      A.fr_ids[q * A.fcap + lane] = pann_key_id(fk);
-      A.fr_dists[q * A.fcap + lane] = pann_key_dist(fk);
+      A.fr_ids[(u64)q * A.fcap + lane] = pann_key_id(fk);
+      A.fr_dists[(u64)q * A.fcap + lane] = pann_key_dist(fk);
     }
     if (lane == 0) {
       if (A.out_visited) A.out_visited[q] = V;

@@ -282,6 +282,17 @@ int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint
   A.bytes_total = idx->bytes_ctr.as<u64>(); A.rowbytes = idx->dims * idx->geom.elt;
   A.qcounter = reinterpret_cast<uint32_t*>(idx->bytes_ctr.as<u64>() + 1);
   { const char* sq = getenv("PANN_STATIC_QUERIES"); if (sq && sq[0] == '1') A.qcounter = nullptr; }
+  {  // K1s row prefetch: always while the point set is about L2-sized (most prefetches are L2 hits), else only while draining
+    const char* tn = getenv("PANN_K1S_TUNE");
+    if (tn) {
+      A.tune = (uint32_t)atoi(tn);
+    } else {
+      int dev = 0, l2 = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, dev);
+      A.tune = ((unsigned long long)idx->n * idx->geom.stride <= 2ull * (unsigned long long)l2) ? 1u : 0u;
+    }
+  }
 
   // shared-memory variant while the hash filter is <= 16 KB per warp; visited-list capacity is a guess
   // that the retry below makes safe
