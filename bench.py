@@ -1,18 +1,25 @@
 #!/usr/bin/env python
 """bench.py — QPS at recall@10 >= 0.95 of the batched beam search (BASELINE.json metric), one JSON line.
 
-Workload (config.workload): Vamana search over a synthetic BIGANN-shaped set (default 1M x 128 uint8, BASELINE.json
-configs[1]), 10 000 queries per GPU per step, graph R=64 L=128 alpha=1.2 built ON THE GPU by pann_vamana_build (the
-build time is reported too), exact ground truth from K4, QueryParams chosen by the reference's own sweep
-(check_nn_recall.h:214-257) as the cheapest setting whose tie-aware recall@10 is >= 0.95.
+Workload (config.workload): the configuration the metric is quoted on — Vamana search over a synthetic BIGANN-shaped
+10M x 128 uint8 set (BASELINE.json configs[3]; 3.9 GB of points + graph, fits one GPU), graph R=64 L=128 alpha=1.2 built
+ON THE GPU by pann_vamana_build (the build time is reported too).  A step is one pass of the search over a batch of
+1 000 000 queries per GPU (the 10 000-query set the reference ships is two waves of warps on one B200;
+throughput and scaling are quoted on the 1M batch, recall and parity on the 10 000-query batch).  QueryParams are chosen
+by the reference's own sweep (check_nn_recall.h:214-257) on the 10 000-query recall batch against exact ground truth
+from K4: the cheapest setting whose tie-aware recall@10 is >= 0.95.  `--n 1000000 --nq 10000` is configs[1].
 
   value   whole-job QPS with queries resident in HBM (device time from CUDA events on the library's stream)
   e2e     the same through pann_search_batch with pinned HOST buffers: H2D queries + search + D2H ids/dists/counters
-  roofline  algorithmic bytes of the batch (counted on the device) / K1's device time, vs measured HBM
-  cpu_baseline  the unmodified reference (oracle/_ref/ref_driver -> qsearchAll) on this box's cores, same graph
+  roofline  algorithmic bytes of the batch (counted on the device) / K1s' device time, vs measured HBM
+  recall_batch  the same search over the 10 000-query recall batch alone (latency-bound end of the curve)
+  cpu_baseline  the unmodified reference (oracle/_ref/ref_driver -> qsearchAll) on this box's cores, same graph,
+                on the 10 000-query recall batch (a bounded sample of the workload)
 
-`--impl reference` runs only the reference's CPU path (it builds its own graph and ground truth with its own code).
-Multi-GPU (torchrun): one rank per GPU, replicated index, every rank searches its own 10 000-query batch
+`--impl reference` times only the reference's CPU search (10 000-query sample per step).  Up to 2M points it also builds
+the graph and the ground truth with the reference's own code; at 10M those would take many minutes of CPU, so the inputs
+are prepared on the GPU (untimed) when one is present.
+Multi-GPU (torchrun): one rank per GPU, replicated index, every rank searches its own 1M-query batch
 (weak scaling, no data-path collective); time = max over ranks.
 """
 import argparse
@@ -132,8 +139,41 @@ def choose_setting(settings, evaluate):
     return best
 
 
+def gpu_prepared_inputs(args, tmp, local_rank=0):
+    """points / graph / recall queries / ground truth for the reference arm at sizes where the reference's own CPU build
+    and ground truth would take many minutes (10M points): made on the GPU, untimed, written in the reference's file
+    formats.  The graph is the same bytes the reference builds (tests/test_build_gpu.py, tests/test_dropin_gpu.py)."""
+    import torch
+    import parlayann_b200 as P
+    from parlayann_b200 import fileio
+    torch.cuda.set_device(local_rank)
+    idx = P.GraphIndex(data_type="uint8", metric="Euclidian", max_degree=64, device=local_rank,
+                       synthetic=dict(n=args.n, d=128, kind="uint8", seed=1234, stream=0, r=24, nc=256))
+    idx.build(R=64, L=128, alpha=1.2, num_passes=1, sort_neighbors=True)
+    idx.synthetic_queries(args.nq_recall, kind="uint8", seed=1234, stream=1)
+    qs = idx.download_queries()
+    idx.groundtruth_resident(k=100)
+    gt_ids, gt_d = idx.fetch_groundtruth()
+    cache = {}
+
+    def ev(s):
+        if s not in cache:
+            kind, k, beam, cut, limit, dl = s
+            idx.search_resident(k=k, beam=beam, cut=cut, limit=None if limit < 0 else limit, degree_limit=None if dl < 0 else dl)
+            ids, _, vis, cmps = idx.fetch_results()
+            cache[s] = (recall_with_ties(ids, gt_ids, gt_d, K), int(cmps.astype(np.int64).sum() // args.nq_recall))
+        return cache[s]
+    s, rec, cm = choose_setting(sweep_settings(64), ev)
+    files = {k: os.path.join(tmp, k) for k in ("base", "query", "graph", "gt")}
+    fileio.write_bin(files["base"], idx.points()); fileio.write_bin(files["query"], qs)
+    fileio.write_graph(files["graph"], idx.graph()); fileio.write_ibin(files["gt"], gt_ids, gt_d)
+    idx.close()
+    return files, s
+
+
 def run_reference(args, rank, world):
-    """--impl reference: everything through the reference's own code on the host cores."""
+    """--impl reference: the reference's own qsearchAll on the host cores, timed by its own checkRecall.  Each step is a
+    bounded sample of the workload: the 10 000-query recall batch (same generator, same QueryParams)."""
     if rank != 0:
         return
     O, drv = ref_tools()
@@ -141,39 +181,52 @@ def run_reference(args, rank, world):
     tmp = tempfile.mkdtemp(prefix="pann_ref_")
     try:
         t0 = time.time()
-        base = O.gen_points("uint8", args.n, 128)
-        qs = O.gen_points("uint8", args.nq, 128, stream=1)
-        files = {k: os.path.join(tmp, k) for k in ("base", "query", "graph", "gt")}
-        fileio.write_bin(files["base"], base); fileio.write_bin(files["query"], qs)
-        common = ["-data_type", "uint8", "-dist_func", "Euclidian", "-base", files["base"]]
-        out = O.ref_run(["build"] + common + ["-R", 64, "-L", 128, "-alpha", 1.2, "-out", os.path.join(tmp, "b")])
-        build_s = float(re.search(r"REF_BUILD_SECONDS (\S+)", out).group(1))
-        os.replace(os.path.join(tmp, "b.graph"), files["graph"])
-        out = O.ref_run(["gt"] + common + ["-query", files["query"], "-k", 100, "-out", os.path.join(tmp, "g")])
-        gt_s = float(re.search(r"REF_GT_SECONDS (\S+)", out).group(1))
-        os.replace(os.path.join(tmp, "g.ibin"), files["gt"])
-        settings = sweep_settings(64)
-        cache = {}
+        build_s = gt_s = None
+        gpu_setup = False
+        if args.n > 2000000:
+            try:
+                import torch
+                gpu_setup = torch.cuda.is_available()
+            except Exception:
+                gpu_setup = False
+        if gpu_setup:
+            files, s = gpu_prepared_inputs(args, tmp)
+            inputs = "points, graph, ground truth and the QueryParams choice prepared on the GPU (untimed); the timed search is the reference's"
+        else:
+            base = O.gen_points("uint8", args.n, 128)
+            qs = O.gen_points("uint8", args.nq_recall, 128, stream=1)
+            files = {k: os.path.join(tmp, k) for k in ("base", "query", "graph", "gt")}
+            fileio.write_bin(files["base"], base); fileio.write_bin(files["query"], qs)
+            common = ["-data_type", "uint8", "-dist_func", "Euclidian", "-base", files["base"]]
+            out = O.ref_run(["build"] + common + ["-R", 64, "-L", 128, "-alpha", 1.2, "-out", os.path.join(tmp, "b")])
+            build_s = float(re.search(r"REF_BUILD_SECONDS (\S+)", out).group(1))
+            os.replace(os.path.join(tmp, "b.graph"), files["graph"])
+            out = O.ref_run(["gt"] + common + ["-query", files["query"], "-k", 100, "-out", os.path.join(tmp, "g")])
+            gt_s = float(re.search(r"REF_GT_SECONDS (\S+)", out).group(1))
+            os.replace(os.path.join(tmp, "g.ibin"), files["gt"])
+            cache = {}
 
-        def ev(s):
-            if s not in cache:
-                r = ref_recall_runs(O, files, [s], 1)[0]
-                cache[s] = (r["recall"], r["avg_cmps"])
-            return cache[s]
-        (s, rec, cm) = choose_setting(settings, ev)
+            def ev(s):
+                if s not in cache:
+                    r = ref_recall_runs(O, files, [s], 1)[0]
+                    cache[s] = (r["recall"], r["avg_cmps"])
+                return cache[s]
+            s = choose_setting(sweep_settings(64), ev)[0]
+            inputs = "everything (points file, graph, ground truth, sweep) made by the reference's own code on the CPU"
         rows = ref_recall_runs(O, files, [s], args.warmup + args.steps)[args.warmup:]
-        ms = [1e3 * args.nq / r["qps"] for r in rows]
+        rec, cm = rows[0]["recall"], rows[0]["avg_cmps"]
+        ms = [1e3 * args.nq_recall / r["qps"] for r in rows]
         ms_per_step = float(np.mean(ms))
-        qps = args.nq / (ms_per_step * 1e-3)
+        qps = args.nq_recall / (ms_per_step * 1e-3)
         cores = os.cpu_count()
         line = {"impl": "reference", "metric": "QPS@recall10>=0.95", "value": qps, "unit": "queries/s", "n_gpus": args.gpus,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic",
                 "config": workload_config(args, s, rec, cm),
                 "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": "reference",
-                                 "sample": f"all {args.nq} queries per step, {args.steps} steps, qsearchAll via checkRecall"},
+                                 "sample": f"{args.nq_recall} queries of the batch per step, {args.steps} steps, qsearchAll via checkRecall"},
                 "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-                "gpu_launches": 0,
+                "gpu_launches": 0, "inputs": inputs,
                 "reference_build_seconds": build_s, "reference_groundtruth_seconds": gt_s, "setup_seconds": time.time() - t0}
         print(json.dumps(line), flush=True)
     finally:
@@ -183,9 +236,10 @@ def run_reference(args, rank, world):
 def workload_config(args, s, rec, cm):
     kind, k, beam, cut, limit, dl = s
     return {"workload": f"vamana_search_{args.n}x128_u8_{args.nq}q_per_gpu", "n": args.n, "dims": 128, "queries_per_gpu_per_step": args.nq,
-            "graph": "Vamana R=64 L=128 alpha=1.2 1 pass", "k": k, "beam": beam, "cut": cut,
+            "recall_batch": args.nq_recall, "graph": "Vamana R=64 L=128 alpha=1.2 1 pass", "k": k, "beam": beam, "cut": cut,
             "visit_limit": limit if limit >= 0 else args.n, "degree_limit": dl if dl >= 0 else 64, "recall10": rec, "avg_cmps": cm,
-            "parallelism": f"replicated index, queries sharded x{args.gpus}", "l2": "index 388 MB > L2; 256 MiB flush between steps"}
+            "parallelism": f"replicated index, queries sharded x{args.gpus}",
+            "l2": f"index {(args.n * (128 + 260)) >> 20} MB and each step's gathers >> 126 MB L2; 256 MiB flush between steps as well"}
 
 
 # ----------------------------------------------------------------------------------------------------------------
@@ -212,7 +266,7 @@ def run_ours(args, rank, local_rank, world):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    n, nq, R, L = args.n, args.nq, 64, 128
+    n, nq, nqr, R, L = args.n, args.nq, args.nq_recall, 64, 128
     # ---- setup (untimed): replicated index, points synthesised on the device, graph built on the device
     t_setup = time.time()
     idx = P.GraphIndex(data_type="uint8", metric="Euclidian", max_degree=R, device=local_rank,
@@ -222,9 +276,10 @@ def run_ours(args, rank, local_rank, world):
     build_s = time.time() - t0
     build_launches = idx.last_timing()[1]
     phases = idx.build_phase_seconds
-    # rank r searches its own query batch (generator stream 1 + r); rank 0's is the parity / recall batch
-    idx.synthetic_queries(nq, kind="uint8", seed=1234, stream=1 + rank)
-    queries = idx.download_queries()
+    # the recall batch (the reference's standard 10 000 queries, generator stream 1): exact ground truth from K4, then the
+    # reference's sweep picks the QueryParams; every rank does the same, so all ranks time the same setting
+    idx.synthetic_queries(nqr, kind="uint8", seed=1234, stream=1)
+    rqueries = idx.download_queries()
     t0 = time.time()
     idx.groundtruth_resident(k=100)
     gt_ms = idx.last_timing()[0]
@@ -242,17 +297,10 @@ def run_ours(args, rank, local_rank, world):
         if s not in cache:
             idx.search_resident(**qp_of(s))
             ids, _, vis, cmps = idx.fetch_results()
-            cache[s] = (recall_with_ties(ids, gt_ids, gt_d, K), int(cmps.astype(np.int64).sum() // nq))
+            cache[s] = (recall_with_ties(ids, gt_ids, gt_d, K), int(cmps.astype(np.int64).sum() // nqr))
         return cache[s]
-    # every rank must time the same QueryParams: rank 0's batch decides
     s, rec, cm = choose_setting(settings, ev)
-    if dist is not None:
-        obj = [s]
-        dist.broadcast_object_list(obj, src=0)
-        s = tuple(obj[0])
-        rec, cm = ev(s)
     qp = qp_of(s)
-    setup_s = time.time() - t_setup
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
@@ -260,8 +308,19 @@ def run_ours(args, rank, local_rank, world):
         flush.zero_()
         torch.cuda.synchronize()
 
-    # pinned host buffers for the end-to-end path
-    hq = torch.from_numpy(queries).pin_memory()
+    # the same setting over the 10 000-query recall batch alone: about two waves of warps on one B200, so this is the
+    # latency-bound end of the curve (SURVEY.md §8d asks for both batch sizes)
+    sm, sb = 0.0, 0
+    for i in range(3 + 10):
+        l2_flush(); idx.search_resident(**qp)
+        if i >= 3:
+            sm += idx.last_timing()[0]; sb += idx.last_bytes()
+    small_ms = allmax(sm / 10)
+    setup_s = time.time() - t_setup
+
+    # ---- the step batch: nq queries per GPU from the same generator (stream 1000 + rank)
+    idx.synthetic_queries(nq, kind="uint8", seed=1234, stream=1000 + rank)
+    hq = torch.from_numpy(idx.download_queries()).pin_memory()
     out = (torch.empty((nq, K), dtype=torch.int32).pin_memory().numpy().view(np.uint32), torch.empty((nq, K), dtype=torch.float32).pin_memory().numpy(),
            torch.empty(nq, dtype=torch.int32).pin_memory().numpy().view(np.uint32), torch.empty(nq, dtype=torch.int32).pin_memory().numpy().view(np.uint32))
     hq_np = hq.numpy()
@@ -297,19 +356,6 @@ def run_ours(args, rank, local_rank, world):
         e2e_ms += (time.perf_counter() - t0) * 1e3
     barrier()
     clocks = sampler.stop()
-    # ---- the same search over a 1 000 000-query batch of the same generator (10 000 queries are about
-    #      two waves of warps on one B200, so the steady-state rate of the kernel is reported next to the headline)
-    big = None
-    if args.big_batch > 0:
-        idx.synthetic_queries(args.big_batch, kind="uint8", seed=1234, stream=1000 + rank)
-        idx.search_resident(**qp)
-        bm, bb = 0.0, 0
-        for _ in range(3):
-            l2_flush(); idx.search_resident(**qp)
-            bm += idx.last_timing()[0]; bb += idx.last_bytes()
-        big_ms = allmax(bm / 3)
-        big = {"queries_per_gpu": args.big_batch, "value": world * args.big_batch / (big_ms * 1e-3), "unit": "queries/s", "ms_per_step": big_ms,
-               "roofline_frac": (bb / 3) / (bm / 3 * 1e-3) / 1e9 / float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))).get("hbm_gbs", 6650.0)) if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else None}
     ms_per_step = allmax(dev_ms / args.steps)
     e2e_ms_per_step = allmax(e2e_ms / args.steps)
     launches_all = int(allmax(launches))  # per rank (identical on every rank)
@@ -324,7 +370,7 @@ def run_ours(args, rank, local_rank, world):
         achieved = (abytes / args.steps) / (dev_ms / args.steps * 1e-3) / 1e9
         traffic = None
         try:
-            traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get("k1_dram_bytes_per_launch")
+            traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get(f"k1s_dram_bytes_per_launch_{n}x{nq}")
         except Exception:
             pass
         line = {"metric": "QPS@recall10>=0.95", "value": world * nq / (ms_per_step * 1e-3), "unit": "queries/s", "n_gpus": world,
@@ -338,15 +384,16 @@ def run_ours(args, rank, local_rank, world):
                              "traffic": traffic, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
                              "algorithmic_bytes_per_launch": abytes / args.steps, "kernel": "pann_beam_search_small_kernel<u8,L2> (beam <= 32) / pann_beam_search_kernel<u8,L2>"},
                 "wall_ms_per_step_incl_l2_flush": wall_ms / args.steps,
+                "recall_batch": {"queries_per_gpu": nqr, "value": world * nqr / (small_ms * 1e-3), "unit": "queries/s", "ms_per_step": small_ms,
+                                 "roofline_frac": (sb / 10) / (sm / 10 * 1e-3) / 1e9 / peak,
+                                 "what": "the same search over the 10 000-query recall batch alone (about two waves of warps: latency-bound)"},
                 "build": {"seconds": build_s, "phase_seconds": {"beam_search+prune": phases[0], "bidirect": phases[1], "reverse_prune": phases[2]},
                           "launches": build_launches, "what": f"pann_vamana_build {n}x128 u8 R=64 L=128 alpha=1.2, final sort incl."},
-                "groundtruth": {"seconds": gt_s, "device_ms": gt_ms, "what": f"{nq} x {n} x 128 u8, k=100"},
+                "groundtruth": {"seconds": gt_s, "device_ms": gt_ms, "what": f"{nqr} x {n} x 128 u8, k=100"},
                 "setup_seconds": setup_s}
-        if big is not None:
-            line["throughput_batch"] = big
         if world == 1 and not args.no_cpu_baseline:
             try:
-                line["cpu_baseline"] = cpu_baseline(args, idx, queries, gt_ids, gt_d, s)
+                line["cpu_baseline"] = cpu_baseline(args, idx, rqueries, gt_ids, gt_d, s)
             except Exception as e:  # the reference binary may be missing on a box that never saw /root/reference
                 line["cpu_baseline"] = {"value": None, "unit": "queries/s", "cores": os.cpu_count(), "kind": "reference", "sample": f"failed: {e}"}
         print(json.dumps(line), flush=True)
@@ -368,7 +415,7 @@ def cpu_baseline(args, idx, queries, gt_ids, gt_d, s):
         qps = float(np.mean([r["qps"] for r in rows]))
         return {"value": qps, "unit": "queries/s", "cores": os.cpu_count(), "kind": "reference", "recall10": rows[0]["recall"],
                 "avg_cmps": rows[0]["avg_cmps"],
-                "sample": f"all {args.nq} queries x 3 timed runs (1 warm-up) of the reference's checkRecall/qsearchAll on the GPU-built graph"}
+                "sample": f"the {args.nq_recall}-query recall batch x 3 timed runs (1 warm-up) of the reference's checkRecall/qsearchAll on the GPU-built graph"}
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
 
@@ -379,11 +426,11 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--n", type=int, default=1000000)
-    ap.add_argument("--nq", type=int, default=10000)
+    ap.add_argument("--n", type=int, default=10000000, help="base points (BASELINE.json metric: 10M x 128 uint8; 1000000 = configs[1])")
+    ap.add_argument("--nq", type=int, default=1000000, help="queries per GPU per step")
+    ap.add_argument("--nq-recall", dest="nq_recall", type=int, default=10000, help="recall / sweep batch (the reference's standard query set size)")
     ap.add_argument("--profile", action="store_true", help="cudaProfilerStart/Stop around the timed device-resident steps")
     ap.add_argument("--no-cpu-baseline", dest="no_cpu_baseline", action="store_true")
-    ap.add_argument("--big-batch", dest="big_batch", type=int, default=1000000, help="extra steady-state measurement over this many queries (0 = off)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

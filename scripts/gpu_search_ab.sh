@@ -6,6 +6,6 @@ for n in 1000000 10000000; do
   python - $n <<'PY'
 import json, sys
 d = json.loads(open("gpurun_out/sab_%s.json" % sys.argv[1]).read().strip().splitlines()[-1])
-print(sys.argv[1], "QPS %.3fM ms %.4f e2e %.3fM frac %.3f" % (d["value"]/1e6, d["ms_per_step"], d["e2e"]["value"]/1e6, d["roofline"]["frac"]), "big", d.get("throughput_batch"), "build", round(d["build"]["seconds"], 2), d["config"]["beam"], d["config"]["recall10"], d["config"]["avg_cmps"])
+print(sys.argv[1], "QPS %.3fM ms %.4f e2e %.3fM frac %.3f" % (d["value"]/1e6, d["ms_per_step"], d["e2e"]["value"]/1e6, d["roofline"]["frac"]), "recall_batch", d.get("recall_batch"), "build", round(d["build"]["seconds"], 2), d["config"]["beam"], d["config"]["recall10"], d["config"]["avg_cmps"])
 PY
 done
