@@ -112,6 +112,10 @@ extern "C" void pann_index_destroy(pann_index* idx) {
   idx->bytes_ctr.release(); idx->starts.release(); idx->flag.release(); idx->qmap.release(); idx->misc.release();
   idx->gt_ids.release(); idx->gt_dists.release();
   if (idx->pinned) cudaFreeHost(idx->pinned);
+  for (cudaEvent_t e : idx->pipe_ev) cudaEventDestroy(e);
+  if (idx->stream2) cudaStreamDestroy(idx->stream2);
+  if (idx->s_in) cudaStreamDestroy(idx->s_in);
+  if (idx->s_out) cudaStreamDestroy(idx->s_out);
   if (idx->ev0) cudaEventDestroy(idx->ev0);
   if (idx->ev1) cudaEventDestroy(idx->ev1);
   if (idx->stream) cudaStreamDestroy(idx->stream);
@@ -182,7 +186,8 @@ static const void* beam_small_kernel(int dtype, int metric, int qr) {
   }
 }
 
-static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap) {
+static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap, cudaStream_t stream = nullptr) {
+  if (!stream) stream = idx->stream;
   const PannRowGeom& g = idx->geom;
   const int qrT = pann_qr_of(g);
   const uint32_t B = (uint32_t)A.beam;
@@ -212,7 +217,7 @@ static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap) {
     int grid = (int)std::min<long long>(want, (long long)per_sm * idx->sms);
     if (grid < 1) grid = 1;
     void* args[] = {(void*)&A};
-    PANN_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(PANN_WARPS_PER_CTA * 32), args, cta_bytes, idx->stream));
+    PANN_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(PANN_WARPS_PER_CTA * 32), args, cta_bytes, stream));
     idx->last_launches++;
     return 0;
   }
@@ -242,27 +247,29 @@ static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap) {
     A.g_vis = idx->scratch_vis.as<u64>();
   }
   void* args[] = {(void*)&A};
-  PANN_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(PANN_WARPS_PER_CTA * 32), args, cta_bytes, idx->stream));
+  PANN_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(PANN_WARPS_PER_CTA * 32), args, cta_bytes, stream));
   idx->last_launches++;
   return 0;
 }
 
-int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint32_t qstride, const uint32_t* d_self_ids,
-                    const uint32_t* h_starts, uint32_t nstarts, const pann_query_params* qp, const SearchOutputs& out,
-                    int* status_or) {
+// validates, uploads the start points, zeroes the counters and the status flag, fills the kernel arguments
+struct BeamPlan { BeamArgs A; bool gs; uint32_t vcap; long long vbig; };
+#define PANN_MAX_CHUNKS 64
+static int beam_plan(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint32_t qstride, const uint32_t* d_self_ids,
+                     const uint32_t* h_starts, uint32_t nstarts, const pann_query_params* qp, const SearchOutputs& out,
+                     BeamPlan& P) {
   if (nstarts == 0 || !h_starts) PANN_FAIL("beam search expects at least one start point");  // beamSearch.h:38-41
   if (qp->beam < 1 || qp->beam > 65536) PANN_FAIL("beam search: beam width out of range");
   if (qp->k < 0) PANN_FAIL("beam search: k must be non-negative");
   for (uint32_t i = 0; i < nstarts; i++)
     if (h_starts[i] >= idx->n) PANN_FAIL("beam search: start point out of range");
-  *status_or = 0;
-  if (nq == 0) return 0;
-  if (idx->starts.reserve(sizeof(uint32_t) * nstarts) || idx->flag.reserve(sizeof(int)) || idx->bytes_ctr.reserve(16)) return 1;
-  PANN_CUDA(cudaMemsetAsync(idx->bytes_ctr.p, 0, 16, idx->stream));
+  if (nq >= 0x7fffffffull) PANN_FAIL("beam search: more than 2^31 - 1 queries in one call");
+  if (idx->starts.reserve(sizeof(uint32_t) * nstarts) || idx->flag.reserve(sizeof(int)) || idx->bytes_ctr.reserve(16 + 4 * PANN_MAX_CHUNKS)) return 1;
+  PANN_CUDA(cudaMemsetAsync(idx->bytes_ctr.p, 0, 16 + 4 * PANN_MAX_CHUNKS, idx->stream));
   PANN_CUDA(cudaMemcpyAsync(idx->starts.p, h_starts, sizeof(uint32_t) * nstarts, cudaMemcpyHostToDevice, idx->stream));
   PANN_CUDA(cudaMemsetAsync(idx->flag.p, 0, sizeof(int), idx->stream));
 
-  BeamArgs A;
+  BeamArgs& A = P.A;
   memset(&A, 0, sizeof(A));
   A.points = idx->points; A.n = idx->n; A.stride = idx->geom.stride; A.nch = idx->geom.nch;
   A.graph = idx->graph; A.maxdeg = idx->maxdeg;
@@ -301,6 +308,24 @@ int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint
   const long long vbig = std::min<long long>(A.limit, std::max<long long>(8 * beam + 4096, 16384));
   uint32_t vcap = gs ? (uint32_t)vbig : (uint32_t)std::min<long long>(A.limit, std::max<long long>(2 * beam, beam + 64));
   if (vcap < 1) vcap = 1;
+  P.gs = gs; P.vcap = vcap; P.vbig = vbig;
+  return 0;
+}
+
+int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint32_t qstride, const uint32_t* d_self_ids,
+                    const uint32_t* h_starts, uint32_t nstarts, const pann_query_params* qp, const SearchOutputs& out,
+                    int* status_or) {
+  *status_or = 0;
+  if (nq == 0) {
+    if (nstarts == 0 || !h_starts) PANN_FAIL("beam search expects at least one start point");
+    return 0;
+  }
+  BeamPlan P;
+  if (beam_plan(idx, d_queries, nq, qstride, d_self_ids, h_starts, nstarts, qp, out, P)) return 1;
+  BeamArgs& A = P.A;
+  const bool gs = P.gs;
+  const uint32_t vcap = P.vcap;
+  const long long vbig = P.vbig;
   if (launch_beam(idx, A, gs, vcap)) return 1;
   if (out.after_kernel) PANN_CUDA(cudaEventRecord(out.after_kernel, idx->stream));
   for (const auto& c : out.after)
@@ -390,6 +415,86 @@ static int search_common(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint3
   return check_status(flag);
 }
 
+// Large host batches (pinned, contiguous rows): the batch is cut into chunks whose H2D copy, search and D2H copies
+// run on separate streams, so the copies hide under the neighbouring chunks' kernels.  Chunk kernels alternate between
+// two compute streams: the next chunk's CTAs fill the SMs as the previous chunk drains, so chunking costs no tail.
+// Returns 2 if some visited list outgrew shared memory (the caller redoes the batch on the plain path).
+#define PANN_PIPE_CHUNK (128u * 1024u)
+static int search_pipelined(pann_index* idx, const uint8_t* host_queries, uint64_t nq, const uint32_t* starts, uint32_t nstarts,
+                            const pann_query_params* qp, void* const* host_out) {
+  const uint32_t k = (uint32_t)qp->k;
+  const uint64_t nchunks = std::min<uint64_t>((nq + PANN_PIPE_CHUNK - 1) / PANN_PIPE_CHUNK, PANN_MAX_CHUNKS);
+  const uint64_t per = ((nq + nchunks - 1) / nchunks + 3) / 4 * 4;
+  if (!idx->stream2) {
+    PANN_CUDA(cudaStreamCreateWithFlags(&idx->stream2, cudaStreamNonBlocking));
+    PANN_CUDA(cudaStreamCreateWithFlags(&idx->s_in, cudaStreamNonBlocking));
+    PANN_CUDA(cudaStreamCreateWithFlags(&idx->s_out, cudaStreamNonBlocking));
+  }
+  while (idx->pipe_ev.size() < 2 * nchunks + 1) {
+    cudaEvent_t e;
+    PANN_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    idx->pipe_ev.push_back(e);
+  }
+  const size_t stride = idx->geom.stride;
+  if (idx->queries.reserve((size_t)nq * stride + 16)) return 1;
+  idx->nq = nq;
+  ResLayout L = res_layout(nq, k);
+  if (idx->results.reserve(L.total + 16)) return 1;
+  idx->res_nq = nq; idx->res_k = k;
+  uint8_t* r = idx->results.as<uint8_t>();
+  SearchOutputs o;
+  o.ids = (uint32_t*)(r + L.ids); o.dists = (float*)(r + L.dists); o.visited = (uint32_t*)(r + L.visited);
+  o.cmps = (uint32_t*)(r + L.cmps); o.status = (int*)(r + L.status);
+  idx->last_launches = 0;
+  PANN_CUDA(cudaEventRecord(idx->ev0, idx->stream));
+  BeamPlan P;
+  if (beam_plan(idx, idx->queries.as<uint8_t>(), nq, (uint32_t)stride, nullptr, starts, nstarts, qp, o, P)) return 1;
+  cudaEvent_t ready = idx->pipe_ev[2 * nchunks];   // counters zeroed, start points uploaded (ordered on idx->stream)
+  PANN_CUDA(cudaEventRecord(ready, idx->stream));
+  PANN_CUDA(cudaStreamWaitEvent(idx->stream2, ready, 0));
+  uint8_t* dq = idx->queries.as<uint8_t>();
+  for (uint64_t c = 0; c < nchunks; c++) {
+    const uint64_t c0 = c * per, cn = std::min<uint64_t>(per, nq - std::min(nq, c0));
+    if (!cn) continue;
+    PANN_CUDA(cudaMemcpyAsync(dq + c0 * stride, host_queries + c0 * stride, cn * stride, cudaMemcpyHostToDevice, idx->s_in));
+    PANN_CUDA(cudaEventRecord(idx->pipe_ev[2 * c], idx->s_in));
+  }
+  cudaStream_t cs_last = idx->stream;
+  for (uint64_t c = 0; c < nchunks; c++) {
+    const uint64_t c0 = c * per, cn = std::min<uint64_t>(per, nq - std::min(nq, c0));
+    if (!cn) continue;
+    cudaStream_t cs = (c & 1) ? idx->stream2 : idx->stream;
+    cs_last = cs;
+    PANN_CUDA(cudaStreamWaitEvent(cs, idx->pipe_ev[2 * c], 0));
+    BeamArgs A = P.A;
+    A.queries = dq + c0 * stride; A.nq = cn;
+    A.out_ids = o.ids + c0 * k; A.out_dists = o.dists + c0 * k; A.out_visited = o.visited + c0; A.out_cmps = o.cmps + c0;
+    A.status = o.status + c0;
+    if (A.qcounter) A.qcounter = reinterpret_cast<uint32_t*>(idx->bytes_ctr.as<uint8_t>() + 16) + c;   // one query counter per chunk
+    if (launch_beam(idx, A, P.gs, P.vcap, cs)) return 1;
+    PANN_CUDA(cudaEventRecord(idx->pipe_ev[2 * c + 1], cs));
+    PANN_CUDA(cudaStreamWaitEvent(idx->s_out, idx->pipe_ev[2 * c + 1], 0));
+    PANN_CUDA(cudaMemcpyAsync((uint32_t*)host_out[0] + c0 * k, A.out_ids, 4ull * cn * k, cudaMemcpyDeviceToHost, idx->s_out));
+    if (host_out[1]) PANN_CUDA(cudaMemcpyAsync((float*)host_out[1] + c0 * k, A.out_dists, 4ull * cn * k, cudaMemcpyDeviceToHost, idx->s_out));
+    if (host_out[2]) PANN_CUDA(cudaMemcpyAsync((uint32_t*)host_out[2] + c0, A.out_visited, 4ull * cn, cudaMemcpyDeviceToHost, idx->s_out));
+    if (host_out[3]) PANN_CUDA(cudaMemcpyAsync((uint32_t*)host_out[3] + c0, A.out_cmps, 4ull * cn, cudaMemcpyDeviceToHost, idx->s_out));
+  }
+  // join: idx->stream waits for the other compute stream, then the flag and the byte counter come back on it
+  if (cs_last != idx->stream || nchunks > 1) {
+    PANN_CUDA(cudaEventRecord(ready, idx->stream2));
+    PANN_CUDA(cudaStreamWaitEvent(idx->stream, ready, 0));
+  }
+  PANN_CUDA(cudaEventRecord(idx->ev1, idx->stream));
+  int flag = 0;
+  PANN_CUDA(cudaMemcpyAsync(&flag, idx->flag.p, sizeof(int), cudaMemcpyDeviceToHost, idx->stream));
+  PANN_CUDA(cudaMemcpyAsync(&idx->last_bytes, idx->bytes_ctr.p, 8, cudaMemcpyDeviceToHost, idx->stream));
+  PANN_CUDA(cudaStreamSynchronize(idx->stream));
+  PANN_CUDA(cudaStreamSynchronize(idx->s_out));
+  PANN_CUDA(cudaEventElapsedTime(&idx->last_ms, idx->ev0, idx->ev1));
+  if (flag & (1 << 1)) return 2;
+  return check_status(flag);
+}
+
 static int upload_queries(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes) {
   const size_t rowb = (size_t)idx->dims * idx->geom.elt;
   if (q_stride_bytes < rowb) PANN_FAIL("query stride smaller than a row");
@@ -464,8 +569,17 @@ extern "C" int pann_search_batch(pann_index* idx, const void* host_queries, uint
   if (validate_qp(qp)) return 1;
   PANN_CUDA(cudaSetDevice(idx->device));
   if (nq == 0) return 0;
-  if (upload_queries(idx, host_queries, nq, q_stride_bytes)) return 1;
   void* const host_out[4] = {out_ids, out_dists, out_visited, out_cmps};
+  {
+    const size_t rowb = (size_t)idx->dims * idx->geom.elt;
+    const char* np = getenv("PANN_NO_PIPELINE");
+    if (nq >= 2ull * PANN_PIPE_CHUNK && out_ids && q_stride_bytes == rowb && idx->geom.stride == rowb && !(np && np[0] == '1') &&
+        is_pinned_host(host_queries) && is_pinned_host(out_ids) && is_pinned_host(out_dists) && is_pinned_host(out_visited) && is_pinned_host(out_cmps)) {
+      const int rc = search_pipelined(idx, (const uint8_t*)host_queries, nq, starts, nstarts, qp, host_out);
+      if (rc != 2) return rc;   // 2: a visited list outgrew shared memory somewhere: take the plain path, which retries those queries
+    }
+  }
+  if (upload_queries(idx, host_queries, nq, q_stride_bytes)) return 1;
   bool delivered = false;
   if (search_common(idx, idx->queries.as<uint8_t>(), nq, idx->geom.stride, starts, nstarts, qp, host_out, &delivered)) return 1;
   return delivered ? 0 : fetch_results(idx, out_ids, out_dists, out_visited, out_cmps);

@@ -38,6 +38,9 @@ struct pann_index {
   uint32_t* graph = nullptr;   // n x (maxdeg+1)
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  // chunk pipeline of pann_search_batch (created on first use): second compute stream, copy-in / copy-out streams
+  cudaStream_t stream2 = nullptr, s_in = nullptr, s_out = nullptr;
+  std::vector<cudaEvent_t> pipe_ev;
   float last_ms = 0.f;
   DevBuf bytes_ctr; uint64_t last_bytes = 0;  // algorithmic bytes of the last search (device counter + host copy)
   int last_launches = 0;

@@ -172,3 +172,38 @@ def test_search_matches_reference_golden():
         for i in range(g.nq):
             assert np.array_equal(got["vis_ids"][i, :cnt[i, 1]], vi[i][:, 0])
             assert np.array_equal(got["vis_dists"][i, :cnt[i, 1]].view(np.uint32), vi[i][:, 1])
+
+
+def test_pipelined_host_batch_identical(dataset, monkeypatch):
+    # large pinned host batches go through the chunk pipeline of pann_search_batch (copies under the neighbouring
+    # chunks' kernels, two compute streams): same results as the plain path, and as the oracle on the original rows
+    torch = pytest.importorskip("torch")
+    ds = dataset("uint8")
+    idx = _index(ds)
+    reps = 300000 // len(ds.queries) + 1
+    nq = reps * len(ds.queries)                       # > 2 x 128K: the pipeline engages; ragged last chunk
+    hq = torch.from_numpy(np.tile(ds.queries, (reps, 1))).pin_memory()
+
+    def pinned(shape, dt):
+        return torch.empty(shape, dtype=dt).pin_memory().numpy()
+
+    def run():
+        out = (pinned((nq, 10), torch.int32).view(np.uint32), pinned((nq, 10), torch.float32),
+               pinned(nq, torch.int32).view(np.uint32), pinned(nq, torch.int32).view(np.uint32))
+        for o in out:
+            o[...] = 0
+        idx.search(hq.numpy(), k=10, beam=16, out=out)
+        return out, idx.last_timing()[1]
+    piped, nl = run()
+    assert nl >= 3, "the chunk pipeline did not engage"
+    monkeypatch.setenv("PANN_NO_PIPELINE", "1")
+    plain, nl0 = run()
+    assert nl0 == 1
+    for a, b in zip(piped, plain):
+        assert np.array_equal(a, b)
+    ref = O.search(ds.base, ds.graph, ds.queries, ds.data_type, ds.metric, k=10, beam=16)
+    n0 = len(ds.queries)
+    for block in (0, reps - 1):
+        sl = slice(block * n0, (block + 1) * n0)
+        assert np.array_equal(piped[0][sl], ref["ids"]) and np.array_equal(piped[1][sl], ref["dists"])
+        assert np.array_equal(piped[2][sl], ref["visited"]) and np.array_equal(piped[3][sl], ref["cmps"])
