@@ -47,6 +47,15 @@ static const void* prune_kernel(int dtype, int metric, int qr, bool gs) {
     default: return pann_prune_kernel_dt2(metric, qr, gs);
   }
 }
+// tie rows back into the graph after the host sorted them
+static __global__ void pann_scatter_rows_kernel(const uint32_t* tie_rows, const uint32_t* tie_graph, uint32_t* graph, uint32_t T, uint32_t maxdeg) {
+  const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (w >= T) return;
+  const uint32_t* src = tie_graph + (u64)w * (maxdeg + 1);
+  uint32_t* dst = graph + (u64)tie_rows[w] * (maxdeg + 1);
+  for (uint32_t j = lane; j < src[0]; j += 32) dst[1 + j] = src[1 + j];
+}
+
 static const void* edge_kernel(int dtype, int metric, int qr) {
   switch (dtype) {
     case PANN_DT_F32: return pann_edge_kernel_dt0(metric, qr);
@@ -249,33 +258,69 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
   if (rc) return 1;
   PANN_CUDA(cudaGetLastError());
 
-  if (sort_neighbors) {  // index.h:180-185: per row, by distance to the owner only; the sort itself is std::sort on the
-    // host so that ties land exactly where the reference's libstdc++ introsort leaves them
-    DevBuf d_ed;
-    if (d_ed.reserve(4ull * n * md)) return 1;
+  if (sort_neighbors) {  // index.h:180-185: per row, by distance to the owner only
+    // Rows with distinct distances are sorted on the device (K6, sort mode).  Rows with ties go through std::sort on the
+    // host so that they land exactly where the reference's libstdc++ introsort leaves them.
+    const char* hs = getenv("PANN_HOST_SORT");
+    bool host_all = hs && hs[0] == '1';
     EdgeDistArgs E;
     memset(&E, 0, sizeof(E));
     E.points = idx->points; E.stride = idx->geom.stride; E.nch = idx->geom.nch;
-    E.graph = idx->graph; E.maxdeg = md; E.n = n; E.out = d_ed.as<float>();
+    E.graph = idx->graph; E.maxdeg = md; E.n = n;
     const int qrT = pann_qr_of(idx->geom);
     E.off_q = al16((size_t)md * 4);
-    E.warp_bytes = E.off_q + idx->geom.stride;
+    E.off_d = E.off_q + idx->geom.stride;
+    E.off_s = E.off_d + al16((size_t)md * 4);
+    E.warp_bytes = E.off_s + al16((size_t)md * 4);
     const void* fn = edge_kernel(idx->dtype, idx->metric, qrT);
     size_t cta_bytes = (size_t)E.warp_bytes * PANN_PRUNE_WARPS;
     PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
     int grid = (int)std::min<uint64_t>((n + PANN_PRUNE_WARPS - 1) / PANN_PRUNE_WARPS, (uint64_t)idx->sms * 16);
     void* args[] = {(void*)&E};
-    PANN_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(PANN_PRUNE_WARPS * 32), args, cta_bytes, s));
-    idx->last_launches++;
-    std::vector<uint32_t> hg((size_t)n * (md + 1));
-    std::vector<float> hd((size_t)n * md);
-    PANN_CUDA(cudaMemcpyAsync(hg.data(), idx->graph, hg.size() * 4, cudaMemcpyDeviceToHost, s));
-    PANN_CUDA(cudaMemcpyAsync(hd.data(), d_ed.p, hd.size() * 4, cudaMemcpyDeviceToHost, s));
-    PANN_CUDA(cudaStreamSynchronize(s));
-    d_ed.release();
-    pann_host_sort_rows(hg.data(), hd.data(), n, md);
-    PANN_CUDA(cudaMemcpyAsync(idx->graph, hg.data(), hg.size() * 4, cudaMemcpyHostToDevice, s));
-    PANN_CUDA(cudaStreamSynchronize(s));
+    if (!host_all) {
+      const uint32_t cap = (uint32_t)std::min<uint64_t>(std::max<uint64_t>(1024, n / 4), n);
+      DevBuf t_cnt, t_rows, t_graph, t_dist;
+      if (t_cnt.reserve(4) || t_rows.reserve(4ull * cap) || t_graph.reserve(4ull * cap * (md + 1)) || t_dist.reserve(4ull * cap * md)) return 1;
+      PANN_CUDA(cudaMemsetAsync(t_cnt.p, 0, 4, s));
+      E.sort = 1; E.tie_count = t_cnt.as<uint32_t>(); E.tie_cap = cap; E.tie_rows = t_rows.as<uint32_t>();
+      E.tie_graph = t_graph.as<uint32_t>(); E.tie_dist = t_dist.as<float>();
+      PANN_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(PANN_PRUNE_WARPS * 32), args, cta_bytes, s));
+      idx->last_launches++;
+      uint32_t T = 0;
+      PANN_CUDA(cudaMemcpyAsync(&T, t_cnt.p, 4, cudaMemcpyDeviceToHost, s));
+      PANN_CUDA(cudaStreamSynchronize(s));
+      if (T > cap) {
+        host_all = true;   // rows without ties are already in their final order; sorting them again on the host changes nothing
+      } else if (T > 0) {
+        std::vector<uint32_t> hg((size_t)T * (md + 1));
+        std::vector<float> hd((size_t)T * md);
+        PANN_CUDA(cudaMemcpyAsync(hg.data(), t_graph.p, hg.size() * 4, cudaMemcpyDeviceToHost, s));
+        PANN_CUDA(cudaMemcpyAsync(hd.data(), t_dist.p, hd.size() * 4, cudaMemcpyDeviceToHost, s));
+        PANN_CUDA(cudaStreamSynchronize(s));
+        pann_host_sort_rows(hg.data(), hd.data(), T, md);
+        PANN_CUDA(cudaMemcpyAsync(t_graph.p, hg.data(), hg.size() * 4, cudaMemcpyHostToDevice, s));
+        pann_scatter_rows_kernel<<<(T * 32 + 255) / 256, 256, 0, s>>>(t_rows.as<uint32_t>(), t_graph.as<uint32_t>(), idx->graph, T, md);
+        idx->last_launches++;
+        PANN_CUDA(cudaStreamSynchronize(s));
+      }
+      if (getenv("PANN_BUILD_VERBOSE")) fprintf(stderr, "  final sort: %u of %llu rows have tied distances (host std::sort)\n", T, (unsigned long long)n);
+    }
+    if (host_all) {
+      DevBuf d_ed;
+      if (d_ed.reserve(4ull * n * md)) return 1;
+      E.sort = 0; E.out = d_ed.as<float>();
+      PANN_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(PANN_PRUNE_WARPS * 32), args, cta_bytes, s));
+      idx->last_launches++;
+      std::vector<uint32_t> hg((size_t)n * (md + 1));
+      std::vector<float> hd((size_t)n * md);
+      PANN_CUDA(cudaMemcpyAsync(hg.data(), idx->graph, hg.size() * 4, cudaMemcpyDeviceToHost, s));
+      PANN_CUDA(cudaMemcpyAsync(hd.data(), d_ed.p, hd.size() * 4, cudaMemcpyDeviceToHost, s));
+      PANN_CUDA(cudaStreamSynchronize(s));
+      d_ed.release();
+      pann_host_sort_rows(hg.data(), hd.data(), n, md);
+      PANN_CUDA(cudaMemcpyAsync(idx->graph, hg.data(), hg.size() * 4, cudaMemcpyHostToDevice, s));
+      PANN_CUDA(cudaStreamSynchronize(s));
+    }
   }
   if (out_visited) PANN_CUDA(cudaMemcpy(out_visited, st_vis, 4 * n, cudaMemcpyDeviceToHost));
   if (out_cmps) PANN_CUDA(cudaMemcpy(out_cmps, st_cmp, 4 * n, cudaMemcpyDeviceToHost));

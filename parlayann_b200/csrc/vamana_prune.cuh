@@ -269,12 +269,19 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
 }
 
 // K6: distance of every edge to its owner, one warp per graph row (build_index's final per-row sort,
-// algorithms/vamana/index.h:180-185, compares exactly these values).  out: n x maxdeg floats.
+// algorithms/vamana/index.h:180-185, compares exactly these values).
+//   sort == 0: out = n x maxdeg floats, the caller sorts.
+//   sort == 1: rows whose distances are all distinct have exactly one sorted order and are rewritten in place (rank
+//     sort in shared memory).  The reference's comparator looks at the distance only and std::sort is not stable, so a
+//     row WITH ties must end up where libstdc++'s introsort leaves it: such rows are copied (edges + distances) to a
+//     compact record list for the host, which runs that very std::sort on them (a few percent of the rows).
 struct EdgeDistArgs {
   const uint8_t* points; uint32_t stride, nch;
-  const uint32_t* graph; uint32_t maxdeg; uint64_t n;
+  uint32_t* graph; uint32_t maxdeg; uint64_t n;
   float* out;
-  uint32_t off_q, warp_bytes;
+  uint32_t off_q, off_d, off_s, warp_bytes;
+  int sort;
+  uint32_t* tie_count; uint32_t tie_cap; uint32_t* tie_rows; uint32_t* tie_graph; float* tie_dist;
 };
 template <int DT, int METRIC, int QR>
 __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_edge_dist_kernel(const EdgeDistArgs A) {
@@ -283,16 +290,18 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_edge_dist_kernel(c
   uint8_t* ws = pann_smem + (size_t)wic * A.warp_bytes;
   uint32_t* ids = reinterpret_cast<uint32_t*>(ws);
   uint4* qsm = reinterpret_cast<uint4*>(ws + A.off_q);
+  float* dsm = reinterpret_cast<float*>(ws + A.off_d);
+  uint32_t* sorted = reinterpret_cast<uint32_t*>(ws + A.off_s);
   const long long wglobal = (long long)blockIdx.x * PANN_PRUNE_WARPS + wic;
   const long long wstride = (long long)gridDim.x * PANN_PRUNE_WARPS;
   for (long long i = wglobal; i < (long long)A.n; i += wstride) {
-    const uint32_t* grow = A.graph + (u64)i * (A.maxdeg + 1);
+    uint32_t* grow = A.graph + (u64)i * (A.maxdeg + 1);
     const int deg = (int)grow[0];
     const uint8_t* row = A.points + (u64)i * A.stride;
     pann_load_query(row, A.nch, qsm, lane);
     for (int j = lane; j < deg; j += 32) ids[j] = grow[1 + j];
     __syncwarp();
-    float* o = A.out + (u64)i * A.maxdeg;
+    float* o = A.sort ? dsm : A.out + (u64)i * A.maxdeg;
     int w = 0;
     pann_row_distances_g<DT, METRIC, QR>(
         A, [&](int r) { return (u64)ids[r] << 1; }, deg, qsm, lane, [&](u64, float d, bool ok) {
@@ -301,9 +310,36 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_edge_dist_kernel(c
           w += __popc(bm);
         });
     __syncwarp();
+    if (A.sort) {
+      bool tie = false;
+      for (int j = lane; j < deg; j += 32) {
+        const float dj = dsm[j];
+        int r = 0;
+        for (int k = 0; k < deg; k++) {
+          const float dk = dsm[k];
+          r += (dk < dj) || (dk == dj && k < j);
+          tie |= (dk == dj) && (k != j);
+        }
+        sorted[r] = ids[j];
+      }
+      __syncwarp();
+      if (!__any_sync(PANN_FULL, tie)) {
+        for (int j = lane; j < deg; j += 32) grow[1 + j] = sorted[j];
+      } else {
+        uint32_t slot = 0;
+        if (lane == 0) slot = atomicAdd(A.tie_count, 1u);
+        slot = __shfl_sync(PANN_FULL, slot, 0);
+        if (slot < A.tie_cap) {
+          uint32_t* tg = A.tie_graph + (u64)slot * (A.maxdeg + 1);
+          float* td = A.tie_dist + (u64)slot * A.maxdeg;
+          if (lane == 0) { A.tie_rows[slot] = (uint32_t)i; tg[0] = (uint32_t)deg; }
+          for (int j = lane; j < deg; j += 32) { tg[1 + j] = ids[j]; td[j] = dsm[j]; }
+        }
+      }
+    }
+    __syncwarp();
   }
 }
-
 const void* pann_prune_kernel_dt0(int metric, int qr, bool gs);
 const void* pann_prune_kernel_dt1(int metric, int qr, bool gs);
 const void* pann_prune_kernel_dt2(int metric, int qr, bool gs);
