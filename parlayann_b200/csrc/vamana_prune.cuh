@@ -209,6 +209,14 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
         if (cnt == 0) break;
         comps += cnt;  // one distance per live later candidate (:108)
         int w = start;
+        // rows of exactly QR chunks: the picked row lives in registers for the whole pass and the candidate's chunks are
+        // all loaded before the arithmetic (this path runs at ~6 warps per SM, shared memory being the limit, so the
+        // instruction-level parallelism inside the warp is what hides the shared-memory latency)
+        uint4 qv[QR > 0 ? QR : 1];
+        if constexpr (QR > 0) {
+#pragma unroll
+          for (int c = 0; c < QR; c++) qv[c] = qrow[c];
+        }
         for (int base = 0; base < cnt; base += 32) {
           const int r = base + lane;
           const bool ok = r < cnt;
@@ -219,7 +227,15 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
             key = S[start + r];
             slot = P[start + r];
             const uint4* row = rc + (uint32_t)slot * pw;
-            for (int c = 0; c < (int)A.nch; c++) acc.add(row[c], qrow[c]);
+            if constexpr (QR > 0) {
+              uint4 v[QR];
+#pragma unroll
+              for (int c = 0; c < QR; c++) v[c] = row[c];
+#pragma unroll
+              for (int c = 0; c < QR; c++) acc.add(v[c], qv[c]);
+            } else {
+              for (int c = 0; c < (int)A.nch; c++) acc.add(row[c], qrow[c]);
+            }
           }
           const float d = acc.result();
           const bool keep = ok && !(A.alpha * (double)d <= (double)pann_key_dist(key));  // :111
