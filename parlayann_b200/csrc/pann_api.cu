@@ -301,10 +301,13 @@ static int beam_plan(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uin
     }
   }
 
-  // shared-memory variant while the hash filter is <= 16 KB per warp; visited-list capacity is a guess
-  // that the retry below makes safe
+  // shared-memory variant while the hash filter is <= 8 KB per warp (beam <= 90): at 16 KB only 8 warps fit on an SM and
+  // the search is latency-bound — with the filter and the visited list in a global slab (L2-resident: 16 KB x ~3500
+  // warps) 24 warps are resident (10M build, search phase: 5.2 s -> 4.1 s).  The visited-list capacity is a guess that
+  // the retry below makes safe.
   const char* force = getenv("PANN_FORCE_GLOBAL_SCRATCH");
-  bool gs = A.bits > 12 || (force && force[0] == '1');
+  bool gs = A.bits >= 12 || (force && force[0] == '1');
+  if (force && force[0] == '0') gs = A.bits > 12;
   const long long vbig = std::min<long long>(A.limit, std::max<long long>(8 * beam + 4096, 16384));
   uint32_t vcap = gs ? (uint32_t)vbig : (uint32_t)std::min<long long>(A.limit, std::max<long long>(2 * beam, beam + 64));
   if (vcap < 1) vcap = 1;

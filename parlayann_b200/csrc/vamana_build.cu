@@ -74,7 +74,12 @@ static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, De
   A.big_count = big.as<uint32_t>();
   A.big_list = big.as<uint32_t>() + 2;
   PANN_CUDA(cudaMemsetAsync(A.big_count, 0, 8, idx->stream));
-  A.cap = 512;
+  const char* rc_env = getenv("PANN_PRUNE_ROW_CACHE");  // 0 / 1 force it off / on
+  const bool rc_on = g.stride <= 256 && (rc_env ? rc_env[0] == '1' : (idx->n * (uint64_t)g.stride > (256ull << 20)));
+  // reverse-edge groups (mode 1) are the vertex's <= R edges plus a handful of new ones: a smaller list and row cache per
+  // warp doubles the resident warps of the row-cache path (the rare longer list takes the uncached scan or the slab launch)
+  const bool small_lists = rc_on && A.mode == 1 && A.R <= 64;
+  A.cap = small_lists ? 256 : 512;
   A.off_b = al16((size_t)A.cap * 8);
   A.off_q = 2 * A.off_b;
   A.warp_bytes = A.off_q + g.stride;
@@ -84,16 +89,14 @@ static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, De
   // so that 32 lanes reading 32 different rows spread over all banks
   // It pays once the point set no longer lives in the 126 MB L2 (measured: 10M x 128 B build 36 s -> 15.5 s); while it
   // does (1M x 128 B), the plain path with more resident warps is ~20 % faster.
-  const char* rc_env = getenv("PANN_PRUNE_ROW_CACHE");  // 0 / 1 force it off / on
-  const bool rc_on = rc_env ? rc_env[0] == '1' : (idx->n * (uint64_t)g.stride > (256ull << 20));
-  if (g.stride <= 256 && rc_on) {
-    A.rc_rows = 160;
+  if (rc_on) {
+    A.rc_rows = small_lists ? 96 : 160;
     A.rc_pitch = g.stride + 16;
     if (((A.rc_pitch / 16) & 1) == 0) A.rc_pitch += 16;
     A.off_pos = A.warp_bytes;
     A.off_rc = A.off_pos + al16((size_t)A.cap * 2);
     A.warp_bytes = A.off_rc + A.rc_rows * A.rc_pitch;
-    wpc = 3;
+    wpc = small_lists ? 4 : 3;
   }
   A.task_map = nullptr; A.ntask_map = 0; A.g_scratch = nullptr;
   {
