@@ -95,6 +95,17 @@ int pann_search_full(pann_index* idx, const void* host_queries, uint64_t nq, uin
                      uint32_t fcap, uint32_t* fr_ids, float* fr_dists, uint32_t* n_frontier,
                      uint32_t vcap, uint32_t* vis_ids, float* vis_dists, uint32_t* n_visited, uint32_t* out_cmps);
 
+/* beam_search_rerank when the searched copy is quantised (beamSearch.h:390-454 with differing byte widths; the
+ * -quantize_mode 1 path of vamana/neighbors.h:117-127 and Python's quant=True, graph_index.cpp:141-186): q_idx holds the
+ * 1-byte points and the graph, base_idx the exact points (same device, same n / dims / metric).  The search runs on
+ * q_idx with the quantised queries; the first min(k * rerank_factor, |frontier|) frontier entries are then re-ranked by
+ * exact distance between host_queries and base_idx's rows, sorted by (distance, id), first k returned.  Counters are the
+ * search's.  HOST buffers.  QueryParams::rerank_factor defaults to 100 in the reference (types.h:224). */
+int pann_search_rerank_batch(pann_index* q_idx, pann_index* base_idx, const void* host_qqueries, uint64_t qq_stride_bytes,
+                             const void* host_queries, uint64_t q_stride_bytes, uint64_t nq, const uint32_t* starts,
+                             uint32_t nstarts, const pann_query_params* qp, int64_t rerank_factor, uint32_t* out_ids,
+                             float* out_dists, uint32_t* out_visited, uint32_t* out_cmps);
+
 /* knn_index::build_index (algorithms/vamana/index.h:150-186): num_passes x batch_insert (:188-316) of all n
  * points in parlay::random_permutation order, start point 0, robustPrune (:63-120) with alpha on the last
  * pass and 1.0 before; optional final per-row sort by distance.  The graph of the index is replaced.

@@ -146,18 +146,57 @@ searchAll(PointRange& Query_Points, Graph<indexType>& G, PointRange& Base_Points
   return searchAll(cached_index(Base_Points, G, false), Query_Points, QueryStats, start_points, QP);
 }
 
-// ---- qsearchAll (beamSearch.h:537-565), reference signature.  The quantised ranges must be the same type as the
-// exact ones (no quantisation: beam_search_rerank then reduces to filtered_beam_search, :409-410, :445-452);
-// quantised search + re-rank is a "next" row.
+// exact points only (the re-rank side of a quantised search): no graph on the device
+template <typename PointRange, typename indexType>
+inline DeviceIndex<PointRange, indexType>& cached_points(const PointRange& Points) {
+  using DI = DeviceIndex<PointRange, indexType>;
+  static std::map<const void*, std::unique_ptr<DI>> cache;
+  static std::mutex mu;
+  std::lock_guard<std::mutex> lock(mu);
+  auto& e = cache[Points.location(0)];
+  if (!e) e = std::make_unique<DI>(Points, 1);
+  return *e;
+}
+
+// ---- qsearchAll (beamSearch.h:537-565), reference signature.
+//  * quantised ranges of the same type as the exact ones: beam_search_rerank reduces to filtered_beam_search
+//    (:409-410, :445-452) -> pann_search_batch;
+//  * a 1-byte quantised copy for the search and its first-level filter (Q == QQ, the -quantize_mode 1 configuration of
+//    vamana/neighbors.h:117-127): search on the quantised index, exact re-rank of the first k * rerank_factor frontier
+//    entries (:426-444) -> pann_search_rerank_batch.  A second, coarser level (QQ != Q, use_filtering) is not built.
 template <typename PointRange, typename QPointRange, typename QQPointRange, typename indexType>
 parlay::sequence<parlay::sequence<indexType>>
-qsearchAll(const PointRange& Query_Points, const QPointRange&, const QQPointRange&, const Graph<indexType>& G,
-           const PointRange& Base_Points, const QPointRange&, const QQPointRange&, stats<indexType>& QueryStats,
+qsearchAll(const PointRange& Query_Points, const QPointRange& Q_Query_Points, const QQPointRange&, const Graph<indexType>& G,
+           const PointRange& Base_Points, const QPointRange& Q_Base_Points, const QQPointRange&, stats<indexType>& QueryStats,
            const indexType starting_point, const QueryParams& QP) {
-  static_assert(std::is_same<PointRange, QPointRange>::value && std::is_same<PointRange, QQPointRange>::value,
-                "parlayann_b200: quantised search + re-rank is not on the GPU path yet (SURVEY.md §8f.2)");
+  static_assert(std::is_same<QPointRange, QQPointRange>::value,
+                "parlayann_b200: two-level quantised search (QQ != Q, use_filtering) is not on the GPU path (SURVEY.md §8f.2)");
   parlay::sequence<indexType> starting_points = {starting_point};
-  return searchAll(cached_index(Base_Points, G, false), Query_Points, QueryStats, starting_points, QP);
+  if constexpr (std::is_same<PointRange, QPointRange>::value) {
+    return searchAll(cached_index(Base_Points, G, false), Query_Points, QueryStats, starting_points, QP);
+  } else {
+    if (QP.k > QP.beamSize) {  // beamSearch.h:549-553
+      std::cout << "Error: beam search parameter Q = " << QP.beamSize << " same size or smaller than k = " << QP.k << std::endl;
+      abort();
+    }
+    auto& DQ = cached_index(Q_Base_Points, G, false);
+    auto& DB = cached_points<PointRange, indexType>(Base_Points);
+    const size_t nq = Query_Points.size();
+    const size_t k = (size_t)QP.k;
+    std::vector<uint32_t> ids(nq * k), visited(nq), cmps(nq);
+    pann_query_params q = to_pann(QP);
+    if (nq)
+      check(pann_search_rerank_batch(DQ.handle(), DB.handle(), Q_Query_Points.location(0), row_stride(Q_Query_Points),
+                                     Query_Points.location(0), row_stride(Query_Points), nq, (const uint32_t*)starting_points.begin(), 1, &q,
+                                     QP.rerank_factor, ids.data(), nullptr, visited.data(), cmps.data()));
+    parlay::sequence<parlay::sequence<indexType>> all_neighbors(nq);
+    parlay::parallel_for(0, nq, [&](size_t i) {
+      all_neighbors[i] = parlay::tabulate(k, [&](size_t j) { return (indexType)ids[i * k + j]; });
+      QueryStats.increment_visited(i, visited[i]);  // beamSearch.h:421-424
+      QueryStats.increment_dist(i, cmps[i]);
+    });
+    return all_neighbors;
+  }
 }
 
 // ---- knn_index::build_index (vamana/index.h:150-186) -------------------------------------------------------------

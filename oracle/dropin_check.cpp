@@ -68,6 +68,24 @@ static int run(int argc, char** argv) {
     printf("DROPIN qsearchAll beam %ld: %zu of %zu queries differ, stats %s\n", beam, dq, Q.size(), s2 ? "identical" : "DIFFER");
     bad += dq != 0 || !s2;
   }
+  // --- 1-byte quantised copy + exact re-rank (-quantize_mode 1, vamana/neighbors.h:117-127): float Euclidean data only
+  if constexpr (std::is_same<PR, PointRange<Euclidian_Point<float>>>::value) {
+    using QPR = PointRange<Euclidian_Point<uint8_t>>;
+    QPR Q_Points(Points);
+    QPR Q_Q(Q, Q_Points.params);
+    for (long beam : {10L, 20L, 40L, 100L}) {
+      if (beam < k) continue;
+      QueryParams QP(k, beam, 1.35, (long)Gc.size(), (long)Gc.max_degree());
+      stats<uint> qc(Q.size()), qg(Q.size());
+      auto rc = qsearchAll<PR, QPR, QPR, uint>(Q, Q_Q, Q_Q, Gc, Points, Q_Points, Q_Points, qc, 0u, QP);
+      auto rg = b200::qsearchAll<PR, QPR, QPR, uint>(Q, Q_Q, Q_Q, Gc, Points, Q_Points, Q_Points, qg, 0u, QP);
+      size_t dq = 0;
+      for (size_t i = 0; i < Q.size(); i++) dq += !(rc[i] == rg[i]);
+      bool s2 = std::equal(qc.visited.begin(), qc.visited.end(), qg.visited.begin()) && std::equal(qc.distances.begin(), qc.distances.end(), qg.distances.begin());
+      printf("DROPIN qsearchAll quantised + re-rank, beam %ld: %zu of %zu queries differ, stats %s\n", beam, dq, Q.size(), s2 ? "identical" : "DIFFER");
+      bad += dq != 0 || !s2;
+    }
+  }
   // --- ground truth: sorted distance rows must be identical
   {
     int gk = 20;

@@ -425,4 +425,58 @@ void oracle_gen_points(int kind, uint64_t model_seed, uint64_t stream, uint64_t 
   });
 }
 
+// ---- 1-byte scalar quantisation of float rows + exact re-rank (the -quantize_mode 1 path, vamana/neighbors.h:117-127)
+// Euclidian_Point<uint8_t>::generate_parameters (euclidian_point.h:211-237) and parameters(min,max,dims) (:104-108):
+// per row min/max START AT 0 (so min_val <= 0 <= max_val), all-integer non-negative data maps to [0,255] unscaled.
+void oracle_quant_params_u8(const float* pts, uint64_t n, uint32_t d, uint64_t stride, float* slope, int32_t* offset) {
+  float min_val = 0.0f, max_val = 0.0f;
+  bool all_ints = true;
+  for (uint64_t i = 0; i < n; i++) {
+    const float* r = (const float*)((const uint8_t*)pts + i * stride);
+    for (uint32_t j = 0; j < d; j++) {
+      all_ints = all_ints && (r[j] >= 0) && (r[j] - (long)r[j]) == 0;
+      min_val = std::min<float>(min_val, r[j]);
+      max_val = std::max<float>(max_val, r[j]);
+    }
+  }
+  if (all_ints) { if (max_val < 256) max_val = 255; min_val = 0; }
+  const long range = 255;
+  *slope = range / (max_val - min_val);
+  *offset = (int32_t)round(min_val * *slope);
+}
+// Euclidian_Point<uint8_t>::translate_point (euclidian_point.h:183-209)
+void oracle_quantize_u8(const float* pts, uint64_t n, uint32_t d, uint64_t stride, float slope, int32_t offset, uint8_t* out) {
+  const long range = 255;
+  for (uint64_t i = 0; i < n; i++) {
+    const float* r = (const float*)((const uint8_t*)pts + i * stride);
+    for (uint32_t j = 0; j < d; j++) {
+      if (slope == 1.0 && offset == 0) { out[i * d + j] = (uint8_t)r[j]; continue; }
+      float x = r[j];
+      int64_t v = (int64_t)(std::round(x * slope)) - offset;
+      if (v < 0) v = 0;
+      if (v > range) v = range;
+      out[i * d + j] = (uint8_t)v;
+    }
+  }
+}
+// beam_search_rerank's re-rank step (beamSearch.h:426-444): exact distances of the first min(k*rerank_factor, |frontier|)
+// frontier entries, std::sort by (dist, id), first k.
+int oracle_rerank(int dtype, int metric, const void* base, uint64_t n, uint32_t d, uint64_t stride, const void* queries,
+                  uint64_t nq, uint64_t qstride, const uint32_t* fr_ids, const uint32_t* nfr, uint32_t fcap, long k,
+                  long rerank_factor, uint32_t* out_ids, float* out_dists, int nthreads) {
+  PointSet P{dtype, metric, (const uint8_t*)base, n, d, stride};
+  std::atomic<int> bad(0);
+  par_for(0, nq, nthreads, [&](size_t i) {
+    if ((long)nfr[i] < k) { bad = 1; return; }
+    const int num_check = (int)std::min<long>(k * rerank_factor, (long)nfr[i]);
+    std::vector<idd> pts;
+    for (int t = 0; t < num_check; t++) {
+      const uint32_t j = fr_ids[i * fcap + t];
+      pts.push_back(idd(j, dist_rows(dtype, metric, P.row(j), (const uint8_t*)queries + i * qstride, d)));
+    }
+    std::sort(pts.begin(), pts.end(), less_idd);
+    for (long t = 0; t < k; t++) { out_ids[i * k + t] = pts[t].first; if (out_dists) out_dists[i * k + t] = pts[t].second; }
+  });
+  return bad;
+}
 }  // extern "C"

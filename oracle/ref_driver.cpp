@@ -11,6 +11,7 @@
 //   search  -> qsearchAll + stats                                    (algorithms/utils/beamSearch.h:537-565)
 //   full    -> beam_search (frontier + visited lists per query)      (algorithms/utils/beamSearch.h:217-223)
 //   recall  -> checkRecall (timed qsearchAll + tie-aware recall)     (algorithms/utils/check_nn_recall.h:17-125)
+//   qsearch -> qsearchAll over a 1-byte quantised copy + exact re-rank (vamana/neighbors.h:117-127, beamSearch.h:409-444)
 //   gt      -> compute_groundtruth + write_ibin                      (data_tools/compute_groundtruth.cpp:22-100)
 //
 // Built by oracle/Makefile into oracle/_ref/ (git-ignored, travels to the GPU box).
@@ -19,6 +20,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "utils/beamSearch.h"
@@ -142,6 +144,35 @@ static int run(const std::string& cmd, int argc, char** argv) {
     dump(out + ".visited", QS.visited.begin(), 4 * nq);
     dump(out + ".distances", QS.distances.begin(), 4 * nq);
     return 0;
+  }
+
+  if (cmd == "qsearch") {
+    // float Euclidean data only: search the reference's own uint8 scalar-quantised copy (euclidian_point.h:182-235,
+    // point_range.h:50-63) and re-rank with the exact points, as ANN() does for -quantize_mode 1
+    if constexpr (std::is_same<typename Point::T, float>::value && std::is_same<Point, Euclidian_Point<float>>::value) {
+      using QPoint = Euclidian_Point<uint8_t>;
+      using QPR = PointRange<QPoint>;
+      QPR Q_Points(Points);
+      QPR Q_Q(Q, Q_Points.params);
+      stats<uint> QS(nq);
+      auto res = qsearchAll<PR, QPR, QPR, uint>(Q, Q_Q, Q_Q, G, Points, Q_Points, Q_Points, QS, start, QP);
+      std::vector<uint> ids(nq * k);
+      for (size_t i = 0; i < nq; i++) for (long j = 0; j < k; j++) ids[i * k + j] = res[i][j];
+      dump(out + ".ids", ids.data(), ids.size() * 4);
+      dump(out + ".visited", QS.visited.begin(), 4 * nq);
+      dump(out + ".distances", QS.distances.begin(), 4 * nq);
+      const size_t d = Points.dimension();
+      std::vector<uint8_t> qb(Points.size() * d), qq(nq * d);
+      for (size_t i = 0; i < Points.size(); i++) for (size_t j = 0; j < d; j++) qb[i * d + j] = Q_Points[i][j];
+      for (size_t i = 0; i < nq; i++) for (size_t j = 0; j < d; j++) qq[i * d + j] = Q_Q[i][j];
+      dump(out + ".qbase", qb.data(), qb.size());
+      dump(out + ".qquery", qq.data(), qq.size());
+      printf("REF_QUANT slope %.9g offset %d\n", (double)Q_Points.params.slope, (int)Q_Points.params.offset);
+      return 0;
+    } else {
+      fprintf(stderr, "ref_driver: qsearch needs -data_type float -dist_func Euclidian\n");
+      return 2;
+    }
   }
 
   if (cmd == "full") {

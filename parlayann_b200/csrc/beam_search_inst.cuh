@@ -46,3 +46,7 @@ static const void* pick_edge(int qr) {
 const void* PANN_CAT(pann_edge_kernel_dt, PANN_INST_DT)(int metric, int qr) {
   return metric == PANN_M_L2 ? pick_edge<PANN_M_L2>(qr) : pick_edge<PANN_M_MIPS>(qr);
 }
+
+const void* PANN_CAT(pann_rerank_kernel_dt, PANN_INST_DT)(int metric) {
+  return metric == PANN_M_L2 ? (const void*)&pann_rerank_kernel<PANN_INST_DT, PANN_M_L2> : (const void*)&pann_rerank_kernel<PANN_INST_DT, PANN_M_MIPS>;
+}

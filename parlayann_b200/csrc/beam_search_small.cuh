@@ -17,8 +17,8 @@
 #include "beam_search.cuh"
 
 // distance from the query (shared memory) to base row `a`, computed by this lane alone, chunks in ascending order
-template <int DT, int METRIC, int QR>
-__device__ __forceinline__ float pann_lane_distance(const BeamArgs& A, uint32_t a, bool on, const uint4* qsm) {
+template <int DT, int METRIC, int QR, class RG>
+__device__ __forceinline__ float pann_lane_distance(const RG& A, uint32_t a, bool on, const uint4* qsm) {
   DistAcc<DT, METRIC> acc;
   if (on) {
     const uint8_t* row = A.points + (u64)a * A.stride;
@@ -260,6 +260,52 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
   }
 }
 
+// K7: the re-rank step of beam_search_rerank when the searched copy is quantised (beamSearch.h:426-444): exact distances
+// from the exact query to the first min(k * rerank_factor, |frontier|) frontier entries, sorted by (dist, id), first k
+// out.  One warp per query; one exact row per lane, summed in the reference's own order (floats included).
+struct RerankArgs {
+  const uint8_t* points; uint32_t stride, nch;   // exact base rows (names as in BeamArgs: pann_lane_distance reads them)
+  const uint8_t* queries; uint32_t qstride;      // exact query rows
+  uint64_t nq;
+  const uint32_t* fr_ids; const uint32_t* n_frontier; uint32_t fcap;
+  int k; long long rerank_factor;
+  uint32_t* out_ids; float* out_dists;
+  uint32_t off_q, warp_bytes;
+};
+template <int DT, int METRIC>
+__global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_rerank_kernel(const RerankArgs A) {
+  extern __shared__ __align__(16) uint8_t pann_smem[];
+  const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
+  uint8_t* ws = pann_smem + (size_t)wic * A.warp_bytes;
+  u64* keys = reinterpret_cast<u64*>(ws);
+  uint4* qsm = reinterpret_cast<uint4*>(ws + A.off_q);
+  for (long long q = (long long)blockIdx.x * PANN_WARPS_PER_CTA + wic; q < (long long)A.nq; q += (long long)gridDim.x * PANN_WARPS_PER_CTA) {
+    pann_load_query(A.queries + (u64)q * A.qstride, A.nch, qsm, lane);
+    const int nfr = (int)A.n_frontier[q];
+    const int nchk = (int)min((long long)A.k * A.rerank_factor, (long long)min(nfr, (int)A.fcap));
+    for (int base = 0; base < nchk; base += 32) {
+      const int i = base + lane;
+      const bool on = i < nchk;
+      const uint32_t id = on ? A.fr_ids[(u64)q * A.fcap + i] : 0u;
+      const float d = pann_lane_distance<DT, METRIC, 0>(A, id, on, qsm);
+      if (on) keys[i] = pann_key(d, id);
+    }
+    __syncwarp();
+    for (int i = lane; i < nchk; i += 32) {   // rank sort: only the first k ranks are written
+      const u64 ki = keys[i];
+      const int r = pann_count_below_any(keys, nchk, ki);   // keys are distinct (distinct ids)
+      if (r < A.k) {
+        A.out_ids[(u64)q * A.k + r] = pann_key_id(ki);
+        if (A.out_dists) A.out_dists[(u64)q * A.k + r] = pann_key_dist(ki);
+      }
+    }
+    __syncwarp();
+  }
+}
+
 const void* pann_beam_small_kernel_dt0(int metric, int qr);
 const void* pann_beam_small_kernel_dt1(int metric, int qr);
 const void* pann_beam_small_kernel_dt2(int metric, int qr);
+const void* pann_rerank_kernel_dt0(int metric);
+const void* pann_rerank_kernel_dt1(int metric);
+const void* pann_rerank_kernel_dt2(int metric);

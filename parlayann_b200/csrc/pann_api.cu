@@ -634,6 +634,78 @@ extern "C" int pann_search_full(pann_index* idx, const void* host_queries, uint6
   return 0;
 }
 
+static const void* rerank_kernel(int dtype, int metric) {
+  switch (dtype) {
+    case PANN_DT_F32: return pann_rerank_kernel_dt0(metric);
+    case PANN_DT_U8: return pann_rerank_kernel_dt1(metric);
+    default: return pann_rerank_kernel_dt2(metric);
+  }
+}
+
+extern "C" int pann_search_rerank_batch(pann_index* q_idx, pann_index* base_idx, const void* host_qqueries, uint64_t qq_stride_bytes,
+                                        const void* host_queries, uint64_t q_stride_bytes, uint64_t nq, const uint32_t* starts,
+                                        uint32_t nstarts, const pann_query_params* qp, int64_t rerank_factor, uint32_t* out_ids,
+                                        float* out_dists, uint32_t* out_visited, uint32_t* out_cmps) {
+  if (!q_idx || !base_idx || (nq && (!host_qqueries || !host_queries)) || !out_ids) PANN_FAIL("pann_search_rerank_batch: null argument");
+  if (validate_qp(qp)) return 1;
+  if (q_idx->device != base_idx->device) PANN_FAIL("pann_search_rerank_batch: both indexes must live on the same device");
+  if (q_idx->n != base_idx->n || q_idx->dims != base_idx->dims) PANN_FAIL("pann_search_rerank_batch: the quantised and the exact point sets disagree on n or dims");
+  if (q_idx->metric != base_idx->metric) PANN_FAIL("pann_search_rerank_batch: the two indexes use different metrics");
+  if (rerank_factor < 1) PANN_FAIL("pann_search_rerank_batch: rerank_factor must be positive");
+  if (qp->beam > 2048) PANN_FAIL("pann_search_rerank_batch: beam widths above 2048 are not supported on the re-rank path");
+  PANN_CUDA(cudaSetDevice(q_idx->device));
+  if (nq == 0) return 0;
+  // 1. the search over the quantised copy, whole frontier kept on the device
+  if (upload_queries(q_idx, host_qqueries, nq, qq_stride_bytes)) return 1;
+  if (upload_queries(base_idx, host_queries, nq, q_stride_bytes)) return 1;
+  PANN_CUDA(cudaStreamSynchronize(base_idx->stream));
+  const uint32_t k = (uint32_t)qp->k, fcap = (uint32_t)qp->beam;
+  size_t need = 4ull * nq * fcap * 2 + 4ull * nq * 4 + 8ull * nq * k + 256;
+  if (q_idx->misc.reserve(need)) return 1;
+  uint8_t* m = q_idx->misc.as<uint8_t>();
+  SearchOutputs o;
+  o.fcap = fcap;
+  o.fr_ids = (uint32_t*)m; m += 4ull * nq * fcap;
+  o.fr_dists = (float*)m; m += 4ull * nq * fcap;
+  o.n_frontier = (uint32_t*)m; m += 4ull * nq;
+  o.visited = (uint32_t*)m; m += 4ull * nq;
+  o.cmps = (uint32_t*)m; m += 4ull * nq;
+  o.status = (int*)m; m += 4ull * nq;
+  uint32_t* d_ids = (uint32_t*)m; m += 4ull * nq * k;
+  float* d_dists = (float*)m; m += 4ull * nq * k;
+  int flag = 0;
+  q_idx->last_launches = 0;
+  PANN_CUDA(cudaEventRecord(q_idx->ev0, q_idx->stream));
+  if (pann_run_search(q_idx, q_idx->queries.as<uint8_t>(), nq, q_idx->geom.stride, nullptr, starts, nstarts, qp, o, &flag)) return 1;
+  if (check_status(flag)) return 1;   // includes "fewer than k results" (beamSearch.h:416-419)
+  // 2. exact re-rank (beamSearch.h:426-444)
+  RerankArgs R;
+  memset(&R, 0, sizeof(R));
+  R.points = base_idx->points; R.stride = base_idx->geom.stride; R.nch = base_idx->geom.nch;
+  R.queries = base_idx->queries.as<uint8_t>(); R.qstride = base_idx->geom.stride; R.nq = nq;
+  R.fr_ids = o.fr_ids; R.n_frontier = o.n_frontier; R.fcap = fcap;
+  R.k = (int)k; R.rerank_factor = rerank_factor;
+  R.out_ids = d_ids; R.out_dists = d_dists;
+  R.off_q = al16((size_t)fcap * 8);
+  R.warp_bytes = R.off_q + base_idx->geom.stride;
+  const size_t cta_bytes = (size_t)R.warp_bytes * PANN_WARPS_PER_CTA;
+  if (cta_bytes > q_idx->smem_optin) PANN_FAIL("pann_search_rerank_batch: rows too long for the re-rank kernel's shared memory");
+  const void* fn = rerank_kernel(base_idx->dtype, base_idx->metric);
+  PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
+  const int grid = (int)std::min<uint64_t>((nq + PANN_WARPS_PER_CTA - 1) / PANN_WARPS_PER_CTA, (uint64_t)q_idx->sms * 8);
+  void* args[] = {(void*)&R};
+  PANN_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(PANN_WARPS_PER_CTA * 32), args, cta_bytes, q_idx->stream));
+  q_idx->last_launches++;
+  PANN_CUDA(cudaEventRecord(q_idx->ev1, q_idx->stream));
+  PANN_CUDA(cudaMemcpyAsync(out_ids, d_ids, 4ull * nq * k, cudaMemcpyDeviceToHost, q_idx->stream));
+  if (out_dists) PANN_CUDA(cudaMemcpyAsync(out_dists, d_dists, 4ull * nq * k, cudaMemcpyDeviceToHost, q_idx->stream));
+  if (out_visited) PANN_CUDA(cudaMemcpyAsync(out_visited, o.visited, 4ull * nq, cudaMemcpyDeviceToHost, q_idx->stream));
+  if (out_cmps) PANN_CUDA(cudaMemcpyAsync(out_cmps, o.cmps, 4ull * nq, cudaMemcpyDeviceToHost, q_idx->stream));
+  PANN_CUDA(cudaStreamSynchronize(q_idx->stream));
+  PANN_CUDA(cudaEventElapsedTime(&q_idx->last_ms, q_idx->ev0, q_idx->ev1));
+  return 0;
+}
+
 extern "C" int pann_random_permutation(int64_t n, int32_t* out) {
   if (n < 0 || !out) PANN_FAIL("pann_random_permutation: bad argument");
   pann_host_random_permutation(n, out);

@@ -15,12 +15,40 @@ def _vp(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
+def quant_params_u8(points):
+    """Euclidian_Point<uint8_t>::generate_parameters (euclidian_point.h:211-237) + parameters(min, max, dims) (:104-108):
+    per-row minima / maxima start at 0, all-integer non-negative data below 256 maps unscaled.  Returns (slope, offset)."""
+    p = np.asarray(points, dtype=np.float32)
+    min_val = np.float32(min(0.0, float(p.min()))) if p.size else np.float32(0)
+    max_val = np.float32(max(0.0, float(p.max()))) if p.size else np.float32(0)
+    if p.size == 0 or bool(((p >= 0) & (p == np.trunc(p))).all()):
+        if max_val < 256:
+            max_val = np.float32(255)
+        min_val = np.float32(0)
+    slope = np.float32(255) / np.float32(max_val - min_val)
+    v = float(np.float32(min_val * slope))
+    offset = int(np.trunc(v) + (np.sign(v) if abs(v - np.trunc(v)) >= 0.5 else 0))   # round(), halves away from zero
+    return slope, offset
+
+
+def quantize_u8(points, slope, offset):
+    """Euclidian_Point<uint8_t>::translate_point (euclidian_point.h:183-209): (int64)std::round(x * slope) - offset,
+    clamped to [0, 255]; the product is a float product, std::round rounds halves away from zero."""
+    p = np.asarray(points, dtype=np.float32)
+    if np.float32(slope) == np.float32(1.0) and offset == 0:
+        return p.astype(np.uint8)
+    v = p * np.float32(slope)                       # float32 product
+    t = np.trunc(v)
+    r = t + np.where(np.abs(v - t) >= np.float32(0.5), np.sign(v), np.float32(0))   # v - t is exact
+    return np.clip(r.astype(np.int64) - int(offset), 0, 255).astype(np.uint8)
+
+
 class GraphIndex:
     """PointRange + Graph resident on one B200 (reference: python/graph_index.cpp:48-118)."""
 
     def __init__(self, points=None, graph=None, data_type="uint8", metric="Euclidian", max_degree=None, device=0,
                  synthetic=None):
-        self.data_type, self.metric = data_type, metric
+        self.data_type, self.metric, self.device = data_type, metric, device
         self._h = C.c_void_p()
         L = _lib.lib()
         if synthetic is not None:  # dict(n, d, kind, seed, stream, r, nc): points generated on the device
@@ -47,6 +75,9 @@ class GraphIndex:
         self.start_point = 0  # knn_index::set_start (vamana/index.h:148)
 
     def close(self):
+        if getattr(self, "_qidx", None) is not None:
+            self._qidx.close()
+            self._qidx = None
         if getattr(self, "_h", None) is not None and self._h:
             _lib.lib().pann_index_destroy(self._h)
             self._h = C.c_void_p()
@@ -185,11 +216,45 @@ class GraphIndex:
         check(_lib.lib().pann_groundtruth_fetch(self._h, _vp(ids), _vp(dists)))
         return ids, dists
 
+    # ---- quantised search + exact re-rank (beam_search_rerank with differing byte widths, beamSearch.h:390-454)
+    def search_rerank(self, qindex, queries, qqueries, k=10, beam=10, cut=1.35, limit=None, degree_limit=None, starts=None,
+                      rerank_factor=100):
+        """`self` holds the exact points; `qindex` (same device) the 1-byte copy and the graph.  The search runs on qindex
+        with `qqueries`; the frontier is re-ranked with exact distances to `queries`.  Returns ids, dists, visited, cmps."""
+        queries = np.ascontiguousarray(queries, dtype=fileio.np_dtype(self.data_type))
+        qqueries = np.ascontiguousarray(qqueries, dtype=fileio.np_dtype(qindex.data_type))
+        nq = queries.shape[0]
+        st = np.asarray([qindex.start_point] if starts is None else starts, dtype=np.uint32)
+        out = (np.empty((nq, k), np.uint32), np.empty((nq, k), np.float32), np.empty(nq, np.uint32), np.empty(nq, np.uint32))
+        qp = qindex._qp(k, beam, cut, limit, degree_limit)
+        check(_lib.lib().pann_search_rerank_batch(qindex._h, self._h, _vp(qqueries), C.c_uint64(qqueries.strides[0] if nq else 0),
+                                                  _vp(queries), C.c_uint64(queries.strides[0] if nq else 0), C.c_uint64(nq), _vp(st),
+                                                  C.c_uint32(len(st)), C.byref(qp), C.c_int64(rerank_factor),
+                                                  _vp(out[0]), _vp(out[1]), _vp(out[2]), _vp(out[3])))
+        return out
+
+    def _quantized(self):
+        """the 1-byte copy graph_index.cpp keeps for 4-byte Euclidean data (:57-88): built once, on first use"""
+        if getattr(self, "_qidx", None) is None:
+            if self.data_type != "float" or self.metric != "Euclidian":
+                raise NotImplementedError("quant=True is built for float Euclidean data (Quantized_Mips_Point is a 'next' row, SURVEY.md §8f.2)")
+            pts = self.points()
+            self._qparams = quant_params_u8(pts)
+            self._qidx = GraphIndex(quantize_u8(pts, *self._qparams), self.graph(), "uint8", "Euclidian", device=self.device)
+        return self._qidx
+
     # ---- the reference's Python methods (python/graph_index.cpp:192-305)
     def batch_search(self, queries, knn, beam_width, quant=False, visit_limit=-1):
-        if quant:
-            raise NotImplementedError("quantized search + re-rank is a 'next' row (SURVEY.md §8f.2)")
         dl = min(self.max_degree, 3 * visit_limit)  # graph_index.cpp:198
+        if quant and fileio.np_dtype(self.data_type)().itemsize >= 4:   # use_quantization (graph_index.cpp:60)
+            qi = self._quantized()
+            queries = np.ascontiguousarray(queries, dtype=np.float32)
+            if self._qparams[0] == np.float32(1.0):   # graph_index.cpp:146-150: plain search of the 1-byte copy
+                ids, dists, _, _ = qi.search(queries.astype(np.uint8), k=knn, beam=beam_width, cut=1.35, limit=max(visit_limit, 0), degree_limit=max(dl, 0))
+                return ids, dists
+            ids, dists, _, _ = self.search_rerank(qi, queries, quantize_u8(queries, *self._qparams), k=knn, beam=beam_width, cut=1.35,
+                                                  limit=max(visit_limit, 0), degree_limit=max(dl, 0))
+            return ids, dists
         # the reference passes visit_limit straight into QueryParams: -1 means "visit nothing"
         ids, dists, _, _ = self.search(queries, k=knn, beam=beam_width, cut=1.35, limit=max(visit_limit, 0), degree_limit=max(dl, 0))
         return ids, dists

@@ -142,3 +142,37 @@ def ref_run(args, threads=None):
     if r.returncode != 0:
         raise RuntimeError(f"ref_driver failed ({r.returncode}): {r.stdout[-2000:]} {r.stderr[-2000:]}")
     return r.stdout
+
+
+def quant_params_u8(points):
+    """Euclidian_Point<uint8_t>::generate_parameters on float rows -> (slope float32, offset int32)"""
+    points = np.ascontiguousarray(points, dtype=np.float32)
+    slope = C.c_float(0); offset = C.c_int32(0)
+    lib().oracle_quant_params_u8(_p(points), C.c_uint64(points.shape[0]), C.c_uint32(points.shape[1]), C.c_uint64(points.strides[0]),
+                                 C.byref(slope), C.byref(offset))
+    return np.float32(slope.value), int(offset.value)
+
+
+def quantize_u8(points, slope, offset):
+    points = np.ascontiguousarray(points, dtype=np.float32)
+    out = np.empty(points.shape, dtype=np.uint8)
+    lib().oracle_quantize_u8(_p(points), C.c_uint64(points.shape[0]), C.c_uint32(points.shape[1]), C.c_uint64(points.strides[0]),
+                             C.c_float(float(slope)), C.c_int32(offset), _p(out))
+    return out
+
+
+def search_rerank(points, qpoints, graph, queries, qqueries, data_type="float", metric="Euclidian", k=10, beam=10, cut=1.35,
+                  limit=None, degree_limit=None, rerank_factor=100):
+    """beam_search_rerank with a 1-byte quantised copy (beamSearch.h:390-454): search qpoints/qqueries (uint8), then the
+    exact re-rank of the first k*rerank_factor frontier entries against points/queries."""
+    r = search(qpoints, graph, qqueries, "uint8", metric, k=k, beam=beam, cut=cut, limit=limit, degree_limit=degree_limit, full=True)
+    points = np.ascontiguousarray(points); queries = np.ascontiguousarray(queries)
+    nq = queries.shape[0]
+    ids = np.zeros((nq, k), dtype=np.uint32); dists = np.zeros((nq, k), dtype=np.float32)
+    fcap = r["fr_ids"].shape[1]
+    rc = lib().oracle_rerank(DT[data_type], METRIC[metric], _p(points), C.c_uint64(points.shape[0]), C.c_uint32(points.shape[1]),
+                             C.c_uint64(points.strides[0]), _p(queries), C.c_uint64(nq), C.c_uint64(queries.strides[0]),
+                             _p(r["fr_ids"]), _p(r["nfr"]), C.c_uint32(fcap), C.c_long(k), C.c_long(rerank_factor), _p(ids), _p(dists), nthreads())
+    if rc:
+        raise RuntimeError("oracle: a query returned fewer than k results (the reference aborts here)")
+    return dict(ids=ids, dists=dists, visited=r["visited"], cmps=r["cmps"])
