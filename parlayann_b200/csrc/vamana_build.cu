@@ -77,9 +77,11 @@ static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, De
   const char* rc_env = getenv("PANN_PRUNE_ROW_CACHE");  // 0 / 1 force it off / on
   const bool rc_on = g.stride <= 256 && (rc_env ? rc_env[0] == '1' : (idx->n * (uint64_t)g.stride > (256ull << 20)));
   // reverse-edge groups (mode 1) are the vertex's <= R edges plus a handful of new ones: a smaller list and row cache per
-  // warp doubles the resident warps of the row-cache path (the rare longer list takes the uncached scan or the slab launch)
+  // warp (80 rows, 128 keys) nearly triples the resident warps of the row-cache path (the rare longer list takes the
+  // uncached scan or the slab launch)
   const bool small_lists = rc_on && A.mode == 1 && A.R <= 64;
-  A.cap = small_lists ? 256 : 512;
+  A.cap = small_lists ? 128 : 512;
+  if (small_lists) if (const char* e = getenv("PANN_PRUNE_CAP")) A.cap = (uint32_t)atoi(e);
   A.off_b = al16((size_t)A.cap * 8);
   A.off_q = 2 * A.off_b;
   A.warp_bytes = A.off_q + g.stride;
@@ -90,7 +92,8 @@ static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, De
   // It pays once the point set no longer lives in the 126 MB L2 (measured: 10M x 128 B build 36 s -> 15.5 s); while it
   // does (1M x 128 B), the plain path with more resident warps is ~20 % faster.
   if (rc_on) {
-    A.rc_rows = small_lists ? 96 : 160;
+    A.rc_rows = small_lists ? 80 : 160;   // measured at 10M (rows, keys): (96,256) 3.14 s, (80,128) 2.54 s, (72,128) 2.83 s, (112,256) 4.26 s
+    if (small_lists) if (const char* e = getenv("PANN_PRUNE_RC_ROWS")) A.rc_rows = (uint32_t)atoi(e);
     A.rc_pitch = g.stride + 16;
     if (((A.rc_pitch / 16) & 1) == 0) A.rc_pitch += 16;
     A.off_pos = A.warp_bytes;
