@@ -307,15 +307,25 @@ class defaults:  # python/module.cpp:142-148
 
 
 def build_vamana_index(metric, dtype, data_dir, index_dir, R, L, alpha, two_pass, device=0):
-    """python/wrapper.py:3-24 -> builder.cpp:36-95.  1-byte types and Euclidian floats build directly on the
-    points; the reference's MIPS normalisation/alpha override and its quantised float build (builder.cpp:45-87)
-    are 'next' rows and raise here rather than silently differing."""
+    """python/wrapper.py:3-24 -> builder.cpp:36-95.  1-byte Euclidean types build directly on the points
+    (builder.cpp:88-94); 4-byte Euclidean types build on the 1-byte scalar-quantised copy, as the reference's builder does
+    (builder.cpp:60-72: the graph file then holds the graph of the quantised points).  Non-metric (MIPS) data would be
+    normalised in place, get its alpha overridden and, for floats, be quantised with Quantized_Mips_Point
+    (builder.cpp:45-54, :73-86), which is not built here: that raises rather than silently differing — use
+    GraphIndex(...).build() to build a MIPS graph over the points as they are."""
     if metric not in _lib.METRIC:
         raise Exception("Invalid metric " + str(metric))
     if dtype not in _lib.DTYPE:
         raise Exception("Invalid data type " + str(dtype))
+    if metric != "Euclidian":
+        raise NotImplementedError("build_vamana_index for MIPS data (in-place normalisation, Quantized_Mips_Point) is a 'next' row (SURVEY.md §8f.2)")
     pts = fileio.read_bin(data_dir, dtype)
-    idx = GraphIndex(pts, None, dtype, metric, max_degree=R, device=device)
+    if fileio.np_dtype(dtype)().itemsize > 1:
+        slope, offset = quant_params_u8(pts)
+        print(f"scalar quantization: slope = {slope}, offset = {offset}")
+        idx = GraphIndex(quantize_u8(pts, slope, offset), None, "uint8", metric, max_degree=R, device=device)
+    else:
+        idx = GraphIndex(pts, None, dtype, metric, max_degree=R, device=device)
     idx.build(R=R, L=L, alpha=alpha, num_passes=2 if two_pass else 1)
     fileio.write_graph(index_dir, idx.graph())
     return idx

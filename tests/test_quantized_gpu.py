@@ -40,3 +40,27 @@ def test_rerank_errors():
     other = P.GraphIndex(base[:100].astype(np.uint8), None, "uint8", "Euclidian", max_degree=32)
     with pytest.raises(P.PannError):   # the two point sets must describe the same points
         idx.search_rerank(other, qs, qs.astype(np.uint8), k=10, beam=10)
+
+
+def test_builder_quantises_float_data(tmp_path):
+    # python/builder.cpp:60-72: 4-byte Euclidean data is built on its 1-byte scalar-quantised copy; the graph must be the
+    # oracle's build over exactly those bytes, and the saved index serves quant=True searches
+    import parlayann_b200 as P
+    from parlayann_b200 import fileio
+    from parlayann_b200.index import quant_params_u8, quantize_u8
+    base = O.gen_points("float", 3000, 64, seed=5)
+    qs = O.gen_points("float", 50, 64, seed=5, stream=1)
+    bp, gp = str(tmp_path / "b.fbin"), str(tmp_path / "g.graph")
+    fileio.write_bin(bp, base)
+    P.build_vamana_index("Euclidian", "float", bp, gp, 16, 32, 1.2, False)
+    qb = quantize_u8(base, *quant_params_u8(base))
+    ref_graph = O.vamana_build(qb, "uint8", "Euclidian", R=16, L=32, alpha=1.2, passes=1, sort_neighbors=True)[0]
+    g = fileio.read_graph(gp)
+    live = np.arange(g.shape[1])[None, :] <= g[:, :1]          # slot 0 = degree; the file format drops the slots beyond it
+    assert np.array_equal(g[:, 0], ref_graph[:, 0]) and np.array_equal(g[live], ref_graph[live])
+    idx = P.load_index("Euclidian", "float", bp, gp)
+    ids, dists = idx.batch_search(qs, 10, 30, quant=True, visit_limit=len(base))
+    want = O.search_rerank(base, qb, g, qs, quantize_u8(qs, *quant_params_u8(base)), k=10, beam=30)
+    assert np.array_equal(ids, want["ids"]) and np.array_equal(dists, want["dists"])
+    with pytest.raises(NotImplementedError):
+        P.build_vamana_index("mips", "float", bp, gp, 16, 32, 1.0, False)
