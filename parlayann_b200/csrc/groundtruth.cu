@@ -282,8 +282,11 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
   uint64_t cb = ((1ull << 28) / nq) / GT_TB * GT_TB;
   cb = std::max<uint64_t>(cb, 4096);
   cb = std::min<uint64_t>(cb, (nb + GT_TB - 1) / GT_TB * GT_TB);
-  DevBuf D, state, state_bak, bnorm, qnorm, thr, cand_ids, cand_cnt, misc;
-  auto fail = [&]() { D.release(); state.release(); state_bak.release(); bnorm.release(); qnorm.release(); thr.release(); cand_ids.release(); cand_cnt.release(); misc.release(); return 1; };
+  // the (up to 1 GiB) v1 distance block is per call; everything else lives in the index and is reused by later calls
+  DevBuf D;
+  DevBuf &state = idx->gt_scratch[0], &state_bak = idx->gt_scratch[1], &bnorm = idx->gt_scratch[2], &qnorm = idx->gt_scratch[3],
+         &thr = idx->gt_scratch[4], &cand_ids = idx->gt_scratch[5], &cand_cnt = idx->gt_scratch[6], &misc = idx->gt_scratch[7];
+  auto fail = [&]() { D.release(); return 1; };
   if ((!use_mma && D.reserve(4ull * nq * cb)) || state.reserve(8ull * nq * k)) return fail();   // the MMA path needs D only for a fallback
   if (idx->gt_ids.reserve(4ull * nq * k) || idx->gt_dists.reserve(4ull * nq * k)) return fail();
   const uint64_t nb_pad = (nb + GTM_N - 1) / GTM_N * GTM_N;

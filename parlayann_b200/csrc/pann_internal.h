@@ -52,6 +52,7 @@ struct pann_index {
   void* pinned = nullptr; size_t pinned_cap = 0;
   // ground truth results (resident)
   DevBuf gt_ids, gt_dists; uint64_t gt_nq = 0; uint32_t gt_k = 0;
+  DevBuf gt_scratch[8];        // ground-truth work buffers, kept between calls (cudaMalloc/cudaFree of ~200 MB cost 5 ms per call)
   int gt_fallback_chunks = 0;  // MMA chunks retaken on the CUDA cores (candidate-list overflow), cumulative
 };
 

@@ -134,4 +134,12 @@ def groundtruth_sharded(index, queries=None, k=100, base_offset=0, group=None, l
     check(L.pann_groundtruth_merge_device(dev.index, C.c_uint32(world), C.c_uint64(nq), C.c_uint32(k), C.c_void_p(all_i.data_ptr()),
                                           C.c_void_p(all_d.data_ptr()), C.c_void_p(out_i.data_ptr()), C.c_void_p(out_d.data_ptr()),
                                           C.c_void_p(st)))
-    return out_i.cpu().numpy(), out_d.cpu().numpy()
+    # results come back through pinned buffers kept on the index (a pageable .cpu() of 8 MB takes 5 ms, this 0.3 ms)
+    pin = getattr(index, "_gt_pinned", None)
+    if pin is None or pin[0].shape != (nq, k):
+        pin = (torch.empty((nq, k), dtype=torch.int32).pin_memory(), torch.empty((nq, k), dtype=torch.float32).pin_memory())
+        index._gt_pinned = pin
+    pin[0].copy_(out_i, non_blocking=True)
+    pin[1].copy_(out_d, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return pin[0].numpy().copy(), pin[1].numpy().copy()
