@@ -459,6 +459,58 @@ void oracle_quantize_u8(const float* pts, uint64_t n, uint32_t d, uint64_t strid
     }
   }
 }
+// ---- Quantized_Mips_Point<8,trim> over normalised float rows (python/graph_index.cpp:88-95, python/builder.cpp:45-54, :73-86)
+// Mips_Point<float>::normalize (mips_point.h:115-124): float products summed into a double in element order, sqrt,
+// 1/norm rounded to float, float products written back in place.
+void oracle_normalize_f32(float* pts, uint64_t n, uint32_t d, uint64_t stride) {
+  for (uint64_t i = 0; i < n; i++) {
+    float* r = (float*)((uint8_t*)pts + i * stride);
+    double norm = 0.0;
+    for (uint32_t j = 0; j < d; j++) { float sq = r[j] * r[j]; norm += sq; }
+    norm = std::sqrt(norm);
+    if (norm == 0) norm = 1.0;
+    float inv_norm = 1.0 / norm;
+    for (uint32_t j = 0; j < d; j++) r[j] = r[j] * inv_norm;
+  }
+}
+// Quantized_Mips_Point::generate_parameters (mips_point.h:437-462): all values sorted; trim drops 1e-4 of each tail
+// (lower index = (long)(float cutoff * float len), upper = (long)((1.0 - cutoff) * (len - 1)) in double); bound = max(max, -min).
+float oracle_quant_params_mips8(const float* pts, uint64_t n, uint32_t d, uint64_t stride, int trim) {
+  const long len = (long)(n * d);
+  if (len == 0) return 1.0f;
+  std::vector<float> vals((size_t)len);
+  for (uint64_t i = 0; i < n; i++) {
+    const float* r = (const float*)((const uint8_t*)pts + i * stride);
+    for (uint32_t j = 0; j < d; j++) vals[i * d + j] = r[j];
+  }
+  std::sort(vals.begin(), vals.end());
+  float min_val, max_val;
+  if (trim) {
+    float cutoff = .0001;
+    min_val = vals[(long)(cutoff * len)];
+    max_val = vals[(long)((1.0 - cutoff) * (len - 1))];
+  } else {
+    min_val = vals[0];
+    max_val = vals[len - 1];
+  }
+  return std::max(max_val, -min_val);
+}
+// Quantized_Mips_Point<8>::translate_point (mips_point.h:421-434), range = 255: scale = 127 / max_val in float,
+// values beyond +-max_val cap at +-127, the rest std::round(x * scale) (halves away from zero).
+void oracle_quantize_mips8(const float* pts, uint64_t n, uint32_t d, uint64_t stride, float max_val, int8_t* out) {
+  const int range = 255;
+  for (uint64_t i = 0; i < n; i++) {
+    const float* r = (const float*)((const uint8_t*)pts + i * stride);
+    for (uint32_t j = 0; j < d; j++) {
+      float mv = max_val;
+      float scale = (range / 2) / mv;
+      float pj = r[j];
+      if (pj < -mv) out[i * d + j] = (int8_t)(-range / 2);
+      else if (pj > mv) out[i * d + j] = (int8_t)(range / 2);
+      else { int32_t v = std::round(pj * scale); out[i * d + j] = (int8_t)v; }
+    }
+  }
+}
 // beam_search_rerank's re-rank step (beamSearch.h:426-444): exact distances of the first min(k*rerank_factor, |frontier|)
 // frontier entries, std::sort by (dist, id), first k.
 int oracle_rerank(int dtype, int metric, const void* base, uint64_t n, uint32_t d, uint64_t stride, const void* queries,

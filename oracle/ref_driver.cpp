@@ -11,7 +11,9 @@
 //   search  -> qsearchAll + stats                                    (algorithms/utils/beamSearch.h:537-565)
 //   full    -> beam_search (frontier + visited lists per query)      (algorithms/utils/beamSearch.h:217-223)
 //   recall  -> checkRecall (timed qsearchAll + tie-aware recall)     (algorithms/utils/check_nn_recall.h:17-125)
-//   qsearch -> qsearchAll over a 1-byte quantised copy + exact re-rank (vamana/neighbors.h:117-127, beamSearch.h:409-444)
+//   qsearch -> qsearchAll over a 1-byte quantised copy + exact re-rank (vamana/neighbors.h:117-127, beamSearch.h:409-444;
+//              MIPS: Quantized_Mips_Point<8,true> over normalised points, python/graph_index.cpp:88-95, :166-181)
+//   qbuild  -> the build python/builder.cpp:36-95 intends for float data: graph over the 1-byte copy
 //   gt      -> compute_groundtruth + write_ibin                      (data_tools/compute_groundtruth.cpp:22-100)
 //
 // Built by oracle/Makefile into oracle/_ref/ (git-ignored, travels to the GPU box).
@@ -110,6 +112,47 @@ static int run(const std::string& cmd, int argc, char** argv) {
     return 0;
   }
 
+  if (cmd == "qbuild") {
+    // what python/builder.cpp:36-95 intends for 4-byte data (it does not compile at this commit): normalise non-metric
+    // points and override alpha (:45-54), build over the 1-byte copy (Euclidian_Point<uint8_t> or
+    // Quantized_Mips_Point<8,true>, :60-87), save that graph.
+    if constexpr (std::is_same<typename Point::T, float>::value) {
+      long R = atol(need(argc, argv, "-R")), L = atol(need(argc, argv, "-L"));
+      double alpha = (float)atof(arg(argc, argv, "-alpha", "1.2"));   // builder.cpp takes alpha as a float
+      int passes = atoi(arg(argc, argv, "-passes", "1"));
+      if (!Point::is_metric()) {
+        for (size_t i = 0; i < Points.size(); i++) Points[i].normalize();
+        if (Points.dimension() <= 200) alpha = Points.dimension() < 100 ? (float)1.0 : (float).98;
+      }
+      BuildParams BP(R, L, alpha, passes, false);
+      stats<uint> BuildStats(Points.size());
+      auto go = [&](auto& Q_Points) {
+        using QPR = std::remove_reference_t<decltype(Q_Points)>;
+        Graph<uint> G(BP.max_degree(), Q_Points.size());
+        knn_index<QPR, QPR, uint> I(BP);
+        I.build_index(G, Q_Points, Q_Points, BuildStats, true);
+        G.save((char*)(out + ".graph").c_str());
+        const size_t d = Q_Points.dimension();
+        std::vector<uint8_t> qb(Q_Points.size() * d);
+        for (size_t i = 0; i < Q_Points.size(); i++) for (size_t j = 0; j < d; j++) qb[i * d + j] = (uint8_t)Q_Points[i][j];
+        dump(out + ".qbase", qb.data(), qb.size());
+      };
+      if constexpr (std::is_same<Point, Euclidian_Point<float>>::value) {
+        PointRange<Euclidian_Point<uint8_t>> Q_Points(Points);
+        printf("REF_QUANT slope %.9g offset %d\n", (double)Q_Points.params.slope, (int)Q_Points.params.offset);
+        go(Q_Points);
+      } else {
+        PointRange<Quantized_Mips_Point<8, true>> Q_Points(Points);
+        printf("REF_QUANT max_val %.9g\n", (double)Q_Points.params.max_val);
+        go(Q_Points);
+      }
+      return 0;
+    } else {
+      fprintf(stderr, "ref_driver: qbuild needs -data_type float\n");
+      return 2;
+    }
+  }
+
   // the remaining commands need a graph and queries
   Graph<uint> G((char*)need(argc, argv, "-graph"));
   PR Q((char*)need(argc, argv, "-query"));
@@ -169,8 +212,36 @@ static int run(const std::string& cmd, int argc, char** argv) {
       dump(out + ".qquery", qq.data(), qq.size());
       printf("REF_QUANT slope %.9g offset %d\n", (double)Q_Points.params.slope, (int)Q_Points.params.offset);
       return 0;
+    } else if constexpr (std::is_same<Point, Mips_Point<float>>::value) {
+      // python/graph_index.cpp:88-95, :166-181: points and queries normalised, Quantized_Mips_Point<8,true> copies,
+      // beam_search_rerank with the exact (normalised) points (dims <= 200: no second-level filter)
+      for (size_t i = 0; i < Points.size(); i++) Points[i].normalize();
+      for (size_t i = 0; i < nq; i++) Q[i].normalize();
+      using QPoint = Quantized_Mips_Point<8, true>;
+      using QPR = PointRange<QPoint>;
+      QPR Q_Points(Points);
+      QPR Q_Q(Q, Q_Points.params);
+      stats<uint> QS(nq);
+      auto res = qsearchAll<PR, QPR, QPR, uint>(Q, Q_Q, Q_Q, G, Points, Q_Points, Q_Points, QS, start, QP);
+      std::vector<uint> ids(nq * k);
+      for (size_t i = 0; i < nq; i++) for (long j = 0; j < k; j++) ids[i * k + j] = res[i][j];
+      dump(out + ".ids", ids.data(), ids.size() * 4);
+      dump(out + ".visited", QS.visited.begin(), 4 * nq);
+      dump(out + ".distances", QS.distances.begin(), 4 * nq);
+      const size_t d = Points.dimension();
+      std::vector<uint8_t> qb(Points.size() * d), qq(nq * d);
+      std::vector<float> nb(64 * d), nqv(nq * d);
+      for (size_t i = 0; i < Points.size(); i++) for (size_t j = 0; j < d; j++) qb[i * d + j] = (uint8_t)Q_Points[i][j];
+      for (size_t i = 0; i < nq; i++) for (size_t j = 0; j < d; j++) { qq[i * d + j] = (uint8_t)Q_Q[i][j]; nqv[i * d + j] = Q[i][j]; }
+      for (size_t i = 0; i < 64 && i < Points.size(); i++) for (size_t j = 0; j < d; j++) nb[i * d + j] = Points[i][j];
+      dump(out + ".qbase", qb.data(), qb.size());
+      dump(out + ".qquery", qq.data(), qq.size());
+      dump(out + ".nbase_head", nb.data(), nb.size() * 4);
+      dump(out + ".nquery", nqv.data(), nqv.size() * 4);
+      printf("REF_QUANT max_val %.9g\n", (double)Q_Points.params.max_val);
+      return 0;
     } else {
-      fprintf(stderr, "ref_driver: qsearch needs -data_type float -dist_func Euclidian\n");
+      fprintf(stderr, "ref_driver: qsearch needs -data_type float\n");
       return 2;
     }
   }

@@ -43,6 +43,50 @@ def quantize_u8(points, slope, offset):
     return np.clip(r.astype(np.int64) - int(offset), 0, 255).astype(np.uint8)
 
 
+def normalize_rows(points):
+    """Mips_Point<float>::normalize over every row (mips_point.h:115-124): the float squares are summed into a double in
+    element order, 1/sqrt is rounded to float, the row is scaled by float products.  Returns a new float32 array."""
+    p = np.array(points, dtype=np.float32, order="C")
+    norm = np.zeros(p.shape[0], np.float64)
+    for j in range(p.shape[1]):                     # element order is part of the result
+        norm += (p[:, j] * p[:, j]).astype(np.float64)
+    norm = np.sqrt(norm)
+    norm[norm == 0] = 1.0
+    p *= (1.0 / norm).astype(np.float32)[:, None]
+    return p
+
+
+def quant_params_mips8(points, trim=True):
+    """Quantized_Mips_Point<8,trim>::generate_parameters (mips_point.h:437-462): bound = max(max_val, -min_val) over all
+    values, after dropping 1e-4 of each tail when trim is set (graph_index.cpp and builder.cpp use trim).  The lower index
+    is a float product, the upper one a double product, as in the reference.  Returns max_val (float32)."""
+    v = np.asarray(points, dtype=np.float32).reshape(-1)
+    ln = v.size
+    if ln == 0:
+        return np.float32(1.0)
+    if trim:
+        cutoff = np.float32(.0001)
+        lo = int(np.float32(cutoff * np.float32(ln)))
+        hi = int((1.0 - float(cutoff)) * (ln - 1))
+        part = np.partition(v, sorted({lo, hi}))
+        min_val, max_val = part[lo], part[hi]
+    else:
+        min_val, max_val = v.min(), v.max()
+    return np.float32(max(max_val, -min_val))
+
+
+def quantize_mips8(points, max_val):
+    """Quantized_Mips_Point<8>::translate_point (mips_point.h:421-434): scale = 127 / max_val (float), values beyond
+    +-max_val cap at +-127, the rest std::round(x * scale) with halves away from zero.  Returns int8."""
+    p = np.asarray(points, dtype=np.float32)
+    mv = np.float32(max_val)
+    scale = np.float32(127) / mv
+    v = p * scale
+    t = np.trunc(v)
+    r = t + np.where(np.abs(v - t) >= np.float32(0.5), np.sign(v), np.float32(0))
+    r = np.where(p < -mv, np.float32(-127), np.where(p > mv, np.float32(127), r))
+    return r.astype(np.int32).astype(np.int8)
+
 class GraphIndex:
     """PointRange + Graph resident on one B200 (reference: python/graph_index.cpp:48-118)."""
 
@@ -234,13 +278,20 @@ class GraphIndex:
         return out
 
     def _quantized(self):
-        """the 1-byte copy graph_index.cpp keeps for 4-byte Euclidean data (:57-88): built once, on first use"""
+        """the 1-byte copy graph_index.cpp keeps for 4-byte data (:57-95): Euclidian_Point<uint8_t> for metric points,
+        Quantized_Mips_Point<8,true> for MIPS (whose exact rows were normalised at load time); built once, on first use"""
         if getattr(self, "_qidx", None) is None:
-            if self.data_type != "float" or self.metric != "Euclidian":
-                raise NotImplementedError("quant=True is built for float Euclidean data (Quantized_Mips_Point is a 'next' row, SURVEY.md §8f.2)")
+            if self.data_type != "float":
+                raise NotImplementedError("quant=True is built for float data")
+            if self.d > (800 if self.metric == "Euclidian" else 200):
+                raise NotImplementedError("the second-level filter copies the reference adds above 800 (Euclidean) / 200 (MIPS) dimensions (graph_index.cpp:91-95, use_filtering) are not built")
             pts = self.points()
-            self._qparams = quant_params_u8(pts)
-            self._qidx = GraphIndex(quantize_u8(pts, *self._qparams), self.graph(), "uint8", "Euclidian", device=self.device)
+            if self.metric == "Euclidian":
+                self._qparams = quant_params_u8(pts)
+                self._qidx = GraphIndex(quantize_u8(pts, *self._qparams), self.graph(), "uint8", "Euclidian", device=self.device)
+            else:
+                self._qparams = (quant_params_mips8(pts, trim=True),)
+                self._qidx = GraphIndex(quantize_mips8(pts, *self._qparams), self.graph(), "int8", "mips", device=self.device)
         return self._qidx
 
     # ---- the reference's Python methods (python/graph_index.cpp:192-305)
@@ -249,10 +300,15 @@ class GraphIndex:
         if quant and fileio.np_dtype(self.data_type)().itemsize >= 4:   # use_quantization (graph_index.cpp:60)
             qi = self._quantized()
             queries = np.ascontiguousarray(queries, dtype=np.float32)
-            if self._qparams[0] == np.float32(1.0):   # graph_index.cpp:146-150: plain search of the 1-byte copy
+            if self.metric != "Euclidian":            # graph_index.cpp:166-181: q.normalize(), Quantized_Mips_Point copy of it
+                queries = normalize_rows(queries)
+                qq = quantize_mips8(queries, *self._qparams)
+            elif self._qparams[0] == np.float32(1.0):   # graph_index.cpp:146-150: plain search of the 1-byte copy
                 ids, dists, _, _ = qi.search(queries.astype(np.uint8), k=knn, beam=beam_width, cut=1.35, limit=max(visit_limit, 0), degree_limit=max(dl, 0))
                 return ids, dists
-            ids, dists, _, _ = self.search_rerank(qi, queries, quantize_u8(queries, *self._qparams), k=knn, beam=beam_width, cut=1.35,
+            else:
+                qq = quantize_u8(queries, *self._qparams)
+            ids, dists, _, _ = self.search_rerank(qi, queries, qq, k=knn, beam=beam_width, cut=1.35,
                                                   limit=max(visit_limit, 0), degree_limit=max(dl, 0))
             return ids, dists
         # the reference passes visit_limit straight into QueryParams: -1 means "visit nothing"
@@ -308,19 +364,30 @@ class defaults:  # python/module.cpp:142-148
 
 def build_vamana_index(metric, dtype, data_dir, index_dir, R, L, alpha, two_pass, device=0):
     """python/wrapper.py:3-24 -> builder.cpp:36-95.  1-byte Euclidean types build directly on the points
-    (builder.cpp:88-94); 4-byte Euclidean types build on the 1-byte scalar-quantised copy, as the reference's builder does
-    (builder.cpp:60-72: the graph file then holds the graph of the quantised points).  Non-metric (MIPS) data would be
-    normalised in place, get its alpha overridden and, for floats, be quantised with Quantized_Mips_Point
-    (builder.cpp:45-54, :73-86), which is not built here: that raises rather than silently differing — use
-    GraphIndex(...).build() to build a MIPS graph over the points as they are."""
+    (builder.cpp:88-94); 4-byte types build on a 1-byte copy, as the reference's builder does, and the graph file holds the
+    graph of that copy: Euclidian_Point<uint8_t> for Euclidean data (builder.cpp:60-72); float MIPS data is normalised
+    first, alpha is overridden (1.0 below 100 dimensions, 0.98 up to 200; builder.cpp:45-54) and the copy is
+    Quantized_Mips_Point<8,true> (builder.cpp:73-86), whose distance is the int8 inner product, so the build runs the int8
+    MIPS kernels over those bytes (pinned against the reference in tests/test_quantized_cpu.py).  1-byte MIPS types would
+    be normalised IN their integer type by the reference (rows collapse to 0/1 values): that raises here."""
     if metric not in _lib.METRIC:
         raise Exception("Invalid metric " + str(metric))
     if dtype not in _lib.DTYPE:
         raise Exception("Invalid data type " + str(dtype))
-    if metric != "Euclidian":
-        raise NotImplementedError("build_vamana_index for MIPS data (in-place normalisation, Quantized_Mips_Point) is a 'next' row (SURVEY.md §8f.2)")
+    wide = fileio.np_dtype(dtype)().itemsize > 1
+    if metric != "Euclidian" and not wide:
+        raise NotImplementedError("build_vamana_index for 1-byte MIPS data: the reference normalises the integer rows in place (builder.cpp:45-49), which is not reproduced")
     pts = fileio.read_bin(data_dir, dtype)
-    if fileio.np_dtype(dtype)().itemsize > 1:
+    alpha = float(np.float32(alpha))                   # builder.cpp takes alpha as a float
+    if metric != "Euclidian":
+        print("normalizing")
+        pts = normalize_rows(pts)
+        if pts.shape[1] <= 200:
+            alpha = float(np.float32(1.0 if pts.shape[1] < 100 else .98))
+        max_val = quant_params_mips8(pts, trim=True)
+        print(f"mips scalar quantization to 8 bits: trimmed to max = {max_val}")
+        idx = GraphIndex(quantize_mips8(pts, max_val), None, "int8", metric, max_degree=R, device=device)
+    elif wide:
         slope, offset = quant_params_u8(pts)
         print(f"scalar quantization: slope = {slope}, offset = {offset}")
         idx = GraphIndex(quantize_u8(pts, slope, offset), None, "uint8", metric, max_degree=R, device=device)
@@ -339,4 +406,7 @@ def load_index(metric, dtype, data_dir, index_dir, hnsw=False, device=0):
         raise Exception("Invalid metric")
     if dtype not in _lib.DTYPE:
         raise Exception("Invalid data type")
-    return GraphIndex(fileio.read_bin(data_dir, dtype), fileio.read_graph(index_dir), dtype, metric, device=device)
+    pts = fileio.read_bin(data_dir, dtype)
+    if metric != "Euclidian" and fileio.np_dtype(dtype)().itemsize > 1:
+        pts = normalize_rows(pts)   # graph_index.cpp:88-90: 4-byte non-metric points are normalised when the index loads
+    return GraphIndex(pts, fileio.read_graph(index_dir), dtype, metric, device=device)

@@ -161,11 +161,33 @@ def quantize_u8(points, slope, offset):
     return out
 
 
+def normalize_rows(points):
+    """Mips_Point<float>::normalize over every row (mips_point.h:115-124) -> a new float32 array"""
+    out = np.array(points, dtype=np.float32, order="C")
+    lib().oracle_normalize_f32(_p(out), C.c_uint64(out.shape[0]), C.c_uint32(out.shape[1]), C.c_uint64(out.strides[0]))
+    return out
+
+
+def quant_params_mips8(points, trim=True):
+    """Quantized_Mips_Point<8,trim>::generate_parameters -> max_val float32"""
+    points = np.ascontiguousarray(points, dtype=np.float32)
+    f = lib().oracle_quant_params_mips8
+    f.restype = C.c_float
+    return np.float32(f(_p(points), C.c_uint64(points.shape[0]), C.c_uint32(points.shape[1]), C.c_uint64(points.strides[0]), C.c_int(int(trim))))
+
+
+def quantize_mips8(points, max_val):
+    points = np.ascontiguousarray(points, dtype=np.float32)
+    out = np.empty(points.shape, dtype=np.int8)
+    lib().oracle_quantize_mips8(_p(points), C.c_uint64(points.shape[0]), C.c_uint32(points.shape[1]), C.c_uint64(points.strides[0]),
+                                C.c_float(float(max_val)), _p(out))
+    return out
+
 def search_rerank(points, qpoints, graph, queries, qqueries, data_type="float", metric="Euclidian", k=10, beam=10, cut=1.35,
-                  limit=None, degree_limit=None, rerank_factor=100):
+                  limit=None, degree_limit=None, rerank_factor=100, qdata_type="uint8"):
     """beam_search_rerank with a 1-byte quantised copy (beamSearch.h:390-454): search qpoints/qqueries (uint8), then the
     exact re-rank of the first k*rerank_factor frontier entries against points/queries."""
-    r = search(qpoints, graph, qqueries, "uint8", metric, k=k, beam=beam, cut=cut, limit=limit, degree_limit=degree_limit, full=True)
+    r = search(qpoints, graph, qqueries, qdata_type, metric, k=k, beam=beam, cut=cut, limit=limit, degree_limit=degree_limit, full=True)
     points = np.ascontiguousarray(points); queries = np.ascontiguousarray(queries)
     nq = queries.shape[0]
     ids = np.zeros((nq, k), dtype=np.uint32); dists = np.zeros((nq, k), dtype=np.float32)
