@@ -42,6 +42,13 @@ PANN_B200_TRAIT(Mips_Point, float, PANN_F32, PANN_MIPS)
 PANN_B200_TRAIT(Mips_Point, uint8_t, PANN_U8, PANN_MIPS)
 PANN_B200_TRAIT(Mips_Point, int8_t, PANN_I8, PANN_MIPS)
 #undef PANN_B200_TRAIT
+// Quantized_Mips_Point<8, trim> (mips_point.h:288-462): rows of int8, distance = -(int8 inner product) (:339-346) — the
+// int8 MIPS kernels compute exactly that (values below 2^24, so the reference's int64 and the kernels' float agree).
+template <bool trim, int range> struct point_traits<Quantized_Mips_Point<8, trim, range>> {
+  static constexpr bool supported = true;
+  static constexpr int dtype = PANN_I8, metric = PANN_MIPS;
+  using elt = int8_t;
+};
 
 inline void check(int rc) {  // the reference's error convention: message, then abort()
   if (rc != 0) { std::cout << pann_last_error() << std::endl; abort(); }
@@ -58,7 +65,7 @@ template <typename indexType> inline indexType* graph_base(const Graph<indexType
 template <typename PointRange, typename indexType = unsigned int>
 class DeviceIndex {
   static_assert(point_traits<typename PointRange::Point>::supported,
-                "parlayann_b200 covers Euclidian_Point / Mips_Point over float, uint8_t, int8_t (SURVEY.md §8)");
+                "parlayann_b200 covers Euclidian_Point / Mips_Point over float, uint8_t, int8_t and Quantized_Mips_Point<8> (SURVEY.md §8)");
   static_assert(sizeof(indexType) == 4, "graph ids are 32-bit");
   using T = point_traits<typename PointRange::Point>;
 
@@ -214,8 +221,9 @@ struct knn_index {
   void set_start() { start_point = 0; }
 
   void build_index(GraphI& G, PointRange& Points, QPointRange&, stats<indexType>& BuildStats, bool sort_neighbors = true) {
+    // a quantised build passes the quantised range twice (bench/neighborsTime.C:157-164, python/builder.cpp:60-87)
     static_assert(std::is_same<PointRange, QPointRange>::value,
-                  "parlayann_b200: building on a quantised copy is not on the GPU path yet (SURVEY.md §8f.2)");
+                  "parlayann_b200: build_index takes the same range for Points and QPoints");
     if (BP.single_batch != 0) { std::cout << "parlayann_b200: single_batch builds are not supported" << std::endl; abort(); }
     std::cout << "Building graph..." << std::endl;
     set_start();

@@ -33,6 +33,48 @@ static const char* arg(int argc, char** argv, const char* name, const char* dflt
   return dflt;
 }
 
+// float MIPS data the way python/graph_index.cpp:88-95 and python/builder.cpp:45-54, :73-86 treat it: rows normalised,
+// Quantized_Mips_Point<8,true> copy; the graph is built over the copy, the search runs on the copy and is re-ranked with
+// the exact rows.  Reference on the CPU and drop-in on the GPU, same process.
+template <typename PR>
+static int run_qmips(PR& Points, PR& Q, long R, long L, long k, int passes) {
+  int bad = 0;
+  for (size_t i = 0; i < Points.size(); i++) Points[i].normalize();
+  for (size_t i = 0; i < Q.size(); i++) Q[i].normalize();
+  using QPR = PointRange<Quantized_Mips_Point<8, true>>;
+  QPR Q_Points(Points);
+  QPR Q_Q(Q, Q_Points.params);
+  double alpha = Points.dimension() < 100 ? (float)1.0 : (float).98;
+  BuildParams BP(R, L, alpha, passes, false);
+  Graph<uint> Gc(BP.max_degree(), Points.size()), Gg(BP.max_degree(), Points.size());
+  stats<uint> Sc(Points.size()), Sg(Points.size());
+  { knn_index<QPR, QPR, uint> I(BP); I.build_index(Gc, Q_Points, Q_Points, Sc, true); }
+  { b200::knn_index<QPR, QPR, uint> I(BP); I.build_index(Gg, Q_Points, Q_Points, Sg, true); }
+  size_t diff_rows = 0;
+  for (size_t i = 0; i < Points.size(); i++) {
+    bool same = Gc[i].size() == Gg[i].size();
+    for (size_t j = 0; same && j < Gc[i].size(); j++) same = Gc[i][j] == Gg[i][j];
+    diff_rows += !same;
+  }
+  bool st_same = std::equal(Sc.visited.begin(), Sc.visited.end(), Sg.visited.begin()) && std::equal(Sc.distances.begin(), Sc.distances.end(), Sg.distances.begin());
+  printf("DROPIN build over Quantized_Mips_Point<8,true>: %zu of %zu rows differ, stats %s\n", diff_rows, Points.size(), st_same ? "identical" : "DIFFER");
+  bad += diff_rows != 0 || !st_same;
+  for (long beam : {10L, 20L, 40L, 100L}) {
+    if (beam < k) continue;
+    QueryParams QP(k, beam, 1.35, (long)Gc.size(), (long)Gc.max_degree());
+    stats<uint> qc(Q.size()), qg(Q.size());
+    auto rc = qsearchAll<PR, QPR, QPR, uint>(Q, Q_Q, Q_Q, Gc, Points, Q_Points, Q_Points, qc, 0u, QP);
+    auto rg = b200::qsearchAll<PR, QPR, QPR, uint>(Q, Q_Q, Q_Q, Gc, Points, Q_Points, Q_Points, qg, 0u, QP);
+    size_t dq = 0;
+    for (size_t i = 0; i < Q.size(); i++) dq += !(rc[i] == rg[i]);
+    bool s2 = std::equal(qc.visited.begin(), qc.visited.end(), qg.visited.begin()) && std::equal(qc.distances.begin(), qc.distances.end(), qg.distances.begin());
+    printf("DROPIN qsearchAll Quantized_Mips_Point<8,true> + re-rank, beam %ld: %zu of %zu queries differ, stats %s\n", beam, dq, Q.size(), s2 ? "identical" : "DIFFER");
+    bad += dq != 0 || !s2;
+  }
+  printf(bad ? "DROPIN_FAIL\n" : "DROPIN_OK\n");
+  return bad ? 1 : 0;
+}
+
 template <typename PR>
 static int run(int argc, char** argv) {
   PR Points((char*)arg(argc, argv, "-base", ""));
@@ -40,6 +82,10 @@ static int run(int argc, char** argv) {
   long R = atol(arg(argc, argv, "-R", "32")), L = atol(arg(argc, argv, "-L", "64")), k = atol(arg(argc, argv, "-k", "10"));
   int passes = atoi(arg(argc, argv, "-passes", "1"));
   int bad = 0;
+  if (!strcmp(arg(argc, argv, "-mode", ""), "qmips")) {
+    if constexpr (std::is_same<PR, PointRange<Mips_Point<float>>>::value) return run_qmips(Points, Q, R, L, k, passes);
+    else { fprintf(stderr, "dropin_check: -mode qmips needs -data_type float -dist_func mips\n"); return 2; }
+  }
   BuildParams BP(R, L, 1.2, passes, false);
   // --- build: reference on the CPU, drop-in on the GPU
   Graph<uint> Gc(BP.max_degree(), Points.size()), Gg(BP.max_degree(), Points.size());
