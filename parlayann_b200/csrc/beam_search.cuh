@@ -25,6 +25,8 @@
 #define PANN_WARPS_PER_CTA 4
 #define PANN_FULL 0xffffffffu
 
+#define PANN_STAGE_SLOT 9  // K1s row staging (pann_staged_distance): uint4 per staged row block = 8 chunks + 1 skew
+#define PANN_STAGE_BYTES (32 * PANN_STAGE_SLOT * 16)
 struct BeamArgs {
   // index
   const uint8_t* points; uint64_t n; uint32_t stride, nch;
@@ -39,7 +41,7 @@ struct BeamArgs {
   double cut;
   // capacities and per-warp shared-memory layout (byte offsets)
   uint32_t ccap, vcap;
-  uint32_t off_frontB, off_cand, off_scand, off_nbr, off_q, off_vis, off_hash, warp_bytes;
+  uint32_t off_frontB, off_cand, off_scand, off_nbr, off_q, off_vis, off_hash, off_stage, warp_bytes;  // off_stage: K1s row staging (float rows)
   // outputs (any may be null)
   uint32_t* out_ids; float* out_dists;       // nq * k
   uint32_t* out_visited; uint32_t* out_cmps; // nq
