@@ -53,7 +53,7 @@ struct BeamArgs {
   // algorithmic bytes of the batch (B_q = cmps*row + sum_hops 4*(1+nbrs read) + row + 4k), one atomic per query
   u64* bytes_total; uint32_t rowbytes;
   uint32_t* qcounter;                        // optional: dynamic query distribution (zeroed before the launch)
-  uint32_t tune;                             // K1s: bit 0 = always prefetch neighbour rows to L2, bit 1 = never (default: only while the launch drains)
+  uint32_t tune;                             // K1s: bit 0 = always prefetch neighbour rows to L2, bit 1 = never (default: only while the launch drains); bit 2 = float rows not staged (A/B)
   // global scratch (GS variant): per resident warp
   uint32_t* g_hash; u64* g_vis;
 };
@@ -149,6 +149,58 @@ __device__ __forceinline__ float pann_quad_distance(const RG& A, uint32_t a, uns
   return res.result();
 }
 
+// Float rows (any row whose sum order is part of the result): a row must be summed by ONE lane in element order, but a
+// lane that also LOADS its row alone makes every 128-bit load of the warp touch 32 different lines (32 L1 wavefronts
+// for 512 useful bytes).  Here the warp loads the rows together and hands them over through shared memory, 128 bytes
+// of every row at a time: lane 8*rr + cc loads chunk cc of the current 128-byte block of rows 4*i + rr (i = 0..7), so a
+// load instruction covers four whole lines (4 wavefronts), the block is parked in `stage` (32 slots of 144 bytes: the
+// 16-byte skew makes both the quarter-warp stores and the one-row-per-lane reads bank-conflict free), and lane l adds
+// the eight chunks of its own row in order into its running sum.  The next block's loads are in flight during the sums.
+// Same operation sequence per row as pann_lane_distance, so the result is bit-identical.
+template <int DT, int METRIC, class RG>
+__device__ __forceinline__ float pann_staged_distance(const RG& A, uint32_t a, unsigned keepmask, const uint4* qsm, uint4* stage, int lane) {
+  const int cc = lane & 7, rr = lane >> 3;
+  const int nch = (int)A.nch;
+  const bool on = (keepmask >> lane) & 1u;
+  uint32_t rid[8];   // ids, not pointers: 8 registers less, one wide multiply-add per load more
+  unsigned onbits = 0;
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    const int src = 4 * i + rr;
+    rid[i] = __shfl_sync(PANN_FULL, a, src);
+    onbits |= ((keepmask >> src) & 1u) << i;
+  }
+  const uint8_t* pbase = A.points + cc * 16;
+  uint4 v[8];
+#pragma unroll
+  for (int i = 0; i < 8; i++) {
+    v[i] = make_uint4(0u, 0u, 0u, 0u);
+    if (((onbits >> i) & 1u) && cc < nch) v[i] = pann_ldg16(pbase + (u64)rid[i] * A.stride);
+  }
+  DistAcc<DT, METRIC> acc;
+  for (int c0 = 0; c0 < nch; c0 += 8) {
+#pragma unroll
+    for (int i = 0; i < 8; i++) stage[(4 * i + rr) * PANN_STAGE_SLOT + cc] = v[i];
+    __syncwarp();
+    if (c0 + 8 < nch) {
+#pragma unroll
+      for (int i = 0; i < 8; i++)
+        if (((onbits >> i) & 1u) && c0 + 8 + cc < nch) v[i] = pann_ldg16(pbase + (u64)rid[i] * A.stride + (c0 + 8) * 16);
+    }
+    if (on) {
+      const uint4* mine = stage + lane * PANN_STAGE_SLOT;
+      if (c0 + 8 <= nch) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) acc.add(mine[j], qsm[c0 + j]);
+      } else {
+        for (int j = 0; c0 + j < nch; j++) acc.add(mine[j], qsm[c0 + j]);
+      }
+    }
+    __syncwarp();
+  }
+  return acc.result();
+}
+template <int DT, int QR> __host__ __device__ constexpr bool pann_staged_rows() { return QR == 0 && DT == PANN_DT_F32; }
 // Distances from the query to `cnt` rows, one row per lane, 32 rows per pass; row r is pann_key_id(keyOf(r))
 // (a 64-bit tag whose id field names the row, so callers can carry a (dist,id) key through).  Calls
 // emit(tag, dist, valid) warp-uniformly once per pass; lane l carries row base + l, so ballot-ranked stores in
@@ -157,13 +209,22 @@ __device__ __forceinline__ float pann_quad_distance(const RG& A, uint32_t a, uns
 // RG: anything with points / stride / nch (BeamArgs, PruneArgs, ...).
 // QUAD: use pann_quad_distance where the row shape allows it (the beam search does; the prune kernel keeps the
 // one-row-per-lane loop, whose 40 registers buy it 48 resident warps per SM).
+// stage: per-warp PANN_STAGE_BYTES of shared memory, or null: float rows then go through pann_staged_distance.
 template <int DT, int METRIC, int QR, bool QUAD = false, class RG, class KeyOf, class Emit>
 __device__ __forceinline__ void pann_row_distances_g(const RG& A, KeyOf keyOf, int cnt, const uint4* qsm, int lane,
-                                                     Emit emit) {
+                                                     Emit emit, uint4* stage = nullptr) {
   for (int base = 0; base < cnt; base += 32) {
     const int r = base + lane;
     const bool ok = r < cnt;
     u64 tag = 0;
+    if constexpr (pann_staged_rows<DT, QR>()) {
+      if (stage) {
+        if (ok) tag = keyOf(r);
+        const float d = pann_staged_distance<DT, METRIC>(A, pann_key_id(tag), __ballot_sync(PANN_FULL, ok), qsm, stage, lane);
+        emit(tag, d, ok);
+        continue;
+      }
+    }
     if constexpr (QUAD && pann_quad_rows<DT, QR>()) {
       if (ok) tag = keyOf(r);
       const float d = pann_quad_distance<DT, METRIC>(A, pann_key_id(tag), __ballot_sync(PANN_FULL, ok), qsm, lane);
@@ -197,10 +258,10 @@ __device__ __forceinline__ void pann_row_distances_g(const RG& A, KeyOf keyOf, i
 // the same over a plain id list (shared memory): emit(id, dist, valid)
 template <int DT, int METRIC, int QR, class RG, class Emit>
 __device__ __forceinline__ void pann_row_distances(const RG& A, const uint32_t* ids, int cnt, const uint4* qsm, int lane,
-                                                   Emit emit) {
+                                                   Emit emit, uint4* stage = nullptr) {
   pann_row_distances_g<DT, METRIC, QR, true>(
       A, [&](int r) { return (u64)ids[r] << 1; }, cnt, qsm, lane,
-      [&](u64 tag, float d, bool ok) { emit(pann_key_id(tag), d, ok); });
+      [&](u64 tag, float d, bool ok) { emit(pann_key_id(tag), d, ok); }, stage);
 }
 // the query row into shared memory
 __device__ __forceinline__ void pann_load_query(const uint8_t* qrow, uint32_t nch, uint4* qsm, int lane) {
@@ -224,6 +285,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1_MINB
   u64* scand = reinterpret_cast<u64*>(ws + A.off_scand);
   uint32_t* nbr = reinterpret_cast<uint32_t*>(ws + A.off_nbr);
   uint4* qsm = reinterpret_cast<uint4*>(ws + A.off_q);
+  uint4* stage = (pann_staged_rows<DT, QR>() && !(A.tune & 4u)) ? reinterpret_cast<uint4*>(ws + A.off_stage) : nullptr;
   const long long wglobal = (long long)blockIdx.x * PANN_WARPS_PER_CTA + wic;
   u64* vis;
   uint32_t* hashf;
@@ -276,7 +338,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1_MINB
           unsigned m = __ballot_sync(PANN_FULL, ok);
           if (ok) cand[C + __popc(m & lt_mask)] = pann_key(d, id);
           C += __popc(m);
-        });
+        }, stage);
         __syncwarp();
       }
       if (lane == 0)
@@ -368,7 +430,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1_MINB
         unsigned m = __ballot_sync(PANN_FULL, take);
         if (take) cand[C + __popc(m & lt_mask)] = pann_key(d, id);
         C += __popc(m);
-      });
+      }, stage);
       __syncwarp();
       // skip the merge while there are too few candidates (:162-168); candidates are kept
       if (C == 0) continue;

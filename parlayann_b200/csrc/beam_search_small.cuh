@@ -41,57 +41,6 @@ __device__ __forceinline__ float pann_lane_distance(const RG& A, uint32_t a, boo
   }
   return acc.result();
 }
-// Float rows (any row whose sum order is part of the result): a row must be summed by ONE lane in element order, but a
-// lane that also LOADS its row alone makes every 128-bit load of the warp touch 32 different lines (32 L1 wavefronts
-// for 512 useful bytes).  Here the warp loads the rows together and hands them over through shared memory, 128 bytes
-// of every row at a time: lane 8*rr + cc loads chunk cc of the current 128-byte block of rows 4*i + rr (i = 0..7), so a
-// load instruction covers four whole lines (4 wavefronts), the block is parked in `stage` (32 slots of 144 bytes: the
-// 16-byte skew makes both the quarter-warp stores and the one-row-per-lane reads bank-conflict free), and lane l adds
-// the eight chunks of its own row in order into its running sum.  The next block's loads are in flight during the sums.
-// Same operation sequence per row as pann_lane_distance, so the result is bit-identical.
-template <int DT, int METRIC, class RG>
-__device__ __forceinline__ float pann_staged_distance(const RG& A, uint32_t a, unsigned keepmask, const uint4* qsm, uint4* stage, int lane) {
-  const int cc = lane & 7, rr = lane >> 3;
-  const int nch = (int)A.nch;
-  const bool on = (keepmask >> lane) & 1u;
-  const uint8_t* rp[8];
-  unsigned onbits = 0;
-#pragma unroll
-  for (int i = 0; i < 8; i++) {
-    const int src = 4 * i + rr;
-    rp[i] = A.points + (u64)__shfl_sync(PANN_FULL, a, src) * A.stride + cc * 16;
-    onbits |= ((keepmask >> src) & 1u) << i;
-  }
-  uint4 v[8];
-#pragma unroll
-  for (int i = 0; i < 8; i++) {
-    v[i] = make_uint4(0u, 0u, 0u, 0u);
-    if (((onbits >> i) & 1u) && cc < nch) v[i] = pann_ldg16(rp[i]);
-  }
-  DistAcc<DT, METRIC> acc;
-  for (int c0 = 0; c0 < nch; c0 += 8) {
-#pragma unroll
-    for (int i = 0; i < 8; i++) stage[(4 * i + rr) * PANN_STAGE_SLOT + cc] = v[i];
-    __syncwarp();
-    if (c0 + 8 < nch) {
-#pragma unroll
-      for (int i = 0; i < 8; i++)
-        if (((onbits >> i) & 1u) && c0 + 8 + cc < nch) v[i] = pann_ldg16(rp[i] + (c0 + 8) * 16);
-    }
-    if (on) {
-      const uint4* mine = stage + lane * PANN_STAGE_SLOT;
-      if (c0 + 8 <= nch) {
-#pragma unroll
-        for (int j = 0; j < 8; j++) acc.add(mine[j], qsm[c0 + j]);
-      } else {
-        for (int j = 0; c0 + j < nch; j++) acc.add(mine[j], qsm[c0 + j]);
-      }
-    }
-    __syncwarp();
-  }
-  return acc.result();
-}
-template <int DT, int QR> __host__ __device__ constexpr bool pann_staged_rows() { return QR == 0 && DT == PANN_DT_F32; }
 __device__ __forceinline__ void pann_prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 __device__ __forceinline__ u64 pann_shfl64(u64 x, int src) {
   const uint32_t lo = __shfl_sync(PANN_FULL, (uint32_t)x, src), hi = __shfl_sync(PANN_FULL, (uint32_t)(x >> 32), src);

@@ -230,7 +230,8 @@ static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap, cud
   A.off_q = A.off_nbr + al16((size_t)std::max<uint32_t>(A.maxdeg, 1) * 4);
   A.off_vis = A.off_q + g.stride;
   A.off_hash = A.off_vis + (gs ? 0 : al16((size_t)vcap * 8));
-  A.warp_bytes = A.off_hash + (gs ? 0 : (4u << A.bits));
+  A.off_stage = A.off_hash + (gs ? 0 : (4u << A.bits));
+  A.warp_bytes = A.off_stage + ((idx->dtype == PANN_DT_F32 && qrT == 0) ? PANN_STAGE_BYTES : 0);   // float rows are staged (pann_staged_distance)
   const size_t cta_bytes = (size_t)A.warp_bytes * PANN_WARPS_PER_CTA;
   if (cta_bytes > idx->smem_optin) PANN_FAIL("beam search: per-CTA shared memory exceeds the device limit (beam too wide for this max degree)");
   const void* fn = beam_kernel(idx->dtype, idx->metric, qrT, gs);
@@ -301,6 +302,7 @@ static int beam_plan(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uin
       cudaDeviceGetAttribute(&l2, cudaDevAttrL2CacheSize, dev);
       A.tune = ((unsigned long long)idx->n * idx->geom.stride <= 2ull * (unsigned long long)l2) ? 1u : 0u;
     }
+    { const char* ns = getenv("PANN_NO_STAGE"); if (ns && ns[0] == '1') A.tune |= 4u; }   // A/B: float rows one lane per row
   }
 
   // shared-memory variant while the hash filter is <= 8 KB per warp (beam <= 90): at 16 KB only 8 warps fit on an SM and
