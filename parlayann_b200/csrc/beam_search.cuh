@@ -200,7 +200,13 @@ __device__ __forceinline__ float pann_staged_distance(const RG& A, uint32_t a, u
   }
   return acc.result();
 }
+#ifdef PANN_STAGE_INT   // A/B: stage integer rows of other lengths than 128 bytes as well (their sums are exact in any order)
+template <int DT, int QR> __host__ __device__ constexpr bool pann_staged_rows() { return QR == 0; }
+inline bool pann_staged_rows_rt(int dtype, int qr) { return qr == 0; }
+#else
 template <int DT, int QR> __host__ __device__ constexpr bool pann_staged_rows() { return QR == 0 && DT == PANN_DT_F32; }
+inline bool pann_staged_rows_rt(int dtype, int qr) { return qr == 0 && dtype == PANN_DT_F32; }
+#endif
 // Distances from the query to `cnt` rows, one row per lane, 32 rows per pass; row r is pann_key_id(keyOf(r))
 // (a 64-bit tag whose id field names the row, so callers can carry a (dist,id) key through).  Calls
 // emit(tag, dist, valid) warp-uniformly once per pass; lane l carries row base + l, so ballot-ranked stores in

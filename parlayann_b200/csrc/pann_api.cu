@@ -207,7 +207,7 @@ static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap, cud
     A.off_vis = A.off_q + g.stride;
     A.off_hash = A.off_vis + al16((size_t)vcap * 4);
     A.off_stage = A.off_hash + (4u << A.bits);
-    A.warp_bytes = A.off_stage + ((idx->dtype == PANN_DT_F32 && qrT == 0) ? PANN_STAGE_BYTES : 0);   // float rows are staged (pann_staged_distance)
+    A.warp_bytes = A.off_stage + (pann_staged_rows_rt(idx->dtype, qrT) ? PANN_STAGE_BYTES : 0);   // float rows are staged (pann_staged_distance)
     size_t cta_bytes = (size_t)A.warp_bytes * PANN_WARPS_PER_CTA;
     if (const char* e = getenv("PANN_K1_PAD_SMEM")) cta_bytes += (size_t)atoi(e);   // experiments: fewer CTAs per SM, more L1
     const void* fn = beam_small_kernel(idx->dtype, idx->metric, qrT);
@@ -231,7 +231,7 @@ static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap, cud
   A.off_vis = A.off_q + g.stride;
   A.off_hash = A.off_vis + (gs ? 0 : al16((size_t)vcap * 8));
   A.off_stage = A.off_hash + (gs ? 0 : (4u << A.bits));
-  A.warp_bytes = A.off_stage + ((idx->dtype == PANN_DT_F32 && qrT == 0) ? PANN_STAGE_BYTES : 0);   // float rows are staged (pann_staged_distance)
+  A.warp_bytes = A.off_stage + (pann_staged_rows_rt(idx->dtype, qrT) ? PANN_STAGE_BYTES : 0);   // float rows are staged (pann_staged_distance)
   const size_t cta_bytes = (size_t)A.warp_bytes * PANN_WARPS_PER_CTA;
   if (cta_bytes > idx->smem_optin) PANN_FAIL("beam search: per-CTA shared memory exceeds the device limit (beam too wide for this max degree)");
   const void* fn = beam_kernel(idx->dtype, idx->metric, qrT, gs);

@@ -101,6 +101,8 @@ static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, De
     A.warp_bytes = A.off_rc + A.rc_rows * A.rc_pitch;
     wpc = small_lists ? 4 : 3;
   }
+  A.off_stage = A.warp_bytes;
+  if (pann_staged_rows_rt(idx->dtype, qrT)) A.warp_bytes += PANN_STAGE_BYTES;
   A.task_map = nullptr; A.ntask_map = 0; A.g_scratch = nullptr;
   {
     const void* fn = prune_kernel(idx->dtype, idx->metric, qrT, false);
@@ -126,6 +128,8 @@ static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, De
   A.off_b = 0; A.off_q = 0;
   A.rc_rows = 0;
   A.warp_bytes = g.stride;
+  A.off_stage = A.warp_bytes;
+  if (pann_staged_rows_rt(idx->dtype, qrT)) A.warp_bytes += PANN_STAGE_BYTES;
   const void* fn = prune_kernel(idx->dtype, idx->metric, qrT, true);
   size_t cta_bytes = (size_t)A.warp_bytes * PANN_PRUNE_WARPS;
   PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));

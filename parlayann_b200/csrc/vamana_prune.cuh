@@ -36,7 +36,7 @@ struct PruneArgs {
   uint32_t cap; uint32_t* big_list; uint32_t* big_count;  // big_count[0] = #deferred, [1] = their largest candidate count
   const uint32_t* task_map; uint32_t ntask_map;  // GS launch: the deferred tasks
   u64* g_scratch;                                 // GS launch: per warp 2 x cap keys
-  uint32_t off_b, off_q, warp_bytes;
+  uint32_t off_b, off_q, off_stage, warp_bytes;   // off_stage: float rows staged for the one-lane sums (pann_staged_distance)
   // row cache (shared memory): the rows of up to rc_rows candidates, rc_pitch bytes apart, and their slot numbers
   uint32_t rc_rows, rc_pitch, off_rc, off_pos;
 };
@@ -59,6 +59,7 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
     bufB = reinterpret_cast<u64*>(ws + A.off_b);
   }
   uint4* qsm = reinterpret_cast<uint4*>(ws + A.off_q);
+  uint4* stage = pann_staged_rows<DT, QR>() ? reinterpret_cast<uint4*>(ws + A.off_stage) : nullptr;
   uint32_t* cid = reinterpret_cast<uint32_t*>(bufB);  // candidate ids before they get their distances
   const uint32_t ntasks = GS ? A.ntask_map : (A.mode == 1 ? *A.ngroups : A.ntasks);
 
@@ -132,7 +133,7 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
             unsigned bm = __ballot_sync(PANN_FULL, ok);
             if (ok) bufA[C + __popc(bm & lt_mask)] = pann_key(d, pann_key_id(tag));
             C += __popc(bm);
-          });
+          }, stage);
       __syncwarp();
     }
     // ---- sort by (dist,id) (:80-83).  Mode 0 without out-neighbours is sorted already.
@@ -265,7 +266,7 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
             unsigned km = __ballot_sync(PANN_FULL, keep);
             if (keep) S[w + __popc(km & lt_mask)] = key;
             w += __popc(km);
-          });
+          }, stage);
       __syncwarp();
       n = w;
     }
