@@ -265,7 +265,8 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
 
 // K7: the re-rank step of beam_search_rerank when the searched copy is quantised (beamSearch.h:426-444): exact distances
 // from the exact query to the first min(k * rerank_factor, |frontier|) frontier entries, sorted by (dist, id), first k
-// out.  One warp per query; one exact row per lane, summed in the reference's own order (floats included).
+// out.  One warp per query; one exact row per lane, summed in the reference's own order (floats included; float rows are
+// loaded by the whole warp and handed over through the shared-memory stage, see pann_staged_distance).
 struct RerankArgs {
   const uint8_t* points; uint32_t stride, nch;   // exact base rows (names as in BeamArgs: pann_lane_distance reads them)
   const uint8_t* queries; uint32_t qstride;      // exact query rows
@@ -273,7 +274,7 @@ struct RerankArgs {
   const uint32_t* fr_ids; const uint32_t* n_frontier; uint32_t fcap;
   int k; long long rerank_factor;
   uint32_t* out_ids; float* out_dists;
-  uint32_t off_q, warp_bytes;
+  uint32_t off_q, off_stage, warp_bytes;   // off_stage: float rows staged (pann_staged_distance)
 };
 template <int DT, int METRIC>
 __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_rerank_kernel(const RerankArgs A) {
@@ -290,7 +291,11 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_rerank_kernel(co
       const int i = base + lane;
       const bool on = i < nchk;
       const uint32_t id = on ? A.fr_ids[(u64)q * A.fcap + i] : 0u;
-      const float d = pann_lane_distance<DT, METRIC, 0>(A, id, on, qsm);
+      float d;
+      if constexpr (pann_staged_rows<DT, 0>())
+        d = pann_staged_distance<DT, METRIC>(A, id, __ballot_sync(PANN_FULL, on), qsm, reinterpret_cast<uint4*>(ws + A.off_stage), lane);
+      else
+        d = pann_lane_distance<DT, METRIC, 0>(A, id, on, qsm);
       if (on) keys[i] = pann_key(d, id);
     }
     __syncwarp();

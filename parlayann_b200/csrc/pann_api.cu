@@ -691,7 +691,8 @@ extern "C" int pann_search_rerank_batch(pann_index* q_idx, pann_index* base_idx,
   R.k = (int)k; R.rerank_factor = rerank_factor;
   R.out_ids = d_ids; R.out_dists = d_dists;
   R.off_q = al16((size_t)fcap * 8);
-  R.warp_bytes = R.off_q + base_idx->geom.stride;
+  R.off_stage = R.off_q + base_idx->geom.stride;
+  R.warp_bytes = R.off_stage + (pann_staged_rows_rt(base_idx->dtype, 0) ? PANN_STAGE_BYTES : 0);
   const size_t cta_bytes = (size_t)R.warp_bytes * PANN_WARPS_PER_CTA;
   if (cta_bytes > q_idx->smem_optin) PANN_FAIL("pann_search_rerank_batch: rows too long for the re-rank kernel's shared memory");
   const void* fn = rerank_kernel(base_idx->dtype, base_idx->metric);
