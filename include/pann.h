@@ -77,6 +77,20 @@ int pann_search_batch(pann_index* idx, const void* host_queries, uint64_t nq, ui
                       const uint32_t* starts, uint32_t nstarts, const pann_query_params* qp,
                       uint32_t* out_ids, float* out_dists, uint32_t* out_visited, uint32_t* out_cmps);
 
+/* The same with ONE START LIST PER QUERY: query i starts from starts[i * starts_stride .. + c_i), c_i = nstarts_q[i]
+ * (or starts_stride for every query when nstarts_q is NULL).  Replaces beamSearchRandom (beamSearch.h:309-351: one random
+ * start per query, see pann_random_starts) and is what HNSW's layer-0 search needs after its per-query descent
+ * (HNSW/HNSW.hpp:1570-1613).  A list longer than the beam is allowed when the cut rule cannot fire (k == 0, k == beam, or
+ * MIPS): the frontier is then longer than the beam until the first merge truncates it (beamSearch.h:185), which is what
+ * the reference does once its unvisited_frontier buffer (:74-76) is made large enough. */
+int pann_search_batch_starts(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes,
+                             const uint32_t* starts, uint32_t starts_stride, const uint32_t* nstarts_q,
+                             const pann_query_params* qp, uint32_t* out_ids, float* out_dists, uint32_t* out_visited,
+                             uint32_t* out_cmps);
+/* beamSearchRandom's start points (beamSearch.h:327-332): parlay::random_generator()[i] through
+ * std::uniform_int_distribution<long>(0, n-1), i = 0..nq-1 */
+int pann_random_starts(uint64_t nq, uint64_t n, uint32_t* out);
+
 /* Device-resident variant: queries are uploaded once, results stay on the device until fetched.
  * Used to time the search with inputs already in HBM. */
 int pann_queries_upload(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes);
@@ -94,6 +108,12 @@ int pann_search_full(pann_index* idx, const void* host_queries, uint64_t nq, uin
                      const uint32_t* self_ids, const uint32_t* starts, uint32_t nstarts, const pann_query_params* qp,
                      uint32_t fcap, uint32_t* fr_ids, float* fr_dists, uint32_t* n_frontier,
                      uint32_t vcap, uint32_t* vis_ids, float* vis_dists, uint32_t* n_visited, uint32_t* out_cmps);
+
+/* pann_search_full with one start list per query (see pann_search_batch_starts); fcap >= max(beam, starts_stride) */
+int pann_search_full_starts(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes,
+                            const uint32_t* self_ids, const uint32_t* starts, uint32_t starts_stride, const uint32_t* nstarts_q,
+                            const pann_query_params* qp, uint32_t fcap, uint32_t* fr_ids, float* fr_dists, uint32_t* n_frontier,
+                            uint32_t vcap, uint32_t* vis_ids, float* vis_dists, uint32_t* n_visited, uint32_t* out_cmps);
 
 /* beam_search_rerank when the searched copy is quantised (beamSearch.h:390-454 with differing byte widths; the
  * -quantize_mode 1 path of vamana/neighbors.h:117-127 and Python's quant=True, graph_index.cpp:141-186): q_idx holds the

@@ -250,9 +250,11 @@ void oracle_random_permutation(int64_t n, int32_t* out) { random_permutation(n, 
 // self_base >= 0: query i is base row self_base+i? no -> selfs[i] (may be NULL) gives the base row a query aliases.
 // Outputs (any may be NULL): out_ids/out_dists nq*k (first k of the frontier), visited/cmps counters nq,
 // full lists: fr_* nq*fcap, vis_* nq*vcap with counts in nfr/nvis.
-int oracle_search_batch(int dtype, int metric, const void* points, uint64_t n, uint32_t d, uint64_t stride,
+// starts_stride == 0: one start list for the batch (searchAll); else query i starts from
+// starts[i * starts_stride .. + (nstarts_q ? nstarts_q[i] : nstarts)) (beamSearchRandom, beamSearch.h:327-338; HNSW).
+int oracle_search_batch_starts(int dtype, int metric, const void* points, uint64_t n, uint32_t d, uint64_t stride,
                         const uint32_t* graph, uint32_t maxdeg, const void* queries, uint64_t nq, uint64_t qstride,
-                        const int64_t* selfs, const uint32_t* starts, uint32_t nstarts,
+                        const int64_t* selfs, const uint32_t* starts, uint32_t nstarts, uint32_t starts_stride, const uint32_t* nstarts_q,
                         long k, long beam, double cut, long limit, long degree_limit,
                         uint32_t* out_ids, float* out_dists, uint32_t* out_visited, uint32_t* out_cmps,
                         uint32_t fcap, uint32_t* fr_ids, float* fr_dists, uint32_t* nfr,
@@ -262,7 +264,8 @@ int oracle_search_batch(int dtype, int metric, const void* points, uint64_t n, u
   std::atomic<int> bad(0);
   par_for(0, nq, nthreads, [&](size_t i) {
     SearchOut o;
-    beam_search(P, graph, maxdeg, (const uint8_t*)queries + i * qstride, selfs ? selfs[i] : -1, starts, nstarts, qp, o);
+    beam_search(P, graph, maxdeg, (const uint8_t*)queries + i * qstride, selfs ? selfs[i] : -1, starts + i * (size_t)starts_stride,
+                (starts_stride && nstarts_q) ? nstarts_q[i] : nstarts, qp, o);
     if ((long)o.frontier.size() < k) { bad = 1; return; }  // beamSearch.h:416-419 aborts
     for (long j = 0; j < k; j++) { if (out_ids) out_ids[i * k + j] = o.frontier[j].first; if (out_dists) out_dists[i * k + j] = o.frontier[j].second; }
     if (out_visited) out_visited[i] = (uint32_t)o.visited.size();
@@ -273,6 +276,18 @@ int oracle_search_batch(int dtype, int metric, const void* points, uint64_t n, u
     for (size_t j = 0; j < o.visited.size() && j < vcap; j++) { if (vis_ids) vis_ids[i * vcap + j] = o.visited[j].first; if (vis_dists) vis_dists[i * vcap + j] = o.visited[j].second; }
   });
   return bad;
+}
+
+int oracle_search_batch(int dtype, int metric, const void* points, uint64_t n, uint32_t d, uint64_t stride,
+                        const uint32_t* graph, uint32_t maxdeg, const void* queries, uint64_t nq, uint64_t qstride,
+                        const int64_t* selfs, const uint32_t* starts, uint32_t nstarts,
+                        long k, long beam, double cut, long limit, long degree_limit,
+                        uint32_t* out_ids, float* out_dists, uint32_t* out_visited, uint32_t* out_cmps,
+                        uint32_t fcap, uint32_t* fr_ids, float* fr_dists, uint32_t* nfr,
+                        uint32_t vcap, uint32_t* vis_ids, float* vis_dists, uint32_t* nvis, int nthreads) {
+  return oracle_search_batch_starts(dtype, metric, points, n, d, stride, graph, maxdeg, queries, nq, qstride, selfs, starts, nstarts, 0, nullptr,
+                                    k, beam, cut, limit, degree_limit, out_ids, out_dists, out_visited, out_cmps, fcap, fr_ids, fr_dists, nfr,
+                                    vcap, vis_ids, vis_dists, nvis, nthreads);
 }
 
 // knn_index::build_index (vamana/index.h:150-186) + batch_insert (:188-316), start_point = 0.

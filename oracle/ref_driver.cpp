@@ -10,6 +10,7 @@
 //   build   -> knn_index::build_index                                (algorithms/vamana/index.h:150-186)
 //   search  -> qsearchAll + stats                                    (algorithms/utils/beamSearch.h:537-565)
 //   full    -> beam_search (frontier + visited lists per query)      (algorithms/utils/beamSearch.h:217-223)
+//   random  -> beamSearchRandom (one random start point per query)     (algorithms/utils/beamSearch.h:309-351)
 //   recall  -> checkRecall (timed qsearchAll + tie-aware recall)     (algorithms/utils/check_nn_recall.h:17-125)
 //   qsearch -> qsearchAll over a 1-byte quantised copy + exact re-rank (vamana/neighbors.h:117-127, beamSearch.h:409-444;
 //              MIPS: Quantized_Mips_Point<8,true> over normalised points, python/graph_index.cpp:88-95, :166-181)
@@ -184,6 +185,23 @@ static int run(const std::string& cmd, int argc, char** argv) {
     std::vector<uint> ids(nq * k);
     for (size_t i = 0; i < nq; i++) for (long j = 0; j < k; j++) ids[i * k + j] = res[i][j];
     dump(out + ".ids", ids.data(), ids.size() * 4);
+    dump(out + ".visited", QS.visited.begin(), 4 * nq);
+    dump(out + ".distances", QS.distances.begin(), 4 * nq);
+    return 0;
+  }
+
+  if (cmd == "random") {
+    // beamSearchRandom (beamSearch.h:309-351): one random start per query; the start indices are re-derived with the very
+    // expressions of :327-332 and dumped beside the results
+    stats<uint> QS(nq);
+    auto res = beamSearchRandom<PR, uint>(Q, G, Points, QS, QP);
+    std::vector<uint> ids(nq * k), st(nq);
+    for (size_t i = 0; i < nq; i++) for (long j = 0; j < k; j++) ids[i * k + j] = res[i][j];
+    parlay::random_generator gen;
+    std::uniform_int_distribution<long> dis(0, G.size() - 1);
+    for (size_t i = 0; i < nq; i++) { auto r = gen[i]; st[i] = (uint)dis(r); }
+    dump(out + ".ids", ids.data(), ids.size() * 4);
+    dump(out + ".starts", st.data(), st.size() * 4);
     dump(out + ".visited", QS.visited.begin(), 4 * nq);
     dump(out + ".distances", QS.distances.begin(), 4 * nq);
     return 0;

@@ -34,7 +34,12 @@ struct BeamArgs {
   // queries: either rows of `queries` (qstride bytes apart, 16-byte padded) or base rows self_ids[i]
   const uint8_t* queries; uint64_t nq; uint32_t qstride;
   const uint32_t* self_ids;
-  const uint32_t* starts; uint32_t nstarts;
+  // start points: one list for the whole batch (starts_stride == 0), or one list per query — query q starts from
+  // starts[q * starts_stride .. + (nstarts_q ? nstarts_q[q] : nstarts)) (beamSearchRandom, beamSearch.h:327-332; HNSW's
+  // per-query entry points, HNSW.hpp:1570-1613).  nstarts = the largest list (sizes the buffers).
+  const uint32_t* starts; uint32_t nstarts; uint32_t starts_stride; const uint32_t* nstarts_q;
+  // optional vertex id -> graph row (compacted upper HNSW layers, where only some vertices have a row); null = identity
+  const uint32_t* rowmap;
   // QueryParams
   int k, beam, bits, degree_limit, cut_rule;  // cut_rule = (k > 0 && metric is L2)
   long long limit;
@@ -329,16 +334,22 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1_MINB
     u64* front = bufA;
     u64* nf = bufB;
     int F = 0, V = 0, C = 0, status = 0;
-    unsigned cmps = A.nstarts;  // beamSearch.h:84
+    const uint32_t* qstarts = A.starts + (u64)q * A.starts_stride;
+    const uint32_t ns = A.nstarts_q ? A.nstarts_q[q] : A.nstarts;
+    unsigned cmps = ns;        // beamSearch.h:84
     unsigned nread = 0;        // neighbour ids read from graph rows
 
-    // ---- starting points (:64-70): distances, hash-filter insertion in list order, sort
-    if ((int)A.nstarts > B || A.nstarts > A.ccap) {
+    // ---- starting points (:64-70): distances, hash-filter insertion in list order, sort.  More starts than the beam
+    // width (HNSW's ef = 1 descent from several entrances) leave a frontier longer than the beam until the first merge
+    // truncates it (:185) — the reference's unvisited_frontier buffer overflows there (:74-76); this follows what the
+    // code does with that buffer made large enough.  With the cut rule on, :195's max(.., old size) would keep it
+    // longer than the beam: that corner is refused.
+    if (ns == 0 || ns > A.nstarts || ns > A.ccap || ((int)ns > B && A.cut_rule && A.k < B)) {
       status = 3;
     } else {
-      for (uint32_t s0 = 0; s0 < A.nstarts; s0 += A.maxdeg) {
-        int cnt = min((int)A.maxdeg, (int)(A.nstarts - s0));
-        for (int i = lane; i < cnt; i += 32) nbr[i] = A.starts[s0 + i];
+      for (uint32_t s0 = 0; s0 < ns; s0 += A.maxdeg) {
+        int cnt = min((int)A.maxdeg, (int)(ns - s0));
+        for (int i = lane; i < cnt; i += 32) nbr[i] = qstarts[s0 + i];
         __syncwarp();
         pann_row_distances<DT, METRIC, QR>(A, nbr, cnt, qsm, lane, [&](uint32_t id, float d, bool ok) {
           unsigned m = __ballot_sync(PANN_FULL, ok);
@@ -348,7 +359,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1_MINB
         __syncwarp();
       }
       if (lane == 0)
-        for (uint32_t i = 0; i < A.nstarts; i++) { uint32_t a = A.starts[i]; hashf[(uint32_t)pann_hash64_2(a) & hmask] = a; }
+        for (uint32_t i = 0; i < ns; i++) { uint32_t a = qstarts[i]; hashf[(uint32_t)pann_hash64_2(a) & hmask] = a; }
       for (int i = lane; i < C; i += 32) {  // rank sort into the frontier
         u64 ci = cand[i];
         int r = 0;
@@ -377,7 +388,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1_MINB
       const bool vis_in_front = (nflag == V);
       // the graph row is requested now (degree + the first 64 slots; slots past the degree are stale but in-row)
       // so that its latency overlaps the visited-list insertion below
-      const uint32_t* grow = A.graph + (u64)pann_key_id(cur) * (A.maxdeg + 1);
+      const uint32_t* grow = A.graph + (u64)(A.rowmap ? __ldg(A.rowmap + pann_key_id(cur)) : pann_key_id(cur)) * (A.maxdeg + 1);
       const int deg = (int)__ldg(grow);
       const uint32_t a0 = (lane < (int)A.maxdeg) ? __ldg(grow + 1 + lane) : 0u;
       const uint32_t a1 = (32 + lane < (int)A.maxdeg) ? __ldg(grow + 33 + lane) : 0u;

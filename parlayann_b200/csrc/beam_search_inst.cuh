@@ -19,12 +19,14 @@ const void* PANN_CAT(pann_beam_kernel_dt, PANN_INST_DT)(int metric, int qr, bool
 }
 
 template <int METRIC>
-static const void* pick_beam_small(int qr) {
-  if (qr == PANN_QR) return (const void*)&pann_beam_search_small_kernel<PANN_INST_DT, METRIC, PANN_QR>;
-  return (const void*)&pann_beam_search_small_kernel<PANN_INST_DT, METRIC, 0>;
+static const void* pick_beam_small(int qr, bool ext) {
+  if (qr == PANN_QR) return ext ? (const void*)&pann_beam_search_small_kernel<PANN_INST_DT, METRIC, PANN_QR, true>
+                                : (const void*)&pann_beam_search_small_kernel<PANN_INST_DT, METRIC, PANN_QR, false>;
+  return ext ? (const void*)&pann_beam_search_small_kernel<PANN_INST_DT, METRIC, 0, true>
+             : (const void*)&pann_beam_search_small_kernel<PANN_INST_DT, METRIC, 0, false>;
 }
-const void* PANN_CAT(pann_beam_small_kernel_dt, PANN_INST_DT)(int metric, int qr) {
-  return metric == PANN_M_L2 ? pick_beam_small<PANN_M_L2>(qr) : pick_beam_small<PANN_M_MIPS>(qr);
+const void* PANN_CAT(pann_beam_small_kernel_dt, PANN_INST_DT)(int metric, int qr, bool ext) {
+  return metric == PANN_M_L2 ? pick_beam_small<PANN_M_L2>(qr, ext) : pick_beam_small<PANN_M_MIPS>(qr, ext);
 }
 
 template <int METRIC>

@@ -51,7 +51,9 @@ __device__ __forceinline__ u64 pann_shfl_up64(u64 x) {
   return ((u64)hi << 32) | lo;
 }
 
-template <int DT, int METRIC, int QR>
+// EXT: per-query start lists and the vertex -> row map (beamSearchRandom, HNSW layers); a separate instantiation so that
+// the plain kernel — which sits exactly at its register budget — is not touched by them.
+template <int DT, int METRIC, int QR, bool EXT>
 #ifndef PANN_K1S_MINB
 #define PANN_K1S_MINB 7  // 72 registers: at 64 the compiler interleaves the row loads with arithmetic (fewer rows in flight per warp); measured 8 / 7 / 6 CTAs per SM: 55.0 / 51.6 / 57.8 ms per 1M queries at 10M points
 #endif
@@ -100,30 +102,32 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
     u64 fk = ~0ull;  // frontier entry `lane` ((dist,id) key, bit 0 = visited), ~0 beyond the frontier
     int F = 0, V = 0, C = 0, status = 0;
     uint32_t vis0 = 0xffffffffu, vis1 = 0xffffffffu;  // visited ids V = lane and lane + 32 (later ones: shared memory)
-    unsigned cmps = A.nstarts, nread = 0;
+    const uint32_t* qstarts = EXT ? A.starts + (u64)q * A.starts_stride : A.starts;
+    const int ns = (int)((EXT && A.nstarts_q) ? A.nstarts_q[q] : A.nstarts);
+    unsigned cmps = ns, nread = 0;
 
-    // ---- starting points (:64-70)
-    if ((int)A.nstarts > B || A.nstarts > 32u) {
+    // ---- starting points (:64-70).  More starts than the beam width: see pann_beam_search_kernel.
+    if (ns < 1 || ns > 32 || (ns > B && A.cut_rule && A.k < B)) {
       status = 3;
     } else {
-      const bool on = lane < (int)A.nstarts;
-      const uint32_t a = on ? A.starts[lane] : 0u;
+      const bool on = lane < ns;
+      const uint32_t a = on ? qstarts[lane] : 0u;
       float d;
       if constexpr (QUAD) d = pann_quad_distance<DT, METRIC>(A, a, __ballot_sync(PANN_FULL, on), qsm, lane);
       else if constexpr (pann_staged_rows<DT, QR>()) d = pann_staged_distance<DT, METRIC>(A, a, __ballot_sync(PANN_FULL, on), qsm, stage, lane);
       else d = pann_lane_distance<DT, METRIC, QR>(A, a, on, qsm);
       const u64 key = on ? pann_key(d, a) : ~0ull;
       if (lane == 0)
-        for (uint32_t i = 0; i < A.nstarts; i++) { const uint32_t s = A.starts[i]; hashf[(uint32_t)pann_hash64_2(s) & hmask] = s; }
+        for (int i = 0; i < ns; i++) { const uint32_t s = qstarts[i]; hashf[(uint32_t)pann_hash64_2(s) & hmask] = s; }
       int r = 0;
-      for (int j = 0; j < (int)A.nstarts; j++) {
+      for (int j = 0; j < ns; j++) {
         const u64 kj = pann_shfl64(key, j);
         r += (kj < key) || (kj == key && j < lane);
       }
       if (on) cand[r] = key;
       __syncwarp();
       if (on) fk = cand[lane];
-      F = (int)A.nstarts;
+      F = ns;
       __syncwarp();
     }
 
@@ -135,7 +139,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
       const bool vis_in_front = (F - __popc(unv)) == V;  // every visited vertex is still a (flagged) frontier entry
       const bool more_after = __popc(unv) > 1;           // offset + 1 < remain (:164)
       const u64 cur = pann_shfl64(fk, pos);
-      const uint32_t* grow = A.graph + (u64)pann_key_id(cur) * (A.maxdeg + 1);
+      const uint32_t* grow = A.graph + (u64)((EXT && A.rowmap) ? __ldg(A.rowmap + pann_key_id(cur)) : pann_key_id(cur)) * (A.maxdeg + 1);
       uint32_t drain_cnt = 0;  // read next to the graph row, so its latency is hidden under that load
       if (drain_watch) asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(drain_cnt) : "l"(A.qcounter));
       const int deg = (int)__ldg(grow);
@@ -225,6 +229,10 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
         F = min(F + 1, B);
       }
       C = 0;
+      if (EXT && F > B) {  // a start list longer than the beam: the merge truncates (:185)
+        F = B;
+        if (lane >= B) fk = ~0ull;
+      }
       // cut rule (:190-195)
       int nfs = F;
       if (A.cut_rule && nfs > A.k) {
@@ -311,9 +319,9 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_rerank_kernel(co
   }
 }
 
-const void* pann_beam_small_kernel_dt0(int metric, int qr);
-const void* pann_beam_small_kernel_dt1(int metric, int qr);
-const void* pann_beam_small_kernel_dt2(int metric, int qr);
+const void* pann_beam_small_kernel_dt0(int metric, int qr, bool ext);
+const void* pann_beam_small_kernel_dt1(int metric, int qr, bool ext);
+const void* pann_beam_small_kernel_dt2(int metric, int qr, bool ext);
 const void* pann_rerank_kernel_dt0(int metric);
 const void* pann_rerank_kernel_dt1(int metric);
 const void* pann_rerank_kernel_dt2(int metric);

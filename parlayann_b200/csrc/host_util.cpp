@@ -5,6 +5,8 @@
 #include <stdint.h>
 
 #include <algorithm>
+#include <limits>
+#include <random>
 #include <utility>
 #include <vector>
 
@@ -101,4 +103,26 @@ void pann_host_sort_rows(uint32_t* graph, const float* dists, uint64_t n, uint32
     if (lo < hi) ts.emplace_back(work, lo, hi);
   }
   for (auto& t : ts) t.join();
+}
+
+// beamSearchRandom's per-query start points (algorithms/utils/beamSearch.h:327-332):
+//   parlay::random_generator gen;  std::uniform_int_distribution<long> dis(0, n - 1);  indices[i] = dis(gen[i]);
+// gen[i] is a generator seeded with hash64((i+1) * 0x7fffffff + state), state = 0 (parlay/random.h:48-61); the draw itself
+// is libstdc++'s uniform_int_distribution over that 64-bit engine — used here as is, so the values are the reference's
+// wherever it is built with the same standard library.
+namespace {
+struct ParlayGen {  // parlay::random_generator
+  using result_type = size_t;
+  size_t state;
+  result_type operator()() { return state = (size_t)hash64(state); }
+  static constexpr result_type max() { return std::numeric_limits<result_type>::max(); }
+  static constexpr result_type min() { return std::numeric_limits<result_type>::lowest(); }
+};
+}  // namespace
+void pann_host_random_starts(uint64_t nq, uint64_t n, uint32_t* out) {
+  std::uniform_int_distribution<long> dis(0, (long)n - 1);
+  for (uint64_t i = 0; i < nq; i++) {
+    ParlayGen r{(size_t)hash64((i + 1) * 0x7fffffffull + 0)};
+    out[i] = (uint32_t)dis(r);
+  }
 }

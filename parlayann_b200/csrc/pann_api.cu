@@ -109,6 +109,7 @@ extern "C" void pann_index_destroy(pann_index* idx) {
   if (idx->points) cudaFree(idx->points);
   if (idx->graph) cudaFree(idx->graph);
   idx->queries.release(); idx->results.release(); idx->scratch_hash.release(); idx->scratch_vis.release();
+  idx->scratch_hash2.release(); idx->scratch_vis2.release();
   idx->bytes_ctr.release(); idx->starts.release(); idx->flag.release(); idx->qmap.release(); idx->misc.release();
   idx->gt_ids.release(); idx->gt_dists.release();
   for (auto& b : idx->gt_scratch) b.release();
@@ -179,15 +180,15 @@ static const void* beam_kernel(int dtype, int metric, int qr, bool gs) {
   }
 }
 
-static const void* beam_small_kernel(int dtype, int metric, int qr) {
+static const void* beam_small_kernel(int dtype, int metric, int qr, bool ext) {
   switch (dtype) {
-    case PANN_DT_F32: return pann_beam_small_kernel_dt0(metric, qr);
-    case PANN_DT_U8: return pann_beam_small_kernel_dt1(metric, qr);
-    default: return pann_beam_small_kernel_dt2(metric, qr);
+    case PANN_DT_F32: return pann_beam_small_kernel_dt0(metric, qr, ext);
+    case PANN_DT_U8: return pann_beam_small_kernel_dt1(metric, qr, ext);
+    default: return pann_beam_small_kernel_dt2(metric, qr, ext);
   }
 }
 
-static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap, cudaStream_t stream = nullptr) {
+static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap, cudaStream_t stream = nullptr, int slab = 0) {
   if (!stream) stream = idx->stream;
   const PannRowGeom& g = idx->geom;
   const int qrT = pann_qr_of(g);
@@ -210,7 +211,8 @@ static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap, cud
     A.warp_bytes = A.off_stage + (pann_staged_rows_rt(idx->dtype, qrT) ? PANN_STAGE_BYTES : 0);   // float rows are staged (pann_staged_distance)
     size_t cta_bytes = (size_t)A.warp_bytes * PANN_WARPS_PER_CTA;
     if (const char* e = getenv("PANN_K1_PAD_SMEM")) cta_bytes += (size_t)atoi(e);   // experiments: fewer CTAs per SM, more L1
-    const void* fn = beam_small_kernel(idx->dtype, idx->metric, qrT);
+    const bool ext = A.starts_stride != 0 || A.nstarts_q != nullptr || A.rowmap != nullptr || A.nstarts > B;
+    const void* fn = beam_small_kernel(idx->dtype, idx->metric, qrT, ext);
     PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
     int per_sm = 0;
     PANN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, fn, PANN_WARPS_PER_CTA * 32, cta_bytes));
@@ -223,8 +225,9 @@ static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap, cud
     idx->last_launches++;
     return 0;
   }
-  A.off_frontB = al16((size_t)B * 8);
-  A.off_cand = A.off_frontB + al16((size_t)B * 8);
+  const uint32_t Bcap = std::max<uint32_t>(B, A.nstarts);   // a start list longer than the beam sits in the frontier until the first merge
+  A.off_frontB = al16((size_t)Bcap * 8);
+  A.off_cand = A.off_frontB + al16((size_t)Bcap * 8);
   A.off_scand = A.off_cand + al16((size_t)A.ccap * 8);
   A.off_nbr = A.off_scand + al16((size_t)A.ccap * 8);
   A.off_q = A.off_nbr + al16((size_t)std::max<uint32_t>(A.maxdeg, 1) * 4);
@@ -244,10 +247,16 @@ static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap, cud
   if (grid < 1) grid = 1;
   if (gs) {
     size_t warps = (size_t)grid * PANN_WARPS_PER_CTA;
-    if (idx->scratch_hash.reserve(warps * (4ull << A.bits))) return 1;
-    if (idx->scratch_vis.reserve(warps * (size_t)vcap * 8)) return 1;
-    A.g_hash = idx->scratch_hash.as<uint32_t>();
-    A.g_vis = idx->scratch_vis.as<u64>();
+    // one slab per compute stream: two chunk kernels of the pipelined batch call may be resident at the same time, and a
+    // slab is indexed by the launch's own warp numbers (the buffers only ever grow while no kernel of their stream runs:
+    // every chunk of a call has the same grid or a smaller one than the first)
+    DevBuf& sh = slab ? idx->scratch_hash2 : idx->scratch_hash;
+    DevBuf& sv = slab ? idx->scratch_vis2 : idx->scratch_vis;
+    if (sh.cap < warps * (4ull << A.bits) || sv.cap < warps * (size_t)vcap * 8) PANN_CUDA(cudaStreamSynchronize(stream));
+    if (sh.reserve(warps * (4ull << A.bits))) return 1;
+    if (sv.reserve(warps * (size_t)vcap * 8)) return 1;
+    A.g_hash = sh.as<uint32_t>();
+    A.g_vis = sv.as<u64>();
   }
   void* args[] = {(void*)&A};
   PANN_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(PANN_WARPS_PER_CTA * 32), args, cta_bytes, stream));
@@ -261,28 +270,34 @@ struct BeamPlan { BeamArgs A; bool gs; uint32_t vcap; long long vbig; };
 static int beam_plan(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint32_t qstride, const uint32_t* d_self_ids,
                      const uint32_t* h_starts, uint32_t nstarts, const pann_query_params* qp, const SearchOutputs& out,
                      BeamPlan& P) {
-  if (nstarts == 0 || !h_starts) PANN_FAIL("beam search expects at least one start point");  // beamSearch.h:38-41
+  if (nstarts == 0 || (!h_starts && !out.d_starts)) PANN_FAIL("beam search expects at least one start point");  // beamSearch.h:38-41
   if (qp->beam < 1 || qp->beam > 65536) PANN_FAIL("beam search: beam width out of range");
   if (qp->k < 0) PANN_FAIL("beam search: k must be non-negative");
-  for (uint32_t i = 0; i < nstarts; i++)
-    if (h_starts[i] >= idx->n) PANN_FAIL("beam search: start point out of range");
+  if (!out.d_starts)
+    for (uint32_t i = 0; i < nstarts; i++)
+      if (h_starts[i] >= idx->n) PANN_FAIL("beam search: start point out of range");
   if (nq >= 0x7fffffffull) PANN_FAIL("beam search: more than 2^31 - 1 queries in one call");
-  if (idx->starts.reserve(sizeof(uint32_t) * nstarts) || idx->flag.reserve(sizeof(int)) || idx->bytes_ctr.reserve(16 + 4 * PANN_MAX_CHUNKS)) return 1;
+  if (idx->flag.reserve(sizeof(int)) || idx->bytes_ctr.reserve(16 + 4 * PANN_MAX_CHUNKS)) return 1;
   PANN_CUDA(cudaMemsetAsync(idx->bytes_ctr.p, 0, 16 + 4 * PANN_MAX_CHUNKS, idx->stream));
-  PANN_CUDA(cudaMemcpyAsync(idx->starts.p, h_starts, sizeof(uint32_t) * nstarts, cudaMemcpyHostToDevice, idx->stream));
+  if (!out.d_starts) {
+    if (idx->starts.reserve(sizeof(uint32_t) * nstarts)) return 1;
+    PANN_CUDA(cudaMemcpyAsync(idx->starts.p, h_starts, sizeof(uint32_t) * nstarts, cudaMemcpyHostToDevice, idx->stream));
+  }
   PANN_CUDA(cudaMemsetAsync(idx->flag.p, 0, sizeof(int), idx->stream));
 
   BeamArgs& A = P.A;
   memset(&A, 0, sizeof(A));
   A.points = idx->points; A.n = idx->n; A.stride = idx->geom.stride; A.nch = idx->geom.nch;
   A.graph = idx->graph; A.maxdeg = idx->maxdeg;
+  if (out.g_graph) { A.graph = out.g_graph; A.maxdeg = out.g_maxdeg; A.rowmap = out.g_rowmap; }
   A.queries = d_queries; A.nq = nq; A.qstride = qstride; A.self_ids = d_self_ids;
   A.starts = idx->starts.as<uint32_t>(); A.nstarts = nstarts;
+  if (out.d_starts) { A.starts = out.d_starts; A.starts_stride = out.starts_stride; A.nstarts_q = out.d_nstarts_q; }
   const long long beam = qp->beam;
   A.k = (int)qp->k; A.beam = (int)beam;
   A.bits = std::max<int>(10, (int)std::ceil(std::log2((double)(int)(beam * beam))) - 2);  // beamSearch.h:52
   A.limit = qp->limit < 0 ? (long long)idx->n : qp->limit;
-  A.degree_limit = qp->degree_limit < 0 ? (int)idx->maxdeg : (int)std::min<int64_t>(qp->degree_limit, idx->maxdeg);
+  A.degree_limit = qp->degree_limit < 0 ? (int)A.maxdeg : (int)std::min<int64_t>(qp->degree_limit, A.maxdeg);
   A.cut = qp->cut;
   A.cut_rule = (qp->k > 0 && idx->metric == PANN_M_L2) ? 1 : 0;
   A.out_ids = out.ids; A.out_dists = out.dists; A.out_visited = out.visited; A.out_cmps = out.cmps;
@@ -324,7 +339,7 @@ int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint
                     int* status_or) {
   *status_or = 0;
   if (nq == 0) {
-    if (nstarts == 0 || !h_starts) PANN_FAIL("beam search expects at least one start point");
+    if (nstarts == 0 || (!h_starts && !out.d_starts)) PANN_FAIL("beam search expects at least one start point");
     return 0;
   }
   BeamPlan P;
@@ -398,12 +413,14 @@ static bool is_pinned_host(const void* p) {
 // host_out (may be null): {ids, dists, visited, cmps} host buffers of the batch call.  When all of them are pinned the
 // results go straight there behind the kernel and the call has ONE host synchronisation; otherwise the caller fetches.
 static int search_common(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t qstride, const uint32_t* starts,
-                         uint32_t nstarts, const pann_query_params* qp, void* const* host_out = nullptr, bool* delivered = nullptr) {
+                         uint32_t nstarts, const pann_query_params* qp, void* const* host_out = nullptr, bool* delivered = nullptr,
+                         const SearchOutputs* per_query = nullptr) {
   ResLayout L = res_layout(nq, (uint32_t)qp->k);
   if (idx->results.reserve(L.total + 16)) return 1;
   idx->res_nq = nq; idx->res_k = (uint32_t)qp->k;
   uint8_t* r = idx->results.as<uint8_t>();
   SearchOutputs o;
+  if (per_query) { o.d_starts = per_query->d_starts; o.starts_stride = per_query->starts_stride; o.d_nstarts_q = per_query->d_nstarts_q; }
   o.ids = (uint32_t*)(r + L.ids); o.dists = (float*)(r + L.dists); o.visited = (uint32_t*)(r + L.visited);
   o.cmps = (uint32_t*)(r + L.cmps); o.status = (int*)(r + L.status);
   int flag = 0;
@@ -478,7 +495,7 @@ static int search_pipelined(pann_index* idx, const uint8_t* host_queries, uint64
     A.out_ids = o.ids + c0 * k; A.out_dists = o.dists + c0 * k; A.out_visited = o.visited + c0; A.out_cmps = o.cmps + c0;
     A.status = o.status + c0;
     if (A.qcounter) A.qcounter = reinterpret_cast<uint32_t*>(idx->bytes_ctr.as<uint8_t>() + 16) + c;   // one query counter per chunk
-    if (launch_beam(idx, A, P.gs, P.vcap, cs)) return 1;
+    if (launch_beam(idx, A, P.gs, P.vcap, cs, (int)(c & 1))) return 1;
     PANN_CUDA(cudaEventRecord(idx->pipe_ev[2 * c + 1], cs));
     PANN_CUDA(cudaStreamWaitEvent(idx->s_out, idx->pipe_ev[2 * c + 1], 0));
     PANN_CUDA(cudaMemcpyAsync((uint32_t*)host_out[0] + c0 * k, A.out_ids, 4ull * cn * k, cudaMemcpyDeviceToHost, idx->s_out));
@@ -592,11 +609,50 @@ extern "C" int pann_search_batch(pann_index* idx, const void* host_queries, uint
   return delivered ? 0 : fetch_results(idx, out_ids, out_dists, out_visited, out_cmps);
 }
 
-extern "C" int pann_search_full(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes,
-                                const uint32_t* self_ids, const uint32_t* starts, uint32_t nstarts,
-                                const pann_query_params* qp, uint32_t fcap, uint32_t* fr_ids, float* fr_dists,
-                                uint32_t* n_frontier, uint32_t vcap, uint32_t* vis_ids, float* vis_dists,
-                                uint32_t* n_visited, uint32_t* out_cmps) {
+// per-query start lists from the host -> idx->starts (nq x stride) [+ counts behind them]; fills the SearchOutputs fields
+static int upload_starts(pann_index* idx, uint64_t nq, const uint32_t* starts, uint32_t stride, const uint32_t* nstarts_q, SearchOutputs& o) {
+  if (!starts || stride == 0) PANN_FAIL("beam search expects at least one start point");  // beamSearch.h:38-41
+  for (uint64_t i = 0; i < nq; i++) {
+    const uint32_t c = nstarts_q ? nstarts_q[i] : stride;
+    if (c == 0) PANN_FAIL("beam search expects at least one start point");
+    if (c > stride) PANN_FAIL("beam search: a per-query start count exceeds the stride of the start array");
+    for (uint32_t j = 0; j < c; j++)
+      if (starts[i * stride + j] >= idx->n) PANN_FAIL("beam search: start point out of range");
+  }
+  const size_t sb = 4ull * nq * stride;
+  if (idx->starts.reserve(sb + (nstarts_q ? 4ull * nq : 0) + 16)) return 1;
+  PANN_CUDA(cudaMemcpyAsync(idx->starts.p, starts, sb, cudaMemcpyHostToDevice, idx->stream));
+  o.d_starts = idx->starts.as<uint32_t>(); o.starts_stride = stride;
+  if (nstarts_q) {
+    uint32_t* dn = reinterpret_cast<uint32_t*>(idx->starts.as<uint8_t>() + sb);
+    PANN_CUDA(cudaMemcpyAsync(dn, nstarts_q, 4ull * nq, cudaMemcpyHostToDevice, idx->stream));
+    o.d_nstarts_q = dn;
+  }
+  return 0;
+}
+
+extern "C" int pann_search_batch_starts(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes,
+                                        const uint32_t* starts, uint32_t starts_stride, const uint32_t* nstarts_q,
+                                        const pann_query_params* qp, uint32_t* out_ids, float* out_dists,
+                                        uint32_t* out_visited, uint32_t* out_cmps) {
+  if (!idx || (!host_queries && nq)) PANN_FAIL("pann_search_batch_starts: null argument");
+  if (validate_qp(qp)) return 1;
+  PANN_CUDA(cudaSetDevice(idx->device));
+  if (nq == 0) return 0;
+  SearchOutputs pq;
+  if (upload_starts(idx, nq, starts, starts_stride, nstarts_q, pq)) return 1;
+  if (upload_queries(idx, host_queries, nq, q_stride_bytes)) return 1;
+  void* const host_out[4] = {out_ids, out_dists, out_visited, out_cmps};
+  bool delivered = false;
+  if (search_common(idx, idx->queries.as<uint8_t>(), nq, idx->geom.stride, nullptr, starts_stride, qp, host_out, &delivered, &pq)) return 1;
+  return delivered ? 0 : fetch_results(idx, out_ids, out_dists, out_visited, out_cmps);
+}
+
+static int search_full_impl(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes,
+                            const uint32_t* self_ids, const uint32_t* starts, uint32_t nstarts, uint32_t starts_stride,
+                            const uint32_t* nstarts_q, const pann_query_params* qp, uint32_t fcap, uint32_t* fr_ids,
+                            float* fr_dists, uint32_t* n_frontier, uint32_t vcap, uint32_t* vis_ids, float* vis_dists,
+                            uint32_t* n_visited, uint32_t* out_cmps) {
   if (!idx || !qp) PANN_FAIL("pann_search_full: null argument");
   if (!self_ids && !host_queries) PANN_FAIL("pann_search_full: need queries or self ids");
   PANN_CUDA(cudaSetDevice(idx->device));
@@ -626,6 +682,10 @@ extern "C" int pann_search_full(pann_index* idx, const void* host_queries, uint6
   }
   int flag = 0;
   idx->last_launches = 0;
+  if (starts_stride) {
+    if (upload_starts(idx, nq, starts, starts_stride, nstarts_q, o)) return 1;
+    nstarts = starts_stride;
+  }
   if (pann_run_search(idx, d_q, nq, idx->geom.stride, d_self, starts, nstarts, qp, o, &flag)) return 1;
   if (check_status(flag & ~(1 << 2))) return 1;
   if (fr_ids) PANN_CUDA(cudaMemcpy(fr_ids, o.fr_ids, 4ull * nq * fcap, cudaMemcpyDeviceToHost));
@@ -636,6 +696,24 @@ extern "C" int pann_search_full(pann_index* idx, const void* host_queries, uint6
   if (n_visited) PANN_CUDA(cudaMemcpy(n_visited, o.n_visited, 4ull * nq, cudaMemcpyDeviceToHost));
   if (out_cmps) PANN_CUDA(cudaMemcpy(out_cmps, o.cmps, 4ull * nq, cudaMemcpyDeviceToHost));
   return 0;
+}
+
+extern "C" int pann_search_full(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes,
+                                const uint32_t* self_ids, const uint32_t* starts, uint32_t nstarts,
+                                const pann_query_params* qp, uint32_t fcap, uint32_t* fr_ids, float* fr_dists,
+                                uint32_t* n_frontier, uint32_t vcap, uint32_t* vis_ids, float* vis_dists,
+                                uint32_t* n_visited, uint32_t* out_cmps) {
+  return search_full_impl(idx, host_queries, nq, q_stride_bytes, self_ids, starts, nstarts, 0, nullptr, qp, fcap, fr_ids, fr_dists,
+                          n_frontier, vcap, vis_ids, vis_dists, n_visited, out_cmps);
+}
+extern "C" int pann_search_full_starts(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes,
+                                       const uint32_t* self_ids, const uint32_t* starts, uint32_t starts_stride,
+                                       const uint32_t* nstarts_q, const pann_query_params* qp, uint32_t fcap, uint32_t* fr_ids,
+                                       float* fr_dists, uint32_t* n_frontier, uint32_t vcap, uint32_t* vis_ids,
+                                       float* vis_dists, uint32_t* n_visited, uint32_t* out_cmps) {
+  if (!starts_stride) PANN_FAIL("beam search expects at least one start point");
+  return search_full_impl(idx, host_queries, nq, q_stride_bytes, self_ids, starts, 0, starts_stride, nstarts_q, qp, fcap, fr_ids,
+                          fr_dists, n_frontier, vcap, vis_ids, vis_dists, n_visited, out_cmps);
 }
 
 static const void* rerank_kernel(int dtype, int metric) {
@@ -714,6 +792,11 @@ extern "C" int pann_search_rerank_batch(pann_index* q_idx, pann_index* base_idx,
 extern "C" int pann_random_permutation(int64_t n, int32_t* out) {
   if (n < 0 || !out) PANN_FAIL("pann_random_permutation: bad argument");
   pann_host_random_permutation(n, out);
+  return 0;
+}
+extern "C" int pann_random_starts(uint64_t nq, uint64_t n, uint32_t* out) {
+  if (!out || n == 0 || n >= (1ull << 31)) PANN_FAIL("pann_random_starts: bad argument");
+  pann_host_random_starts(nq, n, out);
   return 0;
 }
 extern "C" int64_t pann_batch_schedule(uint64_t n, uint64_t m, int64_t* lo, int64_t* hi, int64_t cap) {

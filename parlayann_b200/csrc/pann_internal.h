@@ -49,6 +49,7 @@ struct pann_index {
   DevBuf results;  // packed: ids[nq*k] dists[nq*k] visited[nq] cmps[nq] status[nq]
   uint64_t res_nq = 0; uint32_t res_k = 0;
   DevBuf scratch_hash, scratch_vis, starts, flag, qmap, misc;
+  DevBuf scratch_hash2, scratch_vis2;   // second global-scratch slab: chunk kernels on the second compute stream (pann_search_batch pipeline) run concurrently with the first's
   void* pinned = nullptr; size_t pinned_cap = 0;
   // ground truth results (resident)
   DevBuf gt_ids, gt_dists; uint64_t gt_nq = 0; uint32_t gt_k = 0;
@@ -64,6 +65,12 @@ struct SearchOutputs {  // device pointers (any may be null)
   // optional device->host copies enqueued right after the kernel, ahead of the one host synchronisation of the call
   struct Copy { void* dst; const void* src; size_t bytes; } after[4] = {};
   cudaEvent_t after_kernel = nullptr;  // recorded between the kernel and those copies
+  // ---- per-launch inputs beyond the plain call (all optional)
+  // per-query start lists on the device: query q starts from d_starts[q * starts_stride .. + (d_nstarts_q ? d_nstarts_q[q] :
+  // nstarts)); h_starts of pann_run_search is then ignored and its nstarts is the longest list
+  const uint32_t* d_starts = nullptr; uint32_t starts_stride = 0; const uint32_t* d_nstarts_q = nullptr;
+  // another graph than the index's own (HNSW's upper layers): rows of (g_maxdeg + 1) words, row of vertex v = g_rowmap[v]
+  const uint32_t* g_graph = nullptr; uint32_t g_maxdeg = 0; const uint32_t* g_rowmap = nullptr;
 };
 
 // Runs K1 over nq queries (device rows, or base rows self_ids) and retries visited-list overflows with the
@@ -75,4 +82,5 @@ int pann_pinned(pann_index* idx, size_t bytes, void** p);
 int pann_gen_rows_device(int kind, uint64_t seed, uint64_t stream, uint64_t row0, uint64_t nrows, uint32_t d, uint32_t r,
                          uint32_t nc, void* dev_out, uint64_t stride, cudaStream_t s);
 void pann_host_random_permutation(int64_t n, int32_t* out);
+void pann_host_random_starts(uint64_t nq, uint64_t n, uint32_t* out);
 int64_t pann_host_batch_schedule(uint64_t n, uint64_t m, int64_t* lo, int64_t* hi, int64_t cap);

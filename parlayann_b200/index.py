@@ -164,14 +164,21 @@ class GraphIndex:
         return QueryParams(int(k), int(beam), float(cut), -1 if limit is None else int(limit),
                            -1 if degree_limit is None else int(degree_limit))
 
-    def search(self, queries, k=10, beam=10, cut=1.35, limit=None, degree_limit=None, starts=None, out=None):
+    def search(self, queries, k=10, beam=10, cut=1.35, limit=None, degree_limit=None, starts=None, out=None, nstarts_q=None):
         """One beam search per row of `queries` (host array).  Returns ids, dists, visited, cmps."""
         queries = np.ascontiguousarray(queries, dtype=fileio.np_dtype(self.data_type))
         nq = queries.shape[0]
-        st = np.asarray([self.start_point] if starts is None else starts, dtype=np.uint32)
+        st = np.ascontiguousarray([self.start_point] if starts is None else starts, dtype=np.uint32)
         if out is None:
             out = (np.empty((nq, k), np.uint32), np.empty((nq, k), np.float32), np.empty(nq, np.uint32), np.empty(nq, np.uint32))
         qp = self._qp(k, beam, cut, limit, degree_limit)
+        if st.ndim == 2:   # per-query start lists [nq, stride] (beamSearchRandom, beamSearch.h:309-351; HNSW entry points)
+            if st.shape[0] != nq:
+                raise ValueError("per-query starts need one row per query")
+            nsq = None if nstarts_q is None else np.ascontiguousarray(nstarts_q, dtype=np.uint32)
+            check(_lib.lib().pann_search_batch_starts(self._h, _vp(queries), C.c_uint64(nq), C.c_uint64(queries.strides[0]), _vp(st),
+                                                      C.c_uint32(st.shape[1]), _vp(nsq), C.byref(qp), _vp(out[0]), _vp(out[1]), _vp(out[2]), _vp(out[3])))
+            return out
         check(_lib.lib().pann_search_batch(self._h, _vp(queries), C.c_uint64(nq), C.c_uint64(queries.strides[0]), _vp(st),
                                            C.c_uint32(len(st)), C.byref(qp), _vp(out[0]), _vp(out[1]), _vp(out[2]), _vp(out[3])))
         return out
@@ -205,7 +212,7 @@ class GraphIndex:
         return out
 
     def search_full(self, queries=None, self_ids=None, k=0, beam=10, cut=1.35, limit=None, degree_limit=None, starts=None,
-                    vcap=1024):
+                    vcap=1024, nstarts_q=None):
         """beam_search (beamSearch.h:217-223): whole frontier + whole visited list per query."""
         if self_ids is not None:
             self_ids = np.ascontiguousarray(self_ids, dtype=np.uint32)
@@ -215,12 +222,19 @@ class GraphIndex:
             queries = np.ascontiguousarray(queries, dtype=fileio.np_dtype(self.data_type))
             nq = queries.shape[0]
             qptr, qstride = _vp(queries), queries.strides[0]
-        st = np.asarray([self.start_point] if starts is None else starts, dtype=np.uint32)
+        st = np.ascontiguousarray([self.start_point] if starts is None else starts, dtype=np.uint32)
         qp = self._qp(k, beam, cut, limit, degree_limit)
-        fcap = int(beam)
+        fcap = int(max(beam, st.shape[-1]))
         r = dict(fr_ids=np.zeros((nq, fcap), np.uint32), fr_dists=np.zeros((nq, fcap), np.float32), nfr=np.zeros(nq, np.uint32),
                  vis_ids=np.zeros((nq, vcap), np.uint32), vis_dists=np.zeros((nq, vcap), np.float32), nvis=np.zeros(nq, np.uint32),
                  cmps=np.zeros(nq, np.uint32))
+        if st.ndim == 2:
+            nsq = None if nstarts_q is None else np.ascontiguousarray(nstarts_q, dtype=np.uint32)
+            check(_lib.lib().pann_search_full_starts(self._h, qptr, C.c_uint64(nq), C.c_uint64(qstride), _vp(self_ids), _vp(st),
+                                                     C.c_uint32(st.shape[1]), _vp(nsq), C.byref(qp), C.c_uint32(fcap), _vp(r["fr_ids"]),
+                                                     _vp(r["fr_dists"]), _vp(r["nfr"]), C.c_uint32(vcap), _vp(r["vis_ids"]),
+                                                     _vp(r["vis_dists"]), _vp(r["nvis"]), _vp(r["cmps"])))
+            return r
         check(_lib.lib().pann_search_full(self._h, qptr, C.c_uint64(nq), C.c_uint64(qstride), _vp(self_ids), _vp(st),
                                           C.c_uint32(len(st)), C.byref(qp), C.c_uint32(fcap), _vp(r["fr_ids"]), _vp(r["fr_dists"]),
                                           _vp(r["nfr"]), C.c_uint32(vcap), _vp(r["vis_ids"]), _vp(r["vis_dists"]), _vp(r["nvis"]),
@@ -343,6 +357,13 @@ def groundtruth_merge(ids_list, dists_list, device=0):
 def random_permutation(n):
     out = np.empty(n, np.int32)
     check(_lib.lib().pann_random_permutation(C.c_int64(n), _vp(out)))
+    return out
+
+
+def random_starts(nq, n):
+    """beamSearchRandom's per-query start points (beamSearch.h:327-332)"""
+    out = np.empty(nq, np.uint32)
+    check(_lib.lib().pann_random_starts(C.c_uint64(nq), C.c_uint64(n), _vp(out)))
     return out
 
 

@@ -58,13 +58,16 @@ def batch_schedule(n, m=None):
 
 
 def search(points, graph, queries, data_type, metric="Euclidian", k=10, beam=10, cut=1.35, limit=None,
-           degree_limit=None, starts=(0,), selfs=None, full=False, fcap=None, vcap=4096):
+           degree_limit=None, starts=(0,), selfs=None, full=False, fcap=None, vcap=4096, nstarts_q=None):
+    """starts: one list for the batch, or a 2-D [nq, stride] array of per-query lists (nstarts_q: how many of each row count)"""
     n, d = points.shape
     nq = queries.shape[0]
     maxdeg = graph.shape[1] - 1
     limit = n if limit is None or limit < 0 else limit
     degree_limit = maxdeg if degree_limit is None or degree_limit < 0 else degree_limit
-    st = np.asarray(starts, dtype=np.uint32)
+    st = np.ascontiguousarray(starts, dtype=np.uint32)
+    sstride = st.shape[1] if st.ndim == 2 else 0
+    nsq = None if nstarts_q is None else np.ascontiguousarray(nstarts_q, dtype=np.uint32)
     ids = np.zeros((nq, k), dtype=np.uint32)
     dists = np.zeros((nq, k), dtype=np.float32)
     vis = np.zeros(nq, dtype=np.uint32)
@@ -78,9 +81,10 @@ def search(points, graph, queries, data_type, metric="Euclidian", k=10, beam=10,
     sf = None if selfs is None else np.ascontiguousarray(selfs, dtype=np.int64)
     points = np.ascontiguousarray(points); queries = np.ascontiguousarray(queries)
     graph = np.ascontiguousarray(graph, dtype=np.uint32)
-    rc = lib().oracle_search_batch(DT[data_type], METRIC[metric], _p(points), C.c_uint64(n), C.c_uint32(d),
+    rc = lib().oracle_search_batch_starts(DT[data_type], METRIC[metric], _p(points), C.c_uint64(n), C.c_uint32(d),
                                    C.c_uint64(points.strides[0]), _p(graph), C.c_uint32(maxdeg), _p(queries),
-                                   C.c_uint64(nq), C.c_uint64(queries.strides[0]), _p(sf), _p(st), C.c_uint32(len(st)),
+                                   C.c_uint64(nq), C.c_uint64(queries.strides[0]), _p(sf), _p(st), C.c_uint32(sstride or len(st)),
+                                   C.c_uint32(sstride), _p(nsq),
                                    C.c_long(k), C.c_long(beam), C.c_double(cut), C.c_long(limit), C.c_long(degree_limit),
                                    _p(ids), _p(dists), _p(vis), _p(cmps),
                                    C.c_uint32(fcap), _p(fr_i), _p(fr_d), _p(nfr),

@@ -74,3 +74,21 @@ def test_recall_with_ties():
     gt_d = np.array([[0.0, 1.0, 1.0, 2.0]], np.float32)
     assert recall_with_ties(np.array([[1, 3]]), gt_ids, gt_d, 2) == 1.0   # 3 ties with the 2nd
     assert recall_with_ties(np.array([[1, 4]]), gt_ids, gt_d, 2) == 0.5
+
+
+def test_random_starts_match_beamSearchRandom():
+    """pann_random_starts = parlay::random_generator()[i] through std::uniform_int_distribution<long>(0, n-1)
+    (beamSearch.h:327-332), pinned to the start points the reference's own beamSearchRandom used; the oracle with one start
+    per query reproduces the reference's ids and counters."""
+    from parlayann_b200.index import random_starts
+    g = np.load(os.path.join(GOLDEN, "random_starts.npz"))
+    n, d, nq, R, L, seed = (int(x) for x in g["params"])
+    st = random_starts(nq, n)
+    assert np.array_equal(st, g["starts"])
+    base = O.gen_points("uint8", n, d, seed=seed)
+    qs = O.gen_points("uint8", nq, d, seed=seed, stream=1)
+    for si in range(3):
+        k, beam = (int(x) for x in g[f"r{si}_kb"])
+        r = O.search(base, g["graph"], qs, "uint8", k=k, beam=beam, starts=st.reshape(-1, 1))
+        assert np.array_equal(r["ids"], g[f"r{si}_ids"])
+        assert np.array_equal(r["visited"], g[f"r{si}_visited"]) and np.array_equal(r["cmps"], g[f"r{si}_distances"])

@@ -207,3 +207,126 @@ def test_pipelined_host_batch_identical(dataset, monkeypatch):
         sl = slice(block * n0, (block + 1) * n0)
         assert np.array_equal(piped[0][sl], ref["ids"]) and np.array_equal(piped[1][sl], ref["dists"])
         assert np.array_equal(piped[2][sl], ref["visited"]) and np.array_equal(piped[3][sl], ref["cmps"])
+
+
+@pytest.mark.parametrize("beam,env", [(100, None), (128, None), (40, "PANN_FORCE_GLOBAL_SCRATCH")])
+def test_pipelined_wide_beam_identical(dataset, monkeypatch, beam, env):
+    # wide beams keep the hash filter and the visited list in a global slab: the two compute streams of the chunk pipeline
+    # must not share one (two chunk kernels are resident at the same time) — pipelined == plain == oracle
+    torch = pytest.importorskip("torch")
+    ds = dataset("uint8")
+    idx = _index(ds)
+    if env:
+        monkeypatch.setenv(env, "1")
+    reps = 270000 // len(ds.queries) + 1
+    nq = reps * len(ds.queries)
+    hq = torch.from_numpy(np.tile(ds.queries, (reps, 1))).pin_memory()
+
+    def pinned(shape, dt):
+        return torch.empty(shape, dtype=dt).pin_memory().numpy()
+
+    def run():
+        out = (pinned((nq, 10), torch.int32).view(np.uint32), pinned((nq, 10), torch.float32),
+               pinned(nq, torch.int32).view(np.uint32), pinned(nq, torch.int32).view(np.uint32))
+        for o in out:
+            o[...] = 0
+        idx.search(hq.numpy(), k=10, beam=beam, out=out)
+        return out, idx.last_timing()[1]
+    piped, nl = run()
+    assert nl >= 3, "the chunk pipeline did not engage"
+    monkeypatch.setenv("PANN_NO_PIPELINE", "1")
+    plain, _ = run()
+    for a, b in zip(piped, plain):
+        assert np.array_equal(a, b)
+    ref = O.search(ds.base, ds.graph, ds.queries, ds.data_type, ds.metric, k=10, beam=beam)
+    n0 = len(ds.queries)
+    for block in (0, reps // 2, reps - 1):
+        sl = slice(block * n0, (block + 1) * n0)
+        assert np.array_equal(piped[0][sl], ref["ids"]) and np.array_equal(piped[2][sl], ref["visited"]) and np.array_equal(piped[3][sl], ref["cmps"])
+
+
+# ---- one start list per query (beamSearchRandom, beamSearch.h:309-351; HNSW's per-query entry points)
+def _check_exact_starts(ds, idx, starts, nstarts_q=None, **qp):
+    ids, dists, vis, cmps = idx.search(ds.queries, starts=starts, nstarts_q=nstarts_q, **qp)
+    ref = O.search(ds.base, ds.graph, ds.queries, ds.data_type, ds.metric, starts=starts, nstarts_q=nstarts_q, **qp)
+    assert np.array_equal(ids, ref["ids"]) and np.array_equal(dists, ref["dists"])
+    assert np.array_equal(vis, ref["visited"]) and np.array_equal(cmps, ref["cmps"])
+
+
+@pytest.mark.parametrize("beam", [10, 24, 32, 40, 100])
+def test_per_query_single_start(dataset, beam):
+    import parlayann_b200 as P
+    from parlayann_b200.index import random_starts
+    ds = dataset("uint8")
+    idx = _index(ds)
+    st = random_starts(len(ds.queries), ds.n).reshape(-1, 1)
+    assert st.max() < ds.n and len(np.unique(st)) > len(st) // 2
+    _check_exact_starts(ds, idx, st, k=10, beam=beam)
+
+
+@pytest.mark.parametrize("dt,metric", [("int8", "mips"), ("float", "Euclidian")])
+def test_per_query_ragged_start_lists(dataset, dt, metric):
+    ds = dataset(dt, metric, n=8000, d=100 if dt == "float" else 128, nq=300)
+    idx = _index(ds)
+    rng = np.random.default_rng(5)
+    st = rng.integers(0, ds.n, size=(len(ds.queries), 6), dtype=np.uint32)
+    cnt = rng.integers(1, 7, size=len(ds.queries), dtype=np.uint32)
+    for beam in (12, 48):   # K1s and the general kernel
+        ids, dists, vis, cmps = idx.search(ds.queries, starts=st, nstarts_q=cnt, k=10, beam=beam)
+        ref = O.search(ds.base, ds.graph, ds.queries, ds.data_type, ds.metric, starts=st, nstarts_q=cnt, k=10, beam=beam)
+        assert np.array_equal(vis, ref["visited"]) and np.array_equal(cmps, ref["cmps"])
+        if dt == "float":
+            assert np.allclose(dists, ref["dists"], rtol=1e-5, atol=0)
+        else:
+            assert np.array_equal(ids, ref["ids"]) and np.array_equal(dists, ref["dists"])
+
+
+@pytest.mark.parametrize("beam,k", [(1, 1), (1, 0), (4, 4), (3, 0)])
+def test_more_starts_than_beam(dataset, beam, k):
+    # HNSW's ef = 1 descent from several entrances (HNSW.hpp:869-881): the frontier starts longer than the beam and the
+    # first merge truncates it; whole frontier and visited list against the oracle
+    ds = dataset("uint8")
+    idx = _index(ds)
+    rng = np.random.default_rng(9)
+    st = rng.integers(0, ds.n, size=(len(ds.queries), 7), dtype=np.uint32)
+    cnt = rng.integers(1, 8, size=len(ds.queries), dtype=np.uint32)
+    got = idx.search_full(ds.queries, k=k, beam=beam, starts=st, nstarts_q=cnt, vcap=256)
+    ref = O.search(ds.base, ds.graph, ds.queries, "uint8", k=k, beam=beam, starts=st, nstarts_q=cnt, full=True, fcap=7, vcap=256)
+    assert np.array_equal(got["nvis"], ref["nvis"]) and np.array_equal(got["nfr"], ref["nfr"]) and np.array_equal(got["cmps"], ref["cmps"])
+    for i in range(len(ds.queries)):
+        nv, nf = ref["nvis"][i], ref["nfr"][i]
+        assert np.array_equal(got["vis_ids"][i, :nv], ref["vis_ids"][i, :nv])
+        assert np.array_equal(got["fr_ids"][i, :nf], ref["fr_ids"][i, :nf]) and np.array_equal(got["fr_dists"][i, :nf], ref["fr_dists"][i, :nf])
+    # without the visited list the narrow-beam kernel takes the same searches
+    ids, dists, vis, cmps = idx.search(ds.queries, starts=st, nstarts_q=cnt, k=k if k else 1, beam=beam) if k else (None,) * 4
+    if k:
+        assert np.array_equal(ids, ref["fr_ids"][:, :k]) and np.array_equal(vis, ref["nvis"]) and np.array_equal(cmps, ref["cmps"])
+
+
+def test_more_starts_than_beam_with_cut_rule_is_refused(dataset):
+    import parlayann_b200 as P
+    ds = dataset("uint8")
+    idx = _index(ds)
+    st = np.tile(np.arange(12, dtype=np.uint32), (len(ds.queries), 1))
+    with pytest.raises(P.PannError):
+        idx.search(ds.queries, starts=st, k=2, beam=10)
+
+
+def test_beamSearchRandom_golden():
+    # the reference's own beamSearchRandom (ref_driver random -> tests/golden/random_starts.npz): same start points, ids, counters
+    import os
+    import parlayann_b200 as P
+    from parlayann_b200.index import random_starts
+    from golden_util import GOLDEN
+    g = np.load(os.path.join(GOLDEN, "random_starts.npz"))
+    n, d, nq, R, L, seed = (int(x) for x in g["params"])
+    base = O.gen_points("uint8", n, d, seed=seed)
+    qs = O.gen_points("uint8", nq, d, seed=seed, stream=1)
+    idx = P.GraphIndex(base, g["graph"], "uint8", "Euclidian")
+    st = random_starts(nq, n)
+    assert np.array_equal(st, g["starts"])
+    for si in range(3):
+        k, beam = (int(x) for x in g[f"r{si}_kb"])
+        ids, _, vis, cmps = idx.search(qs, k=k, beam=beam, starts=st.reshape(-1, 1))
+        assert np.array_equal(ids, g[f"r{si}_ids"])
+        assert np.array_equal(vis, g[f"r{si}_visited"]) and np.array_equal(cmps, g[f"r{si}_distances"])
