@@ -3,22 +3,31 @@
 
 Workload (config.workload): the configuration the metric is quoted on — Vamana search over a synthetic BIGANN-shaped
 10M x 128 uint8 set (BASELINE.json configs[3]; 3.9 GB of points + graph, fits one GPU), graph R=64 L=128 alpha=1.2 built
-ON THE GPU by pann_vamana_build (the build time is reported too).  A step is one pass of the search over a batch of
-1 000 000 queries per GPU (SURVEY.md §8d: the 10 000-query set the reference ships is two waves of warps on one B200;
-throughput and scaling are quoted on the 1M batch, recall and parity on the 10 000-query batch).  QueryParams are chosen
-by the reference's own sweep (check_nn_recall.h:214-257) on the 10 000-query recall batch against exact ground truth
-from K4: the cheapest setting whose tie-aware recall@10 is >= 0.95.  `--n 1000000 --nq 10000` is configs[1].
+ON THE GPU by pann_vamana_build (the build time is reported too, with its own roofline and CPU baseline).  A step is one
+pass of the search over a batch of 1 000 000 queries per GPU (the 10 000-query set the reference ships is
+two waves of warps on one B200; throughput and scaling are quoted on the 1M batch, recall and parity on the 10 000-query
+batch).  QueryParams are chosen by the reference's own sweep (check_nn_recall.h:214-257) on the 10 000-query recall batch
+against exact ground truth from K4: the cheapest setting whose tie-aware recall@10 is >= 0.95.
+`--n 1000000 --nq 10000` is configs[1].
 
-  value   whole-job QPS with queries resident in HBM (device time from CUDA events on the library's stream)
-  e2e     the same through pann_search_batch with pinned HOST buffers: H2D queries + search + D2H ids/dists/counters
+  value     whole-job QPS with queries resident in HBM (device time from CUDA events on the library's stream)
+  e2e       the same through pann_search_batch with pinned HOST buffers: H2D queries + search + D2H ids/dists/counters
   roofline  algorithmic bytes of the batch (counted on the device) / K1s' device time, vs measured HBM
-  recall_batch  the same search over the 10 000-query recall batch alone (latency-bound end of the curve)
-  cpu_baseline  the unmodified reference (oracle/_ref/ref_driver -> qsearchAll) on this box's cores, same graph,
-                on the 10 000-query recall batch (a bounded sample of the workload)
+  parity    the reference itself (oracle/_ref/ref_driver -> qsearchAll) on the 10 000-query batch at the chosen QueryParams:
+            ids, visited and distance-comparison counters compared PER QUERY with the GPU's
+  timed_batch_recall  tie-aware recall@10 of a 10 000-row slice of the TIMED 1M batch (exact ground truth from K4)
+  recall_batch   the same search over the 10 000-query batch alone, device-resident and end to end
+  strong    a FIXED batch (1M queries, and the 10 000-query batch) cut over the N ranks through search_sharded(gather=True):
+            H2D + search + NCCL all-gather of the answer + D2H on every rank, max over ranks
+  build     pann_vamana_build seconds, phase split, roofline (B_ins counted on the device), and the reference's CPU build
+            timed next to the GPU build at the largest n that fits ~1 CPU-minute
+  groundtruth   K4 over the recall batch (tensor roofline, CPU baseline on a 1 000-query sample)
+  groundtruth_c3  BASELINE configs[2]: 10 000 x 10M x 96 f32, k=100, base rows sharded over the N ranks, NCCL merge
+  cpu_baseline  the unmodified reference's qsearchAll on this box's cores, same graph / queries / QueryParams
 
 `--impl reference` times only the reference's CPU search (10 000-query sample per step).  Up to 2M points it also builds
 the graph and the ground truth with the reference's own code; at 10M those would take many minutes of CPU, so the inputs
-are prepared on the GPU (untimed) when one is present.
+are prepared on the GPU (untimed) when one is present.  `--workload groundtruth` prints the C3 line alone.
 Multi-GPU (torchrun): one rank per GPU, replicated index, every rank searches its own 1M-query batch
 (weak scaling, no data-path collective); time = max over ranks.
 """
@@ -99,8 +108,8 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------------------------------------------
-# the reference's CPU path (oracle/_ref/ref_driver = the unmodified reference headers); used for cpu_baseline and
-# for --impl reference.  The only place bench.py touches oracle/.
+# the reference's CPU path (oracle/_ref/ref_driver = the unmodified reference headers); used for cpu_baseline, parity and
+# --impl reference.  The only place bench.py touches oracle/.
 def ref_tools():
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import oracle_lib as O
@@ -108,6 +117,16 @@ def ref_tools():
     if drv is None:
         raise RuntimeError("oracle/_ref/ref_driver missing or not runnable on this CPU (build it where /root/reference exists)")
     return O, drv
+
+
+def cpu_model():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
 
 
 def ref_recall_runs(O, files, settings, reps):
@@ -121,6 +140,16 @@ def ref_recall_runs(O, files, settings, reps):
                          beam=int(m.group(8)), limit=int(m.group(9)), dl=int(m.group(10))))
     assert len(rows) == len(settings) * reps, out[-2000:]
     return rows
+
+
+def ref_search_dump(O, files, s, tmp, nq):
+    """the reference's qsearchAll at one setting with its raw per-query outputs (ids, stats.visited, stats.distances)"""
+    kind, k, beam, cut, limit, dl = s
+    out = os.path.join(tmp, "refsearch")
+    O.ref_run(["search", "-data_type", "uint8", "-dist_func", "Euclidian", "-base", files["base"], "-graph", files["graph"],
+               "-query", files["query"], "-k", k, "-beam", beam, "-cut", repr(cut), "-limit", limit, "-degree_limit", dl, "-out", out])
+    return (np.fromfile(out + ".ids", dtype=np.uint32).reshape(nq, k), np.fromfile(out + ".visited", dtype=np.uint32),
+            np.fromfile(out + ".distances", dtype=np.uint32))
 
 
 def choose_setting(settings, evaluate):
@@ -142,7 +171,7 @@ def choose_setting(settings, evaluate):
 def gpu_prepared_inputs(args, tmp, local_rank=0):
     """points / graph / recall queries / ground truth for the reference arm at sizes where the reference's own CPU build
     and ground truth would take many minutes (10M points): made on the GPU, untimed, written in the reference's file
-    formats.  The graph is the same bytes the reference builds (tests/test_build_gpu.py, tests/test_dropin_gpu.py)."""
+    formats.  The graph is the same bytes the reference builds (tests/test_build_gpu.py, tests/test_fullsize_gpu.py)."""
     import torch
     import parlayann_b200 as P
     from parlayann_b200 import fileio
@@ -223,7 +252,7 @@ def run_reference(args, rank, world):
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic",
                 "config": workload_config(args, s, rec, cm),
-                "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": "reference",
+                "cpu_baseline": {"value": qps, "unit": "queries/s", "cores": cores, "kind": "reference", "cpu": cpu_model(), "binary": O.ref_driver_info(),
                                  "sample": f"{args.nq_recall} queries of the batch per step, {args.steps} steps, qsearchAll via checkRecall"},
                 "e2e": {"value": qps, "unit": "queries/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0, "inputs": inputs,
@@ -234,37 +263,108 @@ def run_reference(args, rank, world):
 
 
 def workload_config(args, s, rec, cm):
+    """identical in both arms: the recall is printed to 6 decimals (the arms compute it in different float widths)"""
     kind, k, beam, cut, limit, dl = s
     return {"workload": f"vamana_search_{args.n}x128_u8_{args.nq}q_per_gpu", "n": args.n, "dims": 128, "queries_per_gpu_per_step": args.nq,
-            "recall_batch": args.nq_recall, "graph": "Vamana R=64 L=128 alpha=1.2 1 pass", "k": k, "beam": beam, "cut": cut,
-            "visit_limit": limit if limit >= 0 else args.n, "degree_limit": dl if dl >= 0 else 64, "recall10": rec, "avg_cmps": cm,
+            "recall_batch": args.nq_recall, "graph": "Vamana R=64 L=128 alpha=1.2 1 pass", "k": k, "beam": beam, "cut": round(cut, 6),
+            "visit_limit": limit if limit >= 0 else args.n, "degree_limit": dl if dl >= 0 else 64, "recall10": round(float(rec), 6), "avg_cmps": int(cm),
             "parallelism": f"replicated index, queries sharded x{args.gpus}",
             "l2": f"index {(args.n * (128 + 260)) >> 20} MB and each step's gathers >> 126 MB L2; 256 MiB flush between steps as well"}
 
 
+def load_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return {}
+
+
 # ----------------------------------------------------------------------------------------------------------------
+class Dist:
+    """torch.distributed plumbing: barrier + max over ranks"""
+
+    def __init__(self, local_rank, world):
+        import torch
+        self.torch, self.world, self.d = torch, world, None
+        torch.cuda.set_device(local_rank)
+        if world > 1:
+            import torch.distributed as dist
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+            self.d = dist
+
+    def barrier(self):
+        self.torch.cuda.synchronize()
+        if self.d is not None:
+            self.d.barrier()
+        self.torch.cuda.synchronize()
+
+    def allmax(self, x):
+        t = self.torch.tensor([x], dtype=self.torch.float64, device="cuda")
+        if self.d is not None:
+            self.d.all_reduce(t, op=self.d.ReduceOp.MAX)
+        return float(t.item())
+
+    def close(self):
+        if self.d is not None:
+            self.d.barrier()
+            self.d.destroy_process_group()
+
+
+def groundtruth_c3(D, rank, local_rank, world, n=10_000_000, d=96, nq=10_000, k=100, reps=4):
+    """BASELINE configs[2]: brute-force ground truth k=100 over synthetic 10M x 96 float (Deep-shaped), base rows sharded over
+    the ranks, NCCL all-gather of the local top-k + K5 merge on every rank (compute_groundtruth.cpp:22-100)."""
+    import parlayann_b200 as P
+    from parlayann_b200.sharded import shard_bounds, groundtruth_sharded
+    lo, hi = shard_bounds(n, rank, world)
+    idx = P.GraphIndex(data_type="float", metric="Euclidian", max_degree=1, device=local_rank,
+                       synthetic=dict(n=hi - lo, d=d, kind="float_norm", seed=1234, stream=0, row0=lo))
+    idx.synthetic_queries(nq, kind="float_norm", seed=1234, stream=1)
+    times, local_ms = [], []
+    gi = gd = None
+    for _ in range(reps):
+        D.barrier()
+        t0 = time.perf_counter()
+        gi, gd = groundtruth_sharded(idx, None, k=k, base_offset=lo)
+        D.torch.cuda.synchronize()
+        times.append(D.allmax(time.perf_counter() - t0))
+        local_ms.append(D.allmax(idx.last_timing()[0]))
+    idx.close()
+    best = min(times[1:])
+    peaks = load_peaks()
+    bf16 = float(peaks.get("bf16_tflops", 1600.0))
+    tf32_peak = bf16 / 2.0     # kind::tf32 runs at half the bf16 rate (no measured tf32 number in MEASURED_PEAKS.json)
+    flops = 2.0 * nq * n * d
+    return {"what": f"ground truth {nq} x {n} x {d} f32, k={k}, base rows sharded x{world} (NCCL all-gather of the local top-k + K5 merge)",
+            "n_gpus": world, "seconds": best, "local_device_ms": min(local_ms[1:]), "all_seconds": times,
+            "roofline": {"bound": "tensor", "achieved": flops / best / 1e12 / world, "peak": tf32_peak, "unit": "TFLOP/s", "per": "GPU",
+                         "frac": flops / best / 1e12 / world / tf32_peak, "peak_source": "MEASURED_PEAKS.json bf16_tflops / 2 (tf32 pipe)",
+                         "algorithmic_flop": flops, "kernel": "pann_gt_mma_kernel<false> (tcgen05 kind::tf32) + pann_gt_shrink_kernel"},
+            "checksum": int(gi.astype(np.int64).sum() % 1000003), "dist_checksum": float(gd.astype(np.float64).sum())}
+
+
+def run_groundtruth_workload(args, rank, local_rank, world):
+    D = Dist(local_rank, world)
+    r = groundtruth_c3(D, rank, local_rank, world, reps=max(2, args.steps) + 1)
+    if rank == 0:
+        line = {"metric": "groundtruth_seconds", "value": r["seconds"], "unit": "s", "n_gpus": world, "steps": args.steps, "warmup": 1,
+                "ms_per_step": r["seconds"] * 1e3, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "tf32 filter + f32 exact",
+                "data": "synthetic", "config": {"workload": "groundtruth_10000000x96_f32_k100_10000q", "parallelism": f"base rows sharded x{world}"},
+                "roofline": r["roofline"], "detail": r}
+        print(json.dumps(line), flush=True)
+    D.close()
+
+
 def run_ours(args, rank, local_rank, world):
     import torch
     import parlayann_b200 as P
+    from parlayann_b200 import fileio
+    from parlayann_b200.sharded import search_sharded
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (parlayann_b200 has no CPU fallback)")
-    torch.cuda.set_device(local_rank)
-    dist = None
-    if world > 1:
-        import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-
-    def barrier():
-        torch.cuda.synchronize()
-        if dist is not None:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    def allmax(x):
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        if dist is not None:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
+    D = Dist(local_rank, world)
+    barrier, allmax = D.barrier, D.allmax
+    peaks = load_peaks()
+    peak = float(peaks.get("hbm_gbs", 6650.0))
 
     n, nq, nqr, R, L = args.n, args.nq, args.nq_recall, 64, 128
     # ---- setup (untimed): replicated index, points synthesised on the device, graph built on the device
@@ -276,10 +376,12 @@ def run_ours(args, rank, local_rank, world):
     build_s = time.time() - t0
     build_launches = idx.last_timing()[1]
     phases = idx.build_phase_seconds
+    bstats = idx.build_stats()
     # the recall batch (the reference's standard 10 000 queries, generator stream 1): exact ground truth from K4, then the
     # reference's sweep picks the QueryParams; every rank does the same, so all ranks time the same setting
     idx.synthetic_queries(nqr, kind="uint8", seed=1234, stream=1)
     rqueries = idx.download_queries()
+    idx.groundtruth_resident(k=100)          # warm-up (allocations)
     t0 = time.time()
     idx.groundtruth_resident(k=100)
     gt_ms = idx.last_timing()[0]
@@ -301,6 +403,8 @@ def run_ours(args, rank, local_rank, world):
         return cache[s]
     s, rec, cm = choose_setting(settings, ev)
     qp = qp_of(s)
+    idx.search_resident(**qp)
+    r_ids, _, r_vis, r_cmps = idx.fetch_results()     # the recall batch's answer at the chosen setting (parity below)
 
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 
@@ -308,21 +412,35 @@ def run_ours(args, rank, local_rank, world):
         flush.zero_()
         torch.cuda.synchronize()
 
+    def pinned_out(m):
+        return (torch.empty((m, K), dtype=torch.int32).pin_memory().numpy().view(np.uint32), torch.empty((m, K), dtype=torch.float32).pin_memory().numpy(),
+                torch.empty(m, dtype=torch.int32).pin_memory().numpy().view(np.uint32), torch.empty(m, dtype=torch.int32).pin_memory().numpy().view(np.uint32))
+
     # the same setting over the 10 000-query recall batch alone: about two waves of warps on one B200, so this is the
-    # latency-bound end of the curve (SURVEY.md §8d asks for both batch sizes)
+    # latency-bound end of the curve (SURVEY.md §8d asks for both batch sizes); device-resident, then end to end
     sm, sb = 0.0, 0
     for i in range(3 + 10):
         l2_flush(); idx.search_resident(**qp)
         if i >= 3:
             sm += idx.last_timing()[0]; sb += idx.last_bytes()
     small_ms = allmax(sm / 10)
+    rq_pin = torch.from_numpy(rqueries).pin_memory().numpy()
+    rout = pinned_out(nqr)
+    se = 0.0
+    for i in range(3 + 10):
+        l2_flush()
+        t0 = time.perf_counter()
+        idx.search(rq_pin, out=rout, **qp)
+        if i >= 3:
+            se += (time.perf_counter() - t0) * 1e3
+    small_e2e_ms = allmax(se / 10)
+    assert np.array_equal(rout[0], r_ids)
     setup_s = time.time() - t_setup
 
     # ---- the step batch: nq queries per GPU from the same generator (stream 1000 + rank)
     idx.synthetic_queries(nq, kind="uint8", seed=1234, stream=1000 + rank)
     hq = torch.from_numpy(idx.download_queries()).pin_memory()
-    out = (torch.empty((nq, K), dtype=torch.int32).pin_memory().numpy().view(np.uint32), torch.empty((nq, K), dtype=torch.float32).pin_memory().numpy(),
-           torch.empty(nq, dtype=torch.int32).pin_memory().numpy().view(np.uint32), torch.empty(nq, dtype=torch.int32).pin_memory().numpy().view(np.uint32))
+    out = pinned_out(nq)
     hq_np = hq.numpy()
 
     # ---- device-resident arm: W warm-up steps, then exactly K timed steps
@@ -360,19 +478,55 @@ def run_ours(args, rank, local_rank, world):
     e2e_ms_per_step = allmax(e2e_ms / args.steps)
     launches_all = int(allmax(launches))  # per rank (identical on every rank)
 
-    if rank == 0:
-        peaks = {}
+    # ---- the timed batch itself is checked: exact ground truth (K4) for its first rows, tie-aware recall of the timed answer
+    nsl = min(nqr, nq)
+    idx.upload_queries(hq_np[:nsl])
+    idx.groundtruth_resident(k=100)
+    tg_ids, tg_d = idx.fetch_groundtruth()
+    timed_recall = recall_with_ties(out[0][:nsl], tg_ids, tg_d, K)
+
+    # ---- strong scaling: ONE fixed batch for the whole job (the same rows on every rank: generator stream 999) cut over the
+    # ranks; every rank ends with the whole answer (NCCL all-gather from the device buffers).  Timed end to end, max over ranks.
+    strong = {}
+    for name, m, reps in (("batch_1M", nq, max(3, args.steps // 4)), ("batch_10K", nqr, 10)):
+        if name == "batch_1M":
+            idx.synthetic_queries(m, kind="uint8", seed=1234, stream=999)
+            sq = torch.from_numpy(idx.download_queries()).pin_memory().numpy()
+        else:
+            sq = rq_pin
+        for _ in range(2):
+            search_sharded(idx, sq, gather=True, **qp)
+        barrier()
+        tt = 0.0
+        for _ in range(reps):
+            l2_flush()
+            barrier()
+            t0 = time.perf_counter()
+            res = search_sharded(idx, sq, gather=True, **qp)
+            tt += allmax((time.perf_counter() - t0) * 1e3)
+        strong[name] = {"queries_total": int(m), "ms": tt / reps, "value": m / (tt / reps * 1e-3), "unit": "queries/s",
+                        "what": "fixed batch cut over the ranks, H2D + search + all-gather + D2H on every rank (search_sharded gather=True)"}
+        if name == "batch_10K":
+            strong[name]["ids_equal_single_gpu"] = bool(np.array_equal(res[0], r_ids))
+
+    # ---- ground truth at BASELINE configs[2] (10M x 96 f32, k=100), base rows sharded over the ranks
+    c3 = None
+    if not args.no_c3:
         try:
-            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-        except Exception:
-            pass
-        peak = float(peaks.get("hbm_gbs", 6650.0))
+            c3 = groundtruth_c3(D, rank, local_rank, world)
+        except Exception as e:   # reported, never fatal for the headline
+            c3 = {"failed": str(e)[:300]}
+
+    if rank == 0:
         achieved = (abytes / args.steps) / (dev_ms / args.steps * 1e-3) / 1e9
         traffic = None
         try:
             traffic = json.load(open(os.path.join(ROOT, "profiles", "roofline_traffic.json"))).get(f"k1s_dram_bytes_per_launch_{n}x{nq}")
         except Exception:
             pass
+        bf16 = float(peaks.get("bf16_tflops", 1600.0))
+        int8_peak = 2.0 * bf16   # kind::i8 runs at twice the bf16 rate; MEASURED_PEAKS.json holds no int8 number
+        gt_ops = 2.0 * nqr * n * 128
         line = {"metric": "QPS@recall10>=0.95", "value": world * nq / (ms_per_step * 1e-3), "unit": "queries/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": workload_config(args, s, rec, cm),
@@ -384,26 +538,46 @@ def run_ours(args, rank, local_rank, world):
                              "traffic": traffic, "peak_source": "MEASURED_PEAKS.json" if peaks else "fallback",
                              "algorithmic_bytes_per_launch": abytes / args.steps, "kernel": "pann_beam_search_small_kernel<u8,L2> (beam <= 32) / pann_beam_search_kernel<u8,L2>"},
                 "wall_ms_per_step_incl_l2_flush": wall_ms / args.steps,
+                "timed_batch_recall": {"queries": int(nsl), "recall10": round(timed_recall, 6),
+                                       "what": "first rows of the TIMED batch against exact ground truth from K4, tie-aware recall (check_nn_recall.h:83-109)"},
                 "recall_batch": {"queries_per_gpu": nqr, "value": world * nqr / (small_ms * 1e-3), "unit": "queries/s", "ms_per_step": small_ms,
                                  "roofline_frac": (sb / 10) / (sm / 10 * 1e-3) / 1e9 / peak,
+                                 "e2e": {"value": world * nqr / (small_e2e_ms * 1e-3), "unit": "queries/s", "ms_per_step": small_e2e_ms,
+                                         "h2d_bytes_per_step": int(rq_pin.nbytes), "d2h_bytes_per_step": int(sum(o.nbytes for o in rout))},
                                  "what": "the same search over the 10 000-query recall batch alone (about two waves of warps: latency-bound)"},
+                "strong": strong,
                 "build": {"seconds": build_s, "phase_seconds": {"beam_search+prune": phases[0], "bidirect": phases[1], "reverse_prune": phases[2]},
-                          "launches": build_launches, "what": f"pann_vamana_build {n}x128 u8 R=64 L=128 alpha=1.2, final sort incl."},
-                "groundtruth": {"seconds": gt_s, "device_ms": gt_ms, "what": f"{nqr} x {n} x 128 u8, k=100"},
+                          "launches": build_launches, "what": f"pann_vamana_build {n}x128 u8 R=64 L=128 alpha=1.2, final sort incl.",
+                          "roofline": {"bound": "hbm", "achieved": bstats["algorithmic_bytes"] / build_s / 1e9, "peak": peak, "unit": "GB/s",
+                                       "frac": bstats["algorithmic_bytes"] / build_s / 1e9 / peak, "algorithmic_bytes": bstats["algorithmic_bytes"],
+                                       "search_bytes": bstats["search_bytes"], "prune_bytes": bstats["prune_bytes"], "prune_calls": bstats["prune_calls"],
+                                       "pair_distances": bstats["pair_distances"],
+                                       "what": "SURVEY.md §8d B_ins summed on the device over all insertions / whole build wall time (final sort incl.)"}},
+                "groundtruth": {"seconds": gt_s, "device_ms": gt_ms, "what": f"{nqr} x {n} x 128 u8, k=100",
+                                "roofline": {"bound": "tensor", "achieved": gt_ops / (gt_ms * 1e-3) / 1e12, "peak": int8_peak, "unit": "TOP/s",
+                                             "frac": gt_ops / (gt_ms * 1e-3) / 1e12 / int8_peak, "peak_source": "2 x MEASURED_PEAKS.json bf16_tflops (int8 pipe)",
+                                             "algorithmic_op": gt_ops, "kernel": "pann_gt_mma_kernel<true> (tcgen05 kind::i8) + pann_gt_shrink_kernel"}},
+                "groundtruth_c3": c3,
                 "setup_seconds": setup_s}
         if world == 1 and not args.no_cpu_baseline:
             try:
-                line["cpu_baseline"] = cpu_baseline(args, idx, rqueries, gt_ids, gt_d, s)
+                cb, parity, gtb = cpu_baseline(args, idx, rqueries, gt_ids, gt_d, s, (r_ids, r_vis, r_cmps))
+                line["cpu_baseline"] = cb
+                line["parity"] = parity
+                line["groundtruth"]["cpu_baseline"] = gtb
             except Exception as e:  # the reference binary may be missing on a box that never saw /root/reference
                 line["cpu_baseline"] = {"value": None, "unit": "queries/s", "cores": os.cpu_count(), "kind": "reference", "sample": f"failed: {e}"}
+            try:
+                line["build"]["cpu_baseline"] = build_cpu_baseline(args, local_rank)
+            except Exception as e:
+                line["build"]["cpu_baseline"] = {"value": None, "sample": f"failed: {e}"}
         print(json.dumps(line), flush=True)
-    if dist is not None:
-        dist.barrier()
-        dist.destroy_process_group()
+    D.close()
 
 
-def cpu_baseline(args, idx, queries, gt_ids, gt_d, s):
-    """the unmodified reference's qsearchAll on the host cores, same points / graph / queries / QueryParams"""
+def cpu_baseline(args, idx, queries, gt_ids, gt_d, s, gpu_answer):
+    """the unmodified reference's qsearchAll on the host cores, same points / graph / queries / QueryParams: timed (checkRecall),
+    and its raw per-query output compared with the GPU's (parity).  Also the reference's compute_groundtruth on a query sample."""
     O, drv = ref_tools()
     from parlayann_b200 import fileio
     tmp = tempfile.mkdtemp(prefix="pann_cpu_")
@@ -413,9 +587,58 @@ def cpu_baseline(args, idx, queries, gt_ids, gt_d, s):
         fileio.write_graph(files["graph"], idx.graph()); fileio.write_ibin(files["gt"], gt_ids, gt_d)
         rows = ref_recall_runs(O, files, [s], 4)[1:]
         qps = float(np.mean([r["qps"] for r in rows]))
-        return {"value": qps, "unit": "queries/s", "cores": os.cpu_count(), "kind": "reference", "recall10": rows[0]["recall"],
-                "avg_cmps": rows[0]["avg_cmps"],
-                "sample": f"the {args.nq_recall}-query recall batch x 3 timed runs (1 warm-up) of the reference's checkRecall/qsearchAll on the GPU-built graph"}
+        cb = {"value": qps, "unit": "queries/s", "cores": os.cpu_count(), "kind": "reference", "cpu": cpu_model(), "binary": O.ref_driver_info(),
+              "recall10": rows[0]["recall"], "avg_cmps": rows[0]["avg_cmps"],
+              "sample": f"the {args.nq_recall}-query recall batch x 3 timed runs (1 warm-up) of the reference's checkRecall/qsearchAll on the GPU-built graph"}
+        ref_ids, ref_vis, ref_cmps = ref_search_dump(O, files, s, tmp, args.nq_recall)
+        g_ids, g_vis, g_cmps = gpu_answer
+        bad = (ref_ids != g_ids).any(axis=1)
+        parity = {"queries": int(args.nq_recall), "ids_equal": bool(not bad.any()), "visited_equal": bool(np.array_equal(ref_vis, g_vis)),
+                  "cmps_equal": bool(np.array_equal(ref_cmps, g_cmps)), "queries_with_different_ids": int(bad.sum()),
+                  "what": "ref_driver search (the reference's qsearchAll + stats) vs pann_search_resident, per query, same graph / points / QueryParams"}
+        # ground truth: the reference's compute_groundtruth on the first rows of the query file, against K4's rows
+        nsamp = min(1000, args.nq_recall) if args.n > 2000000 else args.nq_recall
+        qsub = os.path.join(tmp, "qsub")
+        fileio.write_bin(qsub, queries[:nsamp])
+        out = O.ref_run(["gt", "-data_type", "uint8", "-dist_func", "Euclidian", "-base", files["base"], "-query", qsub, "-k", 100, "-out", os.path.join(tmp, "g")])
+        ref_gt_s = float(re.search(r"REF_GT_SECONDS (\S+)", out).group(1))
+        ri, rd = fileio.read_ibin(os.path.join(tmp, "g.ibin"))
+        gtb = {"value": ref_gt_s, "unit": "s", "cores": os.cpu_count(), "kind": "reference", "queries": int(nsamp),
+               "distance_evals_per_s": nsamp * args.n / ref_gt_s, "dists_equal_gpu": bool(np.array_equal(rd, gt_d[:nsamp])),
+               "sample": f"compute_groundtruth over {nsamp} of the {args.nq_recall} queries x {args.n} base rows, k=100 (scale linearly in queries)"}
+        return cb, parity, gtb
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
+
+
+def build_cpu_baseline(args, local_rank):
+    """the reference's knn_index::build_index (timed as vamana/neighbors.h:59-61 times it) at the largest n that fits about a
+    CPU-minute, next to pann_vamana_build at the SAME n — and the two graph files compared byte for byte"""
+    O, drv = ref_tools()
+    import parlayann_b200 as P
+    from parlayann_b200 import fileio
+    nb = min(args.n, args.n_build_cpu)
+    tmp = tempfile.mkdtemp(prefix="pann_bld_")
+    try:
+        idx = P.GraphIndex(data_type="uint8", metric="Euclidian", max_degree=64, device=local_rank,
+                           synthetic=dict(n=nb, d=128, kind="uint8", seed=1234, stream=0, r=24, nc=256))
+        idx.build(R=64, L=128, alpha=1.2, num_passes=1, sort_neighbors=True)   # warm-up
+        t0 = time.time()
+        idx.build(R=64, L=128, alpha=1.2, num_passes=1, sort_neighbors=True)
+        gpu_s = time.time() - t0
+        bs = idx.build_stats()
+        base = os.path.join(tmp, "base")
+        fileio.write_bin(base, idx.points())
+        g_gpu = idx.graph()
+        idx.close()
+        out = O.ref_run(["build", "-data_type", "uint8", "-dist_func", "Euclidian", "-base", base, "-R", 64, "-L", 128, "-alpha", 1.2, "-out", os.path.join(tmp, "b")])
+        ref_s = float(re.search(r"REF_BUILD_SECONDS (\S+)", out).group(1))
+        g_ref = fileio.read_graph(os.path.join(tmp, "b.graph"))
+        m = np.arange(64)[None, :] < g_ref[:, 0][:, None]
+        same = bool(np.array_equal(g_ref[:, 0], g_gpu[:, 0]) and np.array_equal(g_ref[:, 1:][m], g_gpu[:, 1:][m]))
+        return {"value": ref_s, "unit": "s", "cores": os.cpu_count(), "kind": "reference", "cpu": cpu_model(), "binary": O.ref_driver_info(), "n": int(nb),
+                "gpu_seconds_same_n": gpu_s, "gpu_algorithmic_bytes_same_n": bs["algorithmic_bytes"], "graph_identical_to_reference": same,
+                "sample": f"knn_index::build_index over the first {nb} points of the same set (R=64 L=128 alpha=1.2, 1 pass, final sort), 'Graph built in' time"}
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
 
@@ -426,11 +649,14 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="search", choices=["search", "groundtruth"])
     ap.add_argument("--n", type=int, default=10000000, help="base points (BASELINE.json metric: 10M x 128 uint8; 1000000 = configs[1])")
     ap.add_argument("--nq", type=int, default=1000000, help="queries per GPU per step")
     ap.add_argument("--nq-recall", dest="nq_recall", type=int, default=10000, help="recall / sweep batch (the reference's standard query set size)")
+    ap.add_argument("--n-build-cpu", dest="n_build_cpu", type=int, default=1000000, help="points of the reference's CPU build baseline")
     ap.add_argument("--profile", action="store_true", help="cudaProfilerStart/Stop around the timed device-resident steps")
     ap.add_argument("--no-cpu-baseline", dest="no_cpu_baseline", action="store_true")
+    ap.add_argument("--no-c3", dest="no_c3", action="store_true", help="skip the configs[2] ground-truth measurement")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -438,6 +664,8 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.impl == "reference":
         run_reference(args, rank, world)
+    elif args.workload == "groundtruth":
+        run_groundtruth_workload(args, rank, local_rank, world)
     else:
         run_ours(args, rank, local_rank, world)
 

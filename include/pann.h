@@ -100,6 +100,11 @@ int pann_queries_download(pann_index* idx, void* host_out, uint64_t out_stride_b
 int pann_search_resident(pann_index* idx, const uint32_t* starts, uint32_t nstarts, const pann_query_params* qp);
 int pann_search_fetch(pann_index* idx, uint32_t* out_ids, float* out_dists, uint32_t* out_visited, uint32_t* out_cmps);
 
+/* device pointers to the results of the last pann_search_resident (valid until the next search on this index): the
+ * multi-GPU path all-gathers them over NCCL/NVLink without a trip through the host (queries sharded) */
+int pann_search_device_result(pann_index* idx, const uint32_t** d_ids, const float** d_dists, const uint32_t** d_visited,
+                              const uint32_t** d_cmps, uint64_t* nq, uint32_t* k);
+
 /* beam_search (beamSearch.h:217-223) with both result lists, for parity tests and the build:
  * per query the whole frontier (<= beam entries) and the whole visited list (sorted by (dist,id)).
  * self_ids (may be NULL): query i IS base row self_ids[i] (beam_search_rerank__ in the build,
@@ -134,6 +139,13 @@ int pann_search_rerank_batch(pann_index* q_idx, pann_index* base_idx, const void
 int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double alpha, int num_passes, int sort_neighbors,
                       uint32_t* out_visited, uint32_t* out_cmps, double phase_seconds[3]);
 
+/* accounting of the last pann_vamana_build, counted on the device: algorithmic_bytes = B_ins summed over
+ * all insertions = bytes of the build-mode beam searches (as pann_index_last_bytes counts them) + per robustPrune call
+ * (vamana/index.h:63-120) C * row bytes + 4 (R+1) with C the candidates after unique + 2 * 4 (R+1) per inserted point;
+ * pair_distances = the reference's own distance_comps of those calls */
+int pann_index_build_stats(pann_index* idx, uint64_t* algorithmic_bytes, uint64_t* search_bytes, uint64_t* prune_bytes,
+                           uint64_t* prune_calls, uint64_t* pair_distances);
+
 /* parlay::random_permutation<int>(n) with the default seed (parlay/random.h:154-159) — the insertion order. */
 int pann_random_permutation(int64_t n, int32_t* out);
 /* batch boundaries of batch_insert (vamana/index.h:206-209, :223-234); returns the number of batches */
@@ -147,6 +159,9 @@ int pann_groundtruth(pann_index* idx, const void* host_queries, uint64_t nq, uin
 /* same on the resident query set; results stay on the device (pann_groundtruth_fetch) */
 int pann_groundtruth_resident(pann_index* idx, uint32_t k, int64_t id_offset);
 int pann_groundtruth_fetch(pann_index* idx, int32_t* out_ids, float* out_dists);
+/* which path the last ground-truth call took: launches of the tcgen05 kernel (0 = CUDA-core path only) and, cumulative over
+ * the index's life, chunks retaken on the CUDA cores after a candidate-list overflow */
+int pann_index_groundtruth_stats(pann_index* idx, int* mma_launches, int* fallback_chunks);
 /* k-way merge of per-shard results (each [nq, k], sorted) into the global top-k under the (dist,id) order */
 int pann_groundtruth_merge(int device, uint32_t nshards, uint64_t nq, uint32_t k, const int32_t* ids, const float* dists,
                            int32_t* out_ids, float* out_dists);

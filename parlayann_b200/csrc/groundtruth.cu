@@ -299,6 +299,7 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
   int* h_flag = nullptr;
   if (use_mma && pann_pinned(idx, 64, (void**)&h_flag)) return fail();
   const uint64_t tot = nq * k;
+  idx->gt_mma_launches = 0;
   idx->last_launches = 0;
   cudaEventRecord(idx->ev0, s);
   pann_gt_init_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(state.as<u64>(), tot);
@@ -357,6 +358,7 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
       A.subcap = (uint32_t)(GTM_CAND_CAP / ((GTM_EPI_WARPS / 4) * S));
       if (isint) pann_gt_mma_kernel<true><<<dim3(nqb, (unsigned)S), GTM_THREADS, smem, s>>>(tmQ, tmB, A, idesc);
       else pann_gt_mma_kernel<false><<<dim3(nqb, (unsigned)S), GTM_THREADS, smem, s>>>(tmQ, tmB, A, idesc);
+      idx->gt_mma_launches++;
 #define GT_SHRINK(DT, M) gt_launch_shrink<DT, M>(idx, s, d_q, (uint32_t)nq, k, state.as<u64>(), cand_ids.as<uint32_t>(), cand_cnt.as<uint32_t>(), (uint32_t)((GTM_EPI_WARPS / 4) * S), A.subcap, keys_cap, qnorm.p, bnmax, thr.p, overflow)
       // small tier first (8 KB of key slots, many CTAs per SM); queries with more keys raise bit 1 and get the large tier
       uint32_t keys_cap = (k + (lo == 0 ? seed : 0) <= GTS_KEYS_SMALL / 2) ? GTS_KEYS_SMALL : GTS_KEYS;
@@ -470,3 +472,10 @@ extern "C" int pann_groundtruth_merge_device(int device, uint32_t nshards, uint6
   return 0;
 }
 
+
+extern "C" int pann_index_groundtruth_stats(pann_index* idx, int* mma_launches, int* fallback_chunks) {
+  if (!idx) PANN_FAIL("pann_index_groundtruth_stats: null index");
+  if (mma_launches) *mma_launches = idx->gt_mma_launches;
+  if (fallback_chunks) *fallback_chunks = idx->gt_fallback_chunks;
+  return 0;
+}

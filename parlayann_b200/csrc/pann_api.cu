@@ -161,6 +161,16 @@ extern "C" int pann_index_last_bytes(pann_index* idx, uint64_t* algorithmic_byte
   *algorithmic_bytes = idx->last_bytes;
   return 0;
 }
+extern "C" int pann_index_build_stats(pann_index* idx, uint64_t* algorithmic_bytes, uint64_t* search_bytes, uint64_t* prune_bytes,
+                                      uint64_t* prune_calls, uint64_t* pair_distances) {
+  if (!idx) PANN_FAIL("pann_index_build_stats: null index");
+  if (algorithmic_bytes) *algorithmic_bytes = idx->build_bytes;
+  if (search_bytes) *search_bytes = idx->build_search_bytes;
+  if (prune_bytes) *prune_bytes = idx->build_prune_bytes;
+  if (prune_calls) *prune_calls = idx->build_prune_calls;
+  if (pair_distances) *pair_distances = idx->build_pair_dists;
+  return 0;
+}
 extern "C" int pann_index_last_timing(pann_index* idx, float* kernel_ms, int* launches) {
   if (!idx) PANN_FAIL("pann_index_last_timing: null index");
   if (kernel_ms) *kernel_ms = idx->last_ms;
@@ -584,6 +594,21 @@ extern "C" int pann_search_fetch(pann_index* idx, uint32_t* out_ids, float* out_
   if (!idx) PANN_FAIL("pann_search_fetch: null index");
   PANN_CUDA(cudaSetDevice(idx->device));
   return fetch_results(idx, out_ids, out_dists, out_visited, out_cmps);
+}
+
+extern "C" int pann_search_device_result(pann_index* idx, const uint32_t** d_ids, const float** d_dists, const uint32_t** d_visited,
+                                         const uint32_t** d_cmps, uint64_t* nq, uint32_t* k) {
+  if (!idx) PANN_FAIL("pann_search_device_result: null index");
+  if (!idx->results.p || idx->res_nq == 0) PANN_FAIL("pann_search_device_result: no search results on the device");
+  ResLayout L = res_layout(idx->res_nq, idx->res_k);
+  const uint8_t* r = idx->results.as<uint8_t>();
+  if (d_ids) *d_ids = (const uint32_t*)(r + L.ids);
+  if (d_dists) *d_dists = (const float*)(r + L.dists);
+  if (d_visited) *d_visited = (const uint32_t*)(r + L.visited);
+  if (d_cmps) *d_cmps = (const uint32_t*)(r + L.cmps);
+  if (nq) *nq = idx->res_nq;
+  if (k) *k = idx->res_k;
+  return 0;
 }
 
 extern "C" int pann_search_batch(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes,

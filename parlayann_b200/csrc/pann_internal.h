@@ -44,6 +44,8 @@ struct pann_index {
   float last_ms = 0.f;
   DevBuf bytes_ctr; uint64_t last_bytes = 0;  // algorithmic bytes of the last search (device counter + host copy)
   int last_launches = 0;
+  // accounting of the last pann_vamana_build (SURVEY.md §8d B_ins), see pann_index_build_stats
+  uint64_t build_bytes = 0, build_search_bytes = 0, build_prune_bytes = 0, build_prune_calls = 0, build_pair_dists = 0;
   // resident query set and results
   DevBuf queries;  uint64_t nq = 0;
   DevBuf results;  // packed: ids[nq*k] dists[nq*k] visited[nq] cmps[nq] status[nq]
@@ -54,6 +56,7 @@ struct pann_index {
   // ground truth results (resident)
   DevBuf gt_ids, gt_dists; uint64_t gt_nq = 0; uint32_t gt_k = 0;
   DevBuf gt_scratch[8];        // ground-truth work buffers, kept between calls (cudaMalloc/cudaFree of ~200 MB cost 5 ms per call)
+  int gt_mma_launches = 0;     // pann_gt_mma_kernel launches of the last ground-truth call
   int gt_fallback_chunks = 0;  // MMA chunks retaken on the CUDA cores (candidate-list overflow), cumulative
 };
 

@@ -65,14 +65,18 @@ static const void* edge_kernel(int dtype, int metric, int qr) {
 }
 static inline uint32_t al16(size_t x) { return (uint32_t)((x + 15) / 16 * 16); }
 
-// launches K3 over A's tasks (shared-memory variant), then the global-scratch variant over whatever it deferred
-static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevBuf& big, DevBuf& gscratch) {
+// launches K3 over A's tasks (shared-memory variant), then the global-scratch variant over whatever it deferred.  No
+// host synchronisation: the second launch reads its task count on the device (it is usually zero and the CTAs leave at
+// once); its slab has a fixed capacity per warp, and a list beyond even that raises gs_overflow, read once after the build.
+#define PANN_PRUNE_SLAB_CAP_DEFAULT 8192u
+static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevBuf& big, DevBuf& gscratch, int* gs_overflow) {
   const PannRowGeom& g = idx->geom;
   const int qrT = pann_qr_of(g);
   if (ntasks_bound == 0) return 0;
   if (big.reserve(8 + 4ull * ntasks_bound)) return 1;
   A.big_count = big.as<uint32_t>();
   A.big_list = big.as<uint32_t>() + 2;
+  A.gs_overflow = gs_overflow;
   PANN_CUDA(cudaMemsetAsync(A.big_count, 0, 8, idx->stream));
   const char* rc_env = getenv("PANN_PRUNE_ROW_CACHE");  // 0 / 1 force it off / on
   const bool rc_on = g.stride <= 256 && (rc_env ? rc_env[0] == '1' : (idx->n * (uint64_t)g.stride > (256ull << 20)));
@@ -81,7 +85,7 @@ static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, De
   // uncached scan or the slab launch)
   const bool small_lists = rc_on && A.mode == 1 && A.R <= 64;
   A.cap = small_lists ? 128 : 512;
-  if (small_lists) if (const char* e = getenv("PANN_PRUNE_CAP")) A.cap = (uint32_t)atoi(e);
+  if (const char* e = getenv("PANN_PRUNE_CAP")) A.cap = std::max<uint32_t>(8u, std::min<uint32_t>(A.cap, (uint32_t)atoi(e)));   // tests: force the slab launch
   A.off_b = al16((size_t)A.cap * 8);
   A.off_q = 2 * A.off_b;
   A.warp_bytes = A.off_q + g.stride;
@@ -117,14 +121,13 @@ static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, De
     PANN_CUDA(cudaLaunchKernel(fn, dim3(grid), dim3(wpc * 32), args, cta_bytes, idx->stream));
     idx->last_launches++;
   }
-  uint32_t bc[2] = {0, 0};
-  PANN_CUDA(cudaMemcpyAsync(bc, A.big_count, 8, cudaMemcpyDeviceToHost, idx->stream));
-  PANN_CUDA(cudaStreamSynchronize(idx->stream));
-  if (getenv("PANN_BUILD_VERBOSE")) fprintf(stderr, "    prune mode %d: %u tasks deferred to the long-list launch, longest %u\n", A.mode, bc[0], bc[1]);
-  if (bc[0] == 0) return 0;
-  // rare: candidate lists beyond the shared-memory capacity — same kernel, lists in a global scratch slab
-  A.cap = 1024; while (A.cap < bc[1]) A.cap <<= 1;   // power of two: the long-list path sorts bitonically in place
-  A.task_map = A.big_list; A.ntask_map = bc[0];
+  // candidate lists beyond the shared-memory capacity (a hub that collected ~900 reverse edges in one batch) — same
+  // kernel, lists in a global scratch slab, bitonic sort
+  uint32_t slab_cap = PANN_PRUNE_SLAB_CAP_DEFAULT;
+  if (const char* e = getenv("PANN_PRUNE_SLAB_CAP")) slab_cap = std::max<uint32_t>(64u, (uint32_t)atoi(e));
+  { uint32_t c = 64; while (c < slab_cap) c <<= 1; slab_cap = c; }   // power of two: the long-list path sorts bitonically in place
+  A.cap = slab_cap;
+  A.task_map = A.big_list; A.ntask_map = 0;
   A.off_b = 0; A.off_q = 0;
   A.rc_rows = 0;
   A.warp_bytes = g.stride;
@@ -133,7 +136,7 @@ static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, De
   const void* fn = prune_kernel(idx->dtype, idx->metric, qrT, true);
   size_t cta_bytes = (size_t)A.warp_bytes * PANN_PRUNE_WARPS;
   PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
-  int grid = (int)std::min<uint32_t>((bc[0] + PANN_PRUNE_WARPS - 1) / PANN_PRUNE_WARPS, 4u * idx->sms);
+  int grid = (int)std::max<uint32_t>(1u, std::min<uint32_t>((ntasks_bound + PANN_PRUNE_WARPS - 1) / PANN_PRUNE_WARPS, (uint32_t)idx->sms));
   if (gscratch.reserve((size_t)grid * PANN_PRUNE_WARPS * 2 * A.cap * 8)) return 1;
   A.g_scratch = gscratch.as<u64>();
   void* args[] = {(void*)&A};
@@ -165,9 +168,9 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
   uint64_t max_bs = 0;
   for (int64_t b = 0; b < nb; b++) max_bs = std::max<uint64_t>(max_bs, (uint64_t)(bhi[b] - blo[b]));
 
-  DevBuf d_perm, d_vis_ids, d_vis_dists, d_cnt, d_new_out, d_keys, d_keys2, d_gstart, d_sort_tmp, d_big, d_gscr, d_stats;
+  DevBuf d_perm, d_vis_ids, d_vis_dists, d_cnt, d_new_out, d_keys, d_keys2, d_gstart, d_sort_tmp, d_big, d_gscr, d_stats, d_acct;
   auto release_all = [&]() {
-    d_perm.release(); d_vis_ids.release(); d_vis_dists.release(); d_cnt.release(); d_new_out.release(); d_keys.release();
+    d_acct.release(); d_perm.release(); d_vis_ids.release(); d_vis_dists.release(); d_cnt.release(); d_new_out.release(); d_keys.release();
     d_keys2.release(); d_gstart.release(); d_sort_tmp.release(); d_big.release(); d_gscr.release(); d_stats.release();
   };
   struct Guard { decltype(release_all)& f; ~Guard() { f(); } } guard{release_all};
@@ -192,8 +195,16 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
   cub::DeviceRadixSort::SortKeys(nullptr, sort_tmp_bytes, d_keys.as<u64>(), d_keys2.as<u64>(), (int64_t)(max_bs * R), 0, key_bits, s);
   if (d_sort_tmp.reserve(sort_tmp_bytes + 16)) return 1;
 
-  cudaEvent_t ev[4];
-  for (auto& e : ev) PANN_CUDA(cudaEventCreate(&e));
+  // accounting: [0..2] robustPrune bytes / calls / pair distances (vamana_prune.cuh), [3] = slab-overflow flag (int)
+  if (d_acct.reserve(32)) return 1;
+  PANN_CUDA(cudaMemsetAsync(d_acct.p, 0, 32, s));
+  int* gs_overflow = reinterpret_cast<int*>(d_acct.as<u64>() + 3);
+  uint64_t search_bytes = 0;
+  // phase timers: four events per batch, read once after the last batch (no host synchronisation inside the loop
+  // beyond the one the search needs for its retry flag)
+  std::vector<cudaEvent_t> evs((size_t)nb * num_passes * 4);
+  for (auto& e : evs) PANN_CUDA(cudaEventCreate(&e));
+  size_t evi = 0;
   double ph[3] = {0, 0, 0};
   const uint32_t start = 0;  // knn_index::set_start (index.h:148)
   pann_query_params qp; qp.k = 0; qp.beam = L; qp.cut = 0.0; qp.limit = (int64_t)n; qp.degree_limit = md;  // index.h:250
@@ -208,6 +219,7 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
       int* c_status = (int*)(c_cmps + max_bs);
       uint32_t* c_newdeg = (uint32_t*)(c_status + max_bs);
       uint32_t* c_ngroups = c_newdeg + max_bs;
+      cudaEvent_t* ev = &evs[evi]; evi += 4;
       cudaEventRecord(ev[0], s);
       // ---- phase 1: build-mode beam search from the start point, then robustPrune of the visited list
       for (;;) {
@@ -226,6 +238,7 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
         break;
       }
       if (rc) break;
+      search_bytes += idx->last_bytes;
       PruneArgs A;
       memset(&A, 0, sizeof(A));
       A.points = idx->points; A.stride = idx->geom.stride; A.nch = idx->geom.nch;
@@ -234,7 +247,8 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
       A.mode = 0; A.ntasks = bs;
       A.vis_ids = d_vis_ids.as<uint32_t>(); A.vis_dists = d_vis_dists.as<float>(); A.nvis = c_nvis; A.search_cmps = c_cmps; A.vout = vout;
       A.new_out = d_new_out.as<uint32_t>(); A.new_deg = c_newdeg;
-      if (launch_prune(idx, A, bs, d_big, d_gscr)) { rc = 1; break; }
+      A.acct = d_acct.as<u64>(); A.rowbytes = idx->dims * idx->geom.elt;
+      if (launch_prune(idx, A, bs, d_big, d_gscr, gs_overflow)) { rc = 1; break; }
       // ---- phase 2: rows of the inserted points + reverse-edge keys
       const uint64_t nk = (uint64_t)bs * R;
       pann_write_rows_kernel<<<(unsigned)((nk + 255) / 256), 256, 0, s>>>(idx->graph, md, R, n, perm_lo, d_new_out.as<uint32_t>(),
@@ -254,17 +268,31 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
       // ---- phase 3b: per target, append or prune (index.h:289-300)
       A.mode = 1; A.ntasks = (uint32_t)nk;
       A.sorted = d_keys2.as<u64>(); A.nsorted = (uint32_t)nk; A.gstart = d_gstart.as<uint32_t>(); A.ngroups = c_ngroups;
-      if (launch_prune(idx, A, (uint32_t)std::min<uint64_t>(nk, n), d_big, d_gscr)) { rc = 1; break; }
+      if (launch_prune(idx, A, (uint32_t)std::min<uint64_t>(nk, n), d_big, d_gscr, gs_overflow)) { rc = 1; break; }
       cudaEventRecord(ev[3], s);
-      PANN_CUDA(cudaEventSynchronize(ev[3]));
-      for (int i = 0; i < 3; i++) { float ms = 0; cudaEventElapsedTime(&ms, ev[i], ev[i + 1]); ph[i] += ms * 1e-3; }
-      if (getenv("PANN_BUILD_VERBOSE")) {
-        float m0, m1, m2; cudaEventElapsedTime(&m0, ev[0], ev[1]); cudaEventElapsedTime(&m1, ev[1], ev[2]); cudaEventElapsedTime(&m2, ev[2], ev[3]);
-        fprintf(stderr, "  batch %lld size %u: search+prune %.2f ms, group %.2f ms, reverse %.2f ms\n", (long long)b, bs, m0, m1, m2);
-      }
     }
   }
-  for (auto& e : ev) cudaEventDestroy(e);
+  if (!rc) {
+    uint64_t acct[4] = {0, 0, 0, 0};
+    if (cudaMemcpyAsync(acct, d_acct.p, 32, cudaMemcpyDeviceToHost, s) != cudaSuccess || cudaStreamSynchronize(s) != cudaSuccess) {
+      pann_set_error(std::string("pann_vamana_build: ") + cudaGetErrorString(cudaGetLastError())); rc = 1;
+    } else if ((int)acct[3] != 0) {
+      pann_set_error("pann_vamana_build: a robustPrune candidate list of " + std::to_string((int)acct[3]) +
+                     " entries exceeds the long-list slab (set PANN_PRUNE_SLAB_CAP to a larger power of two)");
+      rc = 1;
+    } else {
+      // SURVEY.md §8d B_ins: build search + robustPrune candidate rows + the row written and the reverse-edge row touched
+      idx->build_search_bytes = search_bytes;
+      idx->build_prune_bytes = acct[0]; idx->build_prune_calls = acct[1]; idx->build_pair_dists = acct[2];
+      idx->build_bytes = search_bytes + acct[0] + (uint64_t)num_passes * n * 2ull * 4ull * (md + 1);
+    }
+    for (size_t b = 0; b + 3 < evi; b += 4) {
+      float m[3] = {0, 0, 0};
+      for (int i = 0; i < 3; i++) { cudaEventElapsedTime(&m[i], evs[b + i], evs[b + i + 1]); ph[i] += m[i] * 1e-3; }
+      if (getenv("PANN_BUILD_VERBOSE")) fprintf(stderr, "  batch %zu: search+prune %.2f ms, group %.2f ms, reverse %.2f ms\n", b / 4, m[0], m[1], m[2]);
+    }
+  }
+  for (auto& e : evs) cudaEventDestroy(e);
   if (rc) return 1;
   PANN_CUDA(cudaGetLastError());
 

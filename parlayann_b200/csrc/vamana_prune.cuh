@@ -34,8 +34,12 @@ struct PruneArgs {
   uint32_t* st_visited; uint32_t* st_cmps;
   // tasks whose candidate list exceeds `cap` are deferred to the global-scratch launch
   uint32_t cap; uint32_t* big_list; uint32_t* big_count;  // big_count[0] = #deferred, [1] = their largest candidate count
-  const uint32_t* task_map; uint32_t ntask_map;  // GS launch: the deferred tasks
+  const uint32_t* task_map; uint32_t ntask_map;  // GS launch: the deferred tasks; their number is read on the DEVICE from big_count[0] (ntask_map is unused)
   u64* g_scratch;                                 // GS launch: per warp 2 x cap keys
+  int* gs_overflow;                               // GS launch: set when a list exceeds even the slab capacity (checked once, after the build)
+  // accounting for the build's roofline (SURVEY.md §8d B_ins): [0] += C * row bytes + 4 (R+1) per robustPrune call (C = candidates
+  // after unique), [1] += 1 per call, [2] += pair distances of the call (the reference's own count); may be null
+  u64* acct; uint32_t rowbytes;
   uint32_t off_b, off_q, off_stage, warp_bytes;   // off_stage: float rows staged for the one-lane sums (pann_staged_distance)
   // row cache (shared memory): the rows of up to rc_rows candidates, rc_pitch bytes apart, and their slot numbers
   uint32_t rc_rows, rc_pitch, off_rc, off_pos;
@@ -61,7 +65,7 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
   uint4* qsm = reinterpret_cast<uint4*>(ws + A.off_q);
   uint4* stage = pann_staged_rows<DT, QR>() ? reinterpret_cast<uint4*>(ws + A.off_stage) : nullptr;
   uint32_t* cid = reinterpret_cast<uint32_t*>(bufB);  // candidate ids before they get their distances
-  const uint32_t ntasks = GS ? A.ntask_map : (A.mode == 1 ? *A.ngroups : A.ntasks);
+  const uint32_t ntasks = GS ? *A.big_count : (A.mode == 1 ? *A.ngroups : A.ntasks);
 
   for (long long tl = wglobal; tl < (long long)ntasks; tl += wstride) {
     const uint32_t task = GS ? A.task_map[tl] : (uint32_t)tl;
@@ -81,8 +85,12 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
     uint32_t* grow = A.graph + (u64)p * (A.maxdeg + 1);
     const uint32_t deg = grow[0];
     const uint32_t C0 = nc + deg;
-    if (C0 > A.cap) {  // defer to the global-scratch launch (only GS == false can get here: its cap is exact)
-      if (lane == 0) { A.big_list[atomicAdd(A.big_count, 1u)] = task; atomicMax(A.big_count + 1, C0); }
+    if (C0 > A.cap) {
+      if constexpr (GS) {  // beyond the slab as well: reported, the host fails the build (PANN_PRUNE_SLAB_CAP raises the capacity)
+        if (lane == 0) atomicExch(A.gs_overflow, (int)C0);
+      } else {             // defer to the global-scratch launch
+        if (lane == 0) { A.big_list[atomicAdd(A.big_count, 1u)] = task; atomicMax(A.big_count + 1, C0); }
+      }
       continue;
     }
     // ---- reverse edges that fit: new ones first, then the old ones not among them (index.h:291-294, :140-146)
@@ -272,6 +280,11 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
     }
     }
     if (lane == 0) {
+      if (A.acct) {
+        atomicAdd(A.acct, (u64)C * A.rowbytes + 4ull * (A.R + 1));
+        atomicAdd(A.acct + 1, 1ull);
+        atomicAdd(A.acct + 2, (u64)comps);
+      }
       if (A.mode == 0) {
         A.new_deg[task] = m;
         if (A.st_cmps) A.st_cmps[p] += A.search_cmps[task] + comps;

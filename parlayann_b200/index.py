@@ -154,6 +154,12 @@ class GraphIndex:
         check(_lib.lib().pann_index_last_timing(self._h, C.byref(ms), C.byref(nl)))
         return ms.value, nl.value
 
+    def build_stats(self):
+        """accounting of the last build (pann_index_build_stats): dict of algorithmic bytes and call counts"""
+        v = [C.c_uint64(0) for _ in range(5)]
+        check(_lib.lib().pann_index_build_stats(self._h, *[C.byref(x) for x in v]))
+        return dict(zip(("algorithmic_bytes", "search_bytes", "prune_bytes", "prune_calls", "pair_distances"), (x.value for x in v)))
+
     def last_bytes(self):
         b = C.c_uint64(0)
         check(_lib.lib().pann_index_last_bytes(self._h, C.byref(b)))
@@ -267,6 +273,12 @@ class GraphIndex:
     def groundtruth_resident(self, k=100, id_offset=0):
         check(_lib.lib().pann_groundtruth_resident(self._h, C.c_uint32(k), C.c_int64(id_offset)))
         self._gt_k = k
+
+    def groundtruth_stats(self):
+        """(launches of the tcgen05 kernel in the last ground-truth call, cumulative chunks retaken on the CUDA cores)"""
+        a, b = C.c_int(0), C.c_int(0)
+        check(_lib.lib().pann_index_groundtruth_stats(self._h, C.byref(a), C.byref(b)))
+        return a.value, b.value
 
     def fetch_groundtruth(self):
         ids = np.empty((self.nq, self._gt_k), np.int32)

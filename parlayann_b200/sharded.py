@@ -69,11 +69,17 @@ def all_gather_rows(local, counts, group=None):
 
 def search_sharded(index, queries, gather=True, group=None, **qp):
     """qsearchAll over a query batch cut across the ranks of `group`.  `index` is this rank's replica
-    (GraphIndex).  Returns (ids, dists, visited, cmps) for all queries when gather=True, else this rank's slice."""
+    (GraphIndex).  Returns (ids, dists, visited, cmps) for all queries when gather=True, else this rank's slice.
+
+    With an NCCL group the slice's results never leave the device before the exchange: queries H2D, search, one
+    all-gather per result array straight from the library's device buffers (pann_search_device_result), one D2H of the
+    assembled answer into pinned buffers kept on the index."""
     rank, world = _world(group)
     nq = queries.shape[0]
     lo, hi = shard_bounds(nq, rank, world)
     k = int(qp.get("k", 10))
+    if gather and world > 1 and _dist().get_backend(group) == "nccl":
+        return _search_sharded_nccl(index, queries, lo, hi, k, group, qp)
     if hi > lo:
         ids, dists, vis, cmps = index.search(queries[lo:hi], **qp)
     else:  # more ranks than queries
@@ -83,6 +89,51 @@ def search_sharded(index, queries, gather=True, group=None, **qp):
         return ids, dists, vis, cmps
     counts = [shard_bounds(nq, r, world)[1] - shard_bounds(nq, r, world)[0] for r in range(world)]
     return tuple(all_gather_rows(a, counts, group) for a in (ids, dists, vis, cmps))
+
+
+def _search_sharded_nccl(index, queries, lo, hi, k, group, qp):
+    import torch
+    dist = _dist()
+    rank, world = _world(group)
+    nq = queries.shape[0]
+    counts = [shard_bounds(nq, r, world)[1] - shard_bounds(nq, r, world)[0] for r in range(world)]
+    m = max(counts)
+    dev = torch.device("cuda", torch.cuda.current_device())
+    cache = getattr(index, "_shard_bufs", None)
+    if cache is None or cache["key"] != (world, m, k):
+        cache = {"key": (world, m, k),
+                 "g": [torch.empty((world, m, k), dtype=torch.int32, device=dev), torch.empty((world, m, k), dtype=torch.float32, device=dev),
+                       torch.empty((world, m), dtype=torch.int32, device=dev), torch.empty((world, m), dtype=torch.int32, device=dev)],
+                 "l": [torch.zeros((m, k), dtype=torch.int32, device=dev), torch.zeros((m, k), dtype=torch.float32, device=dev),
+                       torch.zeros((m,), dtype=torch.int32, device=dev), torch.zeros((m,), dtype=torch.int32, device=dev)]}
+        cache["h"] = [torch.empty(t.shape, dtype=t.dtype).pin_memory() for t in cache["g"]]
+        index._shard_bufs = cache
+    n_loc = hi - lo
+    if n_loc > 0:
+        index.upload_queries(queries[lo:hi])
+        index.search_resident(**qp)
+        L = _lib.lib()
+        p = [C.c_void_p() for _ in range(4)]
+        rn, rk = C.c_uint64(), C.c_uint32()
+        check(L.pann_search_device_result(index._h, C.byref(p[0]), C.byref(p[1]), C.byref(p[2]), C.byref(p[3]), C.byref(rn), C.byref(rk)))
+        views = [torch.as_tensor(_DevView(p[0].value, (n_loc, k), "<i4"), device=dev), torch.as_tensor(_DevView(p[1].value, (n_loc, k), "<f4"), device=dev),
+                 torch.as_tensor(_DevView(p[2].value, (n_loc,), "<i4"), device=dev), torch.as_tensor(_DevView(p[3].value, (n_loc,), "<i4"), device=dev)]
+        for dst, src in zip(cache["l"], views):
+            dst[:n_loc].copy_(src)          # equal slices: the padded staging buffer IS the slice (one D2D copy, NVLink-sized)
+    for g, l in zip(cache["g"], cache["l"]):
+        dist.all_gather_into_tensor(g, l, group=group)
+    for h, g in zip(cache["h"], cache["g"]):
+        h.copy_(g, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    outs = []
+    for h, dt in zip(cache["h"], (np.uint32, np.float32, np.uint32, np.uint32)):
+        a = h.numpy()
+        if all(c == m for c in counts):
+            a = a.reshape((world * m,) + a.shape[2:])
+        else:
+            a = np.concatenate([a[r, :counts[r]] for r in range(world)], axis=0)
+        outs.append(a.view(dt) if a.dtype != dt else a)
+    return tuple(outs)
 
 
 class _DevView:

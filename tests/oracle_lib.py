@@ -123,16 +123,40 @@ def groundtruth(base, queries, data_type, metric="Euclidian", k=100):
 
 
 # ---- the real reference (only where oracle/_ref/ref_driver exists and runs on this CPU) ----
+_ref_path = []
+
+
 def ref_driver_path():
-    for name in ("ref_driver", "ref_driver_v3"):
+    """the first of ref_driver (-march=native of the build container), ref_driver_v4 (x86-64-v4), ref_driver_v3 that runs on
+    this CPU (a binary built for an ISA extension this CPU lacks dies with SIGILL in its self test)"""
+    if _ref_path:
+        return _ref_path[0]
+    for name in ("ref_driver", "ref_driver_v4", "ref_driver_v3"):
         p = os.path.join(ORACLE_DIR, "_ref", name)
         if os.path.exists(p):
             try:
                 if subprocess.run([p, "selftest"], capture_output=True, timeout=60).returncode == 0:
+                    _ref_path.append(p)
                     return p
             except Exception:
                 pass
+    _ref_path.append(None)
     return None
+
+
+def ref_driver_info():
+    """which reference binary ref_run uses and the ISA level it was compiled for (oracle/_ref/BUILD_INFO)"""
+    p = ref_driver_path()
+    if p is None:
+        return "unavailable"
+    name = os.path.basename(p)
+    try:
+        for line in open(os.path.join(ORACLE_DIR, "_ref", "BUILD_INFO")):
+            if line.startswith(name + ":"):
+                return line.strip()
+    except OSError:
+        pass
+    return name
 
 
 def ref_run(args, threads=None):

@@ -84,3 +84,48 @@ def test_build_with_row_cache_matches_oracle(dataset, data_type, metric, n, d, R
     """K3 with the candidate rows cached in shared memory (the path large builds take) writes the same graph"""
     monkeypatch.setenv("PANN_PRUNE_ROW_CACHE", "1")
     test_build_matches_oracle(dataset, data_type, metric, n, d, R, L, passes)
+
+
+@pytest.mark.parametrize("row_cache", ["0", "1"])
+@pytest.mark.parametrize("data_type,metric,n,d,R,L,passes", [
+    ("uint8", "Euclidian", 12000, 128, 32, 64, 2), ("float", "mips", 4000, 200, 16, 32, 1),
+])
+def test_build_long_list_slab_launch_matches_oracle(dataset, data_type, metric, n, d, R, L, passes, row_cache, monkeypatch):
+    """K3's second launch (candidate lists beyond the shared-memory capacity: global slab, bitonic sort, device-side task
+    count) is what hubs take in 10M builds; here PANN_PRUNE_CAP forces nearly every list of BOTH modes (visited lists and
+    reverse-edge groups) through it, with and without the row cache — same graph and counters as the oracle."""
+    monkeypatch.setenv("PANN_PRUNE_CAP", "24")
+    monkeypatch.setenv("PANN_PRUNE_ROW_CACHE", row_cache)
+    test_build_matches_oracle(dataset, data_type, metric, n, d, R, L, passes)
+
+
+def test_build_long_list_slab_launch_matches_reference_golden(monkeypatch):
+    monkeypatch.setenv("PANN_PRUNE_CAP", "16")
+    for name in ("u8_l2", "u8_l2_2pass", "f32_l2"):
+        g = golden(name)
+        idx, got, (sv, sd) = _build(g.base, g.data_type, g.metric, g.R, g.L, passes=g.passes)
+        assert np.array_equal(valid_graph(got), valid_graph(g.z["graph_unsorted"])), name
+        assert np.array_equal(sv, g.z["build_visited"]) and np.array_equal(sd, g.z["build_distances"]), name
+
+
+def test_build_slab_overflow_is_reported(dataset, monkeypatch):
+    import parlayann_b200 as P
+    ds = dataset("uint8", n=6000, d=128, nq=10, R=32, L=64)
+    monkeypatch.setenv("PANN_PRUNE_CAP", "16")
+    monkeypatch.setenv("PANN_PRUNE_SLAB_CAP", "64")
+    idx = P.GraphIndex(ds.base, None, "uint8", "Euclidian", max_degree=32)
+    with pytest.raises(P.PannError, match="PANN_PRUNE_SLAB_CAP"):
+        idx.build(R=32, L=64)
+
+
+def test_build_stats_accounting(dataset):
+    """pann_index_build_stats: the device-side B_ins accounting against the oracle's counters: the build's
+    distance comparisons = search comparisons + pair distances, so pair distances must equal sum(stats) - search cmps."""
+    ds = dataset("uint8", n=8000, d=128, nq=10, R=32, L=64)
+    idx, got, (sv, sd) = _build(ds.base, "uint8", "Euclidian", 32, 64)
+    st = idx.build_stats()
+    assert st["prune_calls"] >= ds.n and st["pair_distances"] > 0
+    assert st["algorithmic_bytes"] == st["search_bytes"] + st["prune_bytes"] + ds.n * 2 * 4 * 33
+    # every robustPrune call reads at least its candidates' rows: bytes >= calls * (row + graph row)
+    assert st["prune_bytes"] >= st["prune_calls"] * (128 + 4 * 33)
+    assert st["pair_distances"] < int(sd.astype(np.int64).sum())

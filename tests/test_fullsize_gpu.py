@@ -88,3 +88,46 @@ def test_ragged_batch_sizes(big, nq):
     if nq:
         full = idx.search(q[:5000], k=10, beam=12)
         assert np.array_equal(ids, full[0][:nq]) and np.array_equal(cmps, full[3][:nq])
+
+
+def test_c2_identical_to_reference(big, tmp_path):
+    """BASELINE configs[1] at full size against the UNMODIFIED reference on this box's host cores (oracle/_ref/ref_driver):
+    the 1M x 128 u8 graph — unsorted and after the final sort — byte-identical with the build counters, then qsearchAll on
+    that graph: ids, visited and distance-comparison counters equal per query for narrow, medium and wide beams."""
+    import oracle_lib as O
+    import parlayann_b200 as P
+    from parlayann_b200 import fileio
+    if O.ref_driver_path() is None:
+        pytest.skip("oracle/_ref/ref_driver not built (needs /root/reference at build time)")
+    idx, q, gt_ids, gt_d = big
+    base_f, q_f = str(tmp_path / "base.u8bin"), str(tmp_path / "q.u8bin")
+    fileio.write_bin(base_f, idx.points()); fileio.write_bin(q_f, q)
+    common = ["-data_type", "uint8", "-dist_func", "Euclidian", "-base", base_f]
+    O.ref_run(["build"] + common + ["-R", R, "-L", L, "-alpha", 1.2, "-sort", 0, "-out", str(tmp_path / "ns")])
+    g_ref = fileio.read_graph(str(tmp_path / "ns.graph"))
+    fresh = P.GraphIndex(data_type="uint8", metric="Euclidian", max_degree=R, synthetic=dict(n=N, d=D, kind="uint8", seed=1234, stream=0, r=24, nc=256))
+    sv, sd = fresh.build(R=R, L=L, alpha=1.2, num_passes=1, sort_neighbors=False, stats=True)
+    g = fresh.graph()
+    valid = np.arange(R)[None, :] < g_ref[:, 0][:, None]
+    assert np.array_equal(g[:, 0], g_ref[:, 0]), "degrees differ"
+    bad = ((g[:, 1:] != g_ref[:, 1:]) & valid).any(axis=1)
+    assert not bad.any(), f"{bad.sum()} of {N} unsorted rows differ from the reference's"
+    assert np.array_equal(sv, np.fromfile(str(tmp_path / "ns.bvisited"), dtype=np.uint32))
+    assert np.array_equal(sd, np.fromfile(str(tmp_path / "ns.bdistances"), dtype=np.uint32))
+    fresh.close()
+    # the sorted graph of the fixture (sort_neighbors = true): the reference's own final std::sort of the same rows
+    O.ref_run(["build"] + common + ["-R", R, "-L", L, "-alpha", 1.2, "-sort", 1, "-out", str(tmp_path / "s")])
+    gs_ref = fileio.read_graph(str(tmp_path / "s.graph"))
+    gs = idx.graph()
+    bad = ((gs[:, 1:] != gs_ref[:, 1:]) & valid).any(axis=1)
+    assert np.array_equal(gs[:, 0], gs_ref[:, 0]) and not bad.any(), f"{bad.sum()} sorted rows differ"
+    # per-query search parity on the reference-built sorted graph
+    for k, beam, extra in ((10, 12, []), (10, 24, []), (10, 100, []), (10, 20, ["-limit", 15, "-degree_limit", 64])):
+        out = str(tmp_path / f"s{beam}")
+        O.ref_run(["search"] + common + ["-graph", str(tmp_path / "s.graph"), "-query", q_f, "-k", k, "-beam", beam, "-cutf", 1.35, "-out", out] + extra)
+        rid = np.fromfile(out + ".ids", dtype=np.uint32).reshape(NQ, k)
+        kw = dict(limit=15, degree_limit=64) if extra else {}
+        ids, _, vis, cmps = idx.search(q, k=k, beam=beam, cut=float(np.float32(1.35)), **kw)
+        assert np.array_equal(ids, rid), f"beam {beam}: {(ids != rid).any(axis=1).sum()} queries differ"
+        assert np.array_equal(vis, np.fromfile(out + ".visited", dtype=np.uint32))
+        assert np.array_equal(cmps, np.fromfile(out + ".distances", dtype=np.uint32))

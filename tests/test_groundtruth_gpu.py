@@ -98,9 +98,10 @@ def test_groundtruth_errors():
 def _both_paths(idx, queries, k, monkeypatch):
     monkeypatch.setenv("PANN_GT_V1", "0")
     a = idx.groundtruth(queries, k=k)
-    n_mma = idx.last_timing()[1]
+    n_mma = idx.groundtruth_stats()[0]
     monkeypatch.setenv("PANN_GT_V1", "1")
     b = idx.groundtruth(queries, k=k)
+    assert idx.groundtruth_stats()[0] == 0, "PANN_GT_V1=1 must stay on the CUDA cores"
     return a, b, n_mma
 
 
@@ -115,7 +116,8 @@ def test_mma_path_identical_to_cuda_core_path(data_type, metric, kind, n, d, nq,
     base = O.gen_points(kind, n, d)
     qs = O.gen_points(kind, nq, d, stream=1)
     idx = P.GraphIndex(base, None, data_type, metric, max_degree=4)
-    (gi, gd), (vi, vd), _ = _both_paths(idx, qs, k, monkeypatch)
+    (gi, gd), (vi, vd), n_mma = _both_paths(idx, qs, k, monkeypatch)
+    assert n_mma > 0, "the tcgen05 kernel did not run for this shape"
     assert np.array_equal(gd.view(np.uint32), vd.view(np.uint32))   # bit-identical floats
     assert np.array_equal(gi, vi)                                   # both sorted by (dist, id): same ids, ties included
     oi, od = O.groundtruth(base, qs, data_type, metric, k=k)
