@@ -51,8 +51,85 @@ __device__ __forceinline__ u64 pann_shfl_up64(u64 x) {
   return ((u64)hi << 32) | lo;
 }
 
+// ---- shared memory by 32-bit address (no generic pointers in the hop loop: they cost a register pair each and an
+// address-space conversion wherever the compiler cannot prove the window)
+__device__ __forceinline__ u64 pann_lds64(uint32_t a) { u64 v; asm volatile("ld.shared.u64 %0, [%1];" : "=l"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void pann_sts64(uint32_t a, u64 v) { asm volatile("st.shared.u64 [%0], %1;" ::"r"(a), "l"(v) : "memory"); }
+__device__ __forceinline__ uint32_t pann_lds32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
+__device__ __forceinline__ void pann_sts32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;" ::"r"(a), "r"(v) : "memory"); }
+__device__ __forceinline__ uint4 pann_lds128(uint32_t a) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void pann_sts128(uint32_t a, uint4 v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+// #{j < n : keys[j] < t} over a shared-memory key list (16-byte aligned), two keys per 128-bit broadcast load
+__device__ __forceinline__ int pann_count_below_s(uint32_t keys, int n, u64 t) {
+  int n0 = 0, n1 = 0, j = 0;
+#pragma unroll 1
+  for (; j + 2 <= n; j += 2) {
+    const uint4 v = pann_lds128(keys + 8u * j);
+    pann_borrow_count(n0, ((u64)v.y << 32) | v.x, t);
+    pann_borrow_count(n1, ((u64)v.w << 32) | v.z, t);
+  }
+  if (j < n) pann_borrow_count(n0, pann_lds64(keys + 8u * j), t);
+  return -(n0 + n1);
+}
+__device__ __forceinline__ u64 pann_shfl_xor64(u64 x, int d) {
+  const uint32_t lo = __shfl_xor_sync(PANN_FULL, (uint32_t)x, d), hi = __shfl_xor_sync(PANN_FULL, (uint32_t)(x >> 32), d);
+  return ((u64)hi << 32) | lo;
+}
+// pann_quad_distance with the query row given by its 32-bit shared address
+template <int DT, int METRIC, class RG>
+__device__ __forceinline__ float pann_quad_distance_s(const RG& A, uint32_t a, unsigned keepmask, uint32_t qs, int lane) {
+  const int sub = lane & 3, rowi = lane >> 2;
+  uint4 v[4][2];
+#pragma unroll
+  for (int g = 0; g < 4; g++) {
+    const int src = g * 8 + rowi;
+    const uint32_t ag = __shfl_sync(PANN_FULL, a, src);
+#if defined(PANN_QUAD_ASM)
+    pann_ldg16x2_if(A.points + (u64)ag * A.stride + sub * 16, (keepmask >> src) & 1u, v[g][0], v[g][1]);
+#else
+#ifndef PANN_QUAD_UNDEF   // leaving the unwanted rows' registers undefined (or predicating the loads in inline asm) makes ptxas spill ~400 bytes
+    v[g][0] = v[g][1] = make_uint4(0u, 0u, 0u, 0u);
+#endif
+    if ((keepmask >> src) & 1u) {
+      const uint8_t* row = A.points + (u64)ag * A.stride + sub * 16;
+      v[g][0] = pann_ldg16(row);
+      v[g][1] = pann_ldg16(row + 64);
+    }
+#endif
+  }
+  const uint4 q0 = pann_lds128(qs + 16u * sub), q1 = pann_lds128(qs + 16u * sub + 64u);
+  DistAcc<DT, METRIC> acc[4];
+#pragma unroll
+  for (int g = 0; g < 4; g++) { acc[g].add(v[g][0], q0); acc[g].add(v[g][1], q1); }
+  unsigned part[4];
+#pragma unroll
+  for (int g = 0; g < 4; g++) part[g] = (unsigned)acc[g].acc;
+  const bool b1 = (lane & 2) != 0, b0 = (lane & 1) != 0;
+  const unsigned r0 = (b1 ? part[2] : part[0]) + __shfl_xor_sync(PANN_FULL, b1 ? part[0] : part[2], 2);
+  const unsigned r1 = (b1 ? part[3] : part[1]) + __shfl_xor_sync(PANN_FULL, b1 ? part[1] : part[3], 2);
+  const unsigned tot = (b0 ? r1 : r0) + __shfl_xor_sync(PANN_FULL, b0 ? r0 : r1, 1);
+  const unsigned mine = __shfl_sync(PANN_FULL, tot, (lane & 7) * 4 + (lane >> 3));
+  DistAcc<DT, METRIC> res;
+  res.acc = (decltype(res.acc))mine;
+  return res.result();
+}
+
 // EXT: per-query start lists and the vertex -> row map (beamSearchRandom, HNSW layers); a separate instantiation so that
-// the plain kernel — which sits exactly at its register budget — is not touched by them.
+// the plain kernel — which sits at its register budget — is not touched by them.
+//
+// The merge (beamSearch.h:173-185: sort candidates, unique, set_union with the frontier, truncate to the beam) is ONE
+// batched step per 32 candidates: the candidates are rank-sorted through shared memory into DESCENDING lane order, the
+// lane-wise minimum with the (ascending) register frontier is then the 32 smallest keys of the union as a bitonic
+// sequence, and five compare-exchange stages sort it.  Keys of the same vertex are equal up to the flag bit, so a vertex
+// that is reached twice ends up in adjacent lanes: that (rare) case, and two equal candidates, fall back to the
+// one-at-a-time insertion below, which resolves duplicates exactly as set_union does.
+// "Already visited" is a 1024-bit signature across the warp (one register per lane) with an exact list behind it.
 template <int DT, int METRIC, int QR, bool EXT>
 #ifndef PANN_K1S_MINB
 #define PANN_K1S_MINB 7  // 72 registers: at 64 the compiler interleaves the row loads with arithmetic (fewer rows in flight per warp); measured 8 / 7 / 6 CTAs per SM: 55.0 / 51.6 / 57.8 ms per 1M queries at 10M points
@@ -61,12 +138,8 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
   extern __shared__ __align__(16) uint8_t pann_smem[];
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
   const unsigned lt_mask = (1u << lane) - 1u;
-  uint8_t* ws = pann_smem + (size_t)wic * A.warp_bytes;
-  u64* cand = reinterpret_cast<u64*>(ws + A.off_cand);
-  uint4* qsm = reinterpret_cast<uint4*>(ws + A.off_q);
-  uint32_t* visid = reinterpret_cast<uint32_t*>(ws + A.off_vis);
-  uint32_t* hashf = reinterpret_cast<uint32_t*>(ws + A.off_hash);
-  uint4* stage = reinterpret_cast<uint4*>(ws + A.off_stage);
+  const uint32_t ws = (uint32_t)__cvta_generic_to_shared(pann_smem) + (uint32_t)wic * A.warp_bytes;  // this warp's slab
+  const uint32_t s_cand = ws + A.off_cand, s_srt = ws + A.off_scand, s_q = ws + A.off_q, s_vis = ws + A.off_vis, s_hash = ws + A.off_hash;
   const uint32_t hmask = (1u << A.bits) - 1u;
   const int B = A.beam;
   // query indices fit 32 bits (the host checks nq < 2^31): narrow scalars keep the register file for the gathers
@@ -74,23 +147,34 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
   const int wstride = (int)gridDim.x * PANN_WARPS_PER_CTA;
   const int nq = (int)A.nq;
   const int limit = (int)(A.limit < 0x7fffffffll ? A.limit : 0x7fffffffll);
+  constexpr bool QUAD = pann_quad_rows<DT, QR>();
+  // generic views for the row shapes that do not take the four-lanes-per-row path
+  const uint4* qsm = reinterpret_cast<const uint4*>(pann_smem + (size_t)wic * A.warp_bytes + A.off_q);
+  uint4* stage = reinterpret_cast<uint4*>(pann_smem + (size_t)wic * A.warp_bytes + A.off_stage);
   auto next_query = [&](int ql) -> int {
     if (!A.qcounter) return ql + wstride;
     unsigned nx = 0;
     if (lane == 0) nx = atomicAdd(A.qcounter, 1u);
     return (int)min((unsigned)wstride + __shfl_sync(PANN_FULL, nx, 0), 0x7fffffffu);
   };
+  auto distance = [&](uint32_t a, unsigned mask) -> float {
+    if constexpr (QUAD) return pann_quad_distance_s<DT, METRIC>(A, a, mask, s_q, lane);
+    else if constexpr (pann_staged_rows<DT, QR>()) return pann_staged_distance<DT, METRIC>(A, a, mask, qsm, stage, lane);
+    else return pann_lane_distance<DT, METRIC, QR>(A, a, (mask >> lane) & 1u, qsm);
+  };
   for (int ql = wglobal; ql < nq; ql = next_query(ql)) {
     const int q = A.qmap ? (int)A.qmap[ql] : ql;
     {
       const uint4 ones = make_uint4(~0u, ~0u, ~0u, ~0u);
-      uint4* h4 = reinterpret_cast<uint4*>(hashf);
-      for (int i = lane; i < (1 << A.bits) / 4; i += 32) h4[i] = ones;
+      for (int i = lane; i < (1 << A.bits) / 4; i += 32) pann_sts128(s_hash + 16u * i, ones);
     }
     const uint32_t self = A.self_ids ? A.self_ids[q] : 0xffffffffu;  // ids are < 2^31
-    const uint8_t* qrow = A.self_ids ? A.points + (u64)self * A.stride : A.queries + (u64)q * A.qstride;
-    pann_load_query(qrow, A.nch, qsm, lane);
-    constexpr bool QUAD = pann_quad_rows<DT, QR>();
+    {
+      const uint8_t* qrow = A.self_ids ? A.points + (u64)self * A.stride : A.queries + (u64)q * A.qstride;
+      __syncwarp();
+      for (int ch = lane; ch < (int)A.nch; ch += 32) pann_sts128(s_q + 16u * ch, pann_ldg16(qrow + ch * 16));
+      __syncwarp();
+    }
 
     // row prefetch policy (see the main loop): always, or — for the queries handed out last — once half the warps retired
     const bool always_pf = (A.tune & 1u) != 0;
@@ -101,10 +185,17 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
 #endif
     u64 fk = ~0ull;  // frontier entry `lane` ((dist,id) key, bit 0 = visited), ~0 beyond the frontier
     int F = 0, V = 0, C = 0, status = 0;
-    uint32_t vis0 = 0xffffffffu, vis1 = 0xffffffffu;  // visited ids V = lane and lane + 32 (later ones: shared memory)
+    uint32_t vsig = 0;   // bit (h & 31) of lane (h >> 5) is set for every visited id, h = 10-bit hash of the id
     const uint32_t* qstarts = EXT ? A.starts + (u64)q * A.starts_stride : A.starts;
     const int ns = (int)((EXT && A.nstarts_q) ? A.nstarts_q[q] : A.nstarts);
     unsigned cmps = ns, nread = 0;
+    auto vhash = [](uint32_t id) -> uint32_t { return (id * 2654435761u) >> 22; };
+    // is `id` (warp-uniform) in the visited list?  exact
+    auto visited_exact = [&](uint32_t id) -> bool {
+      bool found = false;
+      for (int b0 = 0; b0 < V; b0 += 32) found |= (b0 + lane < V) && (pann_lds32(s_vis + 4u * (b0 + lane)) == id);
+      return __any_sync(PANN_FULL, found);
+    };
 
     // ---- starting points (:64-70).  More starts than the beam width: see pann_beam_search_kernel.
     if (ns < 1 || ns > 32 || (ns > B && A.cut_rule && A.k < B)) {
@@ -112,21 +203,18 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
     } else {
       const bool on = lane < ns;
       const uint32_t a = on ? qstarts[lane] : 0u;
-      float d;
-      if constexpr (QUAD) d = pann_quad_distance<DT, METRIC>(A, a, __ballot_sync(PANN_FULL, on), qsm, lane);
-      else if constexpr (pann_staged_rows<DT, QR>()) d = pann_staged_distance<DT, METRIC>(A, a, __ballot_sync(PANN_FULL, on), qsm, stage, lane);
-      else d = pann_lane_distance<DT, METRIC, QR>(A, a, on, qsm);
+      const float d = distance(a, __ballot_sync(PANN_FULL, on));
       const u64 key = on ? pann_key(d, a) : ~0ull;
       if (lane == 0)
-        for (int i = 0; i < ns; i++) { const uint32_t s = qstarts[i]; hashf[(uint32_t)pann_hash64_2(s) & hmask] = s; }
+        for (int i = 0; i < ns; i++) { const uint32_t s = qstarts[i]; pann_sts32(s_hash + 4u * ((uint32_t)pann_hash64_2(s) & hmask), s); }
       int r = 0;
       for (int j = 0; j < ns; j++) {
         const u64 kj = pann_shfl64(key, j);
         r += (kj < key) || (kj == key && j < lane);
       }
-      if (on) cand[r] = key;
+      if (on) pann_sts64(s_srt + 8u * r, key);
       __syncwarp();
-      if (on) fk = cand[lane];
+      if (on) fk = pann_lds64(s_srt + 8u * lane);
       F = ns;
       __syncwarp();
     }
@@ -136,10 +224,10 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
       const unsigned unv = __ballot_sync(PANN_FULL, lane < F && !(fk & 1ull));
       if (!unv || V >= limit) break;
       const int pos = __ffs(unv) - 1;
-      const bool vis_in_front = (F - __popc(unv)) == V;  // every visited vertex is still a (flagged) frontier entry
       const bool more_after = __popc(unv) > 1;           // offset + 1 < remain (:164)
       const u64 cur = pann_shfl64(fk, pos);
-      const uint32_t* grow = A.graph + (u64)((EXT && A.rowmap) ? __ldg(A.rowmap + pann_key_id(cur)) : pann_key_id(cur)) * (A.maxdeg + 1);
+      const uint32_t cur_id = pann_key_id(cur);
+      const uint32_t* grow = A.graph + (u64)((EXT && A.rowmap) ? __ldg(A.rowmap + cur_id) : cur_id) * (A.maxdeg + 1);
       uint32_t drain_cnt = 0;  // read next to the graph row, so its latency is hidden under that load
       if (drain_watch) asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(drain_cnt) : "l"(A.qcounter));
       const int deg = (int)__ldg(grow);
@@ -147,10 +235,12 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
       const uint32_t a1 = (32 + lane < (int)A.maxdeg) ? __ldg(grow + 33 + lane) : 0u;
       if (lane == pos) fk |= 1ull;
       if (V >= (int)A.vcap) { status = 1; break; }
-      if (V < 32) { if (lane == V) vis0 = pann_key_id(cur); }
-      else if (V < 64) { if (lane == V - 32) vis1 = pann_key_id(cur); }
-      else if (lane == 0) visid[V] = pann_key_id(cur);
-      V++;
+      {  // visited: exact id list in shared memory + the signature
+        const uint32_t h = vhash(cur_id);
+        if (lane == 0) pann_sts32(s_vis + 4u * V, cur_id);
+        if (lane == (int)(h >> 5)) vsig |= 1u << (h & 31u);
+        V++;
+      }
       const bool full = (F == B);
       const float cutoff = full ? pann_key_dist(pann_shfl64(fk, F - 1)) : 2147483648.0f;  // (float)INT_MAX (:150-152)
       // Early drop (beams < 16, where every hop with a candidate merges): with the cut rule on and more than k entries, a
@@ -185,54 +275,82 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
         const uint32_t from_prev = __shfl_sync(PANN_FULL, a, prev ? (31 - __clz(prev)) : lane);
         bool seen = false;
         if (act) {
-          const uint32_t slot = prev ? from_prev : hashf[loc];
+          const uint32_t slot = prev ? from_prev : pann_lds32(s_hash + 4u * loc);
           seen = (slot == a);
         }
         __syncwarp();
-        if (act && (peers >> lane) <= 1u) hashf[loc] = a;
+        if (act && (peers >> lane) <= 1u) pann_sts32(s_hash + 4u * loc, a);
         const bool keep = act && !seen && (a != self);
         const unsigned keepmask = __ballot_sync(PANN_FULL, keep);
         cmps += __popc(keepmask);  // :155
-        float d;
-        if constexpr (QUAD) d = pann_quad_distance<DT, METRIC>(A, a, keepmask, qsm, lane);
-        else if constexpr (pann_staged_rows<DT, QR>()) d = pann_staged_distance<DT, METRIC>(A, a, keepmask, qsm, stage, lane);
-        else d = pann_lane_distance<DT, METRIC, QR>(A, a, keep, qsm);
+        const float d = distance(a, keepmask);
         const u64 key = pann_key(d, a);
         const bool take = keep && (d < cutoff) && (key <= drop_above);  // :153-158
         const unsigned m = __ballot_sync(PANN_FULL, take);
         if (C + __popc(m) > (int)A.ccap) { status = 1; break; }  // cannot happen (ccap >= maxdeg + beam/8); guards memory
-        if (take) cand[C + __popc(m & lt_mask)] = key;
+        if (take) pann_sts64(s_cand + 8u * (C + __popc(m & lt_mask)), key);
         C += __popc(m);
         __syncwarp();
       }
       if (status) break;
       if (C == 0) continue;
       if (A.limit >= 2ll * B && C < B / 8 && more_after) continue;  // :162-168, candidates are kept
-      // ---- merge (:173-208) as ballot-ranked insertions
+      // ---- merge (:173-208), 32 candidates at a time
       const int F_old = F;
-      for (int j = 0; j < C; j++) {
-        const u64 c = cand[j];
-        const int lb = __popc(__ballot_sync(PANN_FULL, fk < c));  // raw compare: bit 0 of c is clear
-        const unsigned dup = __ballot_sync(PANN_FULL, (fk & ~1ull) == c);
-        if (dup || lb >= B) continue;
-        u64 fl = 0ull;
-        if (!vis_in_front) {  // a vertex that comes back after it was visited stays visited
-          const uint32_t id = pann_key_id(c);
-          bool found = (vis0 == id) || (vis1 == id);   // ids are < 2^31: the 0xffffffff fill never matches
-          for (int b0 = 64; b0 < V; b0 += 32) found |= (b0 + lane < V) && (visid[b0 + lane] == id);
-          fl = __any_sync(PANN_FULL, found) ? 1ull : 0ull;
+      for (int c0 = 0; c0 < C; c0 += 32) {
+        const int n = min(32, C - c0);
+        const uint32_t s_chunk = s_cand + 8u * c0;
+        u64 ck = lane < n ? pann_lds64(s_chunk + 8u * lane) : ~0ull;
+        {  // a vertex that comes back after it was visited stays visited (it is in `visited`, so set_difference drops it, :203-208)
+          const uint32_t cid = pann_key_id(ck);
+          const uint32_t h = vhash(cid);
+          const uint32_t w = __shfl_sync(PANN_FULL, vsig, (int)(h >> 5));
+          unsigned hm = __ballot_sync(PANN_FULL, lane < n && ((w >> (h & 31u)) & 1u));
+          while (hm) {
+            const int j = __ffs(hm) - 1;
+            hm &= hm - 1;
+            if (visited_exact(__shfl_sync(PANN_FULL, cid, j)) && lane == j) ck |= 1ull;
+          }
         }
-        const u64 up = pann_shfl_up64(fk);
-        if (lane == lb) fk = c | fl;
-        else if (lane > lb) fk = up;
-        if (lane >= B) fk = ~0ull;
-        F = min(F + 1, B);
+        const int r = pann_count_below_s(s_chunk, n, ck & ~1ull);   // rank among the chunk's keys (raw keys: bit 0 clear)
+        pann_sts64(s_srt + 8u * lane, ~0ull);
+        __syncwarp();
+        if (lane < n) pann_sts64(s_srt + 8u * (31 - r), ck);          // descending in lane order
+        __syncwarp();
+        const u64 x = pann_lds64(s_srt + 8u * lane);
+        bool slow = __popc(__ballot_sync(PANN_FULL, x != ~0ull)) != n;   // two equal candidates shared a slot
+        u64 v = x < fk ? x : fk;                                     // the 32 smallest of frontier + chunk, bitonic
+#pragma unroll
+        for (int dd = 16; dd > 0; dd >>= 1) {
+          const u64 p = pann_shfl_xor64(v, dd);
+          const bool up = (lane & dd) != 0;
+          v = ((p < v) != up) ? p : v;                               // lower lane keeps the minimum, upper the maximum
+        }
+        {
+          const u64 pv = pann_shfl_up64(v);
+          slow |= __any_sync(PANN_FULL, lane > 0 && v != ~0ull && ((v ^ pv) >> 1) == 0ull);   // the same vertex twice
+        }
+        if (!slow) {
+          fk = (lane < B) ? v : ~0ull;
+          F = min(B, F + n);
+        } else {
+          // one candidate at a time: position by ballot, duplicates skipped, entries above move up one lane
+          for (int j = 0; j < n; j++) {
+            const u64 c = pann_shfl64(ck, j);
+            const int lb = __popc(__ballot_sync(PANN_FULL, (fk | 1ull) < (c & ~1ull)));
+            const unsigned dup = __ballot_sync(PANN_FULL, (fk & ~1ull) == (c & ~1ull));
+            if (dup || lb >= B) continue;
+            const u64 upk = pann_shfl_up64(fk);
+            if (lane == lb) fk = c;
+            else if (lane > lb) fk = upk;
+            if (lane >= B) fk = ~0ull;
+            F = min(F + 1, B);
+          }
+          if (EXT && F > B) { F = B; if (lane >= B) fk = ~0ull; }   // a start list longer than the beam: the merge truncates (:185)
+        }
+        __syncwarp();
       }
       C = 0;
-      if (EXT && F > B) {  // a start list longer than the beam: the merge truncates (:185)
-        F = B;
-        if (lane >= B) fk = ~0ull;
-      }
       // cut rule (:190-195)
       int nfs = F;
       if (A.cut_rule && nfs > A.k) {

@@ -214,7 +214,8 @@ static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap, cud
     vcap = (uint32_t)std::min<long long>(std::max<long long>(A.limit, 1), std::max<long long>(256, 4ll * B));
     A.vcap = vcap;
     A.off_cand = 0;
-    A.off_q = al16((size_t)A.ccap * 8);
+    A.off_scand = al16((size_t)A.ccap * 8);   // 32 keys: the rank-sorted candidate chunk of the batched merge
+    A.off_q = A.off_scand + 256;
     A.off_vis = A.off_q + g.stride;
     A.off_hash = A.off_vis + al16((size_t)vcap * 4);
     A.off_stage = A.off_hash + (4u << A.bits);
