@@ -132,7 +132,7 @@ __device__ __forceinline__ float pann_quad_distance_s(const RG& A, uint32_t a, u
 // "Already visited" is a 1024-bit signature across the warp (one register per lane) with an exact list behind it.
 template <int DT, int METRIC, int QR, bool EXT>
 #ifndef PANN_K1S_MINB
-#define PANN_K1S_MINB 7  // 72 registers: at 64 the compiler interleaves the row loads with arithmetic (fewer rows in flight per warp); measured 8 / 7 / 6 CTAs per SM: 55.0 / 51.6 / 57.8 ms per 1M queries at 10M points
+#define PANN_K1S_MINB 6  // 78 registers, 24 warps per SM.  Measured with the batched merge, 1M queries on 10M x 128 u8 (CTAs per SM: ms): 8: 53.3, 7: 47.5, 6: 46.6, 5: 54.0, 4: 58.9 — and 1 000 queries (latency bound): 0.33 ms at 7, 0.27 ms at 6
 #endif
 __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MINB : 4) pann_beam_search_small_kernel(const BeamArgs A) {
   extern __shared__ __align__(16) uint8_t pann_smem[];
@@ -288,7 +288,9 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
         const bool take = keep && (d < cutoff) && (key <= drop_above);  // :153-158
         const unsigned m = __ballot_sync(PANN_FULL, take);
         if (C + __popc(m) > (int)A.ccap) { status = 1; break; }  // cannot happen (ccap >= maxdeg + beam/8); guards memory
-        if (take) pann_sts64(s_cand + 8u * (C + __popc(m & lt_mask)), key);
+        if (take) {
+          pann_sts64(s_cand + 8u * (C + __popc(m & lt_mask)), key);
+        }
         C += __popc(m);
         __syncwarp();
       }
