@@ -172,6 +172,31 @@ int pann_groundtruth_device_result(pann_index* idx, const int32_t** d_ids, const
 int pann_groundtruth_merge_device(int device, uint32_t nshards, uint64_t nq, uint32_t k, const int32_t* d_ids, const float* d_dists,
                                   int32_t* d_out_ids, float* d_out_dists, void* stream);
 
+/* ---- HNSW (algorithms/HNSW/HNSW.hpp).  Node i = point i of the index; the index must have max_degree = 2 m: its graph IS
+ * level 0 of the model (degree bound 2m, HNSW.hpp:527-531); the upper levels (bound m) live in the pann_hnsw object as
+ * compacted flat arrays.  The model moves in and out in the order of the model file v3 (HNSW.hpp:1655-1685, :690-740):
+ * level[n]; for every node, for l = 0..level[v], a count (counts[]) and that many node ids (edges[]); the entrances. */
+typedef struct pann_hnsw pann_hnsw;
+int pann_hnsw_create(pann_hnsw** out, pann_index* idx, uint32_t m, uint32_t ef_construction, float m_l, float alpha);
+void pann_hnsw_destroy(pann_hnsw* h);
+/* get_level_random (HNSW.hpp:505-516) as one worker draws it: mt19937{0}, uniform_real_distribution<>(FLT_MIN, 1) */
+int pann_hnsw_levels(uint64_t n, float m_l, uint32_t* out);
+/* HNSW(begin, end, dim, m_l, m, ef_construction, alpha) (HNSW.hpp:746-824) = batched insert() (:828-1014) of nodes 1..n-1.
+ * levels (may be NULL = pann_hnsw_levels): the level of every node.  seconds (may be NULL): total, layer searches,
+ * prune_heuristic + forward edges, reverse edges. */
+int pann_hnsw_build(pann_hnsw* h, const uint32_t* levels, double seconds[4]);
+int pann_hnsw_set_model(pann_hnsw* h, const uint32_t* level, const uint64_t* counts, const uint32_t* edges, const uint32_t* entrance,
+                        uint64_t n_entrances);
+/* sizes = {#counts, #edges, #entrances}; call with NULL arrays first to size the buffers */
+int pann_hnsw_get_model(pann_hnsw* h, uint32_t* level, uint64_t* counts, uint32_t* edges, uint32_t* entrance, uint64_t sizes[3]);
+/* HNSW::search (HNSW.hpp:1570-1613) per query: ef = 1 descent from the entrances (search_layer_to, :1545-1568), search_layer(ef)
+ * on level 0 with visit limit `limit` (<= 0: none), the answer cut to k plus the entries tied with the k-th distance.
+ * HOST buffers; out_ids / out_dists: ocap entries per query (k <= ocap <= ef), out_cnt: entries the reference returns,
+ * out_cmps: distance comparisons summed over the layers (search_control::count_cmps). */
+int pann_hnsw_search(pann_hnsw* h, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes, uint32_t k, uint32_t ef,
+                     int64_t limit, uint32_t ocap, uint32_t* out_ids, float* out_dists, uint32_t* out_cnt, uint32_t* out_cmps);
+int pann_hnsw_info(pann_hnsw* h, uint32_t* top_level, uint64_t* upper_rows, uint32_t* n_entrances, double seconds[4]);
+
 /* pinned host memory for callers that want asynchronous copies */
 int pann_host_alloc(void** p, size_t bytes);
 int pann_host_free(void* p);

@@ -18,6 +18,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <limits>
+#include <random>
 #include <thread>
 #include <unordered_map>
 #include <unordered_set>
@@ -98,8 +99,10 @@ struct SearchOut {
 // algorithms/utils/beamSearch.h:22-214 with use_filtering == false, Points == Q_Points.
 // graph: n x (maxdeg+1) u32, slot 0 = degree (algorithms/utils/graph.h:134-141).
 // self >= 0: the query IS base row `self` (build mode) -> same_as() skips it (euclidian_point.h:178-180).
-void beam_search(const PointSet& P, const uint32_t* graph, uint32_t maxdeg, const void* q, long self,
-                 const uint32_t* starts, uint32_t nstarts, const QP& qp, SearchOut& out) {
+// rowfn(v, deg) -> pointer to v's neighbour ids (flat Graph rows, or HNSW's per-node per-level lists)
+template <class RowFn>
+void beam_search_g(const PointSet& P, RowFn rowfn, uint32_t maxdeg, const void* q, long self,
+                   const uint32_t* starts, uint32_t nstarts, const QP& qp, SearchOut& out) {
   const int beam = (int)qp.beam;
   auto dist = [&](uint32_t a) { return dist_rows(P.dtype, P.metric, P.row(a), q, P.d); };
   int bits = std::max<int>(10, (int)std::ceil(std::log2((double)(beam * beam))) - 2);  // :52
@@ -122,11 +125,12 @@ void beam_search(const PointSet& P, const uint32_t* graph, uint32_t maxdeg, cons
     visited.insert(std::upper_bound(visited.begin(), visited.end(), cur, less_idd), cur);  // :112-113
     nvis++;
     bool full = (int)frontier.size() == beam;  // :115
-    const uint32_t* row = graph + (uint64_t)cur.first * (maxdeg + 1);
-    long ne = std::min<long>(row[0], qp.degree_limit);  // :130
+    uint32_t deg = 0;
+    const uint32_t* row = rowfn(cur.first, deg);
+    long ne = std::min<long>(deg, qp.degree_limit);  // :130
     float cutoff = full ? frontier.back().second : (float)std::numeric_limits<int>::max();  // :150-152
     for (long i = 0; i < ne; i++) {
-      uint32_t a = row[1 + i];
+      uint32_t a = row[i];
       if (seen(a) || (long)a == self) continue;  // :133
       float dd = dist(a);
       cmps++;  // :155
@@ -155,6 +159,12 @@ void beam_search(const PointSet& P, const uint32_t* graph, uint32_t maxdeg, cons
   out.frontier = frontier;
   out.visited = visited;
   out.cmps = cmps;
+}
+
+void beam_search(const PointSet& P, const uint32_t* graph, uint32_t maxdeg, const void* q, long self,
+                 const uint32_t* starts, uint32_t nstarts, const QP& qp, SearchOut& out) {
+  beam_search_g(P, [&](uint32_t v, uint32_t& deg) { const uint32_t* r = graph + (uint64_t)v * (maxdeg + 1); deg = r[0]; return r + 1; },
+                maxdeg, q, self, starts, nstarts, qp, out);
 }
 
 // instrumentation for DESIGN.md (not part of the algorithm): log2 histogram of prune candidate counts
@@ -231,6 +241,110 @@ void par_for(size_t lo, size_t hi, int nthreads, F f) {
   for (int t = 0; t < nthreads; t++)
     ts.emplace_back([&] { for (;;) { size_t i = next.fetch_add(16); if (i >= hi) return; for (size_t j = i; j < std::min(hi, i + 16); j++) f(j); } });
   for (auto& t : ts) t.join();
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------------
+// HNSW (algorithms/HNSW/HNSW.hpp): layered graph, per node per level a neighbour list.
+struct Hnsw {
+  uint32_t dim = 0, m = 0, efc = 0, n = 0;
+  float m_l = 0, alpha = 0;
+  std::vector<uint32_t> level;                          // node::level
+  std::vector<std::vector<std::vector<uint32_t>>> nbr;  // nbr[v][l], l = 0..level[v]
+  std::vector<uint32_t> entrance;
+  uint32_t cap(uint32_t l) const { return l == 0 ? 2 * m : m; }   // get_threshold_m, :527-531
+};
+
+// search_layer (:1088-1109): beam_search_impl over level l with QP(ef, ef, 1.35, limit, cap(l)); returns the frontier
+void hnsw_search_layer(const Hnsw& H, const PointSet& P, const void* q, long self, const std::vector<uint32_t>& eps, uint32_t ef,
+                       uint32_t l, long limit, SearchOut& o) {
+  QP qp{(long)ef, (long)ef, 1.35, limit, (long)H.cap(l)};
+  beam_search_g(P, [&](uint32_t v, uint32_t& deg) { const auto& r = H.nbr[v][l]; deg = (uint32_t)r.size(); return r.data(); },
+                H.cap(l), q, self, eps.data(), (uint32_t)eps.size(), qp, o);
+}
+
+// prune_heuristic (:430-486) as select_neighbors calls it (:488-503): candidates sorted by distance; c is dropped when some
+// kept r has d(c, r) < alpha * d(c, u) (float product, strict <); stop at `size` kept
+std::vector<uint32_t> hnsw_prune_heuristic(const Hnsw& H, const PointSet& P, std::vector<idd> cand, uint32_t size) {
+  std::stable_sort(cand.begin(), cand.end(), [](const idd& a, const idd& b) { return a.second < b.second; });
+  std::vector<uint32_t> res;
+  for (const idd& c : cand) {
+    const float d_cu = c.second * H.alpha;
+    bool pruned = false;
+    for (uint32_t r : res)
+      if (dist_rows(P.dtype, P.metric, P.row(c.first), P.row(r), P.d) < d_cu) { pruned = true; break; }
+    if (!pruned) { res.push_back(c.first); if (res.size() == size) break; }
+  }
+  return res;
+}
+
+// get_level_random (:505-516) on ONE worker: thread_local mt19937{worker_id = 0}, uniform_real_distribution<>(FLT_MIN, 1)
+struct HnswLevels {
+  std::mt19937 gen{0};
+  std::uniform_real_distribution<> dis{std::numeric_limits<float>::min(), 1.0};
+  uint32_t next(float m_l) { return (uint32_t)(-log(dis(gen)) * m_l); }
+};
+
+// insert (:828-1014), from_blank = true, nodes [b0, b1) — their levels are already in H.level
+void hnsw_insert(Hnsw& H, const PointSet& P, uint32_t b0, uint32_t b1, int nthreads) {
+  const uint32_t level_ep = H.level[H.entrance[0]];
+  const uint32_t bs = b1 - b0;
+  std::vector<std::vector<uint32_t>> eps(bs), nbh_new(bs);
+  for (uint32_t i = 0; i < bs; i++) H.nbr[b0 + i].assign(H.level[b0 + i] + 1, {});
+  par_for(0, bs, nthreads, [&](size_t i) {  // :865-881: ef = 1 descent to the node's own top level
+    const uint32_t u = b0 + (uint32_t)i;
+    eps[i] = H.entrance;
+    for (uint32_t l = level_ep; l > H.level[u]; --l) {
+      SearchOut o;
+      hnsw_search_layer(H, P, P.row(u), (long)u, eps[i], 1, l, (long)H.n, o);
+      eps[i].assign(1, o.frontier[0].first);
+    }
+  });
+  for (int l_c = (int)level_ep; l_c >= 0; --l_c) {  // :885-1000
+    par_for(0, bs, nthreads, [&](size_t i) {
+      const uint32_t u = b0 + (uint32_t)i;
+      if ((uint32_t)l_c > H.level[u]) return;
+      SearchOut o;
+      hnsw_search_layer(H, P, P.row(u), (long)u, eps[i], H.efc, (uint32_t)l_c, (long)H.n, o);
+      nbh_new[i] = hnsw_prune_heuristic(H, P, o.frontier, H.cap((uint32_t)l_c));
+      eps[i].clear();
+      for (const idd& e : o.frontier) eps[i].push_back(e.first);
+    });
+    for (uint32_t i = 0; i < bs; i++)  // forward edges (:938-942)
+      if ((uint32_t)l_c <= H.level[b0 + i]) H.nbr[b0 + i][l_c] = nbh_new[i];
+    // reverse edges (:944-999): grouped by target, values in batch order
+    std::vector<uint32_t> keys;
+    std::unordered_map<uint32_t, std::vector<uint32_t>> groups;
+    for (uint32_t i = 0; i < bs; i++) {
+      if ((uint32_t)l_c > H.level[b0 + i]) continue;
+      for (uint32_t pv : nbh_new[i]) {
+        auto it = groups.find(pv);
+        if (it == groups.end()) { keys.push_back(pv); it = groups.emplace(pv, std::vector<uint32_t>()).first; }
+        it->second.push_back(b0 + i);
+      }
+    }
+    par_for(0, keys.size(), nthreads, [&](size_t j) {
+      const uint32_t pv = keys[j];
+      std::vector<uint32_t>& nb = H.nbr[pv][l_c];
+      const std::vector<uint32_t>& add = groups.find(pv)->second;
+      const uint32_t cap = H.cap((uint32_t)l_c);
+      if (nb.size() + add.size() > cap) {  // :963-987: keep the cap closest of old + new (plain sort by distance)
+        std::vector<idd> c;
+        for (uint32_t x : nb) c.push_back(idd(x, dist_rows(P.dtype, P.metric, P.row(x), P.row(pv), P.d)));
+        for (uint32_t x : add) c.push_back(idd(x, dist_rows(P.dtype, P.metric, P.row(x), P.row(pv), P.d)));
+        std::stable_sort(c.begin(), c.end(), [](const idd& a, const idd& b) { return a.second < b.second; });
+        nb.resize(cap);
+        for (uint32_t k = 0; k < cap; k++) nb[k] = c[k].first;
+      } else {
+        nb.insert(nb.end(), add.begin(), add.end());
+      }
+    });
+  }
+  // entrance update (:1002-1013): first node of the batch with the highest level
+  uint32_t hi = b0;
+  for (uint32_t u = b0; u < b1; u++) if (H.level[u] > H.level[hi]) hi = u;
+  if (H.level[hi] > level_ep) H.entrance.assign(1, hi);
+  else if (H.level[hi] == level_ep) H.entrance.push_back(hi);
 }
 
 }  // namespace
@@ -546,4 +660,97 @@ int oracle_rerank(int dtype, int metric, const void* base, uint64_t n, uint32_t 
   });
   return bad;
 }
+
+// ---- HNSW entry points.  The model travels as flat arrays: level[n]; adjacency in the model file's own order (for each node,
+// for l = 0..level: a count, then ids), as `counts` (one per (node, level)) and `edges`; the entrance list.
+// oracle_hnsw_build: HNSW(begin, end, dim, m_l, m, efc, alpha) (HNSW.hpp:746-824) with the levels of a single worker.
+// Returns the number of edges; call with edges == NULL first to size the buffers (counts needs sum(level)+n entries).
+static Hnsw g_hnsw;   // the last built / loaded model (one at a time: test infrastructure)
+static void hnsw_export(const Hnsw& H, uint32_t* level, uint64_t* counts, uint32_t* edges, uint32_t* entrance, uint64_t* sizes) {
+  uint64_t nc = 0, ne = 0;
+  for (uint32_t v = 0; v < H.n; v++) {
+    if (level) level[v] = H.level[v];
+    for (uint32_t l = 0; l <= H.level[v]; l++) {
+      if (counts) counts[nc] = H.nbr[v][l].size();
+      nc++;
+      for (uint32_t x : H.nbr[v][l]) { if (edges) edges[ne] = x; ne++; }
+    }
+  }
+  if (entrance) for (size_t i = 0; i < H.entrance.size(); i++) entrance[i] = H.entrance[i];
+  sizes[0] = nc; sizes[1] = ne; sizes[2] = H.entrance.size();
+}
+int oracle_hnsw_build(int dtype, int metric, const void* points, uint64_t n, uint32_t d, uint64_t stride, float m_l, uint32_t m,
+                      uint32_t efc, float alpha, const uint32_t* levels_in, uint64_t* sizes, int nthreads) {
+  PointSet P{dtype, metric, (const uint8_t*)points, n, d, stride};
+  Hnsw& H = g_hnsw;
+  H = Hnsw();
+  H.dim = d; H.m = m; H.efc = efc; H.n = (uint32_t)n; H.m_l = m_l; H.alpha = alpha;
+  H.level.resize(n); H.nbr.resize(n);
+  HnswLevels L;
+  for (uint64_t i = 0; i < n; i++) H.level[i] = levels_in ? levels_in[i] : L.next(m_l);   // node order = draw order on one worker
+  H.nbr[0].assign(H.level[0] + 1, {});
+  H.entrance.assign(1, 0);
+  uint32_t batch_begin = 0, batch_end = 1, size_limit = (uint32_t)(n * 0.02);  // :771
+  while (batch_end < n) {  // :773-799, batch_base = 2
+    batch_begin = batch_end;
+    batch_end = std::min({(uint32_t)n, (uint32_t)std::ceil(batch_begin * 2.0f) + 1, batch_begin + size_limit});
+    hnsw_insert(H, P, batch_begin, batch_end, nthreads);
+  }
+  hnsw_export(H, nullptr, nullptr, nullptr, nullptr, sizes);
+  return 0;
+}
+void oracle_hnsw_export(uint32_t* level, uint64_t* counts, uint32_t* edges, uint32_t* entrance) {
+  uint64_t sizes[3];
+  hnsw_export(g_hnsw, level, counts, edges, entrance, sizes);
+}
+void oracle_hnsw_import(uint32_t n, uint32_t dim, float m_l, uint32_t m, uint32_t efc, float alpha, const uint32_t* level,
+                        const uint64_t* counts, const uint32_t* edges, const uint32_t* entrance, uint64_t nent) {
+  Hnsw& H = g_hnsw;
+  H = Hnsw();
+  H.dim = dim; H.m = m; H.efc = efc; H.n = n; H.m_l = m_l; H.alpha = alpha;
+  H.level.assign(level, level + n); H.nbr.resize(n);
+  uint64_t nc = 0, ne = 0;
+  for (uint32_t v = 0; v < n; v++) {
+    H.nbr[v].resize(level[v] + 1);
+    for (uint32_t l = 0; l <= level[v]; l++) { H.nbr[v][l].assign(edges + ne, edges + ne + counts[nc]); ne += counts[nc]; nc++; }
+  }
+  H.entrance.assign(entrance, entrance + nent);
+}
+// HNSW::search (:1570-1613) for every query: ef = 1 descent from the entrances to level 1 (search_layer_to :1545-1568), then
+// search_layer(ef) on level 0; the result is cut to k plus the entries tied with the k-th distance.  out_* hold up to `ocap`
+// entries per query, out_cnt the number the reference returns, out_cmps the summed distance comparisons of all layers.
+int oracle_hnsw_search(int dtype, int metric, const void* points, uint64_t stride, const void* queries, uint64_t nq, uint64_t qstride,
+                       uint32_t k, uint32_t ef, long limit, uint32_t ocap, uint32_t* out_ids, float* out_dists, uint32_t* out_cnt,
+                       uint32_t* out_cmps, int nthreads) {
+  const Hnsw& H = g_hnsw;
+  PointSet P{dtype, metric, (const uint8_t*)points, H.n, H.dim, stride};
+  par_for(0, nq, nthreads, [&](size_t i) {
+    const void* q = (const uint8_t*)queries + i * qstride;
+    std::vector<uint32_t> eps = H.entrance;
+    size_t cmps = 0;
+    for (uint32_t l = H.level[H.entrance[0]]; l > 0; --l) {
+      SearchOut o;
+      hnsw_search_layer(H, P, q, -1, eps, 1, l, (long)H.n, o);   // limit_eval is not passed down (:1553-1556)
+      cmps += o.cmps;
+      eps.assign(1, o.frontier[0].first);
+    }
+    SearchOut o;
+    hnsw_search_layer(H, P, q, -1, eps, ef, 0, limit > 0 ? limit : (long)H.n, o);
+    cmps += o.cmps;
+    std::vector<idd> R = o.frontier;
+    uint32_t kk = k;
+    if (R.size() > k) {  // :1594-1600: sorted by distance; everything tied with the k-th stays
+      std::stable_sort(R.begin(), R.end(), [](const idd& a, const idd& b) { return a.second < b.second; });
+      if (k > 0) { kk = k; while (kk < R.size() && !(R[k - 1].second < R[kk].second)) kk++; }
+      R.resize(kk);
+    }
+    out_cnt[i] = (uint32_t)R.size();
+    out_cmps[i] = (uint32_t)cmps;
+    for (size_t j = 0; j < R.size() && j < ocap; j++) { out_ids[i * ocap + j] = R[j].first; out_dists[i * ocap + j] = R[j].second; }
+  });
+  return 0;
+}
+// the level sequence of one worker (get_level_random, HNSW.hpp:505-516)
+void oracle_hnsw_levels(uint64_t n, float m_l, uint32_t* out) { HnswLevels L; for (uint64_t i = 0; i < n; i++) out[i] = L.next(m_l); }
+
 }  // extern "C"

@@ -530,7 +530,7 @@ static int search_pipelined(pann_index* idx, const uint8_t* host_queries, uint64
   return check_status(flag);
 }
 
-static int upload_queries(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes) {
+int pann_upload_queries(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes) {
   const size_t rowb = (size_t)idx->dims * idx->geom.elt;
   if (q_stride_bytes < rowb) PANN_FAIL("query stride smaller than a row");
   if (idx->queries.reserve((size_t)nq * idx->geom.stride + 16)) return 1;
@@ -546,7 +546,7 @@ static int upload_queries(pann_index* idx, const void* host_queries, uint64_t nq
 extern "C" int pann_queries_upload(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes) {
   if (!idx || !host_queries) PANN_FAIL("pann_queries_upload: null argument");
   PANN_CUDA(cudaSetDevice(idx->device));
-  if (upload_queries(idx, host_queries, nq, q_stride_bytes)) return 1;
+  if (pann_upload_queries(idx, host_queries, nq, q_stride_bytes)) return 1;
   PANN_CUDA(cudaStreamSynchronize(idx->stream));
   return 0;
 }
@@ -629,7 +629,7 @@ extern "C" int pann_search_batch(pann_index* idx, const void* host_queries, uint
       if (rc != 2) return rc;   // 2: a visited list outgrew shared memory somewhere: take the plain path, which retries those queries
     }
   }
-  if (upload_queries(idx, host_queries, nq, q_stride_bytes)) return 1;
+  if (pann_upload_queries(idx, host_queries, nq, q_stride_bytes)) return 1;
   bool delivered = false;
   if (search_common(idx, idx->queries.as<uint8_t>(), nq, idx->geom.stride, starts, nstarts, qp, host_out, &delivered)) return 1;
   return delivered ? 0 : fetch_results(idx, out_ids, out_dists, out_visited, out_cmps);
@@ -667,7 +667,7 @@ extern "C" int pann_search_batch_starts(pann_index* idx, const void* host_querie
   if (nq == 0) return 0;
   SearchOutputs pq;
   if (upload_starts(idx, nq, starts, starts_stride, nstarts_q, pq)) return 1;
-  if (upload_queries(idx, host_queries, nq, q_stride_bytes)) return 1;
+  if (pann_upload_queries(idx, host_queries, nq, q_stride_bytes)) return 1;
   void* const host_out[4] = {out_ids, out_dists, out_visited, out_cmps};
   bool delivered = false;
   if (search_common(idx, idx->queries.as<uint8_t>(), nq, idx->geom.stride, nullptr, starts_stride, qp, host_out, &delivered, &pq)) return 1;
@@ -703,7 +703,7 @@ static int search_full_impl(pann_index* idx, const void* host_queries, uint64_t 
     d_self = (uint32_t*)m;
     PANN_CUDA(cudaMemcpyAsync(d_self, self_ids, 4ull * nq, cudaMemcpyHostToDevice, idx->stream));
   } else {
-    if (upload_queries(idx, host_queries, nq, q_stride_bytes)) return 1;
+    if (pann_upload_queries(idx, host_queries, nq, q_stride_bytes)) return 1;
     d_q = idx->queries.as<uint8_t>();
   }
   int flag = 0;
@@ -764,8 +764,8 @@ extern "C" int pann_search_rerank_batch(pann_index* q_idx, pann_index* base_idx,
   PANN_CUDA(cudaSetDevice(q_idx->device));
   if (nq == 0) return 0;
   // 1. the search over the quantised copy, whole frontier kept on the device
-  if (upload_queries(q_idx, host_qqueries, nq, qq_stride_bytes)) return 1;
-  if (upload_queries(base_idx, host_queries, nq, q_stride_bytes)) return 1;
+  if (pann_upload_queries(q_idx, host_qqueries, nq, qq_stride_bytes)) return 1;
+  if (pann_upload_queries(base_idx, host_queries, nq, q_stride_bytes)) return 1;
   PANN_CUDA(cudaStreamSynchronize(base_idx->stream));
   const uint32_t k = (uint32_t)qp->k, fcap = (uint32_t)qp->beam;
   size_t need = 4ull * nq * fcap * 2 + 4ull * nq * 4 + 8ull * nq * k + 256;

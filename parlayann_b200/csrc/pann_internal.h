@@ -82,6 +82,7 @@ int pann_run_search(pann_index* idx, const uint8_t* d_queries, uint64_t nq, uint
                     const uint32_t* h_starts, uint32_t nstarts, const pann_query_params* qp, const SearchOutputs& out,
                     int* status_or);
 int pann_pinned(pann_index* idx, size_t bytes, void** p);
+int pann_upload_queries(pann_index* idx, const void* host_queries, uint64_t nq, uint64_t q_stride_bytes);   // -> idx->queries (async on idx->stream)
 int pann_gen_rows_device(int kind, uint64_t seed, uint64_t stream, uint64_t row0, uint64_t nrows, uint32_t d, uint32_t r,
                          uint32_t nc, void* dev_out, uint64_t stride, cudaStream_t s);
 void pann_host_random_permutation(int64_t n, int32_t* out);

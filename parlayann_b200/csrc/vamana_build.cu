@@ -14,14 +14,15 @@
 #include <stdio.h>
 #include "pann_internal.h"
 #include "vamana_prune.cuh"
+#include "vamana_build.h"
 
 __global__ void pann_write_rows_kernel(uint32_t* graph, uint32_t maxdeg, uint32_t R, uint64_t n, const uint32_t* perm_lo,
-                                       const uint32_t* new_out, const uint32_t* new_deg, uint32_t bs, u64* keys) {
+                                       const uint32_t* new_out, const uint32_t* new_deg, uint32_t bs, u64* keys, const uint32_t* rowmap) {
   uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= (uint64_t)bs * R) return;
   uint32_t i = (uint32_t)(t / R), pos = (uint32_t)(t % R);
   uint32_t p = perm_lo[i], deg = new_deg[i];
-  uint32_t* row = graph + (uint64_t)p * (maxdeg + 1);
+  uint32_t* row = graph + (uint64_t)(rowmap ? rowmap[p] : p) * (maxdeg + 1);
   if (pos == 0) row[0] = deg;
   if (pos < deg) {
     uint32_t nb = new_out[t];
@@ -38,6 +39,10 @@ __global__ void pann_find_heads_kernel(const u64* sorted, uint32_t ns, uint64_t 
   uint32_t t = (uint32_t)(sorted[j] >> 32);
   if (t >= n) return;
   if (j == 0 || (uint32_t)(sorted[j - 1] >> 32) != t) gstart[atomicAdd(ngroups, 1u)] = j;
+}
+
+int pann_sort_keys(void* tmp, size_t& tmp_bytes, const u64* in, u64* out, int64_t nk, int bits, cudaStream_t s) {
+  return cub::DeviceRadixSort::SortKeys(tmp, tmp_bytes, in, out, nk, 0, bits, s) == cudaSuccess ? 0 : 1;
 }
 
 static const void* prune_kernel(int dtype, int metric, int qr, bool gs) {
@@ -69,7 +74,7 @@ static inline uint32_t al16(size_t x) { return (uint32_t)((x + 15) / 16 * 16); }
 // host synchronisation: the second launch reads its task count on the device (it is usually zero and the CTAs leave at
 // once); its slab has a fixed capacity per warp, and a list beyond even that raises gs_overflow, read once after the build.
 #define PANN_PRUNE_SLAB_CAP_DEFAULT 8192u
-static int launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevBuf& big, DevBuf& gscratch, int* gs_overflow) {
+int pann_launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevBuf& big, DevBuf& gscratch, int* gs_overflow) {
   const PannRowGeom& g = idx->geom;
   const int qrT = pann_qr_of(g);
   if (ntasks_bound == 0) return 0;
@@ -248,11 +253,11 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
       A.vis_ids = d_vis_ids.as<uint32_t>(); A.vis_dists = d_vis_dists.as<float>(); A.nvis = c_nvis; A.search_cmps = c_cmps; A.vout = vout;
       A.new_out = d_new_out.as<uint32_t>(); A.new_deg = c_newdeg;
       A.acct = d_acct.as<u64>(); A.rowbytes = idx->dims * idx->geom.elt;
-      if (launch_prune(idx, A, bs, d_big, d_gscr, gs_overflow)) { rc = 1; break; }
+      if (pann_launch_prune(idx, A, bs, d_big, d_gscr, gs_overflow)) { rc = 1; break; }
       // ---- phase 2: rows of the inserted points + reverse-edge keys
       const uint64_t nk = (uint64_t)bs * R;
       pann_write_rows_kernel<<<(unsigned)((nk + 255) / 256), 256, 0, s>>>(idx->graph, md, R, n, perm_lo, d_new_out.as<uint32_t>(),
-                                                                       c_newdeg, bs, d_keys.as<u64>());
+                                                                       c_newdeg, bs, d_keys.as<u64>(), nullptr);
       idx->last_launches++;
       cudaEventRecord(ev[1], s);
       // ---- phase 3a: group the reverse edges by target, values in batch order (index.h:278-282)
@@ -268,7 +273,7 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
       // ---- phase 3b: per target, append or prune (index.h:289-300)
       A.mode = 1; A.ntasks = (uint32_t)nk;
       A.sorted = d_keys2.as<u64>(); A.nsorted = (uint32_t)nk; A.gstart = d_gstart.as<uint32_t>(); A.ngroups = c_ngroups;
-      if (launch_prune(idx, A, (uint32_t)std::min<uint64_t>(nk, n), d_big, d_gscr, gs_overflow)) { rc = 1; break; }
+      if (pann_launch_prune(idx, A, (uint32_t)std::min<uint64_t>(nk, n), d_big, d_gscr, gs_overflow)) { rc = 1; break; }
       cudaEventRecord(ev[3], s);
     }
   }

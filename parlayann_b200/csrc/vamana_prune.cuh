@@ -22,6 +22,12 @@ struct PruneArgs {
   uint32_t* graph; uint32_t maxdeg, R;
   uint64_t n;
   double alpha;
+  // rule 0: Vamana's robustPrune (vamana/index.h:63-120).  rule 1: HNSW's prune_heuristic (HNSW/HNSW.hpp:430-486): a later
+  // candidate c dies when d(c, r) < alpha_f * d(c, u) for a kept r (float product, strict <).  rule 2: HNSW's reverse-edge
+  // trim (HNSW.hpp:963-987): the R closest of old + new neighbours, no occlusion test; and in mode 1 the list that fits is
+  // old neighbours followed by the new ones (:989), not Vamana's new-then-old-without-repeats.
+  int rule; float alpha_f;
+  const uint32_t* rowmap;   // optional vertex id -> graph row (HNSW's compacted upper layers); null = identity
   int mode;                 // 0: phase 1 (visited lists -> new_out), 1: phase 3 (reverse-edge groups -> graph rows)
   uint32_t ntasks;          // mode 0: batch size; mode 1: upper bound (real count read from *ngroups)
   const uint32_t* perm_lo;  // insertion order, already offset to the batch: task i inserts perm_lo[i]
@@ -44,6 +50,12 @@ struct PruneArgs {
   // row cache (shared memory): the rows of up to rc_rows candidates, rc_pitch bytes apart, and their slot numbers
   uint32_t rc_rows, rc_pitch, off_rc, off_pos;
 };
+
+// does the picked vertex (at distance d_sc from candidate c) remove c, which is at distance d_c from the pruned vertex?
+__device__ __forceinline__ bool pann_occludes(const PruneArgs& A, float d_sc, float d_c) {
+  if (A.rule == 0) return A.alpha * (double)d_sc <= (double)d_c;   // vamana/index.h:111, evaluated in double
+  return d_sc < d_c * A.alpha_f;                                    // HNSW.hpp:456-469, float
+}
 
 template <int DT, int METRIC, int QR, bool GS>
 __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const PruneArgs A) {
@@ -82,7 +94,7 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
       while (lo < hi) { uint32_t mid = (lo + hi) >> 1; if ((uint32_t)(A.sorted[mid] >> 32) <= p) lo = mid + 1; else hi = mid; }
       nc = lo - g0;
     }
-    uint32_t* grow = A.graph + (u64)p * (A.maxdeg + 1);
+    uint32_t* grow = A.graph + (u64)(A.rowmap ? A.rowmap[p] : p) * (A.maxdeg + 1);
     const uint32_t deg = grow[0];
     const uint32_t C0 = nc + deg;
     if (C0 > A.cap) {
@@ -94,6 +106,12 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
       continue;
     }
     // ---- reverse edges that fit: new ones first, then the old ones not among them (index.h:291-294, :140-146)
+    if (A.mode == 1 && C0 <= A.R && A.rule == 2) {   // HNSW: nbh_v.insert(end, new ones) (HNSW.hpp:989)
+      for (uint32_t i = lane; i < nc; i += 32) grow[1 + deg + i] = A.perm_lo[(uint32_t)A.sorted[g0 + i] / A.R];
+      if (lane == 0) grow[0] = C0;
+      __syncwarp();
+      continue;
+    }
     if (A.mode == 1 && C0 <= A.R) {
       for (uint32_t i = lane; i < nc; i += 32) cid[i] = A.perm_lo[(uint32_t)A.sorted[g0 + i] / A.R];
       __syncwarp();
@@ -193,7 +211,10 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
     uint32_t* outp = A.mode == 0 ? A.new_out + (u64)task * A.R : grow + 1;
     int start = 0, n = C;
     uint32_t m = 0;
-    if (!GS && A.rc_rows && C <= (int)A.rc_rows) {
+    if (A.rule == 2) {   // the R closest, in order (HNSW.hpp:976-980)
+      m = (uint32_t)min(C, (int)A.R);
+      for (uint32_t i = lane; i < m; i += 32) outp[i] = pann_key_id(S[i]);
+    } else if (!GS && A.rc_rows && C <= (int)A.rc_rows) {
       // Row cache: every candidate row is fetched ONCE (all gathers in flight together) into shared memory; the scan
       // below — up to R picks, each a pass over the live candidates — then never leaves the SM.  Without it each pick
       // costs two dependent trips to L2/HBM (the picked row, then the live rows), ~130 per pruned vertex.
@@ -247,7 +268,7 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
             }
           }
           const float d = acc.result();
-          const bool keep = ok && !(A.alpha * (double)d <= (double)pann_key_dist(key));  // :111
+          const bool keep = ok && !pann_occludes(A, d, pann_key_dist(key));  // :111
           const unsigned km = __ballot_sync(PANN_FULL, keep);
           if (keep) { const int o = w + __popc(km & lt_mask); S[o] = key; P[o] = slot; }
           w += __popc(km);
@@ -270,7 +291,7 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
       int w = start;
       pann_row_distances_g<DT, METRIC, QR>(
           A, [&](int r) { return S[start + r]; }, cnt, qsm, lane, [&](u64 key, float d, bool ok) {
-            bool keep = ok && !(A.alpha * (double)d <= (double)pann_key_dist(key));  // :111
+            bool keep = ok && !pann_occludes(A, d, pann_key_dist(key));  // :111
             unsigned km = __ballot_sync(PANN_FULL, keep);
             if (keep) S[w + __popc(km & lt_mask)] = key;
             w += __popc(km);

@@ -226,3 +226,75 @@ def search_rerank(points, qpoints, graph, queries, qqueries, data_type="float", 
     if rc:
         raise RuntimeError("oracle: a query returned fewer than k results (the reference aborts here)")
     return dict(ids=ids, dists=dists, visited=r["visited"], cmps=r["cmps"])
+
+
+# ---- HNSW (algorithms/HNSW/HNSW.hpp): our C++ restatement, and the reference itself (oracle/_ref/ref_hnsw)
+def hnsw_build(points, data_type, metric, m, efc, m_l=0.36, alpha=1.0, levels=None):
+    """-> parlayann_b200.hnsw_file.HnswModel built by the oracle (levels of one worker unless given)"""
+    from parlayann_b200.hnsw_file import HnswModel
+    points = np.ascontiguousarray(points)
+    n, d = points.shape
+    sizes = np.zeros(3, np.uint64)
+    lv = None if levels is None else np.ascontiguousarray(levels, dtype=np.uint32)
+    lib().oracle_hnsw_build(DT[data_type], METRIC[metric], _p(points), C.c_uint64(n), C.c_uint32(d), C.c_uint64(points.strides[0]),
+                            C.c_float(m_l), C.c_uint32(m), C.c_uint32(efc), C.c_float(alpha), _p(lv), _p(sizes), nthreads())
+    level = np.zeros(n, np.uint32); counts = np.zeros(int(sizes[0]), np.uint64); edges = np.zeros(int(sizes[1]), np.uint32)
+    ent = np.zeros(int(sizes[2]), np.uint32)
+    lib().oracle_hnsw_export(_p(level), _p(counts), _p(edges), _p(ent))
+    return HnswModel(d, m_l, m, efc, alpha, level, counts, edges, ent)
+
+
+def hnsw_levels(n, m_l):
+    out = np.zeros(n, np.uint32)
+    lib().oracle_hnsw_levels(C.c_uint64(n), C.c_float(m_l), _p(out))
+    return out
+
+
+def hnsw_search(model, points, queries, data_type, metric, k=10, ef=50, limit=-1):
+    """HNSW::search over `model` -> dict(ids [nq, ef], dists, cnt, cmps); cnt = entries the reference returns (k + ties)"""
+    M = model
+    lib().oracle_hnsw_import(C.c_uint32(M.n), C.c_uint32(M.dim), C.c_float(M.m_l), C.c_uint32(M.m), C.c_uint32(M.efc), C.c_float(M.alpha),
+                             _p(M.level), _p(M.counts), _p(M.edges), _p(M.entrance), C.c_uint64(len(M.entrance)))
+    points = np.ascontiguousarray(points); queries = np.ascontiguousarray(queries)
+    nq = queries.shape[0]
+    ids = np.zeros((nq, ef), np.uint32); dists = np.zeros((nq, ef), np.float32)
+    cnt = np.zeros(nq, np.uint32); cmps = np.zeros(nq, np.uint32)
+    lib().oracle_hnsw_search(DT[data_type], METRIC[metric], _p(points), C.c_uint64(points.strides[0]), _p(queries), C.c_uint64(nq),
+                             C.c_uint64(queries.strides[0]), C.c_uint32(k), C.c_uint32(ef), C.c_long(limit), C.c_uint32(ef),
+                             _p(ids), _p(dists), _p(cnt), _p(cmps), nthreads())
+    return dict(ids=ids, dists=dists, cnt=cnt, cmps=cmps)
+
+
+def ref_hnsw_path():
+    p = os.path.join(ORACLE_DIR, "_ref", "ref_hnsw")
+    try:
+        if os.path.exists(p) and subprocess.run([p, "selftest"], capture_output=True, timeout=60).returncode == 0:
+            return p
+    except Exception:
+        pass
+    return None
+
+
+def ref_hnsw_run(args, threads=None):
+    p = ref_hnsw_path()
+    if p is None:
+        raise RuntimeError("oracle/_ref/ref_hnsw is not available")
+    env = dict(os.environ)
+    if threads:
+        env["PARLAY_NUM_THREADS"] = str(threads)
+    r = subprocess.run([p] + [str(a) for a in args], capture_output=True, text=True, env=env)
+    if r.returncode != 0:
+        raise RuntimeError(f"ref_hnsw failed ({r.returncode}): {r.stdout[-2000:]} {r.stderr[-2000:]}")
+    return r.stdout
+
+
+def parse_hnsw_results(path, nq):
+    """ref_hnsw search output: per query u32 count, then (id, dist bits) pairs"""
+    a = np.fromfile(path, dtype=np.uint32)
+    out, pos = [], 0
+    for _ in range(nq):
+        c = int(a[pos]); pos += 1
+        pr = a[pos:pos + 2 * c].reshape(c, 2); pos += 2 * c
+        out.append((pr[:, 0].copy(), pr[:, 1].copy().view(np.float32)))
+    assert pos == a.size
+    return out

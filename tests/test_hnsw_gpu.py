@@ -1,0 +1,104 @@
+"""HNSW on the GPU (pann_hnsw_*, through the C ABI) against the reference's own HNSW (goldens made with oracle/_ref/ref_hnsw at
+one thread, where its level assignment is deterministic) and against the oracle at larger sizes:
+  * search over the reference-built model: ids, distances, result counts (k + ties) and distance-comparison counts equal;
+  * build with the single-worker level sequence: for float data the MODEL FILE is byte-identical to the reference's; for
+    integer data (tied distances, which the reference orders with non-stable sorts) levels, list sizes and entrances are
+    identical and all but a handful of lists are equal as sets;
+  * recall of the built index against exact ground truth (the gate the reference's nondeterministic builds allow)."""
+import numpy as np
+import pytest
+
+import oracle_lib as O
+from hnsw_util import HNSW_CASES, HNSW_SEARCHES, HnswGolden, same_model, check_search, model_list_mismatches
+
+pytestmark = pytest.mark.gpu
+
+
+def _hnsw(base, data_type, metric, m, efc, m_l, alpha):
+    from parlayann_b200.hnsw import HNSW
+    return HNSW(base, data_type, metric, m=m, efc=efc, m_l=m_l, alpha=alpha)
+
+
+@pytest.mark.parametrize("name", list(HNSW_CASES))
+def test_search_on_reference_model(name):
+    g = HnswGolden(name)
+    h = _hnsw(g.base, g.data_type, g.metric, g.m, g.efc, g.m_l, g.alpha)
+    h.set_model(g.model)
+    assert same_model(h.model(), g.model), "model does not survive the trip through the device layout"
+    for si, (k, ef) in enumerate(HNSW_SEARCHES):
+        rows, cmps = g.search_result(si)
+        check_search(h.search(g.queries, k=k, ef=ef, ocap=ef), rows, cmps, exact_ties=g.data_type == "float")
+    h.close()
+
+
+@pytest.mark.parametrize("name", list(HNSW_CASES))
+def test_build_reproduces_reference_model(name, tmp_path):
+    from parlayann_b200.hnsw_file import read_hnsw, write_hnsw
+    g = HnswGolden(name)
+    h = _hnsw(g.base, g.data_type, g.metric, g.m, g.efc, g.m_l, g.alpha)
+    sec = h.build()
+    assert sec[0] > 0
+    M = h.model()
+    assert np.array_equal(M.level, g.model.level) and np.array_equal(M.entrance, g.model.entrance)
+    if g.data_type == "float":
+        assert same_model(M, g.model), f"{(M.counts != g.model.counts).sum()} list sizes differ"
+        M.code_U, M.size_node = g.model.code_U, g.model.size_node      # type hash / sizeof(node): opaque to every loader
+        write_hnsw(str(tmp_path / "gpu.bin"), M); write_hnsw(str(tmp_path / "ref.bin"), g.model)
+        assert open(str(tmp_path / "gpu.bin"), "rb").read() == open(str(tmp_path / "ref.bin"), "rb").read()
+    else:
+        assert model_list_mismatches(M, g.model) <= 5 and (M.edges != g.model.edges).mean() < 1e-3
+    h.close()
+
+
+@pytest.mark.parametrize("data_type,metric,n,d,m,efc,m_l,alpha,r,nc", [
+    ("float", "mips", 20000, 200, 16, 64, 0.36, 1.0, 32, 1),        # C5's row shape
+    ("float", "Euclidian", 12000, 96, 24, 100, 1.0, 1.2, 24, 256),  # efc > 90: global-scratch beam search; many levels
+    ("float", "Euclidian", 6000, 128, 8, 24, 0.3, 0.9, 24, 256),    # efc <= 32: narrow-beam kernel for the insert searches too
+])
+def test_build_and_search_match_oracle(data_type, metric, n, d, m, efc, m_l, alpha, r, nc):
+    base = O.gen_points(data_type, n, d, r=r, nc=nc)
+    qs = O.gen_points(data_type, 300, d, stream=1, r=r, nc=nc)
+    H = O.hnsw_build(base, data_type, metric, m, efc, m_l, alpha)
+    h = _hnsw(base, data_type, metric, m, efc, m_l, alpha)
+    h.build()
+    M = h.model()
+    assert same_model(M, H), f"levels {np.array_equal(M.level, H.level)} sizes differ in {(M.counts != H.counts).sum()} lists"
+    for k, ef in ((10, 10), (10, 64), (1, 33)):
+        r_ = O.hnsw_search(H, base, qs, data_type, metric, k=k, ef=ef)
+        ids, dists, cnt, cmps = h.search(qs, k=k, ef=ef, ocap=ef)
+        assert np.array_equal(cnt, r_["cnt"]) and np.array_equal(cmps, r_["cmps"])
+        for i in range(len(qs)):
+            c = cnt[i]
+            assert np.array_equal(ids[i, :c], r_["ids"][i, :c]) and np.array_equal(dists[i, :c], r_["dists"][i, :c])
+    h.close()
+
+
+def test_build_recall_u8(dataset):
+    # integer data: recall@10 of the GPU-built index against exact ground truth, next to the oracle-built one (within 0.2 %)
+    from parlayann_b200.harness import recall_with_ties
+    ds = dataset("uint8", n=20000, d=128, nq=500)
+    gi, gd = O.groundtruth(ds.base, ds.queries, "uint8", k=10)
+    h = _hnsw(ds.base, "uint8", "Euclidian", 16, 64, 0.36, 1.0)
+    h.build()
+    ids, _, cnt, _ = h.search(ds.queries, k=10, ef=64)
+    assert (cnt >= 10).all()
+    H = O.hnsw_build(ds.base, "uint8", "Euclidian", 16, 64, 0.36, 1.0)
+    ro = O.hnsw_search(H, ds.base, ds.queries, "uint8", "Euclidian", k=10, ef=64)
+    rg, rr = recall_with_ties(ids, gi, gd, 10), recall_with_ties(ro["ids"][:, :10], gi, gd, 10)
+    assert rg > 0.9 and abs(rg - rr) < 0.002, (rg, rr)
+    h.close()
+
+
+def test_save_load_roundtrip(tmp_path):
+    from parlayann_b200 import fileio
+    from parlayann_b200.hnsw import build_hnsw_index, load_hnsw_index
+    base = O.gen_points("float", 4000, 64)
+    qs = O.gen_points("float", 100, 64, stream=1)
+    fileio.write_bin(str(tmp_path / "b.fbin"), base)
+    h = build_hnsw_index("Euclidian", "float", str(tmp_path / "b.fbin"), str(tmp_path / "m.hnsw"), 12, 48, 1.0)
+    a = h.search(qs, k=10, ef=40)
+    h2 = load_hnsw_index("Euclidian", "float", str(tmp_path / "b.fbin"), str(tmp_path / "m.hnsw"))
+    b = h2.search(qs, k=10, ef=40)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
+    h.close(); h2.close()
