@@ -25,7 +25,7 @@ class HnswGolden:
 
     def search_result(self, si):
         cnt = self.z[f"s{si}_cnt"]
-        off = np.concatenate([[0], np.cumsum(cnt)])
+        off = np.concatenate([[0], np.cumsum(cnt.astype(np.int64))])
         ids, dists = self.z[f"s{si}_ids"], self.z[f"s{si}_dists"]
         return [(ids[off[i]:off[i + 1]], dists[off[i]:off[i + 1]]) for i in range(self.nq)], self.z[f"s{si}_cmps"]
 
