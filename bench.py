@@ -23,6 +23,7 @@ against exact ground truth from K4: the cheapest setting whose tie-aware recall@
             timed next to the GPU build at the largest n that fits ~1 CPU-minute
   groundtruth   K4 over the recall batch (tensor roofline, CPU baseline on a 1 000-query sample)
   groundtruth_c3  BASELINE configs[2]: 10 000 x 10M x 96 f32, k=100, base rows sharded over the N ranks, NCCL merge
+  hnsw_c5   BASELINE configs[4]: HNSW build + search, 1M x 200 f32 inner product, with the reference's HNSW on the host cores
   cpu_baseline  the unmodified reference's qsearchAll on this box's cores, same graph / queries / QueryParams
 
 `--impl reference` times only the reference's CPU search (10 000-query sample per step).  Up to 2M points it also builds
@@ -342,6 +343,102 @@ def groundtruth_c3(D, rank, local_rank, world, n=10_000_000, d=96, nq=10_000, k=
             "checksum": int(gi.astype(np.int64).sum() % 1000003), "dist_checksum": float(gd.astype(np.float64).sum())}
 
 
+def hnsw_c5(args, local_rank, with_cpu=True, n=1_000_000, d=200, nq=10_000, m=32, efc=128, m_l=0.36, alpha=1.2):
+    """BASELINE configs[4]: HNSW build + search, synthetic 1M x 200 float inner product (Text2Image-shaped: latent r = 32, no
+    clusters).  Build on the GPU (pann_hnsw_build, HNSW.hpp:746-1014), exact ground truth from K4, the smallest ef of a fixed
+    list whose recall@10 is >= 0.95, search timed device-side and end to end; next to it the reference's own HNSW on the host
+    cores: its search over the SAME model file (ids compared per query) and its build on a bounded prefix of the points."""
+    import parlayann_b200 as P
+    from parlayann_b200 import fileio
+    from parlayann_b200.hnsw import HNSW
+    peaks = load_peaks()
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    gen = dict(d=d, kind="float", seed=1234, stream=0, r=32, nc=1)
+    h = HNSW(None, "float", "mips", m=m, efc=efc, m_l=m_l, alpha=alpha, device=local_rank, synthetic=dict(n=n, **gen))
+    h.build()                                  # warm-up (allocations, module load)
+    t0 = time.time()
+    sec = h.build()
+    build_s = time.time() - t0
+    M = h.model()
+    h.index.synthetic_queries(nq, kind="float", seed=1234, stream=1, r=32, nc=1)
+    qs = h.index.download_queries()
+    h.index.groundtruth_resident(k=100)
+    gi, gd = h.index.fetch_groundtruth()
+    chosen = None
+    for ef in (10, 12, 14, 16, 20, 24, 28, 32, 40, 50, 64, 80, 100, 128, 160, 200):
+        ids, dists, cnt, cmps = h.search(qs, k=10, ef=ef)
+        rec = recall_with_ties(ids, gi.astype(np.uint32), gd, K)
+        if rec >= 0.95:
+            chosen = (ef, rec)
+            break
+    if chosen is None:
+        chosen = (ef, rec)
+    ef, rec = chosen
+    dev, e2e = [], []
+    for i in range(3 + 10):
+        t0 = time.perf_counter()
+        ids, dists, cnt, cmps = h.search(qs, k=10, ef=ef)
+        if i >= 3:
+            e2e.append((time.perf_counter() - t0) * 1e3); dev.append(h.index.last_timing()[0])
+    dev_ms, e2e_ms = float(np.mean(dev)), float(np.mean(e2e))
+    abytes = float(cmps.astype(np.int64).sum()) * d * 4 + nq * (d * 4 + 4 * K)
+    out = {"what": f"HNSW {n} x {d} f32 inner product, m={m} efc={efc} m_l={m_l} alpha={alpha}; {nq} queries, k=10",
+           "build": {"seconds": build_s, "phase_seconds": {"layer_searches": sec[1], "prune_heuristic+forward": sec[2], "reverse_edges": sec[3]},
+                     "levels": np.bincount(M.level).tolist(), "entrances": int(len(M.entrance)), "edges": int(len(M.edges))},
+           "search": {"ef": int(ef), "recall10": round(rec, 6), "value": nq / (dev_ms * 1e-3), "unit": "queries/s", "device_ms": dev_ms, "avg_cmps": float(cmps.mean()),
+                      "e2e": {"value": nq / (e2e_ms * 1e-3), "unit": "queries/s", "ms": e2e_ms, "h2d_bytes_per_step": int(qs.nbytes),
+                              "d2h_bytes_per_step": int(2 * nq * ef * 4 + 8 * nq)},
+                      "roofline": {"bound": "hbm", "achieved": abytes / (dev_ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s", "frac": abytes / (dev_ms * 1e-3) / 1e9 / peak,
+                                   "what": "distance comparisons x row bytes (all layers) + query + result per query / device time of the 5 layer launches"}}}
+    if with_cpu:
+        try:
+            O, _ = ref_tools()
+            if O.ref_hnsw_path() is None:
+                raise RuntimeError("oracle/_ref/ref_hnsw missing")
+            tmp = tempfile.mkdtemp(prefix="pann_hnsw_")
+            try:
+                bp, qp, mp = (os.path.join(tmp, x) for x in ("base.fbin", "q.fbin", "model.hnsw"))
+                fileio.write_bin(bp, h.index.points()); fileio.write_bin(qp, qs); h.save(mp)
+                common = ["-data_type", "float", "-dist_func", "mips", "-base", bp]
+                o = O.ref_hnsw_run(["search"] + common + ["-model", mp, "-query", qp, "-k", 10, "-ef", ef, "-reps", 3, "-out", os.path.join(tmp, "s")])
+                ref_qps = float(re.search(r"REF_HNSW_SEARCH_QPS (\S+)", o).group(1))
+                rows = O.parse_hnsw_results(os.path.join(tmp, "s.res"), nq)
+                rc = np.fromfile(os.path.join(tmp, "s.cmps"), dtype=np.uint32)
+                same = sum(int(len(a) >= 10 and np.array_equal(a[:10], ids[i])) for i, (a, b) in enumerate(rows))
+                out["search"]["cpu_baseline"] = {"value": ref_qps, "unit": "queries/s", "cores": os.cpu_count(), "kind": "reference",
+                                                 "sample": f"HNSW::search of the unmodified reference (one-line unvisited_frontier fix) over the GPU-built model file, {nq} queries, best of 3"}
+                out["search"]["parity"] = {"queries": nq, "queries_with_equal_ids": int(same), "cmps_equal": bool(np.array_equal(rc, cmps))}
+                nb = min(n, args.n_hnsw_cpu)
+                pb = os.path.join(tmp, "prefix.fbin")
+                fileio.write_bin(pb, h.index.points(0, nb))
+                o = O.ref_hnsw_run(["build", "-data_type", "float", "-dist_func", "mips", "-base", pb, "-m", m, "-efc", efc, "-m_l", m_l, "-alpha", alpha, "-out", os.path.join(tmp, "pm")])
+                ref_b = float(re.search(r"REF_HNSW_BUILD_SECONDS (\S+)", o).group(1))
+                hp = HNSW(None, "float", "mips", m=m, efc=efc, m_l=m_l, alpha=alpha, device=local_rank, synthetic=dict(n=nb, **gen))
+                hp.build()
+                t0 = time.time(); hp.build(); gpu_b = time.time() - t0
+                hp.close()
+                out["build"]["cpu_baseline"] = {"value": ref_b, "unit": "s", "cores": os.cpu_count(), "kind": "reference", "n": int(nb), "gpu_seconds_same_n": gpu_b,
+                                                "sample": f"the reference's HNSW constructor over the first {nb} points, all host cores"}
+            finally:
+                shutil.rmtree(tmp, ignore_errors=True)
+        except Exception as e:
+            out["cpu_baseline_failed"] = str(e)[:300]
+    h.close()
+    return out
+
+
+def run_hnsw_workload(args, rank, local_rank, world):
+    D = Dist(local_rank, world)
+    if rank == 0:
+        r = hnsw_c5(args, local_rank, with_cpu=not args.no_cpu_baseline)
+        line = {"metric": "HNSW QPS@recall10>=0.95", "value": r["search"]["value"], "unit": "queries/s", "n_gpus": 1, "steps": 10, "warmup": 3,
+                "ms_per_step": r["search"]["device_ms"], "higher_is_better": True, "scaling": "replicas only", "vs_baseline": None, "dtype": "f32",
+                "data": "synthetic", "config": {"workload": "hnsw_1000000x200_f32_ip_10000q"}, "e2e": r["search"]["e2e"], "roofline": r["search"]["roofline"],
+                "cpu_baseline": r["search"].get("cpu_baseline"), "detail": r}
+        print(json.dumps(line), flush=True)
+    D.close()
+
+
 def run_groundtruth_workload(args, rank, local_rank, world):
     D = Dist(local_rank, world)
     r = groundtruth_c3(D, rank, local_rank, world, reps=max(2, args.steps) + 1)
@@ -517,6 +614,15 @@ def run_ours(args, rank, local_rank, world):
         except Exception as e:   # reported, never fatal for the headline
             c3 = {"failed": str(e)[:300]}
 
+    # ---- HNSW at BASELINE configs[4] (1M x 200 f32 inner product): one GPU (the build does not shard), rank 0
+    c5 = None
+    if rank == 0 and not args.no_c5:
+        try:
+            c5 = hnsw_c5(args, local_rank, with_cpu=(world == 1 and not args.no_cpu_baseline))
+        except Exception as e:
+            c5 = {"failed": str(e)[:300]}
+    barrier()
+
     if rank == 0:
         achieved = (abytes / args.steps) / (dev_ms / args.steps * 1e-3) / 1e9
         traffic = None
@@ -558,6 +664,7 @@ def run_ours(args, rank, local_rank, world):
                                              "frac": gt_ops / (gt_ms * 1e-3) / 1e12 / int8_peak, "peak_source": "2 x MEASURED_PEAKS.json bf16_tflops (int8 pipe)",
                                              "algorithmic_op": gt_ops, "kernel": "pann_gt_mma_kernel<true> (tcgen05 kind::i8) + pann_gt_shrink_kernel"}},
                 "groundtruth_c3": c3,
+                "hnsw_c5": c5,
                 "setup_seconds": setup_s}
         if world == 1 and not args.no_cpu_baseline:
             try:
@@ -649,7 +756,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="search", choices=["search", "groundtruth"])
+    ap.add_argument("--workload", default="search", choices=["search", "groundtruth", "hnsw"])
     ap.add_argument("--n", type=int, default=10000000, help="base points (BASELINE.json metric: 10M x 128 uint8; 1000000 = configs[1])")
     ap.add_argument("--nq", type=int, default=1000000, help="queries per GPU per step")
     ap.add_argument("--nq-recall", dest="nq_recall", type=int, default=10000, help="recall / sweep batch (the reference's standard query set size)")
@@ -657,6 +764,8 @@ def main():
     ap.add_argument("--profile", action="store_true", help="cudaProfilerStart/Stop around the timed device-resident steps")
     ap.add_argument("--no-cpu-baseline", dest="no_cpu_baseline", action="store_true")
     ap.add_argument("--no-c3", dest="no_c3", action="store_true", help="skip the configs[2] ground-truth measurement")
+    ap.add_argument("--no-c5", dest="no_c5", action="store_true", help="skip the configs[4] HNSW measurement")
+    ap.add_argument("--n-hnsw-cpu", dest="n_hnsw_cpu", type=int, default=100000, help="points of the reference's CPU HNSW build baseline")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -666,6 +775,8 @@ def main():
         run_reference(args, rank, world)
     elif args.workload == "groundtruth":
         run_groundtruth_workload(args, rank, local_rank, world)
+    elif args.workload == "hnsw":
+        run_hnsw_workload(args, rank, local_rank, world)
     else:
         run_ours(args, rank, local_rank, world)
 

@@ -302,7 +302,7 @@ extern "C" int pann_hnsw_build(pann_hnsw* h, const uint32_t* levels, double seco
         A.mode = 0; A.ntasks = na;
         A.vis_ids = c_fr; A.vis_dists = c_frd; A.nvis = c_nfr; A.search_cmps = c_cmps; A.vout = S;
         A.new_out = W[W_NEW].as<uint32_t>(); A.new_deg = c_newdeg;
-        if (pann_launch_prune(idx, A, na, d_big, d_gscr, gs_overflow)) { rc = 1; break; }
+        if (pann_launch_prune(idx, A, na, d_big, d_gscr, gs_overflow, 0)) { rc = 1; break; }
         // ---- forward edges (:938-942) + reverse-edge keys, grouped by target with values in batch order (:944-947)
         const uint64_t nk = (uint64_t)na * cap;
         pann_write_rows_kernel<<<nblk(nk), 256, 0, s>>>(lgraph, cap, cap, n, c_self, W[W_NEW].as<uint32_t>(), c_newdeg, na, W[W_KEYS].as<u64>(), rowmap);
@@ -314,7 +314,8 @@ extern "C" int pann_hnsw_build(pann_hnsw* h, const uint32_t* levels, double seco
         // ---- per target: append, or keep the cap closest of old + new (:949-999)
         A.rule = 2; A.mode = 1; A.ntasks = (uint32_t)nk;
         A.sorted = d_keys2.as<u64>(); A.nsorted = (uint32_t)nk; A.gstart = d_gstart.as<uint32_t>(); A.ngroups = c_ngroups;
-        if (pann_launch_prune(idx, A, (uint32_t)std::min<uint64_t>(nk, n), d_big, d_gscr, gs_overflow)) { rc = 1; break; }
+        // a hub can receive an edge from every node of the batch: the slab holds its old list plus all of them
+        if (pann_launch_prune(idx, A, (uint32_t)std::min<uint64_t>(nk, n), d_big, d_gscr, gs_overflow, na + cap)) { rc = 1; break; }
         cudaEventRecord(ev[3], s);
         idx->last_launches += 4 + (key_bits + 7) / 8;
         PANN_CUDA(cudaEventSynchronize(ev[3]));

@@ -74,7 +74,7 @@ static inline uint32_t al16(size_t x) { return (uint32_t)((x + 15) / 16 * 16); }
 // host synchronisation: the second launch reads its task count on the device (it is usually zero and the CTAs leave at
 // once); its slab has a fixed capacity per warp, and a list beyond even that raises gs_overflow, read once after the build.
 #define PANN_PRUNE_SLAB_CAP_DEFAULT 8192u
-int pann_launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevBuf& big, DevBuf& gscratch, int* gs_overflow) {
+int pann_launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevBuf& big, DevBuf& gscratch, int* gs_overflow, uint32_t slab_cap_min) {
   const PannRowGeom& g = idx->geom;
   const int qrT = pann_qr_of(g);
   if (ntasks_bound == 0) return 0;
@@ -128,7 +128,7 @@ int pann_launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevB
   }
   // candidate lists beyond the shared-memory capacity (a hub that collected ~900 reverse edges in one batch) — same
   // kernel, lists in a global scratch slab, bitonic sort
-  uint32_t slab_cap = PANN_PRUNE_SLAB_CAP_DEFAULT;
+  uint32_t slab_cap = std::max<uint32_t>(PANN_PRUNE_SLAB_CAP_DEFAULT, slab_cap_min);   // the caller's bound on a list (HNSW: a whole batch can point at one hub)
   if (const char* e = getenv("PANN_PRUNE_SLAB_CAP")) slab_cap = std::max<uint32_t>(64u, (uint32_t)atoi(e));
   { uint32_t c = 64; while (c < slab_cap) c <<= 1; slab_cap = c; }   // power of two: the long-list path sorts bitonically in place
   A.cap = slab_cap;
@@ -142,6 +142,7 @@ int pann_launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevB
   size_t cta_bytes = (size_t)A.warp_bytes * PANN_PRUNE_WARPS;
   PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
   int grid = (int)std::max<uint32_t>(1u, std::min<uint32_t>((ntasks_bound + PANN_PRUNE_WARPS - 1) / PANN_PRUNE_WARPS, (uint32_t)idx->sms));
+  grid = (int)std::max<size_t>(1, std::min<size_t>((size_t)grid, (1ull << 30) / ((size_t)PANN_PRUNE_WARPS * 2 * A.cap * 8)));   // at most 1 GB of slabs
   if (gscratch.reserve((size_t)grid * PANN_PRUNE_WARPS * 2 * A.cap * 8)) return 1;
   A.g_scratch = gscratch.as<u64>();
   void* args[] = {(void*)&A};
@@ -253,7 +254,7 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
       A.vis_ids = d_vis_ids.as<uint32_t>(); A.vis_dists = d_vis_dists.as<float>(); A.nvis = c_nvis; A.search_cmps = c_cmps; A.vout = vout;
       A.new_out = d_new_out.as<uint32_t>(); A.new_deg = c_newdeg;
       A.acct = d_acct.as<u64>(); A.rowbytes = idx->dims * idx->geom.elt;
-      if (pann_launch_prune(idx, A, bs, d_big, d_gscr, gs_overflow)) { rc = 1; break; }
+      if (pann_launch_prune(idx, A, bs, d_big, d_gscr, gs_overflow, 0)) { rc = 1; break; }
       // ---- phase 2: rows of the inserted points + reverse-edge keys
       const uint64_t nk = (uint64_t)bs * R;
       pann_write_rows_kernel<<<(unsigned)((nk + 255) / 256), 256, 0, s>>>(idx->graph, md, R, n, perm_lo, d_new_out.as<uint32_t>(),
@@ -273,7 +274,7 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
       // ---- phase 3b: per target, append or prune (index.h:289-300)
       A.mode = 1; A.ntasks = (uint32_t)nk;
       A.sorted = d_keys2.as<u64>(); A.nsorted = (uint32_t)nk; A.gstart = d_gstart.as<uint32_t>(); A.ngroups = c_ngroups;
-      if (pann_launch_prune(idx, A, (uint32_t)std::min<uint64_t>(nk, n), d_big, d_gscr, gs_overflow)) { rc = 1; break; }
+      if (pann_launch_prune(idx, A, (uint32_t)std::min<uint64_t>(nk, n), d_big, d_gscr, gs_overflow, 0)) { rc = 1; break; }
       cudaEventRecord(ev[3], s);
     }
   }

@@ -9,6 +9,7 @@ __global__ void pann_write_rows_kernel(uint32_t* graph, uint32_t maxdeg, uint32_
 // first key of every target in the sorted key list
 __global__ void pann_find_heads_kernel(const u64* sorted, uint32_t ns, uint64_t n, uint32_t* gstart, uint32_t* ngroups);
 // K3 over A's tasks: shared-memory launch + the long-list slab launch (no host synchronisation)
-int pann_launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevBuf& big, DevBuf& gscratch, int* gs_overflow);
+// slab_cap_min: the caller's bound on a candidate list (0 = the default 8192-key slabs)
+int pann_launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevBuf& big, DevBuf& gscratch, int* gs_overflow, uint32_t slab_cap_min);
 // radix sort of the reverse-edge keys (cub), bits = significant key bits
 int pann_sort_keys(void* tmp, size_t& tmp_bytes, const u64* in, u64* out, int64_t nk, int bits, cudaStream_t s);
