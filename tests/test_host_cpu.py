@@ -92,3 +92,36 @@ def test_random_starts_match_beamSearchRandom():
         r = O.search(base, g["graph"], qs, "uint8", k=k, beam=beam, starts=st.reshape(-1, 1))
         assert np.array_equal(r["ids"], g[f"r{si}_ids"])
         assert np.array_equal(r["visited"], g[f"r{si}_visited"]) and np.array_equal(r["cmps"], g[f"r{si}_distances"])
+
+
+def test_ParlayANNpy_compat_surface():
+    """parlayann_b200/compat/_ParlayANNpy.py exposes every name the reference's pybind module defines for this path
+    (python/module.cpp:50-76, :113-126, :139-176) with the reference's argument names and order"""
+    import importlib
+    import inspect
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "parlayann_b200", "compat"))
+    try:
+        m = importlib.import_module("_ParlayANNpy")
+        w = importlib.import_module("wrapper")
+    finally:
+        sys.path.pop(0)
+    for t in ("float", "uint8", "int8"):
+        for met in ("euclidian", "mips"):
+            f = getattr(m, f"build_vamana_{t}_{met}_index")
+            assert list(inspect.signature(f).parameters) == ["distance_metric", "data_file_path", "index_output_path", "graph_degree", "beam_width", "alpha", "two_pass"]
+            f = getattr(m, f"build_hnsw_{t}_{met}_index")
+            assert list(inspect.signature(f).parameters) == ["distance_metric", "data_file_path", "index_output_path", "graph_degree", "efc", "m_l", "alpha"]
+            assert hasattr(m, f"build_hcnng_{t}_{met}_index") and hasattr(m, f"build_pynndescent_{t}_{met}_index")
+    for cls in ("FloatEuclidianIndex", "FloatMipsIndex", "UInt8EuclidianIndex", "UInt8MipsIndex", "Int8EuclidianIndex", "Int8MipsIndex"):
+        c = getattr(m, cls)
+        assert list(inspect.signature(c.__init__).parameters)[1:] == ["index_path", "data_path", "hnsw"]
+        assert list(inspect.signature(c.batch_search).parameters)[1:] == ["queries", "knn", "beam_width", "quant", "visit_limit"]
+        assert list(inspect.signature(c.single_search).parameters)[1:] == ["q", "knn", "beam_width", "quant", "visit_limit"]
+        assert list(inspect.signature(c.batch_search_from_string).parameters)[1:] == ["queries", "knn", "beam_width", "quant", "visit_limit"]
+        assert list(inspect.signature(c.check_recall).parameters)[1:] == ["queries_file", "graph_file", "neighbors", "k"]
+    assert (m.defaults.METRIC, m.defaults.ALPHA, m.defaults.GRAPH_DEGREE, m.defaults.BEAMWIDTH) == ("Euclidian", 1.2, 64, 128)
+    for f in ("build_vamana_index", "build_hcnng_index", "build_pynndescent_index", "build_hnsw_index", "load_index"):
+        assert callable(getattr(w, f))
+    with pytest.raises(Exception, match="Invalid metric"):
+        w.load_index("cosine", "float", "a", "b")
