@@ -235,9 +235,18 @@ struct knn_index {
                             vis.data(), cmp.data(), phase_seconds));
     D.download_graph(G);
     parlay::parallel_for(0, n, [&](size_t i) { BuildStats.increment_visited(i, vis[i]); BuildStats.increment_dist(i, cmp[i]); });
-    std::cout << "beam search time: " << phase_seconds[0] << std::endl;
-    std::cout << "bidirect time: " << phase_seconds[1] << std::endl;
-    std::cout << "prune time: " << phase_seconds[2] << std::endl;
+    // the three phase timers as parlay::internal::timer::total() prints them (index.h:313-315; get_time.h:23-32), including
+    // its side effect: the stream's precision stays at 4 afterwards, which the recall figures of the sweep are printed with
+    auto report = [](const char* name, double seconds) {
+      std::ios::fmtflags cout_settings = std::cout.flags();
+      std::cout.precision(4);
+      std::cout << std::fixed;
+      std::cout << name << ": total: " << seconds << std::endl;
+      std::cout.flags(cout_settings);
+    };
+    report("beam search time", phase_seconds[0]);
+    report("bidirect time", phase_seconds[1]);
+    report("prune time", phase_seconds[2]);
   }
 };
 

@@ -236,7 +236,7 @@ extern "C" int pann_hnsw_build(pann_hnsw* h, const uint32_t* levels, double seco
   if (W[W_EPS].reserve(4 * max_bs * S) || W[W_NEPS].reserve(4 * max_bs) || W[W_ACT].reserve(4 * max_bs * 2) || W[W_CST].reserve(4 * max_bs * S) ||
       W[W_CNS].reserve(4 * max_bs) || W[W_CSELF].reserve(4 * max_bs) || W[W_FR].reserve(4 * max_bs * S) || W[W_FRD].reserve(4 * max_bs * S) ||
       W[W_CNT].reserve(4 * (4 * max_bs + 8)) || W[W_NEW].reserve(4 * max_bs * cap0) || W[W_KEYS].reserve(8 * max_bs * cap0) ||
-      d_keys2.reserve(8 * max_bs * cap0) || d_gstart.reserve(4 * max_bs * cap0) || d_ent.reserve(4 * 4096) || d_acct.reserve(32))
+      d_keys2.reserve(8 * max_bs * cap0) || d_gstart.reserve(8 * max_bs * cap0) || d_ent.reserve(4 * 4096) || d_acct.reserve(32))
     return 1;
   PANN_CUDA(cudaMemsetAsync(d_acct.p, 0, 32, s));
   int* gs_overflow = reinterpret_cast<int*>(d_acct.as<u64>() + 3);

@@ -38,7 +38,15 @@ __global__ void pann_find_heads_kernel(const u64* sorted, uint32_t ns, uint64_t 
   if (j >= ns) return;
   uint32_t t = (uint32_t)(sorted[j] >> 32);
   if (t >= n) return;
-  if (j == 0 || (uint32_t)(sorted[j - 1] >> 32) != t) gstart[atomicAdd(ngroups, 1u)] = j;
+  if (j == 0 || (uint32_t)(sorted[j - 1] >> 32) != t) {
+    // (start, length) pairs; the head walks its group (2 members on average) so that K3 does not have to bisect the key
+    // list with dependent global loads; a group longer than 64 is left to K3's bisection (length 0)
+    uint32_t len = 1;
+    while (len <= 64 && j + len < ns && (uint32_t)(sorted[j + len] >> 32) == t) len++;
+    const uint32_t g = atomicAdd(ngroups, 1u);
+    gstart[2 * g] = j;
+    gstart[2 * g + 1] = len <= 64 ? len : 0u;
+  }
 }
 
 int pann_sort_keys(void* tmp, size_t& tmp_bytes, const u64* in, u64* out, int64_t nk, int bits, cudaStream_t s) {
@@ -109,6 +117,24 @@ int pann_launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevB
     A.off_rc = A.off_pos + al16((size_t)A.cap * 2);
     A.warp_bytes = A.off_rc + A.rc_rows * A.rc_pitch;
     wpc = small_lists ? 4 : 3;
+  }
+  // Gram tile for the cached candidate rows (vamana_prune.cuh): 8-bit rows of 128 bytes, candidate-to-candidate distances as
+  // warp-level integer MMAs.  MEASURED AND LEFT OFF (profiles/r2_k3_gram_10M_summary.txt, 10M x 128 u8 build): the
+  // reverse-prune launch executes 31 % fewer warp instructions (30.4 G vs 44.4 G; the MMAs themselves are < 5 % of them), but
+  // the 16-row distance strip adds 7 KB of shared memory per warp — 8 instead of 16 resident warps per SM — and what remains is
+  // the O(C^2) rank sort and the per-pick mask bookkeeping: reverse-prune phase 2.46 s -> 3.76 s (3.27 s with 2 warps per CTA),
+  // visited-list prune 3.11 s -> 3.77 s.  PANN_PRUNE_GRAM = 1 (reverse-edge lists) / 2 (visited lists as well) turns it on.
+  A.gram_tp = 0; A.off_gram = 0; A.off_nrm = 0;
+  {
+    int gm = 0;
+    if (const char* e = getenv("PANN_PRUNE_GRAM")) gm = atoi(e);
+    if (rc_on && A.rule != 2 && idx->dtype != PANN_DT_F32 && qrT == PANN_QR && A.rc_rows <= 160 && (gm >= 2 || (gm == 1 && small_lists))) {
+      A.gram_tp = ((A.rc_rows + 7) / 8 * 8 + 31) / 32 * 32 + 8;   // = 8 mod 32: the 64-bit stores of a half warp cover all banks once
+      A.off_nrm = A.warp_bytes;
+      A.off_gram = A.off_nrm + al16((size_t)A.rc_rows * 4);
+      A.warp_bytes = A.off_gram + 16 * A.gram_tp * 4;
+      if (const char* e = getenv("PANN_PRUNE_GRAM_WARPS")) wpc = atoi(e);
+    }
   }
   A.off_stage = A.warp_bytes;
   if (pann_staged_rows_rt(idx->dtype, qrT)) A.warp_bytes += PANN_STAGE_BYTES;
@@ -194,7 +220,7 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
   uint32_t vout = std::max<uint32_t>(2 * L, L + 64);
   // per batch: nvis | cmps | status | new_deg | ngroups(1)
   if (d_cnt.reserve(4 * (4 * max_bs + 4)) || d_new_out.reserve(4 * max_bs * R) || d_keys.reserve(8 * max_bs * R) ||
-      d_keys2.reserve(8 * max_bs * R) || d_gstart.reserve(4 * max_bs * R))
+      d_keys2.reserve(8 * max_bs * R) || d_gstart.reserve(8 * max_bs * R))
     return 1;
   int key_bits = 33; while (key_bits < 64 && (n >> (key_bits - 32)) != 0) key_bits++;  // targets 0..n inclusive
   size_t sort_tmp_bytes = 0;

@@ -35,7 +35,7 @@ struct PruneArgs {
   const uint32_t* vis_ids; const float* vis_dists; const uint32_t* nvis; const uint32_t* search_cmps; uint32_t vout;
   uint32_t* new_out; uint32_t* new_deg;  // ntasks x R, ntasks
   // mode 1 inputs: sorted (target << 32 | seq) keys, group heads
-  const u64* sorted; uint32_t nsorted; const uint32_t* gstart; const uint32_t* ngroups;
+  const u64* sorted; uint32_t nsorted; const uint32_t* gstart; const uint32_t* ngroups;   // gstart: (first key, length or 0) per group
   // statistics (stats<indexType>, may be null)
   uint32_t* st_visited; uint32_t* st_cmps;
   // tasks whose candidate list exceeds `cap` are deferred to the global-scratch launch
@@ -49,7 +49,20 @@ struct PruneArgs {
   uint32_t off_b, off_q, off_stage, warp_bytes;   // off_stage: float rows staged for the one-lane sums (pann_staged_distance)
   // row cache (shared memory): the rows of up to rc_rows candidates, rc_pitch bytes apart, and their slot numbers
   uint32_t rc_rows, rc_pitch, off_rc, off_pos;
+  // Gram tile (8-bit rows of 128 bytes in the row cache): gram_tp = pitch in words of the 16-row distance strip (0 = off)
+  uint32_t gram_tp, off_gram, off_nrm;
 };
+
+// D(16x8, s32) += A(16x32, 8-bit, row) * B(32x8, 8-bit, col) on the tensor cores (warp-level MMA)
+template <int DT>
+__device__ __forceinline__ void pann_mma_16x8x32(int (&d)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  if constexpr (DT == PANN_DT_U8)
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.u8.u8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  else
+    asm volatile("mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+r"(d[0]), "+r"(d[1]), "+r"(d[2]), "+r"(d[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
 
 // does the picked vertex (at distance d_sc from candidate c) remove c, which is at distance d_c from the pruned vertex?
 __device__ __forceinline__ bool pann_occludes(const PruneArgs& A, float d_sc, float d_c) {
@@ -87,12 +100,14 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
       p = A.perm_lo[task];
       nc = A.nvis[task];
     } else {
-      g0 = A.gstart[task];
+      g0 = A.gstart[2 * task];
       p = (uint32_t)(A.sorted[g0] >> 32);
-      // group end = first key of a larger target (keys are sorted)
-      uint32_t lo = g0 + 1, hi = A.nsorted;
-      while (lo < hi) { uint32_t mid = (lo + hi) >> 1; if ((uint32_t)(A.sorted[mid] >> 32) <= p) lo = mid + 1; else hi = mid; }
-      nc = lo - g0;
+      nc = A.gstart[2 * task + 1];
+      if (nc == 0) {   // a long group: its end = first key of a larger target (keys are sorted)
+        uint32_t lo = g0 + 1, hi = A.nsorted;
+        while (lo < hi) { uint32_t mid = (lo + hi) >> 1; if ((uint32_t)(A.sorted[mid] >> 32) <= p) lo = mid + 1; else hi = mid; }
+        nc = lo - g0;
+      }
     }
     uint32_t* grow = A.graph + (u64)(A.rowmap ? A.rowmap[p] : p) * (A.maxdeg + 1);
     const uint32_t deg = grow[0];
@@ -227,6 +242,106 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const
       }
       for (int i = lane; i < C; i += 32) P[i] = (uint16_t)i;
       __syncwarp();
+      if constexpr (QR == 8 && DT != PANN_DT_F32) {
+        if (A.gram_tp) {
+          // ---- Gram tile.  With every candidate row on chip the occlusion scan is a dense contraction: the picks walk the
+          // sorted list, and each needs its distance to every later live candidate — for lists that lose few members
+          // (reverse-edge groups: 64 old edges plus a handful of new ones, at most R survive) that is half of the full
+          // C x C matrix.  It is computed on the tensor cores sixteen rows at a time, G = X X^T as 16x8x32 integer MMAs
+          // straight from the row cache (A and B fragments are both 4-byte reads of cached rows: pitch 144 bytes puts the
+          // eight rows of a fragment on disjoint banks), turned into the exact integer distance |xi|^2 + |xj|^2 - 2 G
+          // (the same integer the dp4a loop produces, so the float handed to the alpha test is bit-identical) and parked
+          // in a 16-row strip; the scan then reads one strip row per pick.  Candidates are not compacted any more: a
+          // bit mask per 32 candidates says who is alive.
+          const uint8_t* rcb = reinterpret_cast<const uint8_t*>(rc);
+          int* T = reinterpret_cast<int*>(ws + A.off_gram);
+          int* nrm = reinterpret_cast<int*>(ws + A.off_nrm);
+          const int tp = (int)A.gram_tp, pitch = (int)A.rc_pitch;
+          const int g = lane >> 2, t4 = (lane & 3) * 4;
+          constexpr int NCH = 5;                       // C <= 160
+          unsigned alive[NCH];
+          float kd[NCH];
+#pragma unroll
+          for (int c = 0; c < NCH; c++) {
+            const int j = 32 * c + lane;
+            alive[c] = 32 * c < C ? (C - 32 * c >= 32 ? 0xffffffffu : ((1u << (C - 32 * c)) - 1u)) : 0u;
+            kd[c] = j < C ? pann_key_dist(S[j]) : 0.f;
+            if (METRIC == PANN_M_L2 && j < C) {        // |x_j|^2
+              const uint4* row = rc + (uint32_t)j * pw;
+              DistAcc<DT, PANN_M_MIPS> nn;
+#pragma unroll
+              for (int ch = 0; ch < 8; ch++) { const uint4 v = row[ch]; nn.add(v, v); }
+              nrm[j] = (int)nn.acc;
+            }
+          }
+          __syncwarp();
+          // (the masks are registers: picked by a warp-uniform index through an unrolled select, never indexed dynamically)
+          auto mask_of = [&](int c) -> unsigned {
+            unsigned r = 0;
+#pragma unroll
+            for (int x = 0; x < NCH; x++) r = (x == c) ? alive[x] : r;
+            return r;
+          };
+          const int NB = (C + 7) >> 3;
+          bool done = false;
+          for (int b = 0; 16 * b < C && !done; b++) {
+            if (((mask_of(b >> 1) >> (16 * (b & 1))) & 0xffffu) == 0u) continue;    // nobody left to pick in these rows
+            const int r0 = min(16 * b + g, C - 1), r1 = min(16 * b + g + 8, C - 1);
+            uint32_t af[4][4];
+#pragma unroll
+            for (int ks = 0; ks < 4; ks++) {
+              af[ks][0] = *reinterpret_cast<const uint32_t*>(rcb + r0 * pitch + ks * 32 + t4);
+              af[ks][1] = *reinterpret_cast<const uint32_t*>(rcb + r1 * pitch + ks * 32 + t4);
+              af[ks][2] = *reinterpret_cast<const uint32_t*>(rcb + r0 * pitch + ks * 32 + 16 + t4);
+              af[ks][3] = *reinterpret_cast<const uint32_t*>(rcb + r1 * pitch + ks * 32 + 16 + t4);
+            }
+            const int n0 = METRIC == PANN_M_L2 ? nrm[r0] : 0, n1 = METRIC == PANN_M_L2 ? nrm[r1] : 0;
+            for (int nb = 2 * b; nb < NB; nb++) {      // only columns at or behind the strip's own rows are ever read
+              const int cr = min(8 * nb + g, C - 1);
+              int acc[4] = {0, 0, 0, 0};
+#pragma unroll
+              for (int ks = 0; ks < 4; ks++) {
+                const uint32_t b0 = *reinterpret_cast<const uint32_t*>(rcb + cr * pitch + ks * 32 + t4);
+                const uint32_t b1 = *reinterpret_cast<const uint32_t*>(rcb + cr * pitch + ks * 32 + 16 + t4);
+                pann_mma_16x8x32<DT>(acc, af[ks], b0, b1);
+              }
+              const int c0 = 8 * nb + (lane & 3) * 2;  // columns c0, c0 + 1 of rows g and g + 8
+              if (METRIC == PANN_M_L2) {
+                const int m0 = nrm[min(c0, C - 1)], m1 = nrm[min(c0 + 1, C - 1)];
+                acc[0] = n0 + m0 - 2 * acc[0]; acc[1] = n0 + m1 - 2 * acc[1];
+                acc[2] = n1 + m0 - 2 * acc[2]; acc[3] = n1 + m1 - 2 * acc[3];
+              }
+              *reinterpret_cast<int2*>(T + g * tp + c0) = make_int2(acc[0], acc[1]);
+              *reinterpret_cast<int2*>(T + (g + 8) * tp + c0) = make_int2(acc[2], acc[3]);
+            }
+            __syncwarp();
+            const int iend = min(16 * b + 16, C);
+            for (int i = 16 * b; i < iend; i++) {
+              if (!((mask_of(i >> 5) >> (i & 31)) & 1u)) continue;
+              const uint32_t ps_id = pann_key_id(S[i]);
+              if (ps_id == p) continue;
+              if (lane == 0) outp[m] = ps_id;
+              m++;
+              const int* Ti = T + (i & 15) * tp;
+#pragma unroll
+              for (int c = 0; c < NCH; c++) {
+                if (32 * c + 31 <= i || 32 * c >= C) continue;     // warp-uniform: no later candidate in this chunk
+                const int j = 32 * c + lane;
+                const unsigned later = alive[c] & (i >= 32 * c ? (0xfffffffeu << (i - 32 * c)) : 0xffffffffu);
+                comps += __popc(later);                              // one distance per live later candidate (:108)
+                const bool on = (later >> lane) & 1u;
+                const int v = on ? Ti[j] : 0;
+                const float d = METRIC == PANN_M_L2 ? (float)v : -((float)v);
+                const bool kill = on && pann_occludes(A, d, kd[c]);  // :111
+                alive[c] &= ~__ballot_sync(PANN_FULL, kill);
+              }
+              if (m >= A.R) { done = true; break; }
+            }
+            __syncwarp();
+          }
+          start = n = 0;   // the scan below has nothing left to do
+        }
+      }
       while (m < A.R && start < n) {
         const u64 ps = S[start];
         const uint4* qrow = rc + (uint32_t)P[start] * pw;

@@ -129,3 +129,17 @@ def test_build_stats_accounting(dataset):
     # every robustPrune call reads at least its candidates' rows: bytes >= calls * (row + graph row)
     assert st["prune_bytes"] >= st["prune_calls"] * (128 + 4 * 33)
     assert st["pair_distances"] < int(sd.astype(np.int64).sum())
+
+
+@pytest.mark.parametrize("gram", ["1", "2"])
+@pytest.mark.parametrize("data_type,metric,n,d,R,L,passes", [
+    ("uint8", "Euclidian", 12000, 128, 64, 128, 2), ("int8", "mips", 8000, 128, 32, 64, 1), ("int8", "Euclidian", 8000, 128, 32, 64, 1),
+    ("uint8", "mips", 6000, 128, 24, 48, 1),
+])
+def test_build_with_gram_tile_matches_oracle(dataset, data_type, metric, n, d, R, L, passes, gram, monkeypatch):
+    """the candidate-to-candidate distances of robustPrune as tensor-core tiles over the cached rows (PANN_PRUNE_GRAM; measured
+    slower than the lazy scan at 10M and off by default): integer distances |xi|^2 + |xj|^2 - 2 xi.xj are the same integers the
+    dp4a loop produces, so graphs and counters stay identical — all four 8-bit type / metric combinations"""
+    monkeypatch.setenv("PANN_PRUNE_ROW_CACHE", "1")
+    monkeypatch.setenv("PANN_PRUNE_GRAM", gram)
+    test_build_matches_oracle(dataset, data_type, metric, n, d, R, L, passes)
