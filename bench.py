@@ -169,6 +169,16 @@ def choose_setting(settings, evaluate):
     return best
 
 
+def device_sweep(idx, settings, n, maxdeg):
+    """every setting of the sweep through pann_search_sweep (resident queries + resident ground truth) -> ({setting: (recall, avg_cmps)}, rows)"""
+    from parlayann_b200 import harness
+    rows = harness.search_sweep(idx, [dict(k=k, beam=b, cut=c, limit=n if l < 0 else l, degree_limit=maxdeg if d < 0 else d) for (_, k, b, c, l, d) in settings])
+    bad = [r for r in rows if r["status"] != 0]
+    if bad:
+        raise RuntimeError(f"sweep setting failed: {bad[0]}")
+    return {s: (r["recall"], r["avg_cmps"]) for s, r in zip(settings, rows)}, rows
+
+
 def gpu_prepared_inputs(args, tmp, local_rank=0):
     """points / graph / recall queries / ground truth for the reference arm at sizes where the reference's own CPU build
     and ground truth would take many minutes (10M points): made on the GPU, untimed, written in the reference's file
@@ -184,16 +194,8 @@ def gpu_prepared_inputs(args, tmp, local_rank=0):
     qs = idx.download_queries()
     idx.groundtruth_resident(k=100)
     gt_ids, gt_d = idx.fetch_groundtruth()
-    cache = {}
-
-    def ev(s):
-        if s not in cache:
-            kind, k, beam, cut, limit, dl = s
-            idx.search_resident(k=k, beam=beam, cut=cut, limit=None if limit < 0 else limit, degree_limit=None if dl < 0 else dl)
-            ids, _, vis, cmps = idx.fetch_results()
-            cache[s] = (recall_with_ties(ids, gt_ids, gt_d, K), int(cmps.astype(np.int64).sum() // args.nq_recall))
-        return cache[s]
-    s, rec, cm = choose_setting(sweep_settings(64), ev)
+    cache, _ = device_sweep(idx, sweep_settings(64), args.n, 64)
+    s, rec, cm = choose_setting(sweep_settings(64), lambda x: cache[x])
     files = {k: os.path.join(tmp, k) for k in ("base", "query", "graph", "gt")}
     fileio.write_bin(files["base"], idx.points()); fileio.write_bin(files["query"], qs)
     fileio.write_graph(files["graph"], idx.graph()); fileio.write_ibin(files["gt"], gt_ids, gt_d)
@@ -486,19 +488,17 @@ def run_ours(args, rank, local_rank, world):
     gt_s = time.time() - t0
 
     settings = sweep_settings(R)
-    cache = {}
 
     def qp_of(s):
         kind, k, beam, cut, limit, dl = s
         return dict(k=k, beam=beam, cut=cut, limit=None if limit < 0 else limit, degree_limit=None if dl < 0 else dl)
 
-    def ev(s):
-        if s not in cache:
-            idx.search_resident(**qp_of(s))
-            ids, _, vis, cmps = idx.fetch_results()
-            cache[s] = (recall_with_ties(ids, gt_ids, gt_d, K), int(cmps.astype(np.int64).sum() // nqr))
-        return cache[s]
-    s, rec, cm = choose_setting(settings, ev)
+    # the reference's sweep (check_nn_recall.h:214-254: 43 beams + 20 visit limits) ON THE DEVICE: search, tie-aware recall and
+    # counter statistics of every setting stay there (pann_search_sweep), one copy brings the 63 rows back
+    t0 = time.time()
+    cache, sweep_rows = device_sweep(idx, settings, n, R)
+    sweep_s = time.time() - t0
+    s, rec, cm = choose_setting(settings, lambda x: cache[x])
     qp = qp_of(s)
     idx.search_resident(**qp)
     r_ids, _, r_vis, r_cmps = idx.fetch_results()     # the recall batch's answer at the chosen setting (parity below)
@@ -663,6 +663,9 @@ def run_ours(args, rank, local_rank, world):
                                 "roofline": {"bound": "tensor", "achieved": gt_ops / (gt_ms * 1e-3) / 1e12, "peak": int8_peak, "unit": "TOP/s",
                                              "frac": gt_ops / (gt_ms * 1e-3) / 1e12 / int8_peak, "peak_source": "2 x MEASURED_PEAKS.json bf16_tflops (int8 pipe)",
                                              "algorithmic_op": gt_ops, "kernel": "pann_gt_mma_kernel<true> (tcgen05 kind::i8) + pann_gt_shrink_kernel"}},
+                "sweep": {"settings": len(sweep_rows), "seconds": sweep_s, "device_ms_total": float(sum(r["device_ms"] for r in sweep_rows)),
+                          "what": "the reference's 63-setting search sweep (check_nn_recall.h:214-254) with recall and counter statistics computed on the device (pann_search_sweep)",
+                          "first_beam_rows": [{k_: r[k_] for k_ in ("beam", "recall", "avg_cmps", "avg_visited", "QPS")} for r in sweep_rows[:21:4]]},
                 "groundtruth_c3": c3,
                 "hnsw_c5": c5,
                 "setup_seconds": setup_s}

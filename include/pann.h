@@ -172,6 +172,21 @@ int pann_groundtruth_device_result(pann_index* idx, const int32_t** d_ids, const
 int pann_groundtruth_merge_device(int device, uint32_t nshards, uint64_t nq, uint32_t k, const int32_t* d_ids, const float* d_dists,
                                   int32_t* d_out_ids, float* d_out_dists, void* stream);
 
+/* ---- the evaluation harness on the device: search_and_parse's loop (algorithms/utils/check_nn_recall.h:181-268).  For every
+ * QueryParams: the search over the RESIDENT query set (pann_queries_upload / _synthetic), tie-aware recall against the resident
+ * ground truth (checkRecall, :83-109: the first k ids plus every later id at the k-th distance; pann_groundtruth_resident
+ * leaves one, pann_groundtruth_upload sets one from a .ibin), and stats<indexType>::statistics of both counters (stats.h:84-92).
+ * One copy brings all results back.  status != 0 marks a setting the reference would abort on (k > beam, fewer than k found). */
+typedef struct {
+  double recall;
+  uint32_t avg_cmps, tail_cmps, avg_visited, tail_visited;
+  float device_ms;   /* kernel time of the setting's search (CUDA events) */
+  int status;
+} pann_sweep_result;
+int pann_groundtruth_upload(pann_index* idx, const int32_t* gt_ids, const float* gt_dists, uint64_t nq, uint32_t gt_k);
+int pann_search_sweep(pann_index* idx, const uint32_t* starts, uint32_t nstarts, const pann_query_params* qps, uint32_t nset,
+                      pann_sweep_result* out);
+
 /* ---- HNSW (algorithms/HNSW/HNSW.hpp).  Node i = point i of the index; the index must have max_degree = 2 m: its graph IS
  * level 0 of the model (degree bound 2m, HNSW.hpp:527-531); the upper levels (bound m) live in the pann_hnsw object as
  * compacted flat arrays.  The model moves in and out in the order of the model file v3 (HNSW.hpp:1655-1685, :690-740):

@@ -17,6 +17,12 @@ class QueryParams(C.Structure):
                 ("degree_limit", C.c_int64)]
 
 
+class SweepResult(C.Structure):
+    """= pann_sweep_result (include/pann.h): one row of the reference's search sweep (check_nn_recall.h:111-123)"""
+    _fields_ = [("recall", C.c_double), ("avg_cmps", C.c_uint32), ("tail_cmps", C.c_uint32), ("avg_visited", C.c_uint32),
+                ("tail_visited", C.c_uint32), ("device_ms", C.c_float), ("status", C.c_int)]
+
+
 class PannError(RuntimeError):
     pass
 
@@ -29,6 +35,7 @@ SYMBOLS = [
     "pann_queries_download", "pann_search_resident", "pann_search_fetch", "pann_search_device_result", "pann_search_full", "pann_search_batch_starts", "pann_search_full_starts", "pann_search_rerank_batch", "pann_vamana_build",
     "pann_random_permutation", "pann_random_starts", "pann_batch_schedule", "pann_groundtruth", "pann_groundtruth_resident",
     "pann_groundtruth_fetch", "pann_index_groundtruth_stats", "pann_groundtruth_merge", "pann_groundtruth_device_result", "pann_groundtruth_merge_device",
+    "pann_groundtruth_upload", "pann_search_sweep",
     "pann_hnsw_create", "pann_hnsw_destroy", "pann_hnsw_levels", "pann_hnsw_build", "pann_hnsw_set_model", "pann_hnsw_get_model",
     "pann_hnsw_search", "pann_hnsw_info", "pann_host_alloc", "pann_host_free",
 ]

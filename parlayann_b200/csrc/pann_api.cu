@@ -111,7 +111,7 @@ extern "C" void pann_index_destroy(pann_index* idx) {
   idx->queries.release(); idx->results.release(); idx->scratch_hash.release(); idx->scratch_vis.release();
   idx->scratch_hash2.release(); idx->scratch_vis2.release();
   idx->bytes_ctr.release(); idx->starts.release(); idx->flag.release(); idx->qmap.release(); idx->misc.release();
-  idx->gt_ids.release(); idx->gt_dists.release();
+  idx->gt_ids.release(); idx->gt_dists.release(); idx->sweep.release();
   for (auto& b : idx->gt_scratch) b.release();
   if (idx->pinned) cudaFreeHost(idx->pinned);
   for (cudaEvent_t e : idx->pipe_ev) cudaEventDestroy(e);

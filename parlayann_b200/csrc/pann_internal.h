@@ -55,6 +55,7 @@ struct pann_index {
   void* pinned = nullptr; size_t pinned_cap = 0;
   // ground truth results (resident)
   DevBuf gt_ids, gt_dists; uint64_t gt_nq = 0; uint32_t gt_k = 0;
+  DevBuf sweep;                // pann_search_sweep work area
   DevBuf gt_scratch[8];        // ground-truth work buffers, kept between calls (cudaMalloc/cudaFree of ~200 MB cost 5 ms per call)
   int gt_mma_launches = 0;     // pann_gt_mma_kernel launches of the last ground-truth call
   int gt_fallback_chunks = 0;  // MMA chunks retaken on the CUDA cores (candidate-list overflow), cumulative

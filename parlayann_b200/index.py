@@ -280,6 +280,12 @@ class GraphIndex:
         check(_lib.lib().pann_index_groundtruth_stats(self._h, C.byref(a), C.byref(b)))
         return a.value, b.value
 
+    def upload_groundtruth(self, gt_ids, gt_dists):
+        """ground truth of the resident queries from a .ibin (fileio.read_ibin) for the device-side sweep"""
+        gi = np.ascontiguousarray(gt_ids, dtype=np.int32); gd = np.ascontiguousarray(gt_dists, dtype=np.float32)
+        check(_lib.lib().pann_groundtruth_upload(self._h, _vp(gi), _vp(gd), C.c_uint64(gi.shape[0]), C.c_uint32(gi.shape[1])))
+        self._gt_k = gi.shape[1]
+
     def fetch_groundtruth(self):
         ids = np.empty((self.nq, self._gt_k), np.int32)
         dists = np.empty((self.nq, self._gt_k), np.float32)
