@@ -139,6 +139,14 @@ int pann_search_rerank_batch(pann_index* q_idx, pann_index* base_idx, const void
 int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double alpha, int num_passes, int sort_neighbors,
                       uint32_t* out_visited, uint32_t* out_cmps, double phase_seconds[3]);
 
+/* knn_index::batch_insert (algorithms/vamana/index.h:188-316): inserts the listed vertices into the index's EXISTING graph —
+ * in the given order or in parlay::random_permutation order (random_order, :211-218), batches per :206-209 / :223-234 with
+ * this max_fraction, start point 0, robustPrune with `alpha`.  No final sort.  stats (may be NULL): n u32 each, the
+ * increments this call adds to stats<indexType>.  Fails like the reference on an id >= n (:193-199). */
+int pann_vamana_batch_insert(pann_index* idx, const uint32_t* inserts, uint64_t m, uint32_t R, uint32_t L, double alpha,
+                             int random_order, double max_fraction, uint32_t* out_visited, uint32_t* out_cmps,
+                             double phase_seconds[3]);
+
 /* accounting of the last pann_vamana_build, counted on the device: algorithmic_bytes = B_ins summed over
  * all insertions = bytes of the build-mode beam searches (as pann_index_last_bytes counts them) + per robustPrune call
  * (vamana/index.h:63-120) C * row bytes + 4 (R+1) with C the candidates after unique + 2 * 4 (R+1) per inserted point;

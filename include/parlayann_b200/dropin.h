@@ -14,6 +14,8 @@
 // PointRange's buffer address, so repeated calls (the search sweep of check_nn_recall.h:214-257) upload once.
 #pragma once
 #include <cstdlib>
+#include <cstring>
+#include <algorithm>
 #include <iostream>
 #include <map>
 #include <memory>
@@ -55,7 +57,9 @@ inline void check(int rc) {  // the reference's error convention: message, then 
 }
 
 template <typename PointRange> inline size_t row_stride(const PointRange& P) {
-  return (size_t)(P.location(1) - P.location(0));  // PointRange::aligned_bytes is private (point_range.h:139)
+  // PointRange::aligned_bytes is private (point_range.h:139); a range of one row has no second row to measure against
+  using T = typename point_traits<typename PointRange::Point>::elt;
+  return P.size() > 1 ? (size_t)(P.location(1) - P.location(0)) : (size_t)P.dimension() * sizeof(T);
 }
 template <typename indexType> inline indexType* graph_base(const Graph<indexType>& G) {
   return G[0].begin() - 1;  // flat n x (maxDeg+1) array, slot 0 = degree (graph.h:134-141, :234-242)
@@ -95,21 +99,68 @@ inline pann_query_params to_pann(const QueryParams& QP) {  // types.h:218-231
   return q;
 }
 
-// ---- resident-index cache for the reference-signature overloads (keyed by the PointRange's buffer) ----------------
+// ---- resident-index cache for the reference-signature overloads ----------------------------------------------------
+// Keyed by the PointRange's buffer address AND validated on every call: n, dimension, max degree, and a fingerprint of
+// the contents (every 61st point row's first bytes; every graph row's degree word and every 61st row in full — about 1 %
+// of the bytes, ~10 ms at 10M points).  A buffer that was freed and re-used by another PointRange / Graph, or a graph that
+// was rebuilt in place, therefore gets a fresh device copy.  An in-place edit that keeps all degrees and misses every
+// sampled row is the caller's to announce: b200::invalidate(Points) drops the entry, b200::clear_cache() drops all
+// (they also return the GPU memory).
+inline uint64_t fp_mix(uint64_t h, uint64_t x) { h ^= x + 0x9e3779b97f4a7c15ull + (h << 6) + (h >> 2); return h; }
+template <typename PointRange> inline uint64_t points_fingerprint(const PointRange& P) {
+  uint64_t h = fp_mix(P.size(), P.dimension());
+  const size_t n = P.size(), rb = std::min<size_t>(16, (size_t)P.dimension());
+  for (size_t i = 0; i < n; i += 61) { uint64_t w[2] = {0, 0}; memcpy(w, P.location(i), rb); h = fp_mix(fp_mix(h, w[0]), w[1]); }
+  return h;
+}
+template <typename indexType> inline uint64_t graph_fingerprint(const Graph<indexType>& G) {
+  uint64_t h = fp_mix(G.size(), G.max_degree());
+  const size_t n = G.size(), w = (size_t)G.max_degree() + 1;
+  const indexType* g = graph_base(G);
+  for (size_t i = 0; i < n; i++) h = fp_mix(h, g[i * w]);
+  for (size_t i = 0; i < n; i += 61) for (size_t j = 1; j <= g[i * w] && j < w; j++) h = fp_mix(h, g[i * w + j]);
+  return h;
+}
+struct CacheBase {   // type-erased registry so that invalidate / clear_cache reach every instantiation's map
+  virtual void drop(const void* key) = 0;
+  virtual void clear() = 0;
+  static std::vector<CacheBase*>& all() { static std::vector<CacheBase*> v; return v; }
+  static std::mutex& mu() { static std::mutex m; return m; }
+};
+template <typename PointRange, typename indexType>
+struct IndexCache : CacheBase {
+  using DI = DeviceIndex<PointRange, indexType>;
+  struct Entry { std::unique_ptr<DI> di; size_t n; unsigned dims; long maxdeg; uint64_t pfp, gfp; bool has_graph; };
+  std::map<const void*, Entry> map;
+  IndexCache() { CacheBase::all().push_back(this); }
+  void drop(const void* key) override { map.erase(key); }
+  void clear() override { map.clear(); }
+  static IndexCache& get() { static IndexCache c; return c; }
+};
+template <typename PointRange> inline void invalidate(const PointRange& Points) {
+  std::lock_guard<std::mutex> lock(CacheBase::mu());
+  if (Points.size() == 0) return;
+  for (CacheBase* c : CacheBase::all()) c->drop(Points.location(0));
+}
+inline void clear_cache() {
+  std::lock_guard<std::mutex> lock(CacheBase::mu());
+  for (CacheBase* c : CacheBase::all()) c->clear();
+}
 template <typename PointRange, typename indexType>
 inline DeviceIndex<PointRange, indexType>& cached_index(const PointRange& Points, const Graph<indexType>& G, bool graph_dirty) {
-  using DI = DeviceIndex<PointRange, indexType>;
-  struct Entry { std::unique_ptr<DI> di; const void* graph; long maxdeg; };
-  static std::map<const void*, Entry> cache;
-  static std::mutex mu;
-  std::lock_guard<std::mutex> lock(mu);
+  using IC = IndexCache<PointRange, indexType>;
+  std::lock_guard<std::mutex> lock(CacheBase::mu());
+  IC& C = IC::get();
   const void* key = Points.location(0);
-  auto it = cache.find(key);
-  if (it == cache.end() || it->second.maxdeg != G.max_degree()) {
-    cache[key] = Entry{std::make_unique<DI>(Points, G), graph_base(G), G.max_degree()};
-    return *cache[key].di;
+  const uint64_t pfp = points_fingerprint(Points), gfp = graph_fingerprint(G);
+  auto it = C.map.find(key);
+  if (it == C.map.end() || it->second.n != Points.size() || it->second.dims != Points.dimension() || it->second.maxdeg != G.max_degree() ||
+      it->second.pfp != pfp || !it->second.has_graph) {
+    C.map.erase(key);
+    C.map[key] = typename IC::Entry{std::make_unique<typename IC::DI>(Points, G), Points.size(), (unsigned)Points.dimension(), G.max_degree(), pfp, gfp, true};
+    return *C.map[key].di;
   }
-  if (graph_dirty || it->second.graph != graph_base(G)) { it->second.di->upload_graph(G); it->second.graph = graph_base(G); }
+  if (graph_dirty || it->second.gfp != gfp) { it->second.di->upload_graph(G); it->second.gfp = gfp; }
   return *it->second.di;
 }
 
@@ -153,16 +204,28 @@ searchAll(PointRange& Query_Points, Graph<indexType>& G, PointRange& Base_Points
   return searchAll(cached_index(Base_Points, G, false), Query_Points, QueryStats, start_points, QP);
 }
 
-// exact points only (the re-rank side of a quantised search): no graph on the device
+// exact points only (the re-rank side of a quantised search): no graph on the device; same validation as cached_index
 template <typename PointRange, typename indexType>
 inline DeviceIndex<PointRange, indexType>& cached_points(const PointRange& Points) {
   using DI = DeviceIndex<PointRange, indexType>;
-  static std::map<const void*, std::unique_ptr<DI>> cache;
-  static std::mutex mu;
-  std::lock_guard<std::mutex> lock(mu);
-  auto& e = cache[Points.location(0)];
-  if (!e) e = std::make_unique<DI>(Points, 1);
-  return *e;
+  struct PC : CacheBase {
+    struct Entry { std::unique_ptr<DI> di; size_t n; unsigned dims; uint64_t pfp; };
+    std::map<const void*, Entry> map;
+    PC() { CacheBase::all().push_back(this); }
+    void drop(const void* key) override { map.erase(key); }
+    void clear() override { map.clear(); }
+  };
+  static PC C;
+  std::lock_guard<std::mutex> lock(CacheBase::mu());
+  const void* key = Points.location(0);
+  const uint64_t pfp = points_fingerprint(Points);
+  auto it = C.map.find(key);
+  if (it == C.map.end() || it->second.n != Points.size() || it->second.dims != Points.dimension() || it->second.pfp != pfp) {
+    C.map.erase(key);
+    C.map[key] = typename PC::Entry{std::make_unique<DI>(Points, 1), Points.size(), (unsigned)Points.dimension(), pfp};
+    return *C.map[key].di;
+  }
+  return *it->second.di;
 }
 
 // ---- qsearchAll (beamSearch.h:537-565), reference signature.
@@ -220,6 +283,23 @@ struct knn_index {
   indexType get_start() { return start_point; }
   void set_start() { start_point = 0; }
 
+  // batch_insert (vamana/index.h:188-192): the listed vertices into the existing graph G (uploaded, extended on the GPU,
+  // copied back); same argument order and defaults.  `base` must be 2 (the only value the reference's callers use).
+  void batch_insert(parlay::sequence<indexType>& inserts, GraphI& G, PointRange& Points, QPointRange&, stats<indexType>& BuildStats,
+                    double alpha, bool random_order = false, double base = 2, double max_fraction = .02, bool print = true) {
+    static_assert(std::is_same<PointRange, QPointRange>::value, "parlayann_b200: batch_insert takes the same range for Points and QPoints");
+    if (base != 2) { std::cout << "parlayann_b200: batch_insert supports base = 2 only" << std::endl; abort(); }
+    (void)print;
+    const size_t n = Points.size();
+    DeviceIndex<PointRange, indexType> D(Points, G);
+    std::vector<uint32_t> vis(n), cmp(n);
+    check(pann_vamana_batch_insert(D.handle(), (const uint32_t*)inserts.begin(), inserts.size(), (uint32_t)BP.R, (uint32_t)BP.L, alpha,
+                                   random_order ? 1 : 0, max_fraction, vis.data(), cmp.data(), phase_seconds));
+    D.download_graph(G);
+    invalidate(Points);   // any resident copy of this graph is stale now
+    parlay::parallel_for(0, n, [&](size_t i) { BuildStats.increment_visited(i, vis[i]); BuildStats.increment_dist(i, cmp[i]); });
+  }
+
   void build_index(GraphI& G, PointRange& Points, QPointRange&, stats<indexType>& BuildStats, bool sort_neighbors = true) {
     // a quantised build passes the quantised range twice (bench/neighborsTime.C:157-164, python/builder.cpp:60-87)
     static_assert(std::is_same<PointRange, QPointRange>::value,
@@ -234,6 +314,7 @@ struct knn_index {
     check(pann_vamana_build(D.handle(), (uint32_t)BP.R, (uint32_t)BP.L, BP.alpha, BP.num_passes, sort_neighbors ? 1 : 0,
                             vis.data(), cmp.data(), phase_seconds));
     D.download_graph(G);
+    invalidate(Points);   // any resident copy of an earlier graph over these points is stale now
     parlay::parallel_for(0, n, [&](size_t i) { BuildStats.increment_visited(i, vis[i]); BuildStats.increment_dist(i, cmp[i]); });
     // the three phase timers as parlay::internal::timer::total() prints them (index.h:313-315; get_time.h:23-32), including
     // its side effect: the stream's precision stays at 4 afterwards, which the recall figures of the sweep are printed with

@@ -132,6 +132,49 @@ static int run(int argc, char** argv) {
       bad += dq != 0 || !s2;
     }
   }
+  // --- batch_insert used directly (vamana/index.h:188-192): first half in the given order, second half in random order, a
+  //     scattered subset again with another max_fraction — graphs and statistics after every call
+  {
+    BuildParams BP1(R, L, 1.2, 1, false);
+    Graph<uint> Hc(BP1.max_degree(), Points.size()), Hg(BP1.max_degree(), Points.size());
+    stats<uint> Tc(Points.size()), Tg(Points.size());
+    knn_index<PR, PR, uint> Ic(BP1); Ic.start_point = 0;
+    b200::knn_index<PR, PR, uint> Ig(BP1);
+    const uint n = (uint)Points.size();
+    parlay::sequence<uint> a = parlay::tabulate(n / 2, [&](size_t i) { return (uint)i; });
+    parlay::sequence<uint> b = parlay::tabulate(n - n / 2, [&](size_t i) { return (uint)(n / 2 + i); });
+    parlay::sequence<uint> c = parlay::tabulate(n / 7, [&](size_t i) { return (uint)((i * 7 + 3) % n); });
+    struct Step { parlay::sequence<uint>* ins; double alpha; bool rnd; double frac; } steps[3] = {{&a, 1.2, false, .02}, {&b, 1.2, true, .02}, {&c, 1.0, false, .05}};
+    for (int si = 0; si < 3; si++) {
+      Ic.batch_insert(*steps[si].ins, Hc, Points, Points, Tc, steps[si].alpha, steps[si].rnd, 2, steps[si].frac, false);
+      Ig.batch_insert(*steps[si].ins, Hg, Points, Points, Tg, steps[si].alpha, steps[si].rnd, 2, steps[si].frac, false);
+      size_t dr = 0;
+      for (size_t i = 0; i < Points.size(); i++) {
+        bool same = Hc[i].size() == Hg[i].size();
+        for (size_t j = 0; same && j < Hc[i].size(); j++) same = Hc[i][j] == Hg[i][j];
+        dr += !same;
+      }
+      bool s3 = std::equal(Tc.visited.begin(), Tc.visited.end(), Tg.visited.begin()) && std::equal(Tc.distances.begin(), Tc.distances.end(), Tg.distances.begin());
+      printf("DROPIN batch_insert step %d: %zu of %zu rows differ, stats %s\n", si, dr, Points.size(), s3 ? "identical" : "DIFFER");
+      bad += dr != 0 || !s3;
+    }
+    // --- the resident-index cache must notice a graph that changed in place behind the same addresses: search Hc, rewrite
+    //     its rows with Gc's (same buffer, same max degree), search again — the second answer must be the one for Gc
+    QueryParams QP(k, 20, 1.35, (long)Gc.size(), (long)Gc.max_degree());
+    stats<uint> q1(Q.size()), q2(Q.size()), q3(Q.size());
+    auto r1 = b200::qsearchAll<PR, PR, PR, uint>(Q, Q, Q, Hc, Points, Points, Points, q1, 0u, QP);
+    for (size_t i = 0; i < Points.size(); i++) {
+      parlay::sequence<uint> row = parlay::tabulate(Gc[i].size(), [&](size_t j) { return Gc[i][j]; });
+      Hc[i].update_neighbors(row);
+    }
+    auto r2 = b200::qsearchAll<PR, PR, PR, uint>(Q, Q, Q, Hc, Points, Points, Points, q2, 0u, QP);
+    auto r3 = qsearchAll<PR, PR, PR, uint>(Q, Q, Q, Gc, Points, Points, Points, q3, 0u, QP);
+    size_t dq = 0, changed = 0;
+    for (size_t i = 0; i < Q.size(); i++) { dq += !(r2[i] == r3[i]); changed += !(r1[i] == r2[i]); }
+    printf("DROPIN cache after an in-place graph rewrite: %zu of %zu queries differ from the reference on the new graph (%zu answers changed)\n", dq, Q.size(), changed);
+    bad += dq != 0;
+    b200::clear_cache();
+  }
   // --- ground truth: sorted distance rows must be identical
   {
     int gk = 20;

@@ -406,17 +406,14 @@ int oracle_search_batch(int dtype, int metric, const void* points, uint64_t n, u
 
 // knn_index::build_index (vamana/index.h:150-186) + batch_insert (:188-316), start_point = 0.
 // graph: n x (R+1) u32, zero-filled by the caller for a fresh build.  stats (may be NULL): n u32 each.
-int oracle_vamana_build(int dtype, int metric, const void* points, uint64_t n, uint32_t d, uint64_t stride,
-                        uint32_t R, uint32_t L, double alpha, int num_passes, int sort_neighbors,
-                        uint32_t* graph, uint32_t* st_visited, uint32_t* st_dists, int nthreads) {
-  PointSet P{dtype, metric, (const uint8_t*)points, n, d, stride};
-  const uint32_t maxdeg = R, start = 0;
-  std::vector<int32_t> perm(n);
-  random_permutation((int64_t)n, perm.data());  // :211-216 (inserts = identity, so shuffled = perm)
-  for (int pass = 0; pass < num_passes; pass++) {
-    double a = (pass == num_passes - 1) ? alpha : 1.0;  // :173-178
-    size_t m = n, inc = 0, count = 0;
-    size_t max_batch = std::min((size_t)(0.02 * (double)(float)n), (size_t)1000000);  // :206-207 (double .02 * float n)
+// batch_insert (vamana/index.h:188-316): `order` = the vertices in insertion order (already shuffled, :211-218)
+static void vamana_batch_insert(const PointSet& P, uint32_t* graph, uint32_t maxdeg, uint32_t R, uint32_t L, double a,
+                                const std::vector<uint32_t>& order, double max_fraction, uint32_t* st_visited, uint32_t* st_dists, int nthreads) {
+  const uint64_t n = P.n;
+  const uint32_t start = 0;
+  {
+    size_t m = order.size(), inc = 0, count = 0;
+    size_t max_batch = std::min((size_t)(max_fraction * (double)(float)n), (size_t)1000000);  // :206-207 (double * float n)
     if (max_batch == 0) max_batch = n;
     while (count < m) {
       size_t lo, hi;
@@ -431,7 +428,7 @@ int oracle_vamana_build(int dtype, int metric, const void* points, uint64_t n, u
       }
       std::vector<std::vector<uint32_t>> new_out(hi - lo);
       par_for(lo, hi, nthreads, [&](size_t i) {  // phase 1 :247-266
-        uint32_t p = (uint32_t)perm[i];
+        uint32_t p = order[i];
         QP qp{0, (long)L, 0.0, (long)n, (long)maxdeg};  // :250
         SearchOut o;
         beam_search(P, graph, maxdeg, P.row(p), (long)p, &start, 1, qp, o);
@@ -440,7 +437,7 @@ int oracle_vamana_build(int dtype, int metric, const void* points, uint64_t n, u
         if (st_visited) st_visited[p] += (uint32_t)o.visited.size();
       });
       for (size_t i = lo; i < hi; i++) {  // phase 2 :268-270
-        uint32_t* row = graph + (uint64_t)perm[i] * (maxdeg + 1);
+        uint32_t* row = graph + (uint64_t)order[i] * (maxdeg + 1);
         row[0] = (uint32_t)new_out[i - lo].size();
         std::copy(new_out[i - lo].begin(), new_out[i - lo].end(), row + 1);
       }
@@ -451,7 +448,7 @@ int oracle_vamana_build(int dtype, int metric, const void* points, uint64_t n, u
         for (uint32_t nb : new_out[i - lo]) {
           auto it = groups.find(nb);
           if (it == groups.end()) { keys.push_back(nb); it = groups.emplace(nb, std::vector<uint32_t>()).first; }
-          it->second.push_back((uint32_t)perm[i]);
+          it->second.push_back(order[i]);
         }
       par_for(0, keys.size(), nthreads, [&](size_t j) {
         uint32_t t = keys[j];
@@ -477,6 +474,20 @@ int oracle_vamana_build(int dtype, int metric, const void* points, uint64_t n, u
       inc++;
     }
   }
+}
+
+int oracle_vamana_build(int dtype, int metric, const void* points, uint64_t n, uint32_t d, uint64_t stride,
+                        uint32_t R, uint32_t L, double alpha, int num_passes, int sort_neighbors,
+                        uint32_t* graph, uint32_t* st_visited, uint32_t* st_dists, int nthreads) {
+  PointSet P{dtype, metric, (const uint8_t*)points, n, d, stride};
+  const uint32_t maxdeg = R;
+  std::vector<int32_t> perm(n);
+  random_permutation((int64_t)n, perm.data());  // :211-216 (inserts = identity, so shuffled = perm)
+  std::vector<uint32_t> order(perm.begin(), perm.end());
+  for (int pass = 0; pass < num_passes; pass++) {
+    double a = (pass == num_passes - 1) ? alpha : 1.0;  // :173-178
+    vamana_batch_insert(P, graph, maxdeg, R, L, a, order, 0.02, st_visited, st_dists, nthreads);
+  }
   if (sort_neighbors)  // :180-185 — dist-only comparator; ties unordered in the reference (std::sort)
     par_for(0, n, nthreads, [&](size_t i) {
       uint32_t* row = graph + (uint64_t)i * (maxdeg + 1);
@@ -484,6 +495,20 @@ int oracle_vamana_build(int dtype, int metric, const void* points, uint64_t n, u
         return dist_rows(P.dtype, P.metric, P.row(i), P.row(j), P.d) < dist_rows(P.dtype, P.metric, P.row(i), P.row(k), P.d);
       });
     });
+  return 0;
+}
+
+// knn_index::batch_insert (vamana/index.h:188-316) of `inserts` into an existing graph (alpha as given, no final sort)
+int oracle_vamana_batch_insert(int dtype, int metric, const void* points, uint64_t n, uint32_t d, uint64_t stride, uint32_t R, uint32_t L,
+                               double alpha, const uint32_t* inserts, uint64_t m, int random_order, double max_fraction, uint32_t* graph,
+                               uint32_t* st_visited, uint32_t* st_dists, int nthreads) {
+  PointSet P{dtype, metric, (const uint8_t*)points, n, d, stride};
+  std::vector<int32_t> rperm(m);
+  if (random_order) random_permutation((int64_t)m, rperm.data());
+  else for (uint64_t i = 0; i < m; i++) rperm[i] = (int32_t)i;
+  std::vector<uint32_t> order(m);
+  for (uint64_t i = 0; i < m; i++) order[i] = inserts[rperm[i]];  // :217-218
+  vamana_batch_insert(P, graph, R, R, L, alpha, order, max_fraction, st_visited, st_dists, nthreads);
   return 0;
 }
 

@@ -8,6 +8,7 @@
 //
 //   perm    -> parlay::random_permutation<int>(n)                    (parlay/random.h:154-159)
 //   build   -> knn_index::build_index                                (algorithms/vamana/index.h:150-186)
+//   insert  -> knn_index::batch_insert called directly, three times        (algorithms/vamana/index.h:188-316)
 //   search  -> qsearchAll + stats                                    (algorithms/utils/beamSearch.h:537-565)
 //   full    -> beam_search (frontier + visited lists per query)      (algorithms/utils/beamSearch.h:217-223)
 //   random  -> beamSearchRandom (one random start point per query)     (algorithms/utils/beamSearch.h:309-351)
@@ -88,6 +89,33 @@ static int run(const std::string& cmd, int argc, char** argv) {
     double t1 = now_s();
     printf("REF_BUILD_SECONDS %.6f\n", t1 - t0);
     G.save((char*)(out + ".graph").c_str());
+    dump(out + ".bvisited", BuildStats.visited.begin(), 4 * G.size());
+    dump(out + ".bdistances", BuildStats.distances.begin(), 4 * G.size());
+    return 0;
+  }
+
+  if (cmd == "insert") {
+    // knn_index::batch_insert (vamana/index.h:188-316) used directly, three calls on one graph: the first half of the points
+    // (given order), the second half (random order), then a scattered subset again with another max_fraction; the graph is
+    // dumped after every call
+    long R = atol(need(argc, argv, "-R")), L = atol(need(argc, argv, "-L"));
+    double alpha = atof(arg(argc, argv, "-alpha", "1.2"));
+    BuildParams BP(R, L, alpha, 1, false);
+    Graph<uint> G(BP.max_degree(), Points.size());
+    findex I(BP);
+    I.start_point = 0;   // set_start (index.h:148); build_index does it before its first batch_insert
+    stats<uint> BuildStats(G.size());
+    const uint n = (uint)Points.size();
+    auto dumpg = [&](int step) { G.save((char*)(out + ".g" + std::to_string(step)).c_str()); };
+    parlay::sequence<uint> a = parlay::tabulate(n / 2, [&](size_t i) { return (uint)i; });
+    I.batch_insert(a, G, Points, Points, BuildStats, alpha, false, 2, .02, false);
+    dumpg(0);
+    parlay::sequence<uint> b = parlay::tabulate(n - n / 2, [&](size_t i) { return (uint)(n / 2 + i); });
+    I.batch_insert(b, G, Points, Points, BuildStats, alpha, true, 2, .02, false);
+    dumpg(1);
+    parlay::sequence<uint> c = parlay::tabulate(n / 7, [&](size_t i) { return (uint)((i * 7 + 3) % n); });
+    I.batch_insert(c, G, Points, Points, BuildStats, 1.0, false, 2, .05, false);
+    dumpg(2);
     dump(out + ".bvisited", BuildStats.visited.begin(), 4 * G.size());
     dump(out + ".bdistances", BuildStats.distances.begin(), 4 * G.size());
     return 0;

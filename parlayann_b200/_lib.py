@@ -32,7 +32,7 @@ SYMBOLS = [
     "pann_last_error", "pann_device_count", "pann_version", "pann_index_create", "pann_index_create_synthetic", "pann_index_create_synthetic_shard",
     "pann_index_destroy", "pann_index_set_graph", "pann_index_get_graph", "pann_index_get_points", "pann_index_info",
     "pann_index_last_timing", "pann_index_build_stats", "pann_index_last_bytes", "pann_search_batch", "pann_queries_upload", "pann_queries_synthetic",
-    "pann_queries_download", "pann_search_resident", "pann_search_fetch", "pann_search_device_result", "pann_search_full", "pann_search_batch_starts", "pann_search_full_starts", "pann_search_rerank_batch", "pann_vamana_build",
+    "pann_queries_download", "pann_search_resident", "pann_search_fetch", "pann_search_device_result", "pann_search_full", "pann_search_batch_starts", "pann_search_full_starts", "pann_search_rerank_batch", "pann_vamana_build", "pann_vamana_batch_insert",
     "pann_random_permutation", "pann_random_starts", "pann_batch_schedule", "pann_groundtruth", "pann_groundtruth_resident",
     "pann_groundtruth_fetch", "pann_index_groundtruth_stats", "pann_groundtruth_merge", "pann_groundtruth_device_result", "pann_groundtruth_merge_device",
     "pann_groundtruth_upload", "pann_search_sweep",

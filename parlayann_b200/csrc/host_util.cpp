@@ -55,8 +55,13 @@ void pann_host_random_permutation(int64_t n, int32_t* out) {
 
 // batch_insert's schedule (algorithms/vamana/index.h:206-209, :223-234) with base = 2, max_fraction = .02:
 // prefix-doubling batches [2^i - 1, 2^(i+1) - 1) while 2^i <= max_batch, then fixed strides of max_batch.
+int64_t pann_host_batch_schedule_f(uint64_t n, uint64_t m, double max_fraction, int64_t* lo, int64_t* hi, int64_t cap);
 int64_t pann_host_batch_schedule(uint64_t n, uint64_t m, int64_t* lo, int64_t* hi, int64_t cap) {
-  size_t max_batch = std::min((size_t)(0.02 * (double)(float)n), (size_t)1000000);
+  return pann_host_batch_schedule_f(n, m, 0.02, lo, hi, cap);
+}
+// the same with batch_insert's max_fraction argument (index.h:191, :206-207: double max_fraction * float n)
+int64_t pann_host_batch_schedule_f(uint64_t n, uint64_t m, double max_fraction, int64_t* lo, int64_t* hi, int64_t cap) {
+  size_t max_batch = std::min((size_t)(max_fraction * (double)(float)n), (size_t)1000000);
   if (max_batch == 0) max_batch = n;
   size_t inc = 0, count = 0;
   int64_t nb = 0;

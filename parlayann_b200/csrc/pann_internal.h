@@ -89,3 +89,4 @@ int pann_gen_rows_device(int kind, uint64_t seed, uint64_t stream, uint64_t row0
 void pann_host_random_permutation(int64_t n, int32_t* out);
 void pann_host_random_starts(uint64_t nq, uint64_t n, uint32_t* out);
 int64_t pann_host_batch_schedule(uint64_t n, uint64_t m, int64_t* lo, int64_t* hi, int64_t cap);
+int64_t pann_host_batch_schedule_f(uint64_t n, uint64_t m, double max_fraction, int64_t* lo, int64_t* hi, int64_t cap);

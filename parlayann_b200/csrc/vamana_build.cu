@@ -179,24 +179,34 @@ int pann_launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevB
 
 void pann_host_sort_rows(uint32_t* graph, const float* dists, uint64_t n, uint32_t maxdeg);
 
-extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double alpha, int num_passes, int sort_neighbors,
-                                 uint32_t* out_visited, uint32_t* out_cmps, double phase_seconds[3]) {
+// build_index (fresh graph, all points, num_passes, final sort) and batch_insert (a subset into the existing graph) are the same
+// loop (vamana/index.h:150-186 calls :188-316 once per pass)
+static int vamana_run(pann_index* idx, uint32_t R, uint32_t L, double alpha, int num_passes, int sort_neighbors, const uint32_t* inserts,
+                      uint64_t m_in, int random_order, double max_fraction, bool fresh, uint32_t* out_visited, uint32_t* out_cmps,
+                      double phase_seconds[3]) {
   if (!idx) PANN_FAIL("pann_vamana_build: null index");
   if (R == 0 || R != idx->maxdeg) PANN_FAIL("pann_vamana_build: R must equal the graph's max degree (BuildParams::max_degree, types.h:210-214)");
   if (L < 1 || L > 65536) PANN_FAIL("pann_vamana_build: L out of range");
   if (num_passes < 1) PANN_FAIL("pann_vamana_build: num_passes must be >= 1");
   PANN_CUDA(cudaSetDevice(idx->device));
   const uint64_t n = idx->n;
+  const uint64_t m = inserts ? m_in : n;
   const uint32_t md = idx->maxdeg;
   cudaStream_t s = idx->stream;
   idx->last_launches = 0;
+  if (m == 0) { if (phase_seconds) phase_seconds[0] = phase_seconds[1] = phase_seconds[2] = 0; return 0; }
+  if (inserts)
+    for (uint64_t i = 0; i < m; i++)
+      if (inserts[i] >= n) PANN_FAIL("invalid point " + std::to_string(inserts[i]) + " given to batch_insert");   // index.h:193-199
 
   // insertion order and batch schedule: the reference's, bit for bit (index.h:206-234)
-  std::vector<int32_t> perm(n);
-  pann_host_random_permutation((int64_t)n, perm.data());
-  const int64_t nb = pann_host_batch_schedule(n, n, nullptr, nullptr, 0);
+  std::vector<int32_t> perm(m);
+  if (random_order) pann_host_random_permutation((int64_t)m, perm.data());
+  else for (uint64_t i = 0; i < m; i++) perm[i] = (int32_t)i;
+  if (inserts) for (uint64_t i = 0; i < m; i++) perm[i] = (int32_t)inserts[perm[i]];   // shuffled_inserts (:217-218)
+  const int64_t nb = pann_host_batch_schedule_f(n, m, max_fraction, nullptr, nullptr, 0);
   std::vector<int64_t> blo(nb), bhi(nb);
-  pann_host_batch_schedule(n, n, blo.data(), bhi.data(), nb);
+  pann_host_batch_schedule_f(n, m, max_fraction, blo.data(), bhi.data(), nb);
   uint64_t max_bs = 0;
   for (int64_t b = 0; b < nb; b++) max_bs = std::max<uint64_t>(max_bs, (uint64_t)(bhi[b] - blo[b]));
 
@@ -207,10 +217,10 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
   };
   struct Guard { decltype(release_all)& f; ~Guard() { f(); } } guard{release_all};
 
-  if (d_perm.reserve(4 * n)) return 1;
-  PANN_CUDA(cudaMemcpyAsync(d_perm.p, perm.data(), 4 * n, cudaMemcpyHostToDevice, s));
+  if (d_perm.reserve(4 * m)) return 1;
+  PANN_CUDA(cudaMemcpyAsync(d_perm.p, perm.data(), 4 * m, cudaMemcpyHostToDevice, s));
   // a fresh build starts from the empty graph (Graph(maxDeg, n), graph.h:134-145)
-  PANN_CUDA(cudaMemsetAsync(idx->graph, 0, (size_t)n * (md + 1) * 4, s));
+  if (fresh) PANN_CUDA(cudaMemsetAsync(idx->graph, 0, (size_t)n * (md + 1) * 4, s));
   uint32_t* st_vis = nullptr; uint32_t* st_cmp = nullptr;
   if (out_visited || out_cmps) {
     if (d_stats.reserve(8 * n)) return 1;
@@ -316,7 +326,7 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
       // SURVEY.md §8d B_ins: build search + robustPrune candidate rows + the row written and the reverse-edge row touched
       idx->build_search_bytes = search_bytes;
       idx->build_prune_bytes = acct[0]; idx->build_prune_calls = acct[1]; idx->build_pair_dists = acct[2];
-      idx->build_bytes = search_bytes + acct[0] + (uint64_t)num_passes * n * 2ull * 4ull * (md + 1);
+      idx->build_bytes = search_bytes + acct[0] + (uint64_t)num_passes * m * 2ull * 4ull * (md + 1);
     }
     for (size_t b = 0; b + 3 < evi; b += 4) {
       float m[3] = {0, 0, 0};
@@ -397,4 +407,18 @@ extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double
   PANN_CUDA(cudaStreamSynchronize(s));
   if (phase_seconds) { phase_seconds[0] = ph[0]; phase_seconds[1] = ph[1]; phase_seconds[2] = ph[2]; }
   return 0;
+}
+
+extern "C" int pann_vamana_build(pann_index* idx, uint32_t R, uint32_t L, double alpha, int num_passes, int sort_neighbors,
+                                 uint32_t* out_visited, uint32_t* out_cmps, double phase_seconds[3]) {
+  return vamana_run(idx, R, L, alpha, num_passes, sort_neighbors, nullptr, 0, 1, 0.02, true, out_visited, out_cmps, phase_seconds);
+}
+
+extern "C" int pann_vamana_batch_insert(pann_index* idx, const uint32_t* inserts, uint64_t m, uint32_t R, uint32_t L, double alpha,
+                                        int random_order, double max_fraction, uint32_t* out_visited, uint32_t* out_cmps,
+                                        double phase_seconds[3]) {
+  if (!inserts && m) PANN_FAIL("pann_vamana_batch_insert: null insert list");
+  if (!(max_fraction > 0)) PANN_FAIL("pann_vamana_batch_insert: max_fraction must be positive");
+  static const uint32_t none = 0;
+  return vamana_run(idx, R, L, alpha, 1, 0, inserts ? inserts : &none, m, random_order, max_fraction, false, out_visited, out_cmps, phase_seconds);
 }

@@ -260,6 +260,17 @@ class GraphIndex:
         self.build_phase_seconds = tuple(ph)
         return (sv, sd) if stats else None
 
+    def batch_insert(self, inserts, L=128, alpha=1.2, random_order=False, max_fraction=0.02, stats=False):
+        """knn_index::batch_insert (vamana/index.h:188-316): insert the listed vertices into the graph the index holds"""
+        ins = np.ascontiguousarray(inserts, dtype=np.uint32)
+        sv = np.zeros(self.n, np.uint32) if stats else None
+        sd = np.zeros(self.n, np.uint32) if stats else None
+        ph = (C.c_double * 3)()
+        check(_lib.lib().pann_vamana_batch_insert(self._h, _vp(ins), C.c_uint64(len(ins)), C.c_uint32(self.max_degree), C.c_uint32(L),
+                                                  C.c_double(alpha), int(bool(random_order)), C.c_double(max_fraction), _vp(sv), _vp(sd), ph))
+        self.build_phase_seconds = tuple(ph)
+        return (sv, sd) if stats else None
+
     # ---- ground truth (compute_groundtruth.cpp:22-100)
     def groundtruth(self, queries, k=100, id_offset=0):
         queries = np.ascontiguousarray(queries, dtype=fileio.np_dtype(self.data_type))

@@ -109,6 +109,19 @@ def vamana_build(points, data_type, metric="Euclidian", R=32, L=64, alpha=1.2, p
     return g, sv, sd
 
 
+def vamana_batch_insert(points, graph, inserts, data_type, metric="Euclidian", L=64, alpha=1.2, random_order=False, max_fraction=0.02):
+    """knn_index::batch_insert of `inserts` into `graph` (modified in place); returns the stats increments (visited, distances)"""
+    n, d = points.shape
+    points = np.ascontiguousarray(points)
+    assert graph.dtype == np.uint32 and graph.flags["C_CONTIGUOUS"]
+    ins = np.ascontiguousarray(inserts, dtype=np.uint32)
+    sv = np.zeros(n, dtype=np.uint32); sd = np.zeros(n, dtype=np.uint32)
+    lib().oracle_vamana_batch_insert(DT[data_type], METRIC[metric], _p(points), C.c_uint64(n), C.c_uint32(d), C.c_uint64(points.strides[0]),
+                                     C.c_uint32(graph.shape[1] - 1), C.c_uint32(L), C.c_double(alpha), _p(ins), C.c_uint64(len(ins)),
+                                     int(bool(random_order)), C.c_double(max_fraction), _p(graph), _p(sv), _p(sd), nthreads())
+    return sv, sd
+
+
 def groundtruth(base, queries, data_type, metric="Euclidian", k=100):
     base = np.ascontiguousarray(base); queries = np.ascontiguousarray(queries)
     nq = queries.shape[0]

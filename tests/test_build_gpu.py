@@ -143,3 +143,36 @@ def test_build_with_gram_tile_matches_oracle(dataset, data_type, metric, n, d, R
     monkeypatch.setenv("PANN_PRUNE_ROW_CACHE", "1")
     monkeypatch.setenv("PANN_PRUNE_GRAM", gram)
     test_build_matches_oracle(dataset, data_type, metric, n, d, R, L, passes)
+
+
+def test_batch_insert_matches_reference_golden_and_oracle(dataset):
+    """pann_vamana_batch_insert = knn_index::batch_insert used directly (vamana/index.h:188-316): subsets into an existing graph,
+    given / random order, another max_fraction, re-insertion of inserted vertices — the reference's own graphs (golden), then
+    the oracle at a larger size with the graph uploaded in between (pann_index_set_graph)"""
+    import os
+    import parlayann_b200 as P
+    from golden_util import GOLDEN
+    from test_oracle_vs_reference import insert_steps
+    z = np.load(os.path.join(GOLDEN, "batch_insert.npz"))
+    n, d, R, L, seed = (int(x) for x in z["params"])
+    base = O.gen_points("uint8", n, d, seed=seed)
+    idx = P.GraphIndex(base, None, "uint8", "Euclidian", max_degree=R)
+    sv = np.zeros(n, np.uint32); sd = np.zeros(n, np.uint32)
+    for i, (ins, alpha, rnd, frac) in enumerate(insert_steps(n)):
+        a, b = idx.batch_insert(ins, L=L, alpha=alpha, random_order=rnd, max_fraction=frac, stats=True)
+        sv += a; sd += b
+        assert np.array_equal(valid_graph(idx.graph()), valid_graph(z[f"g{i}"])), i
+    assert np.array_equal(sv, z["bvisited"]) and np.array_equal(sd, z["bdistances"])
+    with pytest.raises(P.PannError, match="invalid point"):
+        idx.batch_insert(np.array([1, n + 5], np.uint32), L=L)
+    idx.batch_insert(np.zeros(0, np.uint32), L=L)   # nothing to insert: the graph stays
+    assert np.array_equal(valid_graph(idx.graph()), valid_graph(z["g2"]))
+    # larger, int8 MIPS, starting from an oracle-built graph over a prefix
+    ds = dataset("int8", "mips", n=9000, d=100, nq=10, R=24, L=48)
+    g = np.zeros((ds.n, 25), np.uint32)
+    O.vamana_batch_insert(ds.base, g, np.arange(6000, dtype=np.uint32), "int8", "mips", L=48, alpha=1.0, random_order=True)
+    idx2 = P.GraphIndex(ds.base, g.copy(), "int8", "mips")
+    ins = np.arange(6000, 9000, dtype=np.uint32)
+    a, b = idx2.batch_insert(ins, L=48, alpha=1.2, random_order=True, stats=True)
+    ra, rb = O.vamana_batch_insert(ds.base, g, ins, "int8", "mips", L=48, alpha=1.2, random_order=True)
+    assert np.array_equal(valid_graph(idx2.graph()), valid_graph(g)) and np.array_equal(a, ra) and np.array_equal(b, rb)

@@ -95,3 +95,25 @@ def test_batch_schedule_known_answer():
     s = O.batch_schedule(100000)
     assert s[:4] == [(0, 1), (1, 3), (3, 7), (7, 15)] and s[10] == (1023, 2047) and s[11] == (2047, 4047)
     assert len(s) == 60 and s[-1][1] == 100000
+
+
+def insert_steps(n):
+    """the three batch_insert calls of ref_driver `insert` / tests/golden/make_golden_insert.py"""
+    return [(np.arange(n // 2, dtype=np.uint32), 1.2, False, .02), (np.arange(n // 2, n, dtype=np.uint32), 1.2, True, .02),
+            (((np.arange(n // 7, dtype=np.uint64) * 7 + 3) % n).astype(np.uint32), 1.0, False, .05)]
+
+
+def test_batch_insert_matches_reference():
+    """knn_index::batch_insert used directly (vamana/index.h:188-316): subsets, random order, another max_fraction, re-insertion"""
+    import os
+    from golden_util import GOLDEN, valid_graph
+    z = np.load(os.path.join(GOLDEN, "batch_insert.npz"))
+    n, d, R, L, seed = (int(x) for x in z["params"])
+    base = O.gen_points("uint8", n, d, seed=seed)
+    g = np.zeros((n, R + 1), np.uint32)
+    sv = np.zeros(n, np.uint32); sd = np.zeros(n, np.uint32)
+    for i, (ins, alpha, rnd, frac) in enumerate(insert_steps(n)):
+        a, b = O.vamana_batch_insert(base, g, ins, "uint8", L=L, alpha=alpha, random_order=rnd, max_fraction=frac)
+        sv += a; sd += b
+        assert np.array_equal(valid_graph(g), valid_graph(z[f"g{i}"])), i
+    assert np.array_equal(sv, z["bvisited"]) and np.array_equal(sd, z["bdistances"])
