@@ -7,7 +7,7 @@ import numpy as np
 from . import _lib, fileio
 from ._lib import check
 from .hnsw_file import HnswModel, read_hnsw, write_hnsw
-from .index import GraphIndex, _vp
+from .index import GraphIndex, _vp, _rstride
 
 
 class HNSW:
@@ -69,7 +69,7 @@ class HNSW:
         ocap = int(k if ocap is None else ocap)
         ids = np.empty((nq, ocap), np.uint32); dists = np.empty((nq, ocap), np.float32)
         cnt = np.empty(nq, np.uint32); cmps = np.empty(nq, np.uint32)
-        check(_lib.lib().pann_hnsw_search(self._h, _vp(queries), C.c_uint64(nq), C.c_uint64(queries.strides[0] if nq else 0), C.c_uint32(k),
+        check(_lib.lib().pann_hnsw_search(self._h, _vp(queries), C.c_uint64(nq), C.c_uint64(_rstride(queries)), C.c_uint32(k),
                                           C.c_uint32(ef), C.c_int64(limit), C.c_uint32(ocap), _vp(ids), _vp(dists), _vp(cnt), _vp(cmps)))
         return ids, dists, cnt, cmps
 

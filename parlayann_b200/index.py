@@ -15,6 +15,11 @@ def _vp(a):
     return None if a is None else a.ctypes.data_as(C.c_void_p)
 
 
+def _rstride(a):
+    """bytes between the rows of a C-contiguous 2-D array (numpy reports an arbitrary stride, even 0, for an axis of length 1)"""
+    return a.shape[1] * a.itemsize if a.ndim == 2 else a.strides[0]
+
+
 def quant_params_u8(points):
     """Euclidian_Point<uint8_t>::generate_parameters (euclidian_point.h:211-237) + parameters(min, max, dims) (:104-108):
     per-row minima / maxima start at 0, all-integer non-negative data below 256 maps unscaled.  Returns (slope, offset)."""
@@ -114,7 +119,7 @@ class GraphIndex:
                 max_degree = graph.shape[1] - 1
             self.max_degree = int(max_degree)
             check(L.pann_index_create(C.byref(self._h), device, _lib.DTYPE[data_type], _lib.METRIC[metric],
-                                      C.c_uint64(self.n), C.c_uint32(self.d), C.c_uint64(points.strides[0]), _vp(points),
+                                      C.c_uint64(self.n), C.c_uint32(self.d), C.c_uint64(_rstride(points)), _vp(points),
                                       C.c_uint32(self.max_degree), _vp(graph)))
         self.start_point = 0  # knn_index::set_start (vamana/index.h:148)
 
@@ -146,7 +151,7 @@ class GraphIndex:
     def points(self, row0=0, nrows=None):
         nrows = self.n - row0 if nrows is None else nrows
         out = np.empty((nrows, self.d), dtype=fileio.np_dtype(self.data_type))
-        check(_lib.lib().pann_index_get_points(self._h, C.c_uint64(row0), C.c_uint64(nrows), _vp(out), C.c_uint64(out.strides[0])))
+        check(_lib.lib().pann_index_get_points(self._h, C.c_uint64(row0), C.c_uint64(nrows), _vp(out), C.c_uint64(_rstride(out))))
         return out
 
     def last_timing(self):
@@ -182,16 +187,16 @@ class GraphIndex:
             if st.shape[0] != nq:
                 raise ValueError("per-query starts need one row per query")
             nsq = None if nstarts_q is None else np.ascontiguousarray(nstarts_q, dtype=np.uint32)
-            check(_lib.lib().pann_search_batch_starts(self._h, _vp(queries), C.c_uint64(nq), C.c_uint64(queries.strides[0]), _vp(st),
+            check(_lib.lib().pann_search_batch_starts(self._h, _vp(queries), C.c_uint64(nq), C.c_uint64(_rstride(queries)), _vp(st),
                                                       C.c_uint32(st.shape[1]), _vp(nsq), C.byref(qp), _vp(out[0]), _vp(out[1]), _vp(out[2]), _vp(out[3])))
             return out
-        check(_lib.lib().pann_search_batch(self._h, _vp(queries), C.c_uint64(nq), C.c_uint64(queries.strides[0]), _vp(st),
+        check(_lib.lib().pann_search_batch(self._h, _vp(queries), C.c_uint64(nq), C.c_uint64(_rstride(queries)), _vp(st),
                                            C.c_uint32(len(st)), C.byref(qp), _vp(out[0]), _vp(out[1]), _vp(out[2]), _vp(out[3])))
         return out
 
     def upload_queries(self, queries):
         queries = np.ascontiguousarray(queries, dtype=fileio.np_dtype(self.data_type))
-        check(_lib.lib().pann_queries_upload(self._h, _vp(queries), C.c_uint64(queries.shape[0]), C.c_uint64(queries.strides[0])))
+        check(_lib.lib().pann_queries_upload(self._h, _vp(queries), C.c_uint64(queries.shape[0]), C.c_uint64(_rstride(queries))))
         self.nq = queries.shape[0]
 
     def synthetic_queries(self, nq, kind=None, seed=1234, stream=1, r=24, nc=256):
@@ -201,7 +206,7 @@ class GraphIndex:
 
     def download_queries(self):
         out = np.empty((self.nq, self.d), dtype=fileio.np_dtype(self.data_type))
-        check(_lib.lib().pann_queries_download(self._h, _vp(out), C.c_uint64(out.strides[0])))
+        check(_lib.lib().pann_queries_download(self._h, _vp(out), C.c_uint64(_rstride(out))))
         return out
 
     def search_resident(self, k=10, beam=10, cut=1.35, limit=None, degree_limit=None, starts=None):
@@ -227,7 +232,7 @@ class GraphIndex:
         else:
             queries = np.ascontiguousarray(queries, dtype=fileio.np_dtype(self.data_type))
             nq = queries.shape[0]
-            qptr, qstride = _vp(queries), queries.strides[0]
+            qptr, qstride = _vp(queries), _rstride(queries)
         st = np.ascontiguousarray([self.start_point] if starts is None else starts, dtype=np.uint32)
         qp = self._qp(k, beam, cut, limit, degree_limit)
         fcap = int(max(beam, st.shape[-1]))
@@ -277,7 +282,7 @@ class GraphIndex:
         nq = queries.shape[0]
         ids = np.empty((nq, k), np.int32)
         dists = np.empty((nq, k), np.float32)
-        check(_lib.lib().pann_groundtruth(self._h, _vp(queries), C.c_uint64(nq), C.c_uint64(queries.strides[0]), C.c_uint32(k),
+        check(_lib.lib().pann_groundtruth(self._h, _vp(queries), C.c_uint64(nq), C.c_uint64(_rstride(queries)), C.c_uint32(k),
                                           C.c_int64(id_offset), _vp(ids), _vp(dists)))
         return ids, dists
 
@@ -314,8 +319,8 @@ class GraphIndex:
         st = np.asarray([qindex.start_point] if starts is None else starts, dtype=np.uint32)
         out = (np.empty((nq, k), np.uint32), np.empty((nq, k), np.float32), np.empty(nq, np.uint32), np.empty(nq, np.uint32))
         qp = qindex._qp(k, beam, cut, limit, degree_limit)
-        check(_lib.lib().pann_search_rerank_batch(qindex._h, self._h, _vp(qqueries), C.c_uint64(qqueries.strides[0] if nq else 0),
-                                                  _vp(queries), C.c_uint64(queries.strides[0] if nq else 0), C.c_uint64(nq), _vp(st),
+        check(_lib.lib().pann_search_rerank_batch(qindex._h, self._h, _vp(qqueries), C.c_uint64(_rstride(qqueries)),
+                                                  _vp(queries), C.c_uint64(_rstride(queries)), C.c_uint64(nq), _vp(st),
                                                   C.c_uint32(len(st)), C.byref(qp), C.c_int64(rerank_factor),
                                                   _vp(out[0]), _vp(out[1]), _vp(out[2]), _vp(out[3])))
         return out
