@@ -313,14 +313,14 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
     cudaMemsetAsync(cand_cnt.p, 0, 4ull * nq * GTM_MAX_SUB, s);
     const int store_zero = idx->metric == PANN_M_MIPS ? 1 : 0;
     if (idx->dtype == PANN_DT_F32) {
-      pann_gt_norm_kernel<PANN_DT_F32><<<(unsigned)((nb_pad + 255) / 256), 256, 0, s>>>(idx->points, nb, nb_pad, stride, idx->geom.nch, bnorm.p, store_zero, bnmax);
-      pann_gt_norm_kernel<PANN_DT_F32><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>(d_q, nq, nq, stride, idx->geom.nch, qnorm.p, 0, nullptr);
+      pann_gt_norm_kernel<PANN_DT_F32><<<(unsigned)((nb_pad + 255) / 256), 256, 0, s>>>(idx->points, nb, nb_pad, stride, idx->geom.nch, bnorm.p, store_zero, bnmax, 1);
+      pann_gt_norm_kernel<PANN_DT_F32><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>(d_q, nq, nq, stride, idx->geom.nch, qnorm.p, 0, nullptr, 0);
     } else if (idx->dtype == PANN_DT_U8) {
-      pann_gt_norm_kernel<PANN_DT_U8><<<(unsigned)((nb_pad + 255) / 256), 256, 0, s>>>(idx->points, nb, nb_pad, stride, idx->geom.nch, bnorm.p, store_zero, nullptr);
-      pann_gt_norm_kernel<PANN_DT_U8><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>(d_q, nq, nq, stride, idx->geom.nch, qnorm.p, 0, nullptr);
+      pann_gt_norm_kernel<PANN_DT_U8><<<(unsigned)((nb_pad + 255) / 256), 256, 0, s>>>(idx->points, nb, nb_pad, stride, idx->geom.nch, bnorm.p, store_zero, nullptr, 1);
+      pann_gt_norm_kernel<PANN_DT_U8><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>(d_q, nq, nq, stride, idx->geom.nch, qnorm.p, 0, nullptr, 0);
     } else {
-      pann_gt_norm_kernel<PANN_DT_I8><<<(unsigned)((nb_pad + 255) / 256), 256, 0, s>>>(idx->points, nb, nb_pad, stride, idx->geom.nch, bnorm.p, store_zero, nullptr);
-      pann_gt_norm_kernel<PANN_DT_I8><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>(d_q, nq, nq, stride, idx->geom.nch, qnorm.p, 0, nullptr);
+      pann_gt_norm_kernel<PANN_DT_I8><<<(unsigned)((nb_pad + 255) / 256), 256, 0, s>>>(idx->points, nb, nb_pad, stride, idx->geom.nch, bnorm.p, store_zero, nullptr, 1);
+      pann_gt_norm_kernel<PANN_DT_I8><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>(d_q, nq, nq, stride, idx->geom.nch, qnorm.p, 0, nullptr, 0);
     }
     idx->last_launches += 2;
     // first thresholds: "everything passes" — the first chunk is just the first `seed` rows, all of which become

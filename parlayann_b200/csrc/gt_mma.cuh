@@ -115,6 +115,31 @@ __device__ __forceinline__ uint4 gtm_lds128(uint32_t saddr) {
   return r;
 }
 __device__ __forceinline__ void gtm_tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// the same 32 columns written from registers (accumulator pre-initialisation)
+__device__ __forceinline__ void gtm_tmem_st32(uint32_t taddr, const uint4 (&b)[8]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+      "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};" ::"r"(taddr),
+      "r"(b[0].x), "r"(b[0].y), "r"(b[0].z), "r"(b[0].w), "r"(b[1].x), "r"(b[1].y), "r"(b[1].z), "r"(b[1].w), "r"(b[2].x), "r"(b[2].y), "r"(b[2].z),
+      "r"(b[2].w), "r"(b[3].x), "r"(b[3].y), "r"(b[3].z), "r"(b[3].w), "r"(b[4].x), "r"(b[4].y), "r"(b[4].z), "r"(b[4].w), "r"(b[5].x), "r"(b[5].y),
+      "r"(b[5].z), "r"(b[5].w), "r"(b[6].x), "r"(b[6].y), "r"(b[6].z), "r"(b[6].w), "r"(b[7].x), "r"(b[7].y), "r"(b[7].z), "r"(b[7].w)
+      : "memory");
+}
+__device__ __forceinline__ void gtm_tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+// mbarrier operations on a 32-bit shared address (the epilogue loop keeps the converted addresses in registers)
+__device__ __forceinline__ void gtm_mbar_arrive_a(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
+__device__ __forceinline__ void gtm_mbar_wait_a(uint32_t bar, uint32_t parity) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "WAIT_%=:\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+      "@p bra DONE_%=;\n\t"
+      "bra WAIT_%=;\n\t"
+      "DONE_%=:\n\t}" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ int gtm_max3(int a, int b, int c) { return __vimax3_s32(a, b, c); }
+__device__ __forceinline__ float gtm_max3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
 
 // ---------------------------------------------------------------------------------------------------------------
 struct GtMmaArgs {
@@ -126,7 +151,7 @@ struct GtMmaArgs {
   uint32_t* cand_ids;          // [nq][nsub][subcap]  (nsub = (GTM_EPI_WARPS / 4) * gridDim.y, nsub * subcap <= GTM_CAND_CAP)
   uint32_t* cand_cnt;          // [nq][GTM_MAX_SUB]
   uint32_t subcap;
-  uint32_t dbg;                // experiments only (PANN_GT_DBG): 1 = skip the filter arithmetic, 2 = skip the TMEM loads as well
+  uint32_t dbg;                // experiments only (PANN_GT_DBG): 1 = skip the filter arithmetic, 2 = skip the TMEM loads and stores as well, 4 = max tree but no appends, 8 = no accumulator pre-initialisation
 };
 
 template <bool ISINT>
@@ -199,7 +224,7 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       gtm_mbar_wait(a_full, 0);
       uint32_t stage = 0, phase = 0, as = 0, aphase = 0;
       for (uint32_t t = 0; t < ntiles; t++) {
-        gtm_mbar_wait(&t_empty[as], aphase ^ 1);
+        gtm_mbar_wait(&t_empty[as], aphase);   // drained AND pre-initialised with -|b|^2 / 2 by the epilogue warps
         gtm_tcgen05_fence_after();
         const uint32_t tmem_d = tmem_base + as * GTM_N;
         for (uint32_t j = 0; j < A.kb; j++) {
@@ -209,7 +234,7 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
           const uint64_t bdesc = gtm_smem_desc(gtm_smem_u32(sB + (size_t)stage * GTM_B_STAGE_BYTES));
 #pragma unroll
           for (uint32_t k4 = 0; k4 < 4; k4++)  // UMMA K = 32 bytes: advance the start address inside the swizzle atom
-            gtm_mma<ISINT>(tmem_d, adesc + 2 * k4, bdesc + 2 * k4, idesc, (j | k4) != 0 ? 1u : 0u);
+            gtm_mma<ISINT>(tmem_d, adesc + 2 * k4, bdesc + 2 * k4, idesc, 1u);
           gtm_tcgen05_commit(&empty[stage]);
           if (++stage == A.nstages) { stage = 0; phase ^= 1; }
         }
@@ -219,74 +244,107 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
       }
     }
   } else {
-    // ===== epilogue: GTM_EPI_WARPS warps; warp w reads TMEM lanes 32*(w%4).. and one column quarter =====
+    // ===== epilogue: GTM_EPI_WARPS warps; warp w owns TMEM lanes 32*(w%4).. and one column quarter =====
+    // The accumulator is PRE-INITIALISED with -|b_j|^2 / 2 per column (tcgen05.st from the tile's row of the ring) and the MMA
+    // always accumulates, so what comes back is s_j = q.b_j - |b_j|^2 / 2 and the filter "|b_j|^2 - 2 q.b_j <= T_q" is
+    // s_j >= -T_q / 2: per 32 columns one TMEM load, a 3-input max tree and one compare — no per-element arithmetic, no
+    // |b|^2 reads in the test (ncu of the previous epilogue: 2.3 CUDA-core instructions per accumulator element, tensor pipe
+    // 23 % busy; profiles/r1_k4_mma_full_summary.txt).
     const uint32_t quad = widx & 3, part = (uint32_t)(widx - 2) >> 2;   // TMEM lanes 32*quad.., columns 64*part..
     const uint32_t q = q0 + quad * 32 + lane;
     const bool qok = q < A.nq;
     typedef typename std::conditional<ISINT, int, float>::type acc_t;
-    acc_t T;
-    if constexpr (ISINT) T = qok ? reinterpret_cast<const int*>(A.thr)[q] : INT_MIN;
-    else T = qok ? reinterpret_cast<const float*>(A.thr)[q] : -INFINITY;
+    acc_t S;   // pass mark on s_j
+    if constexpr (ISINT) S = qok ? ((1 - reinterpret_cast<const int*>(A.thr)[q]) >> 1) : INT_MAX;   // ceil(-T / 2)
+    else S = qok ? -0.5f * reinterpret_cast<const float*>(A.thr)[q] : INFINITY;
     const uint32_t sub = blockIdx.y * (GTM_EPI_WARPS / 4) + part;
     uint32_t* my_ids = A.cand_ids + (size_t)(qok ? q : 0) * GTM_CAND_CAP + (size_t)sub * A.subcap;
     uint32_t cnt = 0;   // appended so far (may run past subcap: the shrink kernel reports the overflow)
     const uint32_t bn_s_addr = gtm_smem_u32(bn_s);
-    uint32_t as = 0, aphase = 0, bs = 0, bphase = 0;
-    for (uint32_t t = 0; t < ntiles; t++) {
-      const uint64_t row0 = seg_row0 + (uint64_t)t * GTM_N;
-      gtm_mbar_wait(&bn_full[bs], bphase);
-      gtm_mbar_wait(&t_full[as], aphase);
-      gtm_tcgen05_fence_after();
+    const uint32_t a_tfull = gtm_smem_u32(t_full), a_tempty = gtm_smem_u32(t_empty), a_bnfull = gtm_smem_u32(bn_full), a_bnempty = gtm_smem_u32(bn_empty);
+    constexpr uint32_t NC = GTM_N / 32 / (GTM_EPI_WARPS / 4);   // 32-column groups per warp and tile
+    const uint32_t tmem_mine = tmem_base + ((quad * 32) << 16) + part * (GTM_N / (GTM_EPI_WARPS / 4));
+    // accumulator stage `st` := -|b|^2 / 2 of tile u (its row sits in ring slot u % GTM_BN), then both are handed on
+    auto preinit = [&](uint32_t u, uint32_t st) {
+      const uint32_t slot = u % GTM_BN;
+      gtm_mbar_wait_a(a_bnfull + 8 * slot, (u / GTM_BN) & 1);
+      if (!(A.dbg & (2 | 8))) {
 #pragma unroll 1
-      for (uint32_t c = 0; c < GTM_N / 32 / (GTM_EPI_WARPS / 4); c++) {
-        const uint32_t col0 = part * (GTM_N / (GTM_EPI_WARPS / 4)) + c * 32;
-        uint32_t v[32];
-        if (A.dbg & 2) continue;
-        gtm_tmem_ld32(tmem_base + ((quad * 32) << 16) + as * GTM_N + col0, v);
-        uint4 bn[8];
-        const uint32_t bnp = bn_s_addr + (bs * GTM_N + col0) * 4;   // broadcast reads
+        for (uint32_t c = 0; c < NC; c++) {
+          uint4 bn[8];
+          const uint32_t bnp = bn_s_addr + (slot * GTM_N + part * (GTM_N / (GTM_EPI_WARPS / 4)) + c * 32) * 4;   // broadcast reads
 #pragma unroll
-        for (int i = 0; i < 8; i++) bn[i] = gtm_lds128(bnp + 16 * i);
-        gtm_tmem_ld_wait();
-        if (A.dbg & 1) { if (v[0] == 0x7fffffffu && v[31] == 0x7ffffffeu) cnt++; continue; }
-        const uint32_t* bnw = reinterpret_cast<const uint32_t*>(bn);
-        // w_j = |b_j|^2 - 2 q.b_j ; almost never <= T_q once the threshold has tightened: test the minimum first
-        acc_t w[32], g4[8];
-#pragma unroll
-        for (int j = 0; j < 32; j++) {
-          if constexpr (ISINT) w[j] = (int)bnw[j] - 2 * (int)v[j];
-          else w[j] = fmaf(-2.0f, __uint_as_float(v[j]), __uint_as_float(bnw[j]));
+          for (int i = 0; i < 8; i++) bn[i] = gtm_lds128(bnp + 16 * i);
+          gtm_tmem_st32(tmem_mine + st * GTM_N + c * 32, bn);
         }
-#pragma unroll
-        for (int g = 0; g < 8; g++) {   // minima of groups of four, then of the 32 (+inf pads, no NaNs: fminf is exact)
-          if constexpr (ISINT) g4[g] = min(min(w[4 * g], w[4 * g + 1]), min(w[4 * g + 2], w[4 * g + 3]));
-          else g4[g] = fminf(fminf(w[4 * g], w[4 * g + 1]), fminf(w[4 * g + 2], w[4 * g + 3]));
-        }
-        acc_t mn;
-        if constexpr (ISINT) mn = min(min(min(g4[0], g4[1]), min(g4[2], g4[3])), min(min(g4[4], g4[5]), min(g4[6], g4[7])));
-        else mn = fminf(fminf(fminf(g4[0], g4[1]), fminf(g4[2], g4[3])), fminf(fminf(g4[4], g4[5]), fminf(g4[6], g4[7])));
-        if (mn <= T) {
-#pragma unroll
-          for (int g = 0; g < 8; g++) {
-            if (g4[g] <= T) {
-#pragma unroll
-              for (int jj = 0; jj < 4; jj++) {
-                const int j = 4 * g + jj;
-                if (w[j] <= T) {
-                  if (cnt < A.subcap) my_ids[cnt] = (uint32_t)(row0 + col0 + j);
-                  cnt++;
-                }
-              }
-            }
-          }
-        }
+        gtm_tmem_st_wait();
       }
       gtm_tcgen05_fence_before();
       __syncwarp();
-      if (lane == 0) { gtm_mbar_arrive(&t_empty[as]); gtm_mbar_arrive(&bn_empty[bs]); }
+      if (lane == 0) { gtm_mbar_arrive_a(a_tempty + 8 * st); gtm_mbar_arrive_a(a_bnempty + 8 * slot); }
+    };
+    if (ntiles > 0) preinit(0, 0);
+    if (ntiles > 1) preinit(1, 1);
+    uint32_t as = 0, aphase = 0;
+    for (uint32_t t = 0; t < ntiles; t++) {
+      const uint64_t row0 = seg_row0 + (uint64_t)t * GTM_N;
+      gtm_mbar_wait_a(a_tfull + 8 * as, aphase);
+      gtm_tcgen05_fence_after();
+      unsigned hits[NC];
+#pragma unroll
+      for (uint32_t c = 0; c < NC; c++) hits[c] = 0u;
+#pragma unroll
+      for (uint32_t c = 0; c < NC; c++) {
+        uint32_t v[32];
+        if (A.dbg & 2) continue;
+        gtm_tmem_ld32(tmem_mine + as * GTM_N + c * 32, v);
+        gtm_tmem_ld_wait();
+        if (A.dbg & 1) { if (v[0] == 0x7fffffffu && v[31] == 0x7ffffffeu) cnt++; continue; }
+        acc_t w[32];
+#pragma unroll
+        for (int j = 0; j < 32; j++) {
+          if constexpr (ISINT) w[j] = (int)v[j];
+          else w[j] = __uint_as_float(v[j]);
+        }
+        // almost never >= S once the threshold has tightened: the maximum of the 32 first (3-input maxima: 16 operations)
+        acc_t m9[11];
+#pragma unroll
+        for (int g = 0; g < 10; g++) m9[g] = gtm_max3(w[3 * g], w[3 * g + 1], w[3 * g + 2]);
+        m9[10] = w[30] > w[31] ? w[30] : w[31];
+        const acc_t m3a = gtm_max3(m9[0], m9[1], m9[2]), m3b = gtm_max3(m9[3], m9[4], m9[5]), m3c = gtm_max3(m9[6], m9[7], m9[8]);
+        const acc_t mx = gtm_max3(gtm_max3(m3a, m3b, m3c), m9[9], m9[10]);
+        if (A.dbg & 4) { if (mx == (acc_t)12345) cnt++; continue; }   // experiments: the max tree without the append path
+        if (mx >= S) {   // which of the 32 columns: a bit mask now, the global stores after the stage has been handed on
+          unsigned m = 0;
+#pragma unroll
+          for (int j = 0; j < 32; j++) m |= (w[j] >= S ? 1u : 0u) << j;
+          hits[c] = m;
+        }
+      }
+      // this stage's next tenant is tile t + 2: initialise it now (its |b|^2 row has been in the ring for a while), which
+      // also releases the stage to the MMA warp
+      if (t + 2 < ntiles) {
+        preinit(t + 2, as);
+      } else {
+        gtm_tcgen05_fence_before();
+        __syncwarp();
+        if (lane == 0) gtm_mbar_arrive_a(a_tempty + 8 * as);
+      }
+      // the candidates of this tile go out now, behind the barrier arrivals: a store that is still in flight when a warp
+      // arrives makes the (releasing) arrive wait for it, and that wait sat on the accumulator hand-over — measured on
+      // 10 000 x 10M x 128 u8: 26.3 ms with the stores inside the column loop
+#pragma unroll
+      for (uint32_t c = 0; c < NC; c++) {
+        unsigned m = hits[c];
+        while (m) {
+          const int j = __ffs(m) - 1;
+          m &= m - 1;
+          if (cnt < A.subcap) my_ids[cnt] = (uint32_t)(row0 + part * (GTM_N / (GTM_EPI_WARPS / 4)) + c * 32 + j);
+          cnt++;
+        }
+      }
       as ^= 1;
       if (as == 0) aphase ^= 1;
-      if (++bs == GTM_BN) { bs = 0; bphase ^= 1; }
     }
     if (qok) A.cand_cnt[(size_t)q * GTM_MAX_SUB + sub] = cnt;
   }
@@ -304,12 +362,16 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 // fails every test (+inf / 2^30).
 template <int DT>
 __global__ void pann_gt_norm_kernel(const uint8_t* __restrict__ rows, uint64_t n, uint64_t n_pad, uint32_t stride, uint32_t nch,
-                                    void* __restrict__ out, int store_zero, float* __restrict__ maxnorm) {
+                                    void* __restrict__ out, int store_zero, float* __restrict__ maxnorm, int as_init) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n_pad) return;
+  // what is stored is the INITIAL VALUE of the row's accumulator column (see pann_gt_mma_kernel): -|b|^2 / 2, so that the
+  // MMA leaves q.b - |b|^2 / 2 behind and the epilogue compares it with -T_q / 2 without touching |b|^2 again.  Integers:
+  // -floor(|b|^2 / 2), the test being relaxed by the dropped half (a superset filter; the shrink kernel is exact).
+  // as_init == 0 (query rows): the plain |q|^2.
   if (i >= n) {
-    if constexpr (DT == PANN_DT_F32) reinterpret_cast<float*>(out)[i] = INFINITY;
-    else reinterpret_cast<int*>(out)[i] = 1 << 30;
+    if constexpr (DT == PANN_DT_F32) reinterpret_cast<float*>(out)[i] = -INFINITY;
+    else reinterpret_cast<int*>(out)[i] = -(1 << 29);
     return;
   }
   const uint4* r = reinterpret_cast<const uint4*>(rows + i * stride);
@@ -320,7 +382,7 @@ __global__ void pann_gt_norm_kernel(const uint8_t* __restrict__ rows, uint64_t n
       const float a = __uint_as_float(v.x), b = __uint_as_float(v.y), cc = __uint_as_float(v.z), d = __uint_as_float(v.w);
       s += a * a + b * b + cc * cc + d * d;
     }
-    reinterpret_cast<float*>(out)[i] = store_zero ? 0.f : s;
+    reinterpret_cast<float*>(out)[i] = store_zero ? 0.f : (as_init ? -0.5f * s : s);
     if (maxnorm) atomicMax(reinterpret_cast<int*>(maxnorm), __float_as_int(s));  // s >= 0: int order = float order
   } else {
     int s = 0;
@@ -329,7 +391,7 @@ __global__ void pann_gt_norm_kernel(const uint8_t* __restrict__ rows, uint64_t n
       if constexpr (DT == PANN_DT_U8) { s = __dp4a(v.x, v.x, (unsigned)s); s = __dp4a(v.y, v.y, (unsigned)s); s = __dp4a(v.z, v.z, (unsigned)s); s = __dp4a(v.w, v.w, (unsigned)s); }
       else { s = __dp4a((int)v.x, (int)v.x, s); s = __dp4a((int)v.y, (int)v.y, s); s = __dp4a((int)v.z, (int)v.z, s); s = __dp4a((int)v.w, (int)v.w, s); }
     }
-    reinterpret_cast<int*>(out)[i] = store_zero ? 0 : s;
+    reinterpret_cast<int*>(out)[i] = store_zero ? 0 : (as_init ? -(s >> 1) : s);
   }
 }
 
