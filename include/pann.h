@@ -167,6 +167,14 @@ int pann_groundtruth(pann_index* idx, const void* host_queries, uint64_t nq, uin
 /* same on the resident query set; results stay on the device (pann_groundtruth_fetch) */
 int pann_groundtruth_resident(pann_index* idx, uint32_t k, int64_t id_offset);
 int pann_groundtruth_fetch(pann_index* idx, int32_t* out_ids, float* out_dists);
+/* One leg of a sharded job (the reference's compute_groundtruth has no sharded form; this is SURVEY.md §8e): base rows
+ * [row_lo, row_hi) only (row_hi = 0: to the end; row_lo a multiple of 256), keep_state != 0 continues from the top-k the
+ * previous leg left on the device, d_tau_cap (device, nq floats, or NULL) = per-query upper bounds of the final k-th distance
+ * — e.g. the k-th distance of the shards' merged samples — that tighten the filter, seen_rows = rows that bound was taken
+ * over.  With a bound a result row may hold fewer than k entries; the rest read id -1, distance +inf and sort last in
+ * pann_groundtruth_merge*.  Results as pann_groundtruth_resident. */
+int pann_groundtruth_resident_range(pann_index* idx, uint32_t k, int64_t id_offset, uint64_t row_lo, uint64_t row_hi,
+                                    int keep_state, const float* d_tau_cap, uint64_t seen_rows);
 /* which path the last ground-truth call took: launches of the tcgen05 kernel (0 = CUDA-core path only) and, cumulative over
  * the index's life, chunks retaken on the CUDA cores after a candidate-list overflow */
 int pann_index_groundtruth_stats(pann_index* idx, int* mma_launches, int* fallback_chunks);

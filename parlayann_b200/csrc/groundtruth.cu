@@ -164,6 +164,7 @@ __global__ void pann_gt_finish_kernel(const u64* state, uint64_t total, int64_t 
   uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= total) return;
   u64 key = state[i];
+  if (key == ~0ull) { ids[i] = -1; dists[i] = __int_as_float(0x7f800000); return; }   // empty slot (bounded runs only): sorts last in K5
   ids[i] = (int32_t)((int64_t)pann_key_id(key) + id_offset);
   dists[i] = pann_key_dist(key);
 }
@@ -177,12 +178,16 @@ __global__ void __launch_bounds__(GT_SEL_THREADS) pann_gt_merge_kernel(const int
   int m = 2; while (m < tot) m <<= 1;
   for (int i = threadIdx.x; i < m; i += blockDim.x) {
     u64 key = ~0ull;
-    if (i < tot) { uint64_t src = ((uint64_t)(i / k) * nq + q) * k + (i % k); key = pann_key(dists[src], (uint32_t)ids[src]); }
+    if (i < tot) { uint64_t src = ((uint64_t)(i / k) * nq + q) * k + (i % k); if (ids[src] >= 0) key = pann_key(dists[src], (uint32_t)ids[src]); }
     buf[i] = key;
   }
   __syncthreads();
   gt_bitonic(buf, m);
-  for (int i = threadIdx.x; i < (int)k; i += blockDim.x) { out_ids[q * k + i] = (int32_t)pann_key_id(buf[i]); out_dists[q * k + i] = pann_key_dist(buf[i]); }
+  for (int i = threadIdx.x; i < (int)k; i += blockDim.x) {
+    const bool empty = buf[i] == ~0ull;
+    out_ids[q * k + i] = empty ? -1 : (int32_t)pann_key_id(buf[i]);
+    out_dists[q * k + i] = empty ? __int_as_float(0x7f800000) : pann_key_dist(buf[i]);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -223,14 +228,14 @@ static int gt_make_tmap(CUtensorMap* tm, const void* ptr, uint64_t rows, uint32_
 static int gt_shrink_threads() { const char* e = getenv("PANN_GT_SHRINK_THREADS"); return e ? atoi(e) : 128; }
 template <int DT, int METRIC>
 static void gt_launch_shrink(pann_index* idx, cudaStream_t s, const uint8_t* d_q, uint32_t nq, uint32_t k, u64* state, const uint32_t* cand_ids,
-                             uint32_t* cand_cnt, uint32_t nsub, uint32_t subcap, uint32_t keys_cap, const void* qnorm, const float* bnmax, void* thr, int* overflow) {
+                             uint32_t* cand_cnt, uint32_t nsub, uint32_t subcap, uint32_t keys_cap, const void* qnorm, const float* bnmax, void* thr, int* overflow, const float* cap) {
   const size_t sm = 8ull * keys_cap + idx->geom.stride;
   cudaFuncSetAttribute(pann_gt_shrink_kernel<DT, METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(8ull * GTS_KEYS + idx->geom.stride));
-  pann_gt_shrink_kernel<DT, METRIC><<<nq, keys_cap == GTS_KEYS_SMALL ? gt_shrink_threads() : 256, sm, s>>>(idx->points, idx->geom.stride, idx->geom.nch, d_q, k, state, cand_ids, cand_cnt, nsub, subcap, keys_cap, qnorm, bnmax, thr, overflow);
+  pann_gt_shrink_kernel<DT, METRIC><<<nq, keys_cap == GTS_KEYS_SMALL ? gt_shrink_threads() : 256, sm, s>>>(idx->points, idx->geom.stride, idx->geom.nch, d_q, k, state, cand_ids, cand_cnt, nsub, subcap, keys_cap, qnorm, bnmax, thr, overflow, cap);
 }
 template <int DT, int METRIC>
-static void gt_launch_thr(cudaStream_t s, const u64* state, uint32_t nq, uint32_t k, const void* qnorm, const float* bnmax, void* thr) {
-  pann_gt_thr_kernel<DT, METRIC><<<(nq + 255) / 256, 256, 0, s>>>(state, nq, k, qnorm, bnmax, thr);
+static void gt_launch_thr(cudaStream_t s, const u64* state, uint32_t nq, uint32_t k, const void* qnorm, const float* bnmax, void* thr, const float* cap) {
+  pann_gt_thr_kernel<DT, METRIC><<<(nq + 255) / 256, 256, 0, s>>>(state, nq, k, qnorm, bnmax, thr, cap);
 }
 #define GT_DISPATCH(idx, CALL)                                                                              \
   do {                                                                                                      \
@@ -254,14 +259,28 @@ static void gt_v1_range(pann_index* idx, cudaStream_t s, const uint8_t* d_q, uin
     idx->last_launches += 2;
   }
 }
-// ground truth of the device-resident query rows d_q against the index's base rows; results stay in idx->gt_*
-static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, int64_t id_offset) {
+// ground truth of the device-resident query rows d_q against the index's base rows; results stay in idx->gt_*.
+// Sharded jobs run it in two legs: rows [0, s) (the sample), then — after the shards have merged their
+// samples — rows [s, n) continuing from the kept state with d_cap = per-query upper bounds of the FINAL k-th distance
+// (device, nq floats; every threshold is min(own k-th, cap)) and seen_rows = the number of rows that bound was computed
+// over (it sets the chunk schedule: survivors of a chunk of c rows ~ k c / rows seen).  The cap only tightens the
+// superset filter; the kept keys are exact, so the merged result does not change.
+struct GtLeg { uint64_t row_lo = 0, row_hi = 0; bool keep_state = false; const float* d_cap = nullptr; uint64_t seen_rows = 0; };
+static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, int64_t id_offset, const GtLeg& leg = GtLeg()) {
   if (k == 0 || k > GT_SEL_CAP / 2) PANN_FAIL("pann_groundtruth: k must be in 1.." + std::to_string(GT_SEL_CAP / 2));
-  if (idx->n < k) PANN_FAIL("pann_groundtruth: fewer base points than k");
+  const bool whole = leg.row_lo == 0 && leg.row_hi == 0 && !leg.keep_state;
+  if (idx->n < k && whole) PANN_FAIL("pann_groundtruth: fewer base points than k");
   if (nq == 0) { idx->gt_nq = 0; idx->gt_k = k; return 0; }
   if ((int64_t)idx->n + id_offset > (int64_t)INT32_MAX) PANN_FAIL("pann_groundtruth: ids do not fit the .ibin format's int32");
+  const uint64_t nb = leg.row_hi ? std::min<uint64_t>(leg.row_hi, idx->n) : idx->n;   // rows [row0, nb)
+  const uint64_t row0 = leg.row_lo;
+  if (row0 > nb) PANN_FAIL("pann_groundtruth: row range out of order");
+  if (row0 % GTM_N) PANN_FAIL("pann_groundtruth: row_lo must be a multiple of " + std::to_string(GTM_N) + " (the MMA tile)");
+  if (leg.keep_state && (idx->gt_nq != nq || idx->gt_k != k || idx->gt_scratch[0].cap < 8ull * nq * k))
+    PANN_FAIL("pann_groundtruth: no kept state of this shape to continue from (run the sample leg first)");
+  const float* d_cap = leg.d_cap;
+  const uint64_t seen_rows = leg.seen_rows;
   cudaStream_t s = idx->stream;
-  const uint64_t nb = idx->n;
   const uint32_t stride = idx->geom.stride;
   const bool isint = idx->dtype != PANN_DT_F32;
 
@@ -273,7 +292,7 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
   uint64_t seed = std::max<uint64_t>(512, ((2ull * k + GTM_N - 1) / GTM_N) * GTM_N);  // sample that sets the first thresholds
   if (const char* e = getenv("PANN_GT_SEED")) seed = std::max<uint64_t>(((uint64_t)atoll(e) + GTM_N - 1) / GTM_N * GTM_N, ((2ull * k + GTM_N - 1) / GTM_N) * GTM_N);
   const char* force_v1 = getenv("PANN_GT_V1");
-  bool use_mma = !(force_v1 && force_v1[0] == '1') && stride >= GTM_KB_BYTES && nstages >= 2 && nb >= 2 * seed && nq < (1ull << 31);
+  bool use_mma = !(force_v1 && force_v1[0] == '1') && stride >= GTM_KB_BYTES && nstages >= 2 && nb - row0 >= 2 * seed && nq < (1ull << 31);
   // growth of the MMA chunks: expected survivors of a chunk of c rows after s rows have been seen ~ k c / s
   double growth = std::min(4.0, 1.0 + (double)GTM_CAND_CAP / (3.0 * k));
   if (const char* e = getenv("PANN_GT_GROWTH")) growth = std::max(1.25, std::min(growth, atof(e)));
@@ -302,10 +321,12 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
   idx->gt_mma_launches = 0;
   idx->last_launches = 0;
   cudaEventRecord(idx->ev0, s);
-  pann_gt_init_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(state.as<u64>(), tot);
-  idx->last_launches++;
+  if (!leg.keep_state) {
+    pann_gt_init_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(state.as<u64>(), tot);
+    idx->last_launches++;
+  }
   if (!use_mma) {
-    gt_v1_range(idx, s, d_q, nq, k, state.as<u64>(), D.as<float>(), cb, 0, nb);
+    if (nb > row0) gt_v1_range(idx, s, d_q, nq, k, state.as<u64>(), D.as<float>(), cb, row0, nb);
   } else {
     float* bnmax = misc.as<float>();
     int* overflow = misc.as<int>() + 1;
@@ -325,8 +346,9 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
     idx->last_launches += 2;
     // first thresholds: "everything passes" — the first chunk is just the first `seed` rows, all of which become
     // candidates; from then on the chunks grow geometrically and the thresholds do the filtering
-#define GT_THR(DT, M) gt_launch_thr<DT, M>(s, state.as<u64>(), (uint32_t)nq, k, qnorm.p, bnmax, thr.p)
-    if (isint) pann_gt_thr_init_kernel<PANN_DT_U8><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>((uint32_t)nq, thr.p);
+#define GT_THR(DT, M) gt_launch_thr<DT, M>(s, state.as<u64>(), (uint32_t)nq, k, qnorm.p, bnmax, thr.p, d_cap)
+    if (d_cap || leg.keep_state) GT_DISPATCH(idx, GT_THR);    // from the kept state and / or the caps
+    else if (isint) pann_gt_thr_init_kernel<PANN_DT_U8><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>((uint32_t)nq, thr.p);
     else pann_gt_thr_init_kernel<PANN_DT_F32><<<(unsigned)((nq + 255) / 256), 256, 0, s>>>((uint32_t)nq, thr.p);
     idx->last_launches++;
     // instruction descriptor: D = s32 / f32, A and B = u8 / s8 / tf32, K-major both, N = 256, M = 128
@@ -341,9 +363,11 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
       fail(); PANN_FAIL("pann_groundtruth: cannot reserve shared memory for the MMA kernel");
     }
     const uint32_t nqb = (uint32_t)((nq + GTM_M - 1) / GTM_M);
-    uint64_t lo = 0;
+    const bool cold = !d_cap && !leg.keep_state;   // thresholds still "everything passes": the first chunk is the seed
+    uint64_t lo = row0;
     while (lo < nb) {
-      uint64_t c = lo == 0 ? seed : (uint64_t)((growth - 1.0) * (double)lo);
+      const uint64_t seen = lo - row0 + (cold ? 0 : std::max<uint64_t>(seen_rows, leg.keep_state ? row0 : 0));
+      uint64_t c = seen == 0 ? seed : (uint64_t)((growth - 1.0) * (double)seen);
       c = std::max<uint64_t>(c / GTM_N * GTM_N, GTM_N);
       const uint64_t hi = std::min<uint64_t>(nb, lo + c);
       const uint64_t tiles = (hi - lo + GTM_N - 1) / GTM_N;
@@ -359,9 +383,9 @@ static int gt_run(pann_index* idx, const uint8_t* d_q, uint64_t nq, uint32_t k, 
       if (isint) pann_gt_mma_kernel<true><<<dim3(nqb, (unsigned)S), GTM_THREADS, smem, s>>>(tmQ, tmB, A, idesc);
       else pann_gt_mma_kernel<false><<<dim3(nqb, (unsigned)S), GTM_THREADS, smem, s>>>(tmQ, tmB, A, idesc);
       idx->gt_mma_launches++;
-#define GT_SHRINK(DT, M) gt_launch_shrink<DT, M>(idx, s, d_q, (uint32_t)nq, k, state.as<u64>(), cand_ids.as<uint32_t>(), cand_cnt.as<uint32_t>(), (uint32_t)((GTM_EPI_WARPS / 4) * S), A.subcap, keys_cap, qnorm.p, bnmax, thr.p, overflow)
+#define GT_SHRINK(DT, M) gt_launch_shrink<DT, M>(idx, s, d_q, (uint32_t)nq, k, state.as<u64>(), cand_ids.as<uint32_t>(), cand_cnt.as<uint32_t>(), (uint32_t)((GTM_EPI_WARPS / 4) * S), A.subcap, keys_cap, qnorm.p, bnmax, thr.p, overflow, d_cap)
       // small tier first (8 KB of key slots, many CTAs per SM); queries with more keys raise bit 1 and get the large tier
-      uint32_t keys_cap = (k + (lo == 0 ? seed : 0) <= GTS_KEYS_SMALL / 2) ? GTS_KEYS_SMALL : GTS_KEYS;
+      uint32_t keys_cap = (k + (seen == 0 ? seed : 0) <= GTS_KEYS_SMALL / 2) ? GTS_KEYS_SMALL : GTS_KEYS;
       GT_DISPATCH(idx, GT_SHRINK);
       idx->last_launches += 2;
       cudaMemcpyAsync(h_flag, overflow, sizeof(int), cudaMemcpyDeviceToHost, s);
@@ -408,6 +432,15 @@ extern "C" int pann_groundtruth_resident(pann_index* idx, uint32_t k, int64_t id
   if (idx->nq == 0) PANN_FAIL("pann_groundtruth_resident: no resident query set");
   PANN_CUDA(cudaSetDevice(idx->device));
   return gt_run(idx, idx->queries.as<uint8_t>(), idx->nq, k, id_offset);
+}
+extern "C" int pann_groundtruth_resident_range(pann_index* idx, uint32_t k, int64_t id_offset, uint64_t row_lo, uint64_t row_hi,
+                                               int keep_state, const float* d_tau_cap, uint64_t seen_rows) {
+  if (!idx) PANN_FAIL("pann_groundtruth_resident_range: null index");
+  if (idx->nq == 0) PANN_FAIL("pann_groundtruth_resident_range: no resident query set");
+  PANN_CUDA(cudaSetDevice(idx->device));
+  GtLeg leg;
+  leg.row_lo = row_lo; leg.row_hi = row_hi; leg.keep_state = keep_state != 0; leg.d_cap = d_tau_cap; leg.seen_rows = seen_rows;
+  return gt_run(idx, idx->queries.as<uint8_t>(), idx->nq, k, id_offset, leg);
 }
 extern "C" int pann_groundtruth_fetch(pann_index* idx, int32_t* out_ids, float* out_dists) {
   if (!idx) PANN_FAIL("pann_groundtruth_fetch: null index");

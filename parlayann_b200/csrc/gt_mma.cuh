@@ -395,13 +395,18 @@ __global__ void pann_gt_norm_kernel(const uint8_t* __restrict__ rows, uint64_t n
   }
 }
 
-// T_q from the current k-th key of query q (see the header comment); conservative by construction
+// T_q from the current k-th key of query q (see the header comment); conservative by construction.  `cap` (optional) is
+// an upper bound of the query's final k-th distance known from elsewhere (the other shards of a sharded job): the
+// threshold uses min(own k-th, cap[q]), so a shard with a loose or still empty top-k filters with the global bound.
 template <int DT, int METRIC>
-__device__ __forceinline__ void gt_write_thr(u64 kth, uint32_t q, const void* qnorm, const float* bnmax, void* thr) {
+__device__ __forceinline__ void gt_write_thr(u64 kth, uint32_t q, const void* qnorm, const float* bnmax, void* thr, const float* cap = nullptr) {
+  bool have = kth != ~0ull;
+  float tau_f = have ? pann_key_dist(kth) : 0.f;
+  if (cap) { const float c = cap[q]; if (c < 3.0e38f && (!have || c < tau_f)) { tau_f = c; have = true; } }
   if constexpr (DT == PANN_DT_F32) {
     float T = 3.0e38f;
-    if (kth != ~0ull) {
-      const double tau = (double)pann_key_dist(kth);
+    if (have) {
+      const double tau = (double)tau_f;
       const double qn = (double)reinterpret_cast<const float*>(qnorm)[q], bm = (double)*bnmax;
       const double margin = 0.0078125 * sqrt(qn * bm) + 1e-4 * (qn + bm) + 1e-30;
       const double t = (METRIC == PANN_M_L2) ? (tau + margin - qn) : 2.0 * (tau + margin);
@@ -410,8 +415,8 @@ __device__ __forceinline__ void gt_write_thr(u64 kth, uint32_t q, const void* qn
     reinterpret_cast<float*>(thr)[q] = T;
   } else {
     int T = 1 << 29;
-    if (kth != ~0ull) {
-      const float tau = pann_key_dist(kth);
+    if (have && fabsf(tau_f) < 5.0e8f) {
+      const float tau = tau_f;
       const int ti = (int)tau + (fabsf(tau) >= 16777216.f ? 64 : 0);  // distances are (float)(int): exact below 2^24
       T = (METRIC == PANN_M_L2) ? ti - reinterpret_cast<const int*>(qnorm)[q] : 2 * ti;
     }
@@ -426,9 +431,9 @@ __global__ void pann_gt_thr_init_kernel(uint32_t nq, void* thr) {   // "everythi
   else reinterpret_cast<int*>(thr)[q] = 1 << 29;
 }
 template <int DT, int METRIC>
-__global__ void pann_gt_thr_kernel(const u64* __restrict__ state, uint32_t nq, uint32_t k, const void* qnorm, const float* bnmax, void* thr) {
+__global__ void pann_gt_thr_kernel(const u64* __restrict__ state, uint32_t nq, uint32_t k, const void* qnorm, const float* bnmax, void* thr, const float* cap) {
   const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
-  if (q < nq) gt_write_thr<DT, METRIC>(state[(uint64_t)q * k + k - 1], q, qnorm, bnmax, thr);
+  if (q < nq) gt_write_thr<DT, METRIC>(state[(uint64_t)q * k + k - 1], q, qnorm, bnmax, thr, cap);
 }
 
 // One CTA per query: exact distances of the candidates (reference operation order), merge with the running top-k
@@ -450,7 +455,7 @@ __global__ void __launch_bounds__(256) pann_gt_shrink_kernel(const uint8_t* __re
                                                              const uint8_t* __restrict__ queries, uint32_t k, u64* __restrict__ state,
                                                              const uint32_t* __restrict__ cand_ids, uint32_t* __restrict__ cand_cnt,
                                                              uint32_t nsub, uint32_t subcap, uint32_t keys_cap,
-                                                             const void* qnorm, const float* bnmax, void* thr, int* overflow) {
+                                                             const void* qnorm, const float* bnmax, void* thr, int* overflow, const float* cap) {
   extern __shared__ __align__(16) uint8_t gts_smem[];
   __shared__ uint32_t s_off[GTM_MAX_SUB + 1];
   __shared__ int s_over;
@@ -494,5 +499,5 @@ __global__ void __launch_bounds__(256) pann_gt_shrink_kernel(const uint8_t* __re
   __syncthreads();
   gtm_bitonic(buf, m);
   for (int i = threadIdx.x; i < (int)k; i += blockDim.x) state[(uint64_t)q * k + i] = buf[i];
-  if (threadIdx.x == 0) gt_write_thr<DT, METRIC>(buf[k - 1], q, qnorm, bnmax, thr);
+  if (threadIdx.x == 0) gt_write_thr<DT, METRIC>(buf[k - 1], q, qnorm, bnmax, thr, cap);
 }

@@ -290,6 +290,12 @@ class GraphIndex:
         check(_lib.lib().pann_groundtruth_resident(self._h, C.c_uint32(k), C.c_int64(id_offset)))
         self._gt_k = k
 
+    def groundtruth_range(self, k=100, id_offset=0, row_lo=0, row_hi=0, keep_state=False, d_tau_cap=0, seen_rows=0):
+        """one leg of a sharded ground-truth job (pann_groundtruth_resident_range); d_tau_cap is a DEVICE pointer or 0"""
+        check(_lib.lib().pann_groundtruth_resident_range(self._h, C.c_uint32(k), C.c_int64(id_offset), C.c_uint64(row_lo), C.c_uint64(row_hi),
+                                                         C.c_int(1 if keep_state else 0), C.c_void_p(d_tau_cap or None), C.c_uint64(seen_rows)))
+        self._gt_k = k
+
     def groundtruth_stats(self):
         """(launches of the tcgen05 kernel in the last ground-truth call, cumulative chunks retaken on the CUDA cores)"""
         a, b = C.c_int(0), C.c_int(0)

@@ -14,6 +14,7 @@ The partition helpers are pure functions (tested on CPU with world_size-2 gloo g
 to the CUDA library and can be replaced by a checker in tests.
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -143,13 +144,41 @@ class _DevView:
         self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
 
 
-def groundtruth_sharded(index, queries=None, k=100, base_offset=0, group=None, local_fn=None, merge_fn=None):
+def _gt_gather_merge(L, index, dist, group, world, k, dev, torch):
+    """all-gather of this rank's device-resident [nq,k] ids / distances + K5 merge on the device -> (ids, dists) tensors"""
+    p_ids, p_d, nq, kk = C.c_void_p(), C.c_void_p(), C.c_uint64(), C.c_uint32()
+    check(L.pann_groundtruth_device_result(index._h, C.byref(p_ids), C.byref(p_d), C.byref(nq), C.byref(kk)))
+    nq = nq.value
+    loc_i = torch.as_tensor(_DevView(p_ids.value, (nq, k), "<i4"), device=dev)
+    loc_d = torch.as_tensor(_DevView(p_d.value, (nq, k), "<f4"), device=dev)
+    all_i = torch.empty((world, nq, k), dtype=torch.int32, device=dev)
+    all_d = torch.empty((world, nq, k), dtype=torch.float32, device=dev)
+    dist.all_gather_into_tensor(all_i, loc_i, group=group)
+    dist.all_gather_into_tensor(all_d, loc_d, group=group)
+    out_i = torch.empty((nq, k), dtype=torch.int32, device=dev)
+    out_d = torch.empty((nq, k), dtype=torch.float32, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    check(L.pann_groundtruth_merge_device(dev.index, C.c_uint32(world), C.c_uint64(nq), C.c_uint32(k), C.c_void_p(all_i.data_ptr()),
+                                          C.c_void_p(all_d.data_ptr()), C.c_void_p(out_i.data_ptr()), C.c_void_p(out_d.data_ptr()),
+                                          C.c_void_p(st)))
+    return out_i, out_d
+
+
+GT_SAMPLE_ROWS = 4096   # rows of every shard that make the shared first bound (a multiple of the 256-row MMA tile)
+
+
+def groundtruth_sharded(index, queries=None, k=100, base_offset=0, group=None, local_fn=None, merge_fn=None, share_bounds=None,
+                        sample_rows=GT_SAMPLE_ROWS):
     """compute_groundtruth with the base rows sharded over the ranks: `index` holds this rank's base shard whose
     first row has global id `base_offset`.  Every rank returns the global (ids [nq,k] int32, dists [nq,k] float32).
 
     Default path (GPU): local top-k stays on the device, NCCL all-gather of the [nq,k] id and distance blocks,
-    K5 merge on the device, one D2H copy of the result.  local_fn(queries, k, base_offset) -> (ids, dists) and
-    merge_fn(list_ids, list_dists) -> (ids, dists) replace the compute for host-logic tests."""
+    K5 merge on the device, one D2H copy of the result.  With share_bounds every shard first takes a sample_rows-row
+    sample, the samples are merged the same way, and the k-th distance of the merged sample bounds every shard's filter
+    for the rest of its rows (a shard on its own only knows the k-th distance of ITS rows, which is ~world times looser
+    in rank): same result, fewer survivors to re-rank per shard.
+    local_fn(queries, k, base_offset) -> (ids, dists) and merge_fn(list_ids, list_dists) -> (ids, dists) replace the
+    compute for host-logic tests."""
     rank, world = _world(group)
     if local_fn is not None or merge_fn is not None:
         ids, dists = local_fn(queries, k, base_offset)
@@ -163,28 +192,38 @@ def groundtruth_sharded(index, queries=None, k=100, base_offset=0, group=None, l
     L = _lib.lib()
     if queries is not None:
         index.upload_queries(queries)
-    index.groundtruth_resident(k=k, id_offset=base_offset)
     if world == 1:
+        index.groundtruth_resident(k=k, id_offset=base_offset)
         return index.fetch_groundtruth()
     dist = _dist()
     if dist.get_backend(group) != "nccl":
         raise RuntimeError("groundtruth_sharded: the GPU path needs an NCCL process group")
-    p_ids, p_d, nq, kk = C.c_void_p(), C.c_void_p(), C.c_uint64(), C.c_uint32()
-    check(L.pann_groundtruth_device_result(index._h, C.byref(p_ids), C.byref(p_d), C.byref(nq), C.byref(kk)))
-    nq = nq.value
     dev = torch.device("cuda", torch.cuda.current_device())
-    loc_i = torch.as_tensor(_DevView(p_ids.value, (nq, k), "<i4"), device=dev)
-    loc_d = torch.as_tensor(_DevView(p_d.value, (nq, k), "<f4"), device=dev)
-    all_i = torch.empty((world, nq, k), dtype=torch.int32, device=dev)
-    all_d = torch.empty((world, nq, k), dtype=torch.float32, device=dev)
-    dist.all_gather_into_tensor(all_i, loc_i, group=group)
-    dist.all_gather_into_tensor(all_d, loc_d, group=group)
-    out_i = torch.empty((nq, k), dtype=torch.int32, device=dev)
-    out_d = torch.empty((nq, k), dtype=torch.float32, device=dev)
-    st = torch.cuda.current_stream().cuda_stream
-    check(L.pann_groundtruth_merge_device(dev.index, C.c_uint32(world), C.c_uint64(nq), C.c_uint32(k), C.c_void_p(all_i.data_ptr()),
-                                          C.c_void_p(all_d.data_ptr()), C.c_void_p(out_i.data_ptr()), C.c_void_p(out_d.data_ptr()),
-                                          C.c_void_p(st)))
+    if share_bounds is None:
+        share_bounds = os.environ.get("PANN_GT_SHARE", "1") != "0"
+    legs = []
+    if share_bounds:
+        n_loc = index.n
+        s_rows = min(n_loc, max(256, sample_rows // 256 * 256))
+        if s_rows < n_loc:
+            s_rows = s_rows // 256 * 256
+        index.groundtruth_range(k=k, id_offset=base_offset, row_lo=0, row_hi=s_rows)
+        legs.append(index.last_timing()[0])
+        seen = torch.tensor([s_rows], dtype=torch.int64, device=dev)
+        dist.all_reduce(seen, group=group)
+        _, samp_d = _gt_gather_merge(L, index, dist, group, world, k, dev, torch)
+        cap = samp_d[:, k - 1].contiguous()          # +inf where the merged sample holds fewer than k rows: no bound
+        torch.cuda.current_stream().synchronize()    # the library runs on its own stream
+        if s_rows < n_loc:
+            index.groundtruth_range(k=k, id_offset=base_offset, row_lo=s_rows, row_hi=0, keep_state=True, d_tau_cap=cap.data_ptr(),
+                                    seen_rows=int(seen.item()))
+            legs.append(index.last_timing()[0])
+    else:
+        index.groundtruth_resident(k=k, id_offset=base_offset)
+        legs.append(index.last_timing()[0])
+    index._gt_leg_ms = legs            # device time of this rank's K4 legs (diagnostics, bench.py)
+    out_i, out_d = _gt_gather_merge(L, index, dist, group, world, k, dev, torch)
+    nq = out_i.shape[0]
     # results come back through pinned buffers kept on the index (a pageable .cpu() of 8 MB takes 5 ms, this 0.3 ms)
     pin = getattr(index, "_gt_pinned", None)
     if pin is None or pin[0].shape != (nq, k):

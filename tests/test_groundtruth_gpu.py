@@ -72,6 +72,50 @@ def test_sharded_groundtruth_merge():
     assert np.array_equal(md, od)
 
 
+@pytest.mark.parametrize("data_type,kind,metric,n,d,nq,k,sample", [
+    ("uint8", "uint8", "Euclidian", 60000, 128, 200, 100, 1024), ("float", "float_norm", "Euclidian", 50000, 96, 130, 100, 2048),
+    ("float", "float", "mips", 40000, 200, 100, 10, 512), ("int8", "int8", "Euclidian", 9000, 128, 64, 20, 4096),
+])
+def test_sharded_groundtruth_shared_bounds(data_type, kind, metric, n, d, nq, k, sample):
+    """the two-leg sharded job (sharded.groundtruth_sharded's GPU path, here with the shards on one device): every shard
+    takes a sample, the merged sample's k-th distance bounds every shard's filter for the rest of its rows; the merged
+    result must be the unsharded one bit for bit, although the bounded shards keep fewer than k rows each"""
+    import torch
+    import parlayann_b200 as P
+    base = O.gen_points(kind, n, d, seed=5)
+    qs = O.gen_points(kind, nq, d, seed=5, stream=1)
+    bounds = [0, n // 2, n // 2 + 300, n]          # the middle shard is smaller than the sample
+    shards = [P.GraphIndex(base[bounds[s]:bounds[s + 1]], None, data_type, metric, max_degree=4) for s in range(3)]
+    srows = []
+    samples = []
+    for s, idx in enumerate(shards):
+        idx.upload_queries(qs)
+        r = min(idx.n, sample)
+        idx.groundtruth_range(k=k, id_offset=bounds[s], row_lo=0, row_hi=r)
+        srows.append(r)
+        samples.append(idx.fetch_groundtruth())
+    mi, md = P.groundtruth_merge([p[0] for p in samples], [p[1] for p in samples])
+    assert (mi >= 0).all()
+    cap = torch.from_numpy(np.ascontiguousarray(md[:, k - 1])).cuda()
+    parts, short = [], 0
+    for s, idx in enumerate(shards):
+        if srows[s] < idx.n:
+            idx.groundtruth_range(k=k, id_offset=bounds[s], row_lo=srows[s], row_hi=0, keep_state=True, d_tau_cap=cap.data_ptr(), seen_rows=sum(srows))
+            if idx.n - srows[s] >= 1024:
+                assert idx.groundtruth_stats()[0] > 0, "the bounded leg must run on the tensor cores"
+        parts.append(idx.fetch_groundtruth())
+    gi, gd = P.groundtruth_merge([p[0] for p in parts], [p[1] for p in parts])
+    full = P.GraphIndex(base, None, data_type, metric, max_degree=4).groundtruth(qs, k=k)
+    assert np.array_equal(gd.view(np.uint32), full[1].view(np.uint32)) and np.array_equal(gi, full[0])
+    # a bounded shard does not chase rows that cannot be in the global top-k: its own k-th is not tighter than the bound
+    unb = shards[0].groundtruth(qs, k=k, id_offset=0)
+    assert (np.where(parts[0][0] >= 0, parts[0][1], np.inf) >= unb[1]).all()
+    with pytest.raises(P.PannError):
+        shards[0].groundtruth_range(k=k, row_lo=100)       # not a tile boundary
+    with pytest.raises(P.PannError):
+        shards[0].groundtruth_range(k=k + 1, row_lo=256, keep_state=True)   # no kept state of that shape
+
+
 def test_groundtruth_recall_of_itself_is_one():
     import parlayann_b200 as P
     from parlayann_b200.harness import recall_with_ties
