@@ -178,6 +178,17 @@ int pann_groundtruth_resident_range(pann_index* idx, uint32_t k, int64_t id_offs
 /* which path the last ground-truth call took: launches of the tcgen05 kernel (0 = CUDA-core path only) and, cumulative over
  * the index's life, chunks retaken on the CUDA cores after a candidate-list overflow */
 int pann_index_groundtruth_stats(pann_index* idx, int* mma_launches, int* fallback_chunks);
+/* No counterpart in the reference; added for callers that may not allocate
+ * device memory (CUDA graph capture, serving loops).  Exact k-NN of DEVICE-resident query rows (nq rows of the index's
+ * element type, q_stride_bytes apart) against the index's base rows into DEVICE buffers d_out_ids / d_out_dists
+ * ([nq,k], rows sorted by (distance, id), as pann_groundtruth).  Calls no cudaMalloc / cudaFree and does not
+ * synchronise: it only enqueues kernels on `stream` (a cudaStream_t; NULL = the legacy default stream).  All working
+ * memory is ONE file-scope device array of 16 MiB per GPU (pann_groundtruth_static_limit), held from library load to
+ * exit: a call whose nq * (8 k + padded row bytes + 256) exceeds it fails with a clear message.  Every call on a
+ * device shares that array, so calls that overlap on the GPU race; successive calls on one stream are safe. */
+int pann_groundtruth_static(pann_index* idx, const void* d_queries, uint64_t nq, uint64_t q_stride_bytes, uint32_t k,
+                            int64_t id_offset, int32_t* d_out_ids, float* d_out_dists, void* stream);
+int pann_groundtruth_static_limit(uint64_t* scratch_bytes);
 /* k-way merge of per-shard results (each [nq, k], sorted) into the global top-k under the (dist,id) order */
 int pann_groundtruth_merge(int device, uint32_t nshards, uint64_t nq, uint32_t k, const int32_t* ids, const float* dists,
                            int32_t* out_ids, float* out_dists);

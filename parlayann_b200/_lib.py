@@ -34,7 +34,7 @@ SYMBOLS = [
     "pann_index_last_timing", "pann_index_build_stats", "pann_index_last_bytes", "pann_search_batch", "pann_queries_upload", "pann_queries_synthetic",
     "pann_queries_download", "pann_search_resident", "pann_search_fetch", "pann_search_device_result", "pann_search_full", "pann_search_batch_starts", "pann_search_full_starts", "pann_search_rerank_batch", "pann_vamana_build", "pann_vamana_batch_insert",
     "pann_random_permutation", "pann_random_starts", "pann_batch_schedule", "pann_groundtruth", "pann_groundtruth_resident",
-    "pann_groundtruth_resident_range", "pann_groundtruth_fetch", "pann_index_groundtruth_stats", "pann_groundtruth_merge", "pann_groundtruth_device_result", "pann_groundtruth_merge_device",
+    "pann_groundtruth_resident_range", "pann_groundtruth_fetch", "pann_index_groundtruth_stats", "pann_groundtruth_static", "pann_groundtruth_static_limit", "pann_groundtruth_merge", "pann_groundtruth_device_result", "pann_groundtruth_merge_device",
     "pann_groundtruth_upload", "pann_search_sweep",
     "pann_hnsw_create", "pann_hnsw_destroy", "pann_hnsw_levels", "pann_hnsw_build", "pann_hnsw_set_model", "pann_hnsw_get_model",
     "pann_hnsw_search", "pann_hnsw_info", "pann_host_alloc", "pann_host_free",

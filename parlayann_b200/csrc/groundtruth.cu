@@ -512,3 +512,78 @@ extern "C" int pann_index_groundtruth_stats(pann_index* idx, int* mma_launches, 
   if (fallback_chunks) *fallback_chunks = idx->gt_fallback_chunks;
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// pann_groundtruth_static — exact k-NN of device-resident query rows on the CUDA-core kernels above (K4 v1: distance
+// chunk -> select), with EVERY byte of working memory in one file-scope device array: no cudaMalloc / cudaFree, no
+// synchronisation, only kernel launches on the caller's stream.  For callers that may not allocate (graph capture,
+// serving loops).  No counterpart in the reference.
+//   scratch layout: [ top-k state nq*k*8 | query rows in the index's 16-byte-chunk layout nq*stride | distance block nq*cb*4 ]
+// All calls on a device share the array: calls that overlap on the GPU (two streams, two threads) race.  Nothing in it
+// has to survive a call — the state is re-initialised, the query rows and every distance that is read are rewritten.
+#define PANN_STATIC_SCRATCH_BYTES (16u << 20)
+#define PANN_STATIC_MAX_DEVICES 64
+static __device__ __align__(256) uint8_t pann_static_scratch[PANN_STATIC_SCRATCH_BYTES];
+static uint8_t* g_static_scratch_ptr[PANN_STATIC_MAX_DEVICES];   // device addresses of the array, one per device (set-up)
+
+__global__ void pann_static_stage_rows_kernel(const uint8_t* __restrict__ src, uint64_t src_stride, uint32_t rowb, uint8_t* __restrict__ dst,
+                                              uint32_t stride, uint64_t total) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;   // one byte of the padded layout per thread
+  if (i >= total) return;
+  const uint64_t r = i / stride;
+  const uint32_t c = (uint32_t)(i - r * stride);
+  dst[i] = c < rowb ? src[r * src_stride + c] : (uint8_t)0;
+}
+
+// the array's device address on the current device: the symbol itself is only a host-side stand-in
+static int pann_static_scratch_address(int device, uint8_t** out) {
+  if (device < 0 || device >= PANN_STATIC_MAX_DEVICES) PANN_FAIL("pann_groundtruth_static: device ordinal out of range");
+  if (!g_static_scratch_ptr[device]) {
+    void* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&p, pann_static_scratch);
+    if (e != cudaSuccess || !p) PANN_FAIL(std::string("pann_groundtruth_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+    g_static_scratch_ptr[device] = static_cast<uint8_t*>(p);
+  }
+  *out = g_static_scratch_ptr[device];
+  return 0;
+}
+
+extern "C" int pann_groundtruth_static_limit(uint64_t* scratch_bytes) {
+  if (scratch_bytes) *scratch_bytes = PANN_STATIC_SCRATCH_BYTES;
+  return 0;
+}
+
+extern "C" int pann_groundtruth_static(pann_index* idx, const void* d_queries, uint64_t nq, uint64_t q_stride_bytes, uint32_t k,
+                                       int64_t id_offset, int32_t* d_out_ids, float* d_out_dists, void* stream) {
+  if (!idx || !d_queries || !d_out_ids || !d_out_dists) PANN_FAIL("pann_groundtruth_static: null argument");
+  if (k == 0 || k > GT_SEL_CAP / 2) PANN_FAIL("pann_groundtruth_static: k must be in 1.." + std::to_string(GT_SEL_CAP / 2));
+  if (idx->n < k) PANN_FAIL("pann_groundtruth_static: fewer base points than k");
+  if (nq == 0) PANN_FAIL("pann_groundtruth_static: no queries");
+  if ((int64_t)idx->n + id_offset > (int64_t)INT32_MAX) PANN_FAIL("pann_groundtruth_static: ids do not fit int32");
+  const uint32_t stride = idx->geom.stride;
+  const uint32_t rowb = idx->dims * idx->geom.elt;
+  if (q_stride_bytes < rowb) PANN_FAIL("pann_groundtruth_static: query stride smaller than a row");
+  // the fixed part and at least one 64-row distance chunk must fit the array
+  const uint64_t state_b = (8ull * nq * k + 255) / 256 * 256, q_b = ((uint64_t)nq * stride + 255) / 256 * 256;
+  const uint64_t need = state_b + q_b + 4ull * nq * GT_TB;
+  if (nq > (1ull << 20) || need > PANN_STATIC_SCRATCH_BYTES)
+    PANN_FAIL("pann_groundtruth_static: " + std::to_string(nq) + " queries x k=" + std::to_string(k) + " x " + std::to_string(stride) +
+              "-byte rows need " + std::to_string(need) + " bytes of scratch; the static array holds " + std::to_string(PANN_STATIC_SCRATCH_BYTES) +
+              " (nq * (8 k + row bytes + 256) must stay below it): split the batch or use pann_groundtruth");
+  PANN_CUDA(cudaSetDevice(idx->device));
+  uint8_t* scratch = nullptr;
+  if (pann_static_scratch_address(idx->device, &scratch)) return 1;
+  cudaStream_t s = (cudaStream_t)stream;
+  u64* state = reinterpret_cast<u64*>(scratch);
+  uint8_t* qrows = scratch + state_b;
+  float* D = reinterpret_cast<float*>(scratch + state_b + q_b);
+  uint64_t cb = ((PANN_STATIC_SCRATCH_BYTES - state_b - q_b) / (4ull * nq)) / GT_TB * GT_TB;   // rows per distance chunk
+  cb = std::min<uint64_t>(cb, (idx->n + GT_TB - 1) / GT_TB * GT_TB);
+  const uint64_t tot = nq * k, qbytes = nq * stride;
+  pann_static_stage_rows_kernel<<<(unsigned)((qbytes + 255) / 256), 256, 0, s>>>(static_cast<const uint8_t*>(d_queries), q_stride_bytes, rowb, qrows, stride, qbytes);
+  pann_gt_init_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(state, tot);
+  gt_v1_range(idx, s, qrows, nq, k, state, D, cb, 0, idx->n);
+  pann_gt_finish_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, s>>>(state, tot, id_offset, d_out_ids, d_out_dists);
+  PANN_CUDA(cudaGetLastError());
+  return 0;
+}
