@@ -9,7 +9,7 @@ idx = P.GraphIndex(data_type="uint8", metric="Euclidian", max_degree=64, device=
 idx.build(R=64, L=128, alpha=1.2, num_passes=1, sort_neighbors=True)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 ref = None
-for nq in (1000, 10000, 100000, 1000000):
+for nq in (1250, 2500, 5000, 10000, 100000, 1000000):
     idx.synthetic_queries(nq, kind="uint8", seed=1234, stream=1)
     line = f"nq {nq:7d}"
     for t in tunes:
