@@ -173,7 +173,8 @@ def groundtruth_sharded(index, queries=None, k=100, base_offset=0, group=None, l
     first row has global id `base_offset`.  Every rank returns the global (ids [nq,k] int32, dists [nq,k] float32).
 
     Default path (GPU): local top-k stays on the device, NCCL all-gather of the [nq,k] id and distance blocks,
-    K5 merge on the device, one D2H copy of the result.  With share_bounds every shard first takes a sample_rows-row
+    K5 merge on the device, one D2H copy of the result.  With share_bounds (or PANN_GT_SHARE=1; off by default: measured
+    on 10 000 x 10M x 96 f32 it saves 0.6 ms of K4 per shard at 8 GPUs and costs 0.8 ms of extra exchange) every shard first takes a sample_rows-row
     sample, the samples are merged the same way, and the k-th distance of the merged sample bounds every shard's filter
     for the rest of its rows (a shard on its own only knows the k-th distance of ITS rows, which is ~world times looser
     in rank): same result, fewer survivors to re-rank per shard.
@@ -200,7 +201,7 @@ def groundtruth_sharded(index, queries=None, k=100, base_offset=0, group=None, l
         raise RuntimeError("groundtruth_sharded: the GPU path needs an NCCL process group")
     dev = torch.device("cuda", torch.cuda.current_device())
     if share_bounds is None:
-        share_bounds = os.environ.get("PANN_GT_SHARE", "1") != "0"
+        share_bounds = os.environ.get("PANN_GT_SHARE", "0") == "1"
     legs = []
     if share_bounds:
         n_loc = index.n

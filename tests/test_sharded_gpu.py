@@ -81,6 +81,8 @@ def _nccl_worker(rank, world, port, tmp):
         gi, gd = P.sharded.groundtruth_sharded(shard, qs, k=k, base_offset=lo)
         oi, od = O.groundtruth(base, qs, "float", k=k)
         assert np.array_equal(gd, od), "sharded ground-truth distances differ from the oracle"
+        si, sd = P.sharded.groundtruth_sharded(shard, qs, k=k, base_offset=lo, share_bounds=True, sample_rows=2048)
+        assert np.array_equal(sd, gd) and np.array_equal(si, gi), "shared-bound legs changed the sharded ground truth"
         g = O.vamana_build(base[:8000], "float", R=32, L=64, sort_neighbors=False)[0]
         rep = P.GraphIndex(base[:8000], g, "float", "Euclidian", device=rank)
         got = P.sharded.search_sharded(rep, qs, k=10, beam=24)
