@@ -605,6 +605,21 @@ def run_ours(args, rank, local_rank, world):
                         "what": "fixed batch cut over the ranks, H2D + search + all-gather + D2H on every rank (search_sharded gather=True)"}
         if name == "batch_10K":
             strong[name]["ids_equal_single_gpu"] = bool(np.array_equal(res[0], r_ids))
+        if world > 1:   # the same with the answer assembled on rank 0 only (a single driving process; NCCL gather instead of all-gather)
+            for _ in range(2):
+                search_sharded(idx, sq, gather=True, root=0, **qp)
+            barrier()
+            tt = 0.0
+            for _ in range(reps):
+                l2_flush()
+                barrier()
+                t0 = time.perf_counter()
+                res0 = search_sharded(idx, sq, gather=True, root=0, **qp)
+                tt += allmax((time.perf_counter() - t0) * 1e3)
+            strong[name + "_root"] = {"queries_total": int(m), "ms": tt / reps, "value": m / (tt / reps * 1e-3), "unit": "queries/s",
+                                      "what": "as above, answer gathered to rank 0 only (search_sharded root=0)"}
+            if rank == 0:
+                strong[name + "_root"]["ids_equal_all_gather"] = bool(np.array_equal(res0[0], res[0]))
 
     # ---- ground truth at BASELINE configs[2] (10M x 96 f32, k=100), base rows sharded over the ranks
     c3 = None

@@ -15,6 +15,14 @@
 #include "beam_search.cuh"
 
 #define PANN_PRUNE_WARPS 4
+#ifndef PANN_PRUNE_MINB
+#define PANN_PRUNE_MINB 3   // without a min-blocks bound ptxas pins the kernel at an occupancy step (80 / 48 registers, spilling)
+#endif
+#if PANN_PRUNE_MINB > 0
+#define PANN_PRUNE_BOUNDS __launch_bounds__(PANN_PRUNE_WARPS * 32, PANN_PRUNE_MINB)
+#else
+#define PANN_PRUNE_BOUNDS __launch_bounds__(PANN_PRUNE_WARPS * 32)   // A/B: the round-1 bound
+#endif
 
 struct PruneArgs {
   // row geometry (same member names as BeamArgs: pann_row_distances_g reads them)
@@ -71,7 +79,7 @@ __device__ __forceinline__ bool pann_occludes(const PruneArgs& A, float d_sc, fl
 }
 
 template <int DT, int METRIC, int QR, bool GS>
-__global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_prune_kernel(const PruneArgs A) {
+__global__ void PANN_PRUNE_BOUNDS pann_prune_kernel(const PruneArgs A) {
   extern __shared__ __align__(16) uint8_t pann_smem[];
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
   const unsigned lt_mask = (1u << lane) - 1u;
@@ -450,7 +458,7 @@ struct EdgeDistArgs {
   uint32_t* tie_count; uint32_t tie_cap; uint32_t* tie_rows; uint32_t* tie_graph; float* tie_dist;
 };
 template <int DT, int METRIC, int QR>
-__global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32) pann_edge_dist_kernel(const EdgeDistArgs A) {
+__global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32, 4) pann_edge_dist_kernel(const EdgeDistArgs A) {
   extern __shared__ __align__(16) uint8_t pann_smem[];
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
   uint8_t* ws = pann_smem + (size_t)wic * A.warp_bytes;

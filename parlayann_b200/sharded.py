@@ -68,19 +68,20 @@ def all_gather_rows(local, counts, group=None):
     return np.concatenate(parts, axis=0)
 
 
-def search_sharded(index, queries, gather=True, group=None, **qp):
+def search_sharded(index, queries, gather=True, group=None, root=None, **qp):
     """qsearchAll over a query batch cut across the ranks of `group`.  `index` is this rank's replica
     (GraphIndex).  Returns (ids, dists, visited, cmps) for all queries when gather=True, else this rank's slice.
 
     With an NCCL group the slice's results never leave the device before the exchange: queries H2D, search, one
     all-gather per result array straight from the library's device buffers (pann_search_device_result), one D2H of the
-    assembled answer into pinned buffers kept on the index."""
+    assembled answer into pinned buffers kept on the index.  root=r: only rank r assembles (and returns) the answer — what
+    a single driving process needs; the other ranks return None and skip the device-to-host copy of the whole batch."""
     rank, world = _world(group)
     nq = queries.shape[0]
     lo, hi = shard_bounds(nq, rank, world)
     k = int(qp.get("k", 10))
     if gather and world > 1 and _dist().get_backend(group) == "nccl":
-        return _search_sharded_nccl(index, queries, lo, hi, k, group, qp)
+        return _search_sharded_nccl(index, queries, lo, hi, k, group, qp, root)
     if hi > lo:
         ids, dists, vis, cmps = index.search(queries[lo:hi], **qp)
     else:  # more ranks than queries
@@ -92,7 +93,7 @@ def search_sharded(index, queries, gather=True, group=None, **qp):
     return tuple(all_gather_rows(a, counts, group) for a in (ids, dists, vis, cmps))
 
 
-def _search_sharded_nccl(index, queries, lo, hi, k, group, qp):
+def _search_sharded_nccl(index, queries, lo, hi, k, group, qp, root=None):
     import torch
     dist = _dist()
     rank, world = _world(group)
@@ -121,8 +122,15 @@ def _search_sharded_nccl(index, queries, lo, hi, k, group, qp):
                  torch.as_tensor(_DevView(p[2].value, (n_loc,), "<i4"), device=dev), torch.as_tensor(_DevView(p[3].value, (n_loc,), "<i4"), device=dev)]
         for dst, src in zip(cache["l"], views):
             dst[:n_loc].copy_(src)          # equal slices: the padded staging buffer IS the slice (one D2D copy, NVLink-sized)
-    for g, l in zip(cache["g"], cache["l"]):
-        dist.all_gather_into_tensor(g, l, group=group)
+    if root is None:
+        for g, l in zip(cache["g"], cache["l"]):
+            dist.all_gather_into_tensor(g, l, group=group)
+    else:
+        for g, l in zip(cache["g"], cache["l"]):
+            dist.gather(l, [g[r] for r in range(world)] if rank == root else None, dst=dist.get_global_rank(group, root) if group is not None else root, group=group)
+        if rank != root:
+            torch.cuda.current_stream().synchronize()
+            return None
     for h, g in zip(cache["h"], cache["g"]):
         h.copy_(g, non_blocking=True)
     torch.cuda.current_stream().synchronize()

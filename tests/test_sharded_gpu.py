@@ -88,6 +88,11 @@ def _nccl_worker(rank, world, port, tmp):
         got = P.sharded.search_sharded(rep, qs, k=10, beam=24)
         ref = O.search(base[:8000], g, qs, "float", k=10, beam=24)
         assert np.array_equal(got[0], ref["ids"]) and np.array_equal(got[2], ref["visited"])
+        got0 = P.sharded.search_sharded(rep, qs, k=10, beam=24, root=0)     # answer assembled on rank 0 only
+        if rank == 0:
+            assert all(np.array_equal(a, b) for a, b in zip(got0, got))
+        else:
+            assert got0 is None
         open(os.path.join(tmp, f"ok{rank}"), "w").write("ok")
     finally:
         dist.destroy_process_group()
