@@ -125,7 +125,11 @@ __device__ __forceinline__ float pann_quad_distance(const RG& A, uint32_t a, uns
   for (int g = 0; g < 4; g++) {
     const int src = g * 8 + rowi;
     const uint32_t ag = __shfl_sync(PANN_FULL, a, src);
-#ifdef PANN_QUAD_ASM
+#if !defined(PANN_QUAD_ZERO)   // unwanted rows read row 0 (an L1 hit) instead of zeroed registers, see beam_search_small.cuh
+    const uint8_t* row0 = A.points + (u64)(((keepmask >> src) & 1u) ? ag : 0u) * A.stride + sub * 16;
+    v[g][0] = pann_ldg16(row0);
+    v[g][1] = pann_ldg16(row0 + 64);
+#elif defined(PANN_QUAD_ASM)
     pann_ldg16x2_if(A.points + (u64)ag * A.stride + sub * 16, (keepmask >> src) & 1u, v[g][0], v[g][1]);
 #else
     v[g][0] = v[g][1] = make_uint4(0u, 0u, 0u, 0u);

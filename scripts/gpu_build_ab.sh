@@ -1,4 +1,6 @@
-mkdir -p gpurun_out
-python -m pytest tests/test_build_gpu.py -x -q -m gpu 2>&1 | tail -2
-for n in 1000000 10000000; do echo "=== default n=$n"; SORT=1 python scripts/build_only.py $n 2>&1 | tail -1; SORT=1 python scripts/build_only.py $n 2>&1 | tail -1; done
-for lib in "$@"; do for n in 1000000 10000000; do echo "=== $lib n=$n"; SORT=1 PANN_LIB_PATH=$PWD/parlayann_b200/ab/$lib python scripts/build_only.py $n 2>&1 | tail -1; done; done
+# 10M build A/B of several builds of the library (parlayann_b200/<path>.so), interleaved
+for r in 1 2 3; do
+for lib in "$@"; do
+  echo -n "$lib  "; PANN_LIB_PATH=$PWD/parlayann_b200/$lib SORT=1 python scripts/build_only.py 10000000 2>&1 | tail -1
+done
+done
