@@ -77,6 +77,19 @@ __device__ __forceinline__ int pann_count_below_s(uint32_t keys, int n, u64 t) {
   if (j < n) pann_borrow_count(n0, pann_lds64(keys + 8u * j), t);
   return -(n0 + n1);
 }
+// the same over a list padded with ~0 keys to a multiple of four: four keys per iteration, no tail
+__device__ __forceinline__ int pann_count_below_s4(uint32_t keys, int n4, u64 t) {
+  int n0 = 0, n1 = 0;
+#pragma unroll 1
+  for (int j = 0; j < n4; j += 4) {
+    const uint4 v = pann_lds128(keys + 8u * j), w = pann_lds128(keys + 8u * j + 16u);
+    pann_borrow_count(n0, ((u64)v.y << 32) | v.x, t);
+    pann_borrow_count(n1, ((u64)v.w << 32) | v.z, t);
+    pann_borrow_count(n0, ((u64)w.y << 32) | w.x, t);
+    pann_borrow_count(n1, ((u64)w.w << 32) | w.z, t);
+  }
+  return -(n0 + n1);
+}
 __device__ __forceinline__ u64 pann_shfl_xor64(u64 x, int d) {
   const uint32_t lo = __shfl_xor_sync(PANN_FULL, (uint32_t)x, d), hi = __shfl_xor_sync(PANN_FULL, (uint32_t)(x >> 32), d);
   return ((u64)hi << 32) | lo;
@@ -307,6 +320,12 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
         const int n = min(32, C - c0);
         const uint32_t s_chunk = s_cand + 8u * c0;
         u64 ck = lane < n ? pann_lds64(s_chunk + 8u * lane) : ~0ull;
+#ifndef PANN_K1S_RANK2
+        // pad the (last) chunk with ~0 keys to a multiple of four for the rank loop; up to three slots past the list: inside
+        // the candidate array, or the head of s_srt, which is dead until it is rewritten below
+        if (lane >= n && lane < ((n + 3) & ~3)) pann_sts64(s_chunk + 8u * lane, ~0ull);
+        __syncwarp();
+#endif
         {  // a vertex that comes back after it was visited stays visited (it is in `visited`, so set_difference drops it, :203-208)
           const uint32_t cid = pann_key_id(ck);
           const uint32_t h = vhash(cid);
@@ -318,7 +337,11 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
             if (visited_exact(__shfl_sync(PANN_FULL, cid, j)) && lane == j) ck |= 1ull;
           }
         }
-        const int r = pann_count_below_s(s_chunk, n, ck & ~1ull);   // rank among the chunk's keys (raw keys: bit 0 clear)
+#ifndef PANN_K1S_RANK2
+        const int r = pann_count_below_s4(s_chunk, (n + 3) & ~3, ck & ~1ull);   // rank among the chunk's keys (raw keys: bit 0 clear)
+#else
+        const int r = pann_count_below_s(s_chunk, n, ck & ~1ull);
+#endif
         pann_sts64(s_srt + 8u * lane, ~0ull);
         __syncwarp();
         if (lane < n) pann_sts64(s_srt + 8u * (31 - r), ck);          // descending in lane order
