@@ -243,6 +243,22 @@ int pann_hnsw_info(pann_hnsw* h, uint32_t* top_level, uint64_t* upper_rows, uint
 int pann_host_alloc(void** p, size_t bytes);
 int pann_host_free(void* p);
 
+/* ---- point conversions of the reference's Python builder / index loader, on the device (host arrays in and out) ----
+ * pann_rows_normalize: Mips_Point<float>::normalize over every row, in place (utils/mips_point.h:115-124; called by
+ *   python/builder.cpp:45-49 and python/graph_index.cpp:88-90).
+ * pann_rows_quant_params_u8 / pann_rows_quantize_u8: Euclidian_Point<uint8_t>::generate_parameters + parameters(min, max, dims)
+ *   and translate_point (utils/euclidian_point.h:211-237, :104-108, :183-209): the 1-byte copy of float Euclidean data.
+ * pann_rows_quant_params_mips8 / pann_rows_quantize_mips8: Quantized_Mips_Point<8,trim>::generate_parameters and
+ *   translate_point (utils/mips_point.h:437-462, :421-434): the int8 copy of normalised float MIPS data.
+ * rows: n rows of dims floats, stride_bytes apart; outputs: n rows of dims bytes, out_stride_bytes apart. */
+int pann_rows_normalize(int device, float* rows, uint64_t n, uint32_t dims, uint64_t stride_bytes);
+int pann_rows_quant_params_u8(int device, const float* rows, uint64_t n, uint32_t dims, uint64_t stride_bytes, float* slope, int64_t* offset);
+int pann_rows_quantize_u8(int device, const float* rows, uint64_t n, uint32_t dims, uint64_t stride_bytes, float slope, int64_t offset,
+                          uint8_t* out, uint64_t out_stride_bytes);
+int pann_rows_quant_params_mips8(int device, const float* rows, uint64_t n, uint32_t dims, uint64_t stride_bytes, int trim, float* max_val);
+int pann_rows_quantize_mips8(int device, const float* rows, uint64_t n, uint32_t dims, uint64_t stride_bytes, float max_val,
+                             int8_t* out, uint64_t out_stride_bytes);
+
 #ifdef __cplusplus
 }
 #endif

@@ -37,7 +37,8 @@ SYMBOLS = [
     "pann_groundtruth_resident_range", "pann_groundtruth_fetch", "pann_index_groundtruth_stats", "pann_groundtruth_static", "pann_groundtruth_static_limit", "pann_groundtruth_merge", "pann_groundtruth_device_result", "pann_groundtruth_merge_device",
     "pann_groundtruth_upload", "pann_search_sweep",
     "pann_hnsw_create", "pann_hnsw_destroy", "pann_hnsw_levels", "pann_hnsw_build", "pann_hnsw_set_model", "pann_hnsw_get_model",
-    "pann_hnsw_search", "pann_hnsw_info", "pann_host_alloc", "pann_host_free",
+    "pann_hnsw_search", "pann_hnsw_info", "pann_host_alloc", "pann_host_free", "pann_rows_normalize", "pann_rows_quant_params_u8", "pann_rows_quantize_u8",
+    "pann_rows_quant_params_mips8", "pann_rows_quantize_mips8",
 ]
 
 _lib = None

@@ -92,6 +92,50 @@ def quantize_mips8(points, max_val):
     r = np.where(p < -mv, np.float32(-127), np.where(p > mv, np.float32(127), r))
     return r.astype(np.int32).astype(np.int8)
 
+# ---- the same conversions on the device (csrc/quantize.cu): what the product path uses; the numpy versions above are the
+# host-side mirror the CPU tests pin against the reference's bytes (tests/test_quantized_cpu.py)
+def _f32_rows(points):
+    return np.ascontiguousarray(points, dtype=np.float32)    # _rstride assumes dense rows; the C call itself takes any row stride
+
+
+def normalize_rows_device(points, device=0):
+    p = np.array(points, dtype=np.float32, order="C")
+    check(_lib.lib().pann_rows_normalize(device, _vp(p), C.c_uint64(p.shape[0]), C.c_uint32(p.shape[1]), C.c_uint64(_rstride(p))))
+    return p
+
+
+def quant_params_u8_device(points, device=0):
+    p = _f32_rows(points)
+    slope, offset = C.c_float(0), C.c_int64(0)
+    check(_lib.lib().pann_rows_quant_params_u8(device, _vp(p), C.c_uint64(p.shape[0]), C.c_uint32(p.shape[1]), C.c_uint64(_rstride(p)),
+                                               C.byref(slope), C.byref(offset)))
+    return np.float32(slope.value), int(offset.value)
+
+
+def quantize_u8_device(points, slope, offset, device=0):
+    p = _f32_rows(points)
+    out = np.empty(p.shape, np.uint8)
+    check(_lib.lib().pann_rows_quantize_u8(device, _vp(p), C.c_uint64(p.shape[0]), C.c_uint32(p.shape[1]), C.c_uint64(_rstride(p)),
+                                           C.c_float(float(np.float32(slope))), C.c_int64(int(offset)), _vp(out), C.c_uint64(p.shape[1])))
+    return out
+
+
+def quant_params_mips8_device(points, trim=True, device=0):
+    p = _f32_rows(points)
+    mv = C.c_float(0)
+    check(_lib.lib().pann_rows_quant_params_mips8(device, _vp(p), C.c_uint64(p.shape[0]), C.c_uint32(p.shape[1]), C.c_uint64(_rstride(p)),
+                                                  C.c_int(1 if trim else 0), C.byref(mv)))
+    return np.float32(mv.value)
+
+
+def quantize_mips8_device(points, max_val, device=0):
+    p = _f32_rows(points)
+    out = np.empty(p.shape, np.int8)
+    check(_lib.lib().pann_rows_quantize_mips8(device, _vp(p), C.c_uint64(p.shape[0]), C.c_uint32(p.shape[1]), C.c_uint64(_rstride(p)),
+                                              C.c_float(float(np.float32(max_val))), _vp(out), C.c_uint64(p.shape[1])))
+    return out
+
+
 class GraphIndex:
     """PointRange + Graph resident on one B200 (reference: python/graph_index.cpp:48-118)."""
 
@@ -341,11 +385,11 @@ class GraphIndex:
                 raise NotImplementedError("the second-level filter copies the reference adds above 800 (Euclidean) / 200 (MIPS) dimensions (graph_index.cpp:91-95, use_filtering) are not built")
             pts = self.points()
             if self.metric == "Euclidian":
-                self._qparams = quant_params_u8(pts)
-                self._qidx = GraphIndex(quantize_u8(pts, *self._qparams), self.graph(), "uint8", "Euclidian", device=self.device)
+                self._qparams = quant_params_u8_device(pts, self.device)
+                self._qidx = GraphIndex(quantize_u8_device(pts, *self._qparams, device=self.device), self.graph(), "uint8", "Euclidian", device=self.device)
             else:
-                self._qparams = (quant_params_mips8(pts, trim=True),)
-                self._qidx = GraphIndex(quantize_mips8(pts, *self._qparams), self.graph(), "int8", "mips", device=self.device)
+                self._qparams = (quant_params_mips8_device(pts, trim=True, device=self.device),)
+                self._qidx = GraphIndex(quantize_mips8_device(pts, *self._qparams, device=self.device), self.graph(), "int8", "mips", device=self.device)
         return self._qidx
 
     # ---- the reference's Python methods (python/graph_index.cpp:192-305)
@@ -355,13 +399,13 @@ class GraphIndex:
             qi = self._quantized()
             queries = np.ascontiguousarray(queries, dtype=np.float32)
             if self.metric != "Euclidian":            # graph_index.cpp:166-181: q.normalize(), Quantized_Mips_Point copy of it
-                queries = normalize_rows(queries)
-                qq = quantize_mips8(queries, *self._qparams)
+                queries = normalize_rows_device(queries, self.device)
+                qq = quantize_mips8_device(queries, *self._qparams, device=self.device)
             elif self._qparams[0] == np.float32(1.0):   # graph_index.cpp:146-150: plain search of the 1-byte copy
                 ids, dists, _, _ = qi.search(queries.astype(np.uint8), k=knn, beam=beam_width, cut=1.35, limit=max(visit_limit, 0), degree_limit=max(dl, 0))
                 return ids, dists
             else:
-                qq = quantize_u8(queries, *self._qparams)
+                qq = quantize_u8_device(queries, *self._qparams, device=self.device)
             ids, dists, _, _ = self.search_rerank(qi, queries, qq, k=knn, beam=beam_width, cut=1.35,
                                                   limit=max(visit_limit, 0), degree_limit=max(dl, 0))
             return ids, dists
@@ -442,16 +486,16 @@ def build_vamana_index(metric, dtype, data_dir, index_dir, R, L, alpha, two_pass
     alpha = float(np.float32(alpha))                   # builder.cpp takes alpha as a float
     if metric != "Euclidian":
         print("normalizing")
-        pts = normalize_rows(pts)
+        pts = normalize_rows_device(pts, device)
         if pts.shape[1] <= 200:
             alpha = float(np.float32(1.0 if pts.shape[1] < 100 else .98))
-        max_val = quant_params_mips8(pts, trim=True)
+        max_val = quant_params_mips8_device(pts, trim=True, device=device)
         print(f"mips scalar quantization to 8 bits: trimmed to max = {max_val}")
-        idx = GraphIndex(quantize_mips8(pts, max_val), None, "int8", metric, max_degree=R, device=device)
+        idx = GraphIndex(quantize_mips8_device(pts, max_val, device=device), None, "int8", metric, max_degree=R, device=device)
     elif wide:
-        slope, offset = quant_params_u8(pts)
+        slope, offset = quant_params_u8_device(pts, device)
         print(f"scalar quantization: slope = {slope}, offset = {offset}")
-        idx = GraphIndex(quantize_u8(pts, slope, offset), None, "uint8", metric, max_degree=R, device=device)
+        idx = GraphIndex(quantize_u8_device(pts, slope, offset, device=device), None, "uint8", metric, max_degree=R, device=device)
     else:
         idx = GraphIndex(pts, None, dtype, metric, max_degree=R, device=device)
     idx.build(R=R, L=L, alpha=alpha, num_passes=2 if two_pass else 1)
@@ -461,13 +505,14 @@ def build_vamana_index(metric, dtype, data_dir, index_dir, R, L, alpha, two_pass
 
 def load_index(metric, dtype, data_dir, index_dir, hnsw=False, device=0):
     """python/wrapper.py:96-116."""
-    if hnsw:
-        raise NotImplementedError("HNSW model files are a 'next' row (SURVEY.md §8f.1)")
+    if hnsw:   # GraphIndex(data_path, index_path, is_hnsw=true) (graph_index.cpp:103-109): the v3 model file
+        from .hnsw import load_hnsw_index
+        return load_hnsw_index(metric, dtype, data_dir, index_dir, device=device)
     if metric not in _lib.METRIC:
         raise Exception("Invalid metric")
     if dtype not in _lib.DTYPE:
         raise Exception("Invalid data type")
     pts = fileio.read_bin(data_dir, dtype)
     if metric != "Euclidian" and fileio.np_dtype(dtype)().itemsize > 1:
-        pts = normalize_rows(pts)   # graph_index.cpp:88-90: 4-byte non-metric points are normalised when the index loads
+        pts = normalize_rows_device(pts, device)   # graph_index.cpp:88-90: 4-byte non-metric points are normalised when the index loads
     return GraphIndex(pts, fileio.read_graph(index_dir), dtype, metric, device=device)
