@@ -33,6 +33,10 @@ CASES = [
     ("f32_mips", "float", "mips", 1500, 24, 30, 12, 24, 1),
     ("u8_l2_2pass", "uint8", "Euclidian", 1500, 32, 30, 8, 16, 2),
     ("u8_l2_big", "uint8", "Euclidian", 9000, 16, 30, 8, 16, 1),   # n >= 8192: the bucketed random_permutation
+    # float rows whose length is not a multiple of 8 (or 16) elements: whatever the reference's compiler does with the tail
+    # of its distance loop (vector body / scalar remainder, contraction) is in these outputs
+    ("f32_l2_d100", "float", "Euclidian", 2000, 100, 40, 12, 24, 1),
+    ("f32_mips_d100", "float", "mips", 1500, 100, 30, 12, 24, 1),
 ]
 SEARCHES = [dict(k=10, beam=10), dict(k=10, beam=13), dict(k=10, beam=40), dict(k=5, beam=128, cut=1.1),
             dict(k=10, beam=20, limit=15), dict(k=10, beam=30, degree_limit=5), dict(k=1, beam=200)]
@@ -54,7 +58,10 @@ def parse_full(buf, nq):
 def main():
     assert O.ref_driver_path(), "build oracle/_ref first (make -C oracle ref)"
     tmp = tempfile.mkdtemp(prefix="pann_golden_")
+    only = set(sys.argv[1:])          # `make_golden.py name ...` regenerates just those fixtures
     for name, dt, metric, n, d, nq, R, L, passes in CASES:
+        if only and name not in only:
+            continue
         base = O.gen_points(dt, n, d, seed=77)
         qs = O.gen_points(dt, nq, d, seed=77, stream=1)
         bp, qp = os.path.join(tmp, f"{name}.base.{EXT[dt]}"), os.path.join(tmp, f"{name}.query.{EXT[dt]}")
@@ -106,6 +113,8 @@ def main():
         g["params"] = np.array([n, d, nq, R, L, passes, 77, k], dtype=np.int64)
         np.savez_compressed(os.path.join(HERE, f"{name}.npz"), **g)
         print(name, "ok", {k_: v.shape for k_, v in g.items() if k_.startswith("graph")})
+    if only:
+        return
     # permutations and distance known-answers
     perms = {}
     for n in (1, 2, 7, 100, 8191, 8192, 20000):

@@ -13,6 +13,7 @@ CASES = {
     "u8_l2": ("uint8", "Euclidian"), "i8_l2": ("int8", "Euclidian"), "u8_mips": ("uint8", "mips"),
     "i8_mips": ("int8", "mips"), "f32_l2": ("float", "Euclidian"), "f32_mips": ("float", "mips"),
     "u8_l2_2pass": ("uint8", "Euclidian"), "u8_l2_big": ("uint8", "Euclidian"),
+    "f32_l2_d100": ("float", "Euclidian"), "f32_mips_d100": ("float", "mips"),   # row length not a multiple of 8 elements
 }
 SEARCHES = [dict(k=10, beam=10), dict(k=10, beam=13), dict(k=10, beam=40), dict(k=5, beam=128, cut=1.1),
             dict(k=10, beam=20, limit=15), dict(k=10, beam=30, degree_limit=5), dict(k=1, beam=200)]

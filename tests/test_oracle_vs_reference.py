@@ -1,7 +1,9 @@
 """Pins the checker: oracle/pann_oracle.cpp (our C++ restatement) against outputs of the UNMODIFIED
 reference (tests/golden/*.npz, made by tests/golden/make_golden.py through oracle/_ref/ref_driver).
 CPU only.  Integer element types: bit-exact.  Floats: the restatement reproduces g++'s sequential float
-sum (oracle/Makefile: -ffp-contract=off), so it is checked bit-exact too where d % 8 == 0."""
+sum (oracle/Makefile: -ffp-contract=off), so it is checked bit-exact too — including rows whose length is not a multiple of
+8 elements (f32_*_d100: the reference binary built here with its own flags, -O3 -march=native, produces the sequential
+non-contracted sums there as well)."""
 import numpy as np
 import pytest
 
