@@ -229,9 +229,11 @@ static int gt_shrink_threads() { const char* e = getenv("PANN_GT_SHRINK_THREADS"
 template <int DT, int METRIC>
 static void gt_launch_shrink(pann_index* idx, cudaStream_t s, const uint8_t* d_q, uint32_t nq, uint32_t k, u64* state, const uint32_t* cand_ids,
                              uint32_t* cand_cnt, uint32_t nsub, uint32_t subcap, uint32_t keys_cap, const void* qnorm, const float* bnmax, void* thr, int* overflow, const float* cap) {
-  const size_t sm = 8ull * keys_cap + idx->geom.stride;
-  cudaFuncSetAttribute(pann_gt_shrink_kernel<DT, METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(8ull * GTS_KEYS + idx->geom.stride));
-  pann_gt_shrink_kernel<DT, METRIC><<<nq, keys_cap == GTS_KEYS_SMALL ? gt_shrink_threads() : 256, sm, s>>>(idx->points, idx->geom.stride, idx->geom.nch, d_q, k, state, cand_ids, cand_cnt, nsub, subcap, keys_cap, qnorm, bnmax, thr, overflow, cap);
+  const int threads = keys_cap == GTS_KEYS_SMALL ? gt_shrink_threads() : 256;
+  const size_t stage_b = DT == PANN_DT_F32 ? (size_t)(threads / 32) * PANN_STAGE_BYTES : 0;   // per-warp row staging (float rows)
+  const size_t sm = 8ull * keys_cap + idx->geom.stride + stage_b;
+  cudaFuncSetAttribute(pann_gt_shrink_kernel<DT, METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(8ull * GTS_KEYS + idx->geom.stride + 8 * PANN_STAGE_BYTES));
+  pann_gt_shrink_kernel<DT, METRIC><<<nq, threads, sm, s>>>(idx->points, idx->geom.stride, idx->geom.nch, d_q, k, state, cand_ids, cand_cnt, nsub, subcap, keys_cap, qnorm, bnmax, thr, overflow, cap);
 }
 template <int DT, int METRIC>
 static void gt_launch_thr(cudaStream_t s, const u64* state, uint32_t nq, uint32_t k, const void* qnorm, const float* bnmax, void* thr, const float* cap) {

@@ -17,6 +17,7 @@
 #include <type_traits>
 
 #include "pann_internal.h"
+#include "beam_search.cuh"   // pann_staged_distance / pann_quad_distance: the coalesced row gathers of K1
 
 #define GTM_M 128          // queries per CTA (UMMA M)
 #define GTM_N 256          // base rows per tile (UMMA N)
@@ -470,7 +471,19 @@ __global__ void __launch_bounds__(256, 2) pann_gt_shrink_kernel(const uint8_t* _
   }
   __syncthreads();
   if (s_over) { if (threadIdx.x == 0) atomicOr(overflow, 1); return; }
-  if (threadIdx.x == 0) { s_off[0] = 0; for (uint32_t i = 0; i < nsub; i++) s_off[i + 1] += s_off[i]; }
+  if (threadIdx.x < 32) {   // inclusive scan of the <= 64 sub-list lengths: two per lane (a serial loop here was 4 000 cycles per query)
+    const int ln = threadIdx.x;
+    uint32_t a = ln < (int)nsub ? s_off[ln + 1] : 0u, b = 32 + ln < (int)nsub ? s_off[33 + ln] : 0u;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t ua = __shfl_up_sync(0xffffffffu, a, d), ub = __shfl_up_sync(0xffffffffu, b, d);
+      if (ln >= d) { a += ua; b += ub; }
+    }
+    b += __shfl_sync(0xffffffffu, a, 31);
+    if (ln < (int)nsub) s_off[ln + 1] = a;
+    if (32 + ln < (int)nsub) s_off[33 + ln] = b;
+    if (ln == 0) s_off[0] = 0;
+  }
   __syncthreads();
   const uint32_t cnt = s_off[nsub];
   if (cnt == 0) return;                                              // nothing can have changed (or done by the small tier)
@@ -483,27 +496,42 @@ __global__ void __launch_bounds__(256, 2) pann_gt_shrink_kernel(const uint8_t* _
   __syncthreads();
   // the sub-lists are mostly empty: gather the ids densely first (staged in the key slots), then one dense pass of
   // exact distances
-  for (uint32_t sl = threadIdx.x >> 5; sl < nsub; sl += blockDim.x >> 5) {
-    const uint32_t o = s_off[sl], c = s_off[sl + 1] - o;
-    for (uint32_t i = threadIdx.x & 31; i < c; i += 32)
-      buf[k + o + i] = cand_ids[(uint64_t)q * GTM_CAND_CAP + (uint64_t)sl * subcap + i];
+  for (uint32_t ci = threadIdx.x; ci < cnt; ci += blockDim.x) {   // one independent load per candidate: its sub-list by bisection
+    uint32_t lo = 0, hi = nsub;                                    // s_off[lo] <= ci < s_off[hi]
+    while (hi - lo > 1) { const uint32_t mid = (lo + hi) >> 1; if (s_off[mid] <= ci) lo = mid; else hi = mid; }
+    buf[k + ci] = cand_ids[(uint64_t)q * GTM_CAND_CAP + (uint64_t)lo * subcap + (ci - s_off[lo])];
   }
   __syncthreads();
-  for (uint32_t ci = threadIdx.x; ci < cnt; ci += blockDim.x) {
-    const uint32_t id = (uint32_t)buf[k + ci];
-    const uint4* row = reinterpret_cast<const uint4*>(points + (uint64_t)id * stride);
-    DistAcc<DT, METRIC> acc;
-    uint32_t c = 0;
-    for (; c + 8 <= nch; c += 8) {   // eight 16-byte loads in flight per thread (one at a time this kernel ran at the latency
-      uint4 v[8];                    // bound: 2.4 TB/s of row gathers); the adds stay in ascending chunk order
-#pragma unroll
-      for (int j = 0; j < 8; j++)    // volatile: ptxas otherwise keeps ~3 loads in flight to stay at 32 registers
-        asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v[j].x), "=r"(v[j].y), "=r"(v[j].z), "=r"(v[j].w) : "l"(row + c + j));
-#pragma unroll
-      for (int j = 0; j < 8; j++) acc.add(v[j], qs[c + j]);
+  // exact distances, 32 candidates per warp and pass.  One row per THREAD makes every 128-bit load of a warp touch 32 lines
+  // (32 L1 wavefronts for 512 bytes): at 3M candidates per launch that alone was half of this kernel's 0.48 ms.  Float rows
+  // are therefore loaded by the whole warp, 128 bytes of four rows per instruction, and summed per lane in element order
+  // from shared memory (pann_staged_distance); 128-byte 8-bit rows are read four lanes per row (pann_quad_distance).
+  {
+    struct { const uint8_t* points; uint32_t stride, nch; } RG = {points, stride, nch};
+    const int lane = threadIdx.x & 31, wi = threadIdx.x >> 5, nw = blockDim.x >> 5;
+    uint4* stage = reinterpret_cast<uint4*>(gts_smem + 8ull * keys_cap + stride) + (size_t)wi * (PANN_STAGE_BYTES / 16);
+    for (uint32_t base = wi * 32; base < cnt; base += nw * 32) {
+      const uint32_t ci = base + lane;
+      const bool ok = ci < cnt;
+      const uint32_t id = ok ? (uint32_t)buf[k + ci] : 0u;
+      const unsigned mask = __ballot_sync(0xffffffffu, ok);
+      float d;
+      if constexpr (DT == PANN_DT_F32) {
+        d = pann_staged_distance<DT, METRIC>(RG, id, mask, qs, stage, lane);
+      } else {
+        if (nch == 8) {
+          d = pann_quad_distance<DT, METRIC>(RG, id, mask, qs, lane);
+        } else {
+          DistAcc<DT, METRIC> acc;
+          if (ok) {
+            const uint4* row = reinterpret_cast<const uint4*>(points + (uint64_t)id * stride);
+            for (uint32_t c = 0; c < nch; c++) acc.add(__ldg(row + c), qs[c]);
+          }
+          d = acc.result();
+        }
+      }
+      if (ok) buf[k + ci] = pann_key(d, id);
     }
-    for (; c < nch; c++) acc.add(__ldg(row + c), qs[c]);
-    buf[k + ci] = pann_key(acc.result(), id);
   }
   __syncthreads();
   gtm_bitonic(buf, m);
