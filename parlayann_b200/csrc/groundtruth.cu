@@ -233,6 +233,7 @@ static void gt_launch_shrink(pann_index* idx, cudaStream_t s, const uint8_t* d_q
   const size_t stage_b = DT == PANN_DT_F32 ? (size_t)(threads / 32) * PANN_STAGE_BYTES : 0;   // per-warp row staging (float rows)
   const size_t sm = 8ull * keys_cap + idx->geom.stride + stage_b;
   cudaFuncSetAttribute(pann_gt_shrink_kernel<DT, METRIC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(8ull * GTS_KEYS + idx->geom.stride + 8 * PANN_STAGE_BYTES));
+  cudaFuncSetAttribute(pann_gt_shrink_kernel<DT, METRIC>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
   pann_gt_shrink_kernel<DT, METRIC><<<nq, threads, sm, s>>>(idx->points, idx->geom.stride, idx->geom.nch, d_q, k, state, cand_ids, cand_cnt, nsub, subcap, keys_cap, qnorm, bnmax, thr, overflow, cap);
 }
 template <int DT, int METRIC>

@@ -452,7 +452,7 @@ __device__ __forceinline__ void gtm_bitonic(u64* a, int m) {
     }
 }
 template <int DT, int METRIC>
-__global__ void __launch_bounds__(256, 2) pann_gt_shrink_kernel(const uint8_t* __restrict__ points, uint32_t stride, uint32_t nch,
+__global__ void __launch_bounds__(256, 3) pann_gt_shrink_kernel(const uint8_t* __restrict__ points, uint32_t stride, uint32_t nch,
                                                              const uint8_t* __restrict__ queries, uint32_t k, u64* __restrict__ state,
                                                              const uint32_t* __restrict__ cand_ids, uint32_t* __restrict__ cand_cnt,
                                                              uint32_t nsub, uint32_t subcap, uint32_t keys_cap,
