@@ -451,6 +451,67 @@ __device__ __forceinline__ void gtm_bitonic(u64* a, int m) {
       __syncthreads();
     }
 }
+// The same network with E = m / blockDim.x keys per thread held in registers (thread t owns keys t*E .. t*E+E-1): partners
+// closer than E are in the thread, closer than 32 E in the warp (shuffles), and only the few strides beyond that go through
+// shared memory — 3 barrier-separated steps instead of 45 for 512 keys on 128 threads.
+template <int E>
+__device__ __forceinline__ void gtm_bitonic_reg(u64* a, int m) {
+  const int t = threadIdx.x;
+  u64 v[E];
+#pragma unroll
+  for (int e = 0; e < E; e++) v[e] = a[t * E + e];
+  for (int k = 2; k <= m; k <<= 1) {
+    const bool up_t = ((t * E) & k) == 0;                 // direction of this thread's keys once k >= E
+    for (int j = k >> 1; j >= 32 * E; j >>= 1) {          // partner in another warp
+      __syncthreads();
+#pragma unroll
+      for (int e = 0; e < E; e++) a[t * E + e] = v[e];
+      __syncthreads();
+      const int pt = t ^ (j / E);
+      const bool take_min = ((t & (j / E)) == 0) == up_t;
+#pragma unroll
+      for (int e = 0; e < E; e++) {
+        const u64 p = a[pt * E + e];
+        v[e] = take_min ? (p < v[e] ? p : v[e]) : (p > v[e] ? p : v[e]);
+      }
+    }
+    for (int j = min(k >> 1, 16 * E); j >= E; j >>= 1) {  // partner in this warp
+      const int d = j / E;
+      const bool take_min = ((t & d) == 0) == up_t;
+#pragma unroll
+      for (int e = 0; e < E; e++) {
+        const uint32_t lo = __shfl_xor_sync(0xffffffffu, (uint32_t)v[e], d), hi = __shfl_xor_sync(0xffffffffu, (uint32_t)(v[e] >> 32), d);
+        const u64 p = ((u64)hi << 32) | lo;
+        v[e] = take_min ? (p < v[e] ? p : v[e]) : (p > v[e] ? p : v[e]);
+      }
+    }
+#pragma unroll
+    for (int jj = E / 2; jj >= 1; jj >>= 1) {             // partner in this thread
+      if (jj < k) {
+#pragma unroll
+        for (int e = 0; e < E; e++) {
+          if ((e & jj) == 0) {
+            const bool up = k >= E ? up_t : ((e & k) == 0);
+            const u64 x = v[e], y = v[e | jj];
+            if ((x > y) == up) { v[e] = y; v[e | jj] = x; }
+          }
+        }
+      }
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int e = 0; e < E; e++) a[t * E + e] = v[e];
+  __syncthreads();
+}
+__device__ __forceinline__ void gtm_sort_keys(u64* a, int m) {
+  const int T = (int)blockDim.x;
+  if (m == T) gtm_bitonic_reg<1>(a, m);
+  else if (m == 2 * T) gtm_bitonic_reg<2>(a, m);
+  else if (m == 4 * T) gtm_bitonic_reg<4>(a, m);
+  else if (m == 8 * T) gtm_bitonic_reg<8>(a, m);
+  else gtm_bitonic(a, m);
+}
 template <int DT, int METRIC>
 __global__ void __launch_bounds__(256, 3) pann_gt_shrink_kernel(const uint8_t* __restrict__ points, uint32_t stride, uint32_t nch,
                                                              const uint8_t* __restrict__ queries, uint32_t k, u64* __restrict__ state,
@@ -534,7 +595,7 @@ __global__ void __launch_bounds__(256, 3) pann_gt_shrink_kernel(const uint8_t* _
     }
   }
   __syncthreads();
-  gtm_bitonic(buf, m);
+  gtm_sort_keys(buf, m);
   for (int i = threadIdx.x; i < (int)k; i += blockDim.x) state[(uint64_t)q * k + i] = buf[i];
   if (threadIdx.x == 0) gt_write_thr<DT, METRIC>(buf[k - 1], q, qnorm, bnmax, thr, cap);
 }
