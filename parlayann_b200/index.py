@@ -136,6 +136,32 @@ def quantize_mips8_device(points, max_val, device=0):
     return out
 
 
+class _PinnedBlock:
+    """page-locked host memory from the library (cudaHostAlloc), freed with the last numpy view of it"""
+
+    def __init__(self, nbytes):
+        self.p = C.c_void_p()
+        check(_lib.lib().pann_host_alloc(C.byref(self.p), C.c_size_t(max(1, nbytes))))
+        self.nbytes = nbytes
+
+    def __del__(self):
+        try:
+            if self.p:
+                _lib.lib().pann_host_free(self.p)
+        except Exception:
+            pass
+
+
+def pinned_empty(shape, dtype):
+    """np.empty in page-locked memory: copies to and from the device run at full PCIe speed and can overlap kernels"""
+    dt = np.dtype(dtype)
+    n = int(np.prod(shape)) * dt.itemsize
+    blk = _PinnedBlock(n)
+    buf = (C.c_uint8 * max(1, n)).from_address(blk.p.value)
+    buf._pann_block = blk      # the numpy array keeps `buf` alive (its base), `buf` keeps the block: freed with the last view
+    return np.frombuffer(buf, dtype=dt, count=int(np.prod(shape))).reshape(shape)
+
+
 class GraphIndex:
     """PointRange + Graph resident on one B200 (reference: python/graph_index.cpp:48-118)."""
 

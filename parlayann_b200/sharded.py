@@ -75,13 +75,22 @@ def search_sharded(index, queries, gather=True, group=None, root=None, **qp):
     With an NCCL group the slice's results never leave the device before the exchange: queries H2D, search, one
     all-gather per result array straight from the library's device buffers (pann_search_device_result), one D2H of the
     assembled answer into pinned buffers kept on the index.  root=r: only rank r assembles (and returns) the answer — what
-    a single driving process needs; the other ranks return None and skip the device-to-host copy of the whole batch."""
+    a single driving process needs; the other ranks return None and skip the device-to-host copy of the whole batch.
+    The gathered arrays live in page-locked buffers kept on the index and are overwritten by the next call: copy what must
+    outlive it."""
     rank, world = _world(group)
     nq = queries.shape[0]
     lo, hi = shard_bounds(nq, rank, world)
     k = int(qp.get("k", 10))
     if gather and world > 1 and _dist().get_backend(group) == "nccl":
         return _search_sharded_nccl(index, queries, lo, hi, k, group, qp, root)
+    if world == 1 and nq:   # one rank: the whole batch, into page-locked result buffers kept on the index (as the NCCL path does)
+        from .index import pinned_empty
+        out = getattr(index, "_sharded_out", None)
+        if out is None or out[0].shape != (nq, k):
+            out = (pinned_empty((nq, k), np.uint32), pinned_empty((nq, k), np.float32), pinned_empty((nq,), np.uint32), pinned_empty((nq,), np.uint32))
+            index._sharded_out = out
+        return index.search(queries, out=out, **qp)
     if hi > lo:
         ids, dists, vis, cmps = index.search(queries[lo:hi], **qp)
     else:  # more ranks than queries
