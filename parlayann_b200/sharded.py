@@ -187,7 +187,8 @@ GT_SAMPLE_ROWS = 4096   # rows of every shard that make the shared first bound (
 def groundtruth_sharded(index, queries=None, k=100, base_offset=0, group=None, local_fn=None, merge_fn=None, share_bounds=None,
                         sample_rows=GT_SAMPLE_ROWS):
     """compute_groundtruth with the base rows sharded over the ranks: `index` holds this rank's base shard whose
-    first row has global id `base_offset`.  Every rank returns the global (ids [nq,k] int32, dists [nq,k] float32).
+    first row has global id `base_offset`.  Every rank returns the global (ids [nq,k] int32, dists [nq,k] float32) — on the
+    GPU path as views of page-locked buffers kept on the index (copy them if they must outlive the next call).
 
     Default path (GPU): local top-k stays on the device, NCCL all-gather of the [nq,k] id and distance blocks,
     K5 merge on the device, one D2H copy of the result.  With share_bounds (or PANN_GT_SHARE=1; off by default: measured
@@ -250,4 +251,4 @@ def groundtruth_sharded(index, queries=None, k=100, base_offset=0, group=None, l
     pin[0].copy_(out_i, non_blocking=True)
     pin[1].copy_(out_d, non_blocking=True)
     torch.cuda.current_stream().synchronize()
-    return pin[0].numpy().copy(), pin[1].numpy().copy()
+    return pin[0].numpy(), pin[1].numpy()      # views of the page-locked buffers: overwritten by the next call on this index

@@ -78,7 +78,7 @@ def _nccl_worker(rank, world, port, tmp):
         qs = O.gen_points("float_norm", nq, d, stream=1)
         lo, hi = P.sharded.shard_bounds(n, rank, world)
         shard = P.GraphIndex(base[lo:hi], None, "float", "Euclidian", max_degree=4, device=rank)
-        gi, gd = P.sharded.groundtruth_sharded(shard, qs, k=k, base_offset=lo)
+        gi, gd = (a.copy() for a in P.sharded.groundtruth_sharded(shard, qs, k=k, base_offset=lo))   # views of reused buffers
         oi, od = O.groundtruth(base, qs, "float", k=k)
         assert np.array_equal(gd, od), "sharded ground-truth distances differ from the oracle"
         si, sd = P.sharded.groundtruth_sharded(shard, qs, k=k, base_offset=lo, share_bounds=True, sample_rows=2048)
