@@ -130,11 +130,11 @@ def cpu_model():
     return "unknown"
 
 
-def ref_recall_runs(O, files, settings, reps):
+def ref_recall_runs(O, files, settings, reps, threads=None):
     """runs checkRecall (timed qsearchAll + tie-aware recall) for each setting; returns list of dict per (setting, rep)"""
     st = ";".join(f"{k}:{b}:{c!r}:{l}:{d}" for (_, k, b, c, l, d) in settings)
     out = O.ref_run(["recall", "-data_type", "uint8", "-dist_func", "Euclidian", "-base", files["base"], "-graph", files["graph"],
-                     "-query", files["query"], "-gt", files["gt"], "-settings", st, "-reps", reps])
+                     "-query", files["query"], "-gt", files["gt"], "-settings", st, "-reps", reps], threads=threads)
     rows = []
     for m in re.finditer(r"REF_RECALL (\S+) QPS (\S+) avg_cmps (\d+) tail_cmps (\d+) avg_visited (\d+) tail_visited (\d+) k (\d+) beam (\d+) limit (\d+) dl (\d+)", out):
         rows.append(dict(recall=float(m.group(1)), qps=float(m.group(2)), avg_cmps=int(m.group(3)), avg_visited=int(m.group(5)),
@@ -715,6 +715,12 @@ def cpu_baseline(args, idx, queries, gt_ids, gt_d, s, gpu_answer):
         cb = {"value": qps, "unit": "queries/s", "cores": os.cpu_count(), "kind": "reference", "cpu": cpu_model(), "binary": O.ref_driver_info(),
               "recall10": rows[0]["recall"], "avg_cmps": rows[0]["avg_cmps"],
               "sample": f"the {args.nq_recall}-query recall batch x 3 timed runs (1 warm-up) of the reference's checkRecall/qsearchAll on the GPU-built graph"}
+        # one thread (PARLAY_NUM_THREADS=1) on the first 1 000 queries: the per-core rate
+        n1 = min(1000, args.nq_recall)
+        f1 = dict(files, query=os.path.join(tmp, "query1"), gt=os.path.join(tmp, "gt1"))
+        fileio.write_bin(f1["query"], queries[:n1]); fileio.write_ibin(f1["gt"], gt_ids[:n1], gt_d[:n1])
+        r1 = ref_recall_runs(O, f1, [s], 3, threads=1)[1:]
+        cb["one_thread"] = {"value": float(np.mean([r["qps"] for r in r1])), "unit": "queries/s", "queries": int(n1)}
         ref_ids, ref_vis, ref_cmps = ref_search_dump(O, files, s, tmp, args.nq_recall)
         g_ids, g_vis, g_cmps = gpu_answer
         bad = (ref_ids != g_ids).any(axis=1)
