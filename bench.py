@@ -594,14 +594,15 @@ def run_ours(args, rank, local_rank, world):
         for _ in range(2):
             search_sharded(idx, sq, gather=True, **qp)
         barrier()
-        tt = 0.0
+        tt, each = 0.0, []
         for _ in range(reps):
             l2_flush()
             barrier()
             t0 = time.perf_counter()
             res = search_sharded(idx, sq, gather=True, **qp)
-            tt += allmax((time.perf_counter() - t0) * 1e3)
-        strong[name] = {"queries_total": int(m), "ms": tt / reps, "value": m / (tt / reps * 1e-3), "unit": "queries/s",
+            each.append(allmax((time.perf_counter() - t0) * 1e3))
+            tt += each[-1]
+        strong[name] = {"queries_total": int(m), "ms": tt / reps, "ms_each": [round(x, 3) for x in each], "value": m / (tt / reps * 1e-3), "unit": "queries/s",
                         "what": "fixed batch cut over the ranks, H2D + search + all-gather + D2H on every rank (search_sharded gather=True)"}
         if name == "batch_10K":
             strong[name]["ids_equal_single_gpu"] = bool(np.array_equal(res[0], r_ids))

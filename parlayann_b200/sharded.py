@@ -86,10 +86,13 @@ def search_sharded(index, queries, gather=True, group=None, root=None, **qp):
         return _search_sharded_nccl(index, queries, lo, hi, k, group, qp, root)
     if world == 1 and nq:   # one rank: the whole batch, into page-locked result buffers kept on the index (as the NCCL path does)
         from .index import pinned_empty
-        out = getattr(index, "_sharded_out", None)
-        if out is None or out[0].shape != (nq, k):
+        cache = index.__dict__.setdefault("_sharded_out", {})   # per batch shape: freeing page-locked memory costs milliseconds
+        out = cache.get((nq, k))
+        if out is None:
+            if len(cache) >= 4:
+                cache.clear()
             out = (pinned_empty((nq, k), np.uint32), pinned_empty((nq, k), np.float32), pinned_empty((nq,), np.uint32), pinned_empty((nq,), np.uint32))
-            index._sharded_out = out
+            cache[(nq, k)] = out
         return index.search(queries, out=out, **qp)
     if hi > lo:
         ids, dists, vis, cmps = index.search(queries[lo:hi], **qp)
