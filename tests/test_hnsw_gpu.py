@@ -101,4 +101,8 @@ def test_save_load_roundtrip(tmp_path):
     b = h2.search(qs, k=10, ef=40)
     for x, y in zip(a, b):
         assert np.array_equal(x, y)
-    h.close(); h2.close()
+    import parlayann_b200 as P
+    h3 = P.load_index("Euclidian", "float", str(tmp_path / "b.fbin"), str(tmp_path / "m.hnsw"), hnsw=True)   # wrapper.py:96-116 with hnsw=True
+    for x, y in zip(a, h3.search(qs, k=10, ef=40)):
+        assert np.array_equal(x, y)
+    h.close(); h2.close(); h3.close()
