@@ -97,7 +97,15 @@ int pann_launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevB
   // warp (80 rows, 128 keys) nearly triples the resident warps of the row-cache path (the rare longer list takes the
   // uncached scan or the slab launch)
   const bool small_lists = rc_on && A.mode == 1 && A.R <= 64;
-  A.cap = small_lists ? 128 : 512;
+  // visited lists (mode 0): 152 cached rows, 256 keys, 4 warps per CTA = 8 resident warps per SM.  Measured at 10M (search +
+  // prune phase; rows,keys,warps): (160,512,3) 3.01 s, (160,256,3) 3.01 s, (152,256,4) 2.89 s, (144,256,4) 2.90 s, (136,256,4) 2.94 s,
+  // (128,256,4) 3.2-3.3 s (too many lists fall out of the cache), (176,256,3) 3.03 s
+  A.cap = small_lists ? 128 : 256;
+  uint32_t p1_rows = 152, p1_wpc = 4;
+  if (!small_lists) if (const char* e = getenv("PANN_PRUNE_P1")) {   // A/B: "rows,keys,warps" of the visited-list launch
+    unsigned a = 0, b = 0, c = 0;
+    if (sscanf(e, "%u,%u,%u", &a, &b, &c) == 3 && a >= 32 && b >= 64 && c >= 1 && c <= PANN_PRUNE_WARPS) { p1_rows = a; A.cap = b; p1_wpc = c; }
+  }
   if (const char* e = getenv("PANN_PRUNE_CAP")) A.cap = std::max<uint32_t>(8u, std::min<uint32_t>(A.cap, (uint32_t)atoi(e)));   // tests: force the slab launch
   A.off_b = al16((size_t)A.cap * 8);
   A.off_q = 2 * A.off_b;
@@ -109,14 +117,14 @@ int pann_launch_prune(pann_index* idx, PruneArgs& A, uint32_t ntasks_bound, DevB
   // It pays once the point set no longer lives in the 126 MB L2 (measured: 10M x 128 B build 36 s -> 15.5 s); while it
   // does (1M x 128 B), the plain path with more resident warps is ~20 % faster.
   if (rc_on) {
-    A.rc_rows = small_lists ? 80 : 160;   // measured at 10M (rows, keys): (96,256) 3.14 s, (80,128) 2.54 s, (72,128) 2.83 s, (112,256) 4.26 s
+    A.rc_rows = small_lists ? 80 : p1_rows;   // measured at 10M (rows, keys): (96,256) 3.14 s, (80,128) 2.54 s, (72,128) 2.83 s, (112,256) 4.26 s
     if (small_lists) if (const char* e = getenv("PANN_PRUNE_RC_ROWS")) A.rc_rows = (uint32_t)atoi(e);
     A.rc_pitch = g.stride + 16;
     if (((A.rc_pitch / 16) & 1) == 0) A.rc_pitch += 16;
     A.off_pos = A.warp_bytes;
     A.off_rc = A.off_pos + al16((size_t)A.cap * 2);
     A.warp_bytes = A.off_rc + A.rc_rows * A.rc_pitch;
-    wpc = small_lists ? 4 : 3;
+    wpc = small_lists ? 4 : (int)p1_wpc;
   }
   // Gram tile for the cached candidate rows (vamana_prune.cuh): 8-bit rows of 128 bytes, candidate-to-candidate distances as
   // warp-level integer MMAs.  MEASURED AND LEFT OFF (profiles/r2_k3_gram_10M_summary.txt, 10M x 128 u8 build): the
