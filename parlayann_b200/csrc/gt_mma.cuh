@@ -143,6 +143,13 @@ __device__ __forceinline__ int gtm_max3(int a, int b, int c) { return __vimax3_s
 __device__ __forceinline__ float gtm_max3(float a, float b, float c) { return fmaxf(fmaxf(a, b), c); }
 
 // ---------------------------------------------------------------------------------------------------------------
+// the PANN_GT_DBG breakdown switches (profiles/r2_gt_breakdown.txt) are compiled in only with -DPANN_GT_DEBUG: as run-time tests
+// inside the column loop they were ~10 % of the epilogue's instructions
+#ifdef PANN_GT_DEBUG
+#define GTM_DBG(A, bits) ((A).dbg & (bits))
+#else
+#define GTM_DBG(A, bits) (false)
+#endif
 struct GtMmaArgs {
   uint32_t nq, kb, nstages;    // queries; 128-byte k-blocks per row; B pipeline depth (<= GTM_STAGES)
   uint64_t row_lo, row_hi;     // base rows of this chunk; row_lo is a multiple of GTM_N
@@ -269,7 +276,7 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
     auto preinit = [&](uint32_t u, uint32_t st) {
       const uint32_t slot = u % GTM_BN;
       gtm_mbar_wait_a(a_bnfull + 8 * slot, (u / GTM_BN) & 1);
-      if (!(A.dbg & (2 | 8))) {
+      if (!GTM_DBG(A, 2 | 8)) {
 #pragma unroll 1
         for (uint32_t c = 0; c < NC; c++) {
           uint4 bn[8];
@@ -297,10 +304,10 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
 #pragma unroll
       for (uint32_t c = 0; c < NC; c++) {
         uint32_t v[32];
-        if (A.dbg & 2) continue;
+        if (GTM_DBG(A, 2)) continue;
         gtm_tmem_ld32(tmem_mine + as * GTM_N + c * 32, v);
         gtm_tmem_ld_wait();
-        if (A.dbg & 1) { if (v[0] == 0x7fffffffu && v[31] == 0x7ffffffeu) cnt++; continue; }
+        if (GTM_DBG(A, 1)) { if (v[0] == 0x7fffffffu && v[31] == 0x7ffffffeu) cnt++; continue; }
         acc_t w[32];
 #pragma unroll
         for (int j = 0; j < 32; j++) {
@@ -314,7 +321,7 @@ pann_gt_mma_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constan
         m9[10] = w[30] > w[31] ? w[30] : w[31];
         const acc_t m3a = gtm_max3(m9[0], m9[1], m9[2]), m3b = gtm_max3(m9[3], m9[4], m9[5]), m3c = gtm_max3(m9[6], m9[7], m9[8]);
         const acc_t mx = gtm_max3(gtm_max3(m3a, m3b, m3c), m9[9], m9[10]);
-        if (A.dbg & 4) { if (mx == (acc_t)12345) cnt++; continue; }   // experiments: the max tree without the append path
+        if (GTM_DBG(A, 4)) { if (mx == (acc_t)12345) cnt++; continue; }   // experiments: the max tree without the append path
         if (mx >= S) {   // which of the 32 columns: a bit mask now, the global stores after the stage has been handed on
           unsigned m = 0;
 #pragma unroll
