@@ -102,7 +102,8 @@ def search_sharded(index, queries, gather=True, group=None, root=None, **qp):
     if not gather or world == 1:
         return ids, dists, vis, cmps
     counts = [shard_bounds(nq, r, world)[1] - shard_bounds(nq, r, world)[0] for r in range(world)]
-    return tuple(all_gather_rows(a, counts, group) for a in (ids, dists, vis, cmps))
+    out = tuple(all_gather_rows(a, counts, group) for a in (ids, dists, vis, cmps))
+    return out if root is None or rank == root else None      # host-logic path (gloo): same contract as the NCCL gather to one rank
 
 
 def _search_sharded_nccl(index, queries, lo, hi, k, group, qp, root=None):

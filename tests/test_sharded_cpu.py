@@ -73,6 +73,10 @@ def _worker(rank, world, port, tmp):
             assert np.array_equal(x, y)
         mine = S.search_sharded(idx, qs, gather=False, k=k, beam=16)
         assert np.array_equal(mine[0], ref[0][lo:hi])
+        at_root = S.search_sharded(idx, qs, root=1, k=k, beam=16)      # the answer on one rank only
+        assert (at_root is None) == (rank != 1)
+        if rank == 1:
+            assert all(np.array_equal(x, y) for x, y in zip(at_root, ref))
         # sharded ground truth == ground truth of the whole base set (ties: distances identical, ids by (dist,id))
         blo, bhi = S.shard_bounds(n, rank, world)
 
