@@ -208,11 +208,13 @@ __global__ void PANN_PRUNE_BOUNDS pann_prune_kernel(const PruneArgs A) {
           }
         src = bufA;
       } else {
+        // rank sort by strict "less" (four keys per iteration, borrow-counted): equal keys — the same vertex reached twice, with
+        // the same distance — land in the same slot, and the slot they leave empty keeps the sentinel that unique drops below
+        for (int i = lane; i < C; i += 32) bufB[i] = ~0ull;
+        __syncwarp();
         for (int i = lane; i < C; i += 32) {
-          u64 ci = bufA[i];
-          int r = 0;
-          for (int j = 0; j < C; j++) { u64 cj = bufA[j]; r += (cj < ci) || (cj == ci && j < i); }
-          bufB[r] = ci;
+          const u64 ci = bufA[i];
+          bufB[pann_count_below_any(bufA, C, ci)] = ci;
         }
         __syncwarp();
       }
@@ -221,7 +223,7 @@ __global__ void PANN_PRUNE_BOUNDS pann_prune_kernel(const PruneArgs A) {
       for (int base = 0; base < C; base += 32) {
         int i = base + lane;
         u64 c = i < C ? src[i] : 0;
-        bool keep = i < C && (i == 0 || pann_key_id(src[i - 1]) != pann_key_id(c));
+        bool keep = i < C && c != ~0ull && (i == 0 || pann_key_id(src[i - 1]) != pann_key_id(c));
         unsigned km = __ballot_sync(PANN_FULL, keep);
         __syncwarp();
         if (keep) bufB[w + __popc(km & lt_mask)] = c;

@@ -176,3 +176,24 @@ def test_batch_insert_matches_reference_golden_and_oracle(dataset):
     a, b = idx2.batch_insert(ins, L=48, alpha=1.2, random_order=True, stats=True)
     ra, rb = O.vamana_batch_insert(ds.base, g, ins, "int8", "mips", L=48, alpha=1.2, random_order=True)
     assert np.array_equal(valid_graph(idx2.graph()), valid_graph(g)) and np.array_equal(a, ra) and np.array_equal(b, rb)
+
+
+def test_tie_rows_sorted_on_the_device_as_std_sort_sorts_them(monkeypatch):
+    """the final sort of rows with tied distances: a kernel that runs libstdc++'s introsort per row (vamana_build.cu) against
+    the host's std::sort over the same rows (PANN_HOST_SORT=2) and against sorting every row on the host (=1) — 64-entry rows,
+    so the quicksort part runs, and 8-bit data of few dimensions, so almost every row has ties"""
+    import parlayann_b200 as P
+    graphs = {}
+    for n, d, R, L in ((30000, 16, 64, 96), (8000, 8, 100, 128)):
+        base = O.gen_points("uint8", n, d, seed=9)
+        for mode in ("", "2", "1"):
+            if mode:
+                monkeypatch.setenv("PANN_HOST_SORT", mode)
+            else:
+                monkeypatch.delenv("PANN_HOST_SORT", raising=False)
+            idx = P.GraphIndex(base, None, "uint8", "Euclidian", max_degree=R)
+            idx.build(R=R, L=L, alpha=1.2, sort_neighbors=True)
+            graphs[mode] = idx.graph()
+            idx.close()
+        assert (graphs[""][:, 0] > 16).mean() > 0.5, "rows too short to reach the quicksort part"
+        assert np.array_equal(graphs[""], graphs["2"]) and np.array_equal(graphs[""], graphs["1"])
