@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <limits>
 #include <random>
+#include <thread>
 #include <utility>
 #include <vector>
 
@@ -44,13 +45,37 @@ void pann_host_random_permutation(int64_t n, int32_t* out) {
   for (uint64_t b = (uint64_t)n - 1; b > 0; b >>= 1) lg++;
   const size_t bits = ((uint64_t)n < (1ull << 27)) ? (lg - 7) / 2 : (lg - 17);
   const size_t nb = (size_t)1 << bits, mask = nb - 1;
+  // the stable counting sort, blocked over threads (per-block counts -> offsets, each block scatters its slice in index order:
+  // the same permutation as the sequential loop), then the buckets' shuffles side by side.  10M: ~0.12 s on one core.
+  unsigned nt = std::thread::hardware_concurrency();
+  nt = std::max(1u, std::min(nt, 32u));
+  if ((uint64_t)n < (1ull << 20)) nt = 1;
+  const int64_t chunk = (n + nt - 1) / nt;
+  std::vector<std::vector<size_t>> cnt(nt, std::vector<size_t>(nb, 0));
+  auto run = [&](auto&& fn) {
+    if (nt == 1) { fn(0u); return; }
+    std::vector<std::thread> ts;
+    for (unsigned t = 0; t < nt; t++) ts.emplace_back(fn, t);
+    for (auto& t : ts) t.join();
+  };
+  run([&](unsigned t) {
+    const int64_t lo = (int64_t)t * chunk, hi = std::min<int64_t>(n, lo + chunk);
+    for (int64_t i = lo; i < hi; i++) cnt[t][r.ith((uint64_t)i) & mask]++;
+  });
   std::vector<size_t> start(nb + 1, 0);
-  for (int64_t i = 0; i < n; i++) start[(r.ith((uint64_t)i) & mask) + 1]++;
-  for (size_t b = 0; b < nb; b++) start[b + 1] += start[b];
-  std::vector<size_t> fill(start.begin(), start.end() - 1);
-  for (int64_t i = 0; i < n; i++) out[fill[r.ith((uint64_t)i) & mask]++] = (int32_t)i;
-  for (size_t b = 0; b < nb; b++)
-    if (start[b + 1] - start[b] > 1) knuth_shuffle(out + start[b], start[b + 1] - start[b], r.fork(b));
+  for (size_t b = 0; b < nb; b++) {
+    size_t acc = start[b];
+    for (unsigned t = 0; t < nt; t++) { const size_t c = cnt[t][b]; cnt[t][b] = acc; acc += c; }   // cnt becomes this block's write cursor
+    start[b + 1] = acc;
+  }
+  run([&](unsigned t) {
+    const int64_t lo = (int64_t)t * chunk, hi = std::min<int64_t>(n, lo + chunk);
+    for (int64_t i = lo; i < hi; i++) out[cnt[t][r.ith((uint64_t)i) & mask]++] = (int32_t)i;
+  });
+  run([&](unsigned t) {
+    for (size_t b = t; b < nb; b += nt)
+      if (start[b + 1] - start[b] > 1) knuth_shuffle(out + start[b], start[b + 1] - start[b], r.fork(b));
+  });
 }
 
 // batch_insert's schedule (algorithms/vamana/index.h:206-209, :223-234) with base = 2, max_fraction = .02:
