@@ -1,7 +1,7 @@
 """K1 (build mode) + K3 (robustPrune) + reverse-edge grouping = pann_vamana_build, through the C ABI.
 Gates: with sort_neighbors=false the graph is byte-identical to the reference's (golden
 fixtures) and to the oracle's at larger sizes; build statistics identical; with the final sort the rows are
-identical too (the sort itself is the host's std::sort on device-computed distances)."""
+identical too (rows without ties are rank-sorted on the device, rows with ties by a kernel that runs std::sort's algorithm)."""
 import numpy as np
 import pytest
 
