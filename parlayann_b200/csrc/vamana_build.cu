@@ -76,38 +76,7 @@ static __global__ void pann_scatter_rows_kernel(const uint32_t* tie_rows, const 
 // __final_insertion_sort) — on the (id, distance) pairs, so the row ends up byte for byte as the host's std::sort leaves
 // it, the heap-sort fallback of an exhausted depth limit included (nearly sorted rows do run into it).  *fallback is a guard
 // that sends every tie row to the host's std::sort.
-#define PANN_TIE_MAXDEG 128
-struct TieRow {
-  uint32_t id[PANN_TIE_MAXDEG];
-  float d[PANN_TIE_MAXDEG];
-  __device__ __forceinline__ bool lt(int a, int b) const { return d[a] < d[b]; }
-  __device__ __forceinline__ void swp(int a, int b) { const uint32_t ti = id[a]; id[a] = id[b]; id[b] = ti; const float td = d[a]; d[a] = d[b]; d[b] = td; }
-  // the heap-sort fallback, on [f, l): std::__partial_sort(first, last, last) = __make_heap + __sort_heap (bits/stl_heap.h)
-  __device__ void push_heap(int f, int hole, int top, uint32_t vi, float vd) {
-    int parent = (hole - 1) / 2;
-    while (hole > top && d[f + parent] < vd) { id[f + hole] = id[f + parent]; d[f + hole] = d[f + parent]; hole = parent; parent = (hole - 1) / 2; }
-    id[f + hole] = vi; d[f + hole] = vd;
-  }
-  __device__ void adjust_heap(int f, int hole, int len, uint32_t vi, float vd) {
-    const int top = hole;
-    int child = hole;
-    while (child < (len - 1) / 2) {
-      child = 2 * (child + 1);
-      if (d[f + child] < d[f + child - 1]) child--;
-      id[f + hole] = id[f + child]; d[f + hole] = d[f + child]; hole = child;
-    }
-    if ((len & 1) == 0 && child == (len - 2) / 2) {
-      child = 2 * (child + 1);
-      id[f + hole] = id[f + child - 1]; d[f + hole] = d[f + child - 1]; hole = child - 1;
-    }
-    push_heap(f, hole, top, vi, vd);
-  }
-  __device__ void heap_sort(int f, int l) {
-    const int len = l - f;
-    if (len >= 2) { int parent = (len - 2) / 2; while (true) { adjust_heap(f, parent, len, id[f + parent], d[f + parent]); if (parent == 0) break; parent--; } }
-    while (l - f > 1) { --l; const uint32_t vi = id[l]; const float vd = d[l]; id[l] = id[f]; d[l] = d[f]; adjust_heap(f, 0, l - f, vi, vd); }
-  }
-};
+#include "tie_sort.h"
 static __global__ void __launch_bounds__(128) pann_tie_sort_kernel(const uint32_t* __restrict__ tie_rows, const uint32_t* __restrict__ tie_graph,
                                                                   const float* __restrict__ tie_dist, uint32_t* __restrict__ graph, uint32_t T,
                                                                   uint32_t maxdeg, int* fallback) {
@@ -118,60 +87,7 @@ static __global__ void __launch_bounds__(128) pann_tie_sort_kernel(const uint32_
   const float* sd = tie_dist + (u64)t * maxdeg;
   const int n = (int)src[0];
   for (int j = 0; j < n; j++) { r.id[j] = src[1 + j]; r.d[j] = sd[j]; }
-  // __introsort_loop(first, last, 2 * lg(n)); the recursion on the right part becomes a stack (the parts are disjoint)
-  int stk_f[16], stk_l[16], stk_d[16], sp = 0;
-  int depth0 = 0; for (int m = n; m > 1; m >>= 1) depth0++;
-  if (n > 1) { stk_f[0] = 0; stk_l[0] = n; stk_d[0] = 2 * depth0; sp = 1; }
-  while (sp > 0) {
-    sp--;
-    int first = stk_f[sp], last = stk_l[sp], depth = stk_d[sp];
-    while (last - first > 16) {
-      if (sp >= 15) { atomicOr(fallback, 1); return; }   // cannot happen (the depth limit bounds the stack at 2 lg n <= 14)
-      if (depth == 0) { r.heap_sort(first, last); break; }   // the depth limit ran out (pruned rows arrive nearly sorted: this is not rare)
-      --depth;
-      const int mid = first + (last - first) / 2;
-      {  // __move_median_to_first(first, first + 1, mid, last - 1)
-        const int a = first + 1, b = mid, c = last - 1;
-        if (r.lt(a, b)) {
-          if (r.lt(b, c)) r.swp(first, b);
-          else if (r.lt(a, c)) r.swp(first, c);
-          else r.swp(first, a);
-        } else if (r.lt(a, c)) r.swp(first, a);
-        else if (r.lt(b, c)) r.swp(first, c);
-        else r.swp(first, b);
-      }
-      int lo = first + 1, hi = last;   // __unguarded_partition(first + 1, last, pivot = first)
-      while (true) {
-        while (r.lt(lo, first)) ++lo;
-        --hi;
-        while (r.lt(first, hi)) --hi;
-        if (!(lo < hi)) break;
-        r.swp(lo, hi);
-        ++lo;
-      }
-      stk_f[sp] = lo; stk_l[sp] = last; stk_d[sp] = depth; sp++;   // __introsort_loop(cut, last, depth_limit)
-      last = lo;
-    }
-  }
-  // __final_insertion_sort: __insertion_sort over the first 16, __unguarded_insertion_sort over the rest
-  const int head = n > 16 ? 16 : n;
-  for (int i = 1; i < head; i++) {
-    const uint32_t vi = r.id[i]; const float vd = r.d[i];
-    if (vd < r.d[0]) {
-      for (int j = i; j > 0; j--) { r.id[j] = r.id[j - 1]; r.d[j] = r.d[j - 1]; }
-      r.id[0] = vi; r.d[0] = vd;
-    } else {
-      int j = i;
-      while (vd < r.d[j - 1]) { r.id[j] = r.id[j - 1]; r.d[j] = r.d[j - 1]; j--; }
-      r.id[j] = vi; r.d[j] = vd;
-    }
-  }
-  for (int i = head; i < n; i++) {
-    const uint32_t vi = r.id[i]; const float vd = r.d[i];
-    int j = i;
-    while (vd < r.d[j - 1]) { r.id[j] = r.id[j - 1]; r.d[j] = r.d[j - 1]; j--; }
-    r.id[j] = vi; r.d[j] = vd;
-  }
+  if (!pann_tie_sort_row(r, n)) { atomicOr(fallback, 1); return; }
   uint32_t* dst = graph + (u64)tie_rows[t] * (maxdeg + 1);
   for (int j = 0; j < n; j++) dst[1 + j] = r.id[j];
 }
