@@ -29,6 +29,14 @@ const void* PANN_CAT(pann_beam_small_kernel_dt, PANN_INST_DT)(int metric, int qr
   return metric == PANN_M_L2 ? pick_beam_small<PANN_M_L2>(qr, ext) : pick_beam_small<PANN_M_MIPS>(qr, ext);
 }
 
+// the WIDE variant (small batches): 128-byte integer rows only
+const void* PANN_CAT(pann_beam_small_wide_kernel_dt, PANN_INST_DT)(int metric) {
+  if constexpr (pann_quad_rows<PANN_INST_DT, PANN_QR>())
+    return metric == PANN_M_L2 ? (const void*)&pann_beam_search_small_kernel<PANN_INST_DT, PANN_M_L2, PANN_QR, false, true>
+                               : (const void*)&pann_beam_search_small_kernel<PANN_INST_DT, PANN_M_MIPS, PANN_QR, false, true>;
+  else return nullptr;
+}
+
 template <int METRIC>
 static const void* pick_prune(int qr, bool gs) {
   if (qr == PANN_QR) return gs ? (const void*)&pann_prune_kernel<PANN_INST_DT, METRIC, PANN_QR, true>

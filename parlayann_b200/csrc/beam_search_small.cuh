@@ -137,6 +137,39 @@ __device__ __forceinline__ float pann_quad_distance_s(const RG& A, uint32_t a, u
   return res.result();
 }
 
+// The same in two steps, for the WIDE kernel: all loads of BOTH 32-neighbour rounds go out before anything is summed.
+template <class RG>
+__device__ __forceinline__ void pann_quad_gather_s(const RG& A, uint32_t a, unsigned keepmask, int lane, uint4 (&v)[4][2]) {
+  const int sub = lane & 3, rowi = lane >> 2;
+#pragma unroll
+  for (int g = 0; g < 4; g++) {
+    const int src = g * 8 + rowi;
+    const uint32_t ag = __shfl_sync(PANN_FULL, a, src);
+    const uint8_t* row = A.points + (u64)(((keepmask >> src) & 1u) ? ag : 0u) * A.stride + sub * 16;
+    v[g][0] = pann_ldg16(row);
+    v[g][1] = pann_ldg16(row + 64);
+  }
+}
+template <int DT, int METRIC>
+__device__ __forceinline__ float pann_quad_reduce_s(const uint4 (&v)[4][2], uint32_t qs, int lane) {
+  const int sub = lane & 3;
+  const uint4 q0 = pann_lds128(qs + 16u * sub), q1 = pann_lds128(qs + 16u * sub + 64u);
+  DistAcc<DT, METRIC> acc[4];
+#pragma unroll
+  for (int g = 0; g < 4; g++) { acc[g].add(v[g][0], q0); acc[g].add(v[g][1], q1); }
+  unsigned part[4];
+#pragma unroll
+  for (int g = 0; g < 4; g++) part[g] = (unsigned)acc[g].acc;
+  const bool b1 = (lane & 2) != 0, b0 = (lane & 1) != 0;
+  const unsigned r0 = (b1 ? part[2] : part[0]) + __shfl_xor_sync(PANN_FULL, b1 ? part[0] : part[2], 2);
+  const unsigned r1 = (b1 ? part[3] : part[1]) + __shfl_xor_sync(PANN_FULL, b1 ? part[1] : part[3], 2);
+  const unsigned tot = (b0 ? r1 : r0) + __shfl_xor_sync(PANN_FULL, b0 ? r0 : r1, 1);
+  const unsigned mine = __shfl_sync(PANN_FULL, tot, (lane & 7) * 4 + (lane >> 3));
+  DistAcc<DT, METRIC> res;
+  res.acc = (decltype(res.acc))mine;
+  return res.result();
+}
+
 // EXT: per-query start lists and the vertex -> row map (beamSearchRandom, HNSW layers); a separate instantiation so that
 // the plain kernel — which sits at its register budget — is not touched by them.
 //
@@ -147,11 +180,14 @@ __device__ __forceinline__ float pann_quad_distance_s(const RG& A, uint32_t a, u
 // that is reached twice ends up in adjacent lanes: that (rare) case, and two equal candidates, fall back to the
 // one-at-a-time insertion below, which resolves duplicates exactly as set_union does.
 // "Already visited" is a 1024-bit signature across the warp (one register per lane) with an exact list behind it.
-template <int DT, int METRIC, int QR, bool EXT>
+// WIDE (small batches: the launch cannot fill the GPU, so a walk's latency is the run time): a hop's two 32-neighbour
+// rounds are filtered first, then the row gathers of BOTH go out together and are summed afterwards — one memory round trip
+// per hop instead of two, at 32 more registers (3 CTAs per SM, which a small batch does not need anyway).
+template <int DT, int METRIC, int QR, bool EXT, bool WIDE = false>
 #ifndef PANN_K1S_MINB
 #define PANN_K1S_MINB 6  // 78 registers, 24 warps per SM.  Measured with the batched merge, 1M queries on 10M x 128 u8 (CTAs per SM: ms): 8: 53.3, 7: 47.5, 6: 46.6, 5: 54.0, 4: 58.9 — and 1 000 queries (latency bound): 0.33 ms at 7, 0.27 ms at 6
 #endif
-__global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MINB : 4) pann_beam_search_small_kernel(const BeamArgs A) {
+__global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, WIDE ? 3 : (QR > 0 ? PANN_K1S_MINB : 4)) pann_beam_search_small_kernel(const BeamArgs A) {
   extern __shared__ __align__(16) uint8_t pann_smem[];
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
   const unsigned lt_mask = (1u << lane) - 1u;
@@ -282,6 +318,50 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1S_MIN
         if (lane < ne) pann_prefetch_l2(A.points + (u64)a0 * A.stride);
         if (32 + lane < ne) pann_prefetch_l2(A.points + (u64)a1 * A.stride);
       }
+      if constexpr (WIDE && QUAD) {
+        // both rounds through the hash filter first (in list order, as the reference walks the row), then all row gathers
+        // of the hop in flight together; the host launches this variant only for max degree <= 64
+        uint32_t aa[2];
+        bool kp[2];
+        unsigned km[2];
+#pragma unroll
+        for (int rd = 0; rd < 2; rd++) {
+          const int i = rd * 32 + lane;
+          const bool act = i < ne;
+          const uint32_t a = rd == 0 ? a0 : a1;
+          const uint32_t loc = act ? ((uint32_t)pann_hash64_2(a) & hmask) : (0x80000000u | lane);
+          const unsigned peers = __match_any_sync(PANN_FULL, loc);
+          const unsigned prev = peers & lt_mask;
+          const uint32_t from_prev = __shfl_sync(PANN_FULL, a, prev ? (31 - __clz(prev)) : lane);
+          bool seen = false;
+          if (act) {
+            const uint32_t slot = prev ? from_prev : pann_lds32(s_hash + 4u * loc);
+            seen = (slot == a);
+          }
+          __syncwarp();
+          if (act && (peers >> lane) <= 1u) pann_sts32(s_hash + 4u * loc, a);
+          __syncwarp();
+          kp[rd] = act && !seen && (a != self);
+          km[rd] = __ballot_sync(PANN_FULL, kp[rd]);
+          aa[rd] = a;
+        }
+        cmps += __popc(km[0]) + __popc(km[1]);  // :155
+        uint4 v0[4][2], v1[4][2];
+        pann_quad_gather_s(A, aa[0], km[0], lane, v0);
+        if (km[1]) pann_quad_gather_s(A, aa[1], km[1], lane, v1);
+#pragma unroll
+        for (int rd = 0; rd < 2; rd++) {
+          if (rd == 1 && !km[1]) break;
+          const float d = rd == 0 ? pann_quad_reduce_s<DT, METRIC>(v0, s_q, lane) : pann_quad_reduce_s<DT, METRIC>(v1, s_q, lane);
+          const u64 key = pann_key(d, aa[rd]);
+          const bool take = kp[rd] && (d < cutoff) && (key <= drop_above);  // :153-158
+          const unsigned m = __ballot_sync(PANN_FULL, take);
+          if (C + __popc(m) > (int)A.ccap) { status = 1; break; }
+          if (take) pann_sts64(s_cand + 8u * (C + __popc(m & lt_mask)), key);
+          C += __popc(m);
+          __syncwarp();
+        }
+      } else
       for (int base = 0; base < ne; base += 32) {
         const int i = base + lane;
         const bool act = i < ne;
@@ -469,6 +549,9 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32) pann_rerank_kernel(co
 const void* pann_beam_small_kernel_dt0(int metric, int qr, bool ext);
 const void* pann_beam_small_kernel_dt1(int metric, int qr, bool ext);
 const void* pann_beam_small_kernel_dt2(int metric, int qr, bool ext);
+const void* pann_beam_small_wide_kernel_dt0(int metric);
+const void* pann_beam_small_wide_kernel_dt1(int metric);
+const void* pann_beam_small_wide_kernel_dt2(int metric);
 const void* pann_rerank_kernel_dt0(int metric);
 const void* pann_rerank_kernel_dt1(int metric);
 const void* pann_rerank_kernel_dt2(int metric);

@@ -330,3 +330,20 @@ def test_beamSearchRandom_golden():
         ids, _, vis, cmps = idx.search(qs, k=k, beam=beam, starts=st.reshape(-1, 1))
         assert np.array_equal(ids, g[f"r{si}_ids"])
         assert np.array_equal(vis, g[f"r{si}_visited"]) and np.array_equal(cmps, g[f"r{si}_distances"])
+
+
+@pytest.mark.parametrize("data_type,metric", [("uint8", "Euclidian"), ("int8", "mips")])
+def test_small_batch_wide_variant_identical(dataset, monkeypatch, data_type, metric):
+    """K1s WIDE (both 32-neighbour rounds of a hop filtered first, then all row gathers in flight together — the kernel small
+    batches get) against the default kernel and the oracle: ids, distances, visited and comparison counters"""
+    ds = dataset(data_type, metric, n=20000, d=128, nq=300, R=64, L=96)
+    idx = _index(ds)
+    for kw in (dict(k=10, beam=24), dict(k=10, beam=12, limit=20), dict(k=5, beam=32, cut=1.1), dict(k=10, beam=16, degree_limit=40)):
+        monkeypatch.setenv("PANN_K1S_WIDE", "0")
+        a = idx.search(ds.queries, **kw)
+        monkeypatch.setenv("PANN_K1S_WIDE", "1")
+        b = idx.search(ds.queries, **kw)
+        ref = O.search(ds.base, ds.graph, ds.queries, data_type, metric, **kw)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y), kw
+        assert np.array_equal(b[0], ref["ids"]) and np.array_equal(b[2], ref["visited"]) and np.array_equal(b[3], ref["cmps"]), kw
