@@ -182,12 +182,15 @@ __device__ __forceinline__ float pann_quad_reduce_s(const uint4 (&v)[4][2], uint
 // "Already visited" is a 1024-bit signature across the warp (one register per lane) with an exact list behind it.
 // WIDE (small batches: the launch cannot fill the GPU, so a walk's latency is the run time): a hop's two 32-neighbour
 // rounds are filtered first, then the row gathers of BOTH go out together and are summed afterwards — one memory round trip
-// per hop instead of two, at 32 more registers (3 CTAs per SM, which a small batch does not need anyway).
+// per hop instead of two, at 45 more registers (4 CTAs per SM instead of 6, which a small batch does not need anyway).
 template <int DT, int METRIC, int QR, bool EXT, bool WIDE = false>
+#ifndef PANN_K1S_WIDE_MINB
+#define PANN_K1S_WIDE_MINB 4   // 124 registers, 16 warps per SM (3: 134 registers; the same times up to 1 776 queries, and 2 368 queries 0.282 vs 0.240 ms)
+#endif
 #ifndef PANN_K1S_MINB
 #define PANN_K1S_MINB 6  // 78 registers, 24 warps per SM.  Measured with the batched merge, 1M queries on 10M x 128 u8 (CTAs per SM: ms): 8: 53.3, 7: 47.5, 6: 46.6, 5: 54.0, 4: 58.9 — and 1 000 queries (latency bound): 0.33 ms at 7, 0.27 ms at 6
 #endif
-__global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, WIDE ? 3 : (QR > 0 ? PANN_K1S_MINB : 4)) pann_beam_search_small_kernel(const BeamArgs A) {
+__global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, WIDE ? PANN_K1S_WIDE_MINB : (QR > 0 ? PANN_K1S_MINB : 4)) pann_beam_search_small_kernel(const BeamArgs A) {
   extern __shared__ __align__(16) uint8_t pann_smem[];
   const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
   const unsigned lt_mask = (1u << lane) - 1u;

@@ -224,13 +224,15 @@ static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap, cud
     if (const char* e = getenv("PANN_K1_PAD_SMEM")) cta_bytes += (size_t)atoi(e);   // experiments: fewer CTAs per SM, more L1
     const bool ext = A.starts_stride != 0 || A.nstarts_q != nullptr || A.rowmap != nullptr || A.nstarts > B;
     const void* fn = beam_small_kernel(idx->dtype, idx->metric, qrT, ext);
-    {  // small batches (fewer queries than the WIDE variant keeps resident: 3 CTAs per SM): both rounds' gathers in flight
+    if (!ext && qrT == PANN_QR && idx->dtype != PANN_DT_F32 && A.maxdeg <= 64) {
+      // small batches — at most what the WIDE variant keeps resident — get it: both rounds' gathers of a hop in flight together
+      const void* fw = idx->dtype == PANN_DT_U8 ? pann_beam_small_wide_kernel_dt1(idx->metric) : pann_beam_small_wide_kernel_dt2(idx->metric);
       const char* w = getenv("PANN_K1S_WIDE");   // 0 / 1 force it off / on (A/B, tests)
-      const long long wide_max = (long long)idx->sms * 3 * PANN_WARPS_PER_CTA;
-      const bool want_wide = w ? w[0] == '1' : (long long)A.nq <= wide_max;
-      if (want_wide && !ext && qrT == PANN_QR && idx->dtype != PANN_DT_F32 && A.maxdeg <= 64) {
-        const void* fw = idx->dtype == PANN_DT_U8 ? pann_beam_small_wide_kernel_dt1(idx->metric) : pann_beam_small_wide_kernel_dt2(idx->metric);
-        if (fw) fn = fw;
+      if (fw && !(w && w[0] == '0')) {
+        int per_sm_w = 0;
+        PANN_CUDA(cudaFuncSetAttribute(fw, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));
+        PANN_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_w, fw, PANN_WARPS_PER_CTA * 32, cta_bytes));
+        if (per_sm_w >= 1 && ((w && w[0] == '1') || (long long)A.nq <= (long long)per_sm_w * idx->sms * PANN_WARPS_PER_CTA)) fn = fw;
       }
     }
     PANN_CUDA(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)cta_bytes));

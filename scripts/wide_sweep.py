@@ -6,7 +6,7 @@ n = int(os.environ.get("N", "10000000")); beam = int(os.environ.get("BEAM", "24"
 idx = P.GraphIndex(data_type="uint8", metric="Euclidian", max_degree=64, device=0, synthetic=dict(n=n, d=128, kind="uint8", seed=1234, stream=0, r=24, nc=256))
 idx.build(R=64, L=128, alpha=1.2, num_passes=1, sort_neighbors=True)
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-for nq in (1, 32, 500, 1250, 1776, 2500, 5000, 10000, 100000):
+for nq in [int(x) for x in os.environ.get("NQS", "1,32,500,1250,1776,2500,5000,10000,100000").split(",")]:
     idx.synthetic_queries(nq, kind="uint8", seed=1234, stream=1)
     line, ref = f"nq {nq:7d}", None
     for w in ("0", "1"):
