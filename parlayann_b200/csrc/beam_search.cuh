@@ -323,6 +323,13 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1_MINB
     if (lane == 0) nx = atomicAdd(A.qcounter, 1u);
     return wstride + (long long)__shfl_sync(PANN_FULL, nx, 0);
   };
+  if constexpr (GS) {
+    if (A.tune & 16u) {   // the two-round filter's slot bitmap: all zero between hops
+      uint32_t* fb = reinterpret_cast<uint32_t*>(ws + A.off_hash);
+      for (int i = lane; i < (1 << A.bits) / 32; i += 32) fb[i] = 0u;
+      __syncwarp();
+    }
+  }
   for (long long ql = wglobal; ql < (long long)A.nq; ql = next_query(ql)) {
     const long long q = A.qmap ? (long long)A.qmap[ql] : ql;
     // ---- per-query init: hash filter := -1 (beamSearch.h:53), query chunks into registers / shared memory
@@ -423,6 +430,45 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1_MINB
       nread += ne;
       int S = 0;
       __syncwarp();
+      bool filtered = false;
+      if constexpr (GS) {
+        if (A.tune & 16u) {
+          // The filter lives in global memory here (an L2 round trip per lookup).  Both 32-neighbour rounds look their slots up
+          // at once; what round 0 writes in between is accounted for by a per-warp bitmap of the slots it touches: a round-1
+          // neighbour whose slot round 0 overwrote finds another vertex's id there (ids of a row are distinct), i.e. "not seen"
+          // — exactly what the sequential walk over the row sees (:54-58, :130-136).  max degree <= 64, bitmap of 2^bits bits.
+          uint32_t* fb = reinterpret_cast<uint32_t*>(ws + A.off_hash);
+          const bool act0 = lane < ne, act1 = 32 + lane < ne;
+          const uint32_t loc0 = act0 ? ((uint32_t)pann_hash64_2(a0) & hmask) : (0x80000000u | lane);
+          const uint32_t loc1 = act1 ? ((uint32_t)pann_hash64_2(a1) & hmask) : (0x80000000u | lane);
+          const unsigned peers0 = __match_any_sync(PANN_FULL, loc0), peers1 = __match_any_sync(PANN_FULL, loc1);
+          const unsigned prev0 = peers0 & lt_mask, prev1 = peers1 & lt_mask;
+          const uint32_t fp0 = __shfl_sync(PANN_FULL, a0, prev0 ? (31 - __clz(prev0)) : lane);
+          const uint32_t fp1 = __shfl_sync(PANN_FULL, a1, prev1 ? (31 - __clz(prev1)) : lane);
+          uint32_t s0 = 0xffffffffu, s1 = 0xffffffffu;
+          if (act0 && !prev0) s0 = hashf[loc0];
+          if (act1 && !prev1) s1 = hashf[loc1];
+          if (act0) atomicOr(&fb[loc0 >> 5], 1u << (loc0 & 31u));
+          __syncwarp();
+          const bool hit1 = act1 && ((fb[loc1 >> 5] >> (loc1 & 31u)) & 1u);
+          __syncwarp();
+          if (act0) fb[loc0 >> 5] = 0u;
+          const bool seen0 = act0 && ((prev0 ? fp0 : s0) == a0);
+          const bool seen1 = act1 && !hit1 && ((prev1 ? fp1 : s1) == a1);
+          __syncwarp();   // every lookup has been consumed: the stores may go
+          if (act0 && (peers0 >> lane) <= 1u) hashf[loc0] = a0;
+          __syncwarp();
+          if (act1 && (peers1 >> lane) <= 1u) hashf[loc1] = a1;
+          const bool keep0 = act0 && !seen0 && ((long long)a0 != self), keep1 = act1 && !seen1 && ((long long)a1 != self);
+          const unsigned km0 = __ballot_sync(PANN_FULL, keep0), km1 = __ballot_sync(PANN_FULL, keep1);
+          if (keep0) nbr[__popc(km0 & lt_mask)] = a0;
+          if (keep1) nbr[__popc(km0) + __popc(km1 & lt_mask)] = a1;
+          S = __popc(km0) + __popc(km1);
+          __syncwarp();
+          filtered = true;
+        }
+      }
+      if (!filtered)
       for (int base = 0; base < ne; base += 32) {
         int i = base + lane;
         bool act = i < ne;

@@ -256,6 +256,14 @@ static int launch_beam(pann_index* idx, BeamArgs& A, bool gs, uint32_t vcap, cud
   A.off_vis = A.off_q + g.stride;
   A.off_hash = A.off_vis + (gs ? 0 : al16((size_t)vcap * 8));
   A.off_stage = A.off_hash + (gs ? 0 : (4u << A.bits));
+  A.tune &= ~16u;
+  {  // global-scratch variant: both rounds of a hop look the filter up together (beam_search.cuh); needs a 2^bits-bit map per warp
+    const char* e = getenv("PANN_K1_TWO_ROUND");
+    if (gs && A.bits <= 14 && A.maxdeg <= 64 && !(e && e[0] == '0')) {
+      A.tune |= 16u;
+      A.off_stage = A.off_hash + al16((size_t)(1u << A.bits) / 8);
+    }
+  }
   A.warp_bytes = A.off_stage + (pann_staged_rows_rt(idx->dtype, qrT) ? PANN_STAGE_BYTES : 0);   // float rows are staged (pann_staged_distance)
   const size_t cta_bytes = (size_t)A.warp_bytes * PANN_WARPS_PER_CTA;
   if (cta_bytes > idx->smem_optin) PANN_FAIL("beam search: per-CTA shared memory exceeds the device limit (beam too wide for this max degree)");
