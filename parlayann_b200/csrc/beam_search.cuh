@@ -89,6 +89,27 @@ __device__ __forceinline__ int pann_count_below(const u64* a, int n, u64 t) {  /
   while (lo < hi) { int mid = (lo + hi) >> 1; if (a[mid] < t) lo = mid + 1; else hi = mid; }
   return lo;
 }
+// The same for a sorted list in GLOBAL memory (the visited list of the global-scratch variant): a binary search there is
+// ~8 dependent L2 round trips; seven pivots per round, loaded together, make it three.
+__device__ __forceinline__ int pann_count_below_far(const u64* a, int n, u64 t) {
+  int lo = 0, hi = n;   // the count lies in [lo, hi]: a[0..lo) < t, a[hi..n) >= t
+  while (hi - lo > 8) {
+    const int step = (hi - lo + 7) >> 3;
+    u64 p[7];
+#pragma unroll
+    for (int j = 0; j < 7; j++) { const int ix = lo + (j + 1) * step - 1; p[j] = ix < hi ? a[ix] : ~0ull; }
+    int c = 0;
+#pragma unroll
+    for (int j = 0; j < 7; j++) c += (p[j] < t) ? 1 : 0;   // the pivots are sorted: the first c are below t
+    const int nlo = lo + c * step;
+    if (c < 7 && nlo + step - 1 < hi) hi = nlo + step - 1;
+    lo = nlo;
+  }
+  int r = lo;
+#pragma unroll
+  for (int j = 0; j < 8; j++) r += (lo + j < hi && a[lo + j] < t) ? 1 : 0;
+  return r;
+}
 // t = a (dist,id) key with bit 0 clear
 __device__ __forceinline__ int pann_lower_bound(const u64* a, int n, u64 t) { return pann_count_below(a, n, t); }       // #{x>>1 <  t>>1}
 __device__ __forceinline__ int pann_upper_bound(const u64* a, int n, u64 t) { return pann_count_below(a, n, t + 2); }   // #{x>>1 <= t>>1}
@@ -543,7 +564,7 @@ __global__ void __launch_bounds__(PANN_WARPS_PER_CTA * 32, QR > 0 ? PANN_K1_MINB
           if (np < B) {
             u64 fl = 0ull;
             if (!vis_in_front) {  // re-entering an already visited vertex keeps it visited
-              int vp = pann_count_below(vis, V, c);
+              int vp = GS ? pann_count_below_far(vis, V, c) : pann_count_below(vis, V, c);
               fl = (vp < V && vis[vp] == c) ? 1ull : 0ull;
             }
             nf[np] = c | fl;
