@@ -177,7 +177,7 @@ __global__ void PANN_PRUNE_BOUNDS pann_prune_kernel(const PruneArgs A) {
       m += deg;
       __syncwarp();
       comps += m;
-      pann_row_distances_g<DT, METRIC, QR>(
+      pann_row_distances_g<DT, METRIC, QR, true>(
           A, [&](int r) { return (u64)cid[r] << 1; }, (int)m, qsm, lane, [&](u64 tag, float d, bool ok) {
             unsigned bm = __ballot_sync(PANN_FULL, ok);
             if (ok) bufA[C + __popc(bm & lt_mask)] = pann_key(d, pann_key_id(tag));
@@ -414,7 +414,7 @@ __global__ void PANN_PRUNE_BOUNDS pann_prune_kernel(const PruneArgs A) {
       comps += cnt;  // one distance per live later candidate (:108)
       load_q(A.points + (u64)ps_id * A.stride);
       int w = start;
-      pann_row_distances_g<DT, METRIC, QR>(
+      pann_row_distances_g<DT, METRIC, QR, true>(
           A, [&](int r) { return S[start + r]; }, cnt, qsm, lane, [&](u64 key, float d, bool ok) {
             bool keep = ok && !pann_occludes(A, d, pann_key_dist(key));  // :111
             unsigned km = __ballot_sync(PANN_FULL, keep);
@@ -479,7 +479,7 @@ __global__ void __launch_bounds__(PANN_PRUNE_WARPS * 32, 4) pann_edge_dist_kerne
     __syncwarp();
     float* o = A.sort ? dsm : A.out + (u64)i * A.maxdeg;
     int w = 0;
-    pann_row_distances_g<DT, METRIC, QR>(
+    pann_row_distances_g<DT, METRIC, QR, true>(
         A, [&](int r) { return (u64)ids[r] << 1; }, deg, qsm, lane, [&](u64, float d, bool ok) {
           unsigned bm = __ballot_sync(PANN_FULL, ok);
           if (ok) o[w + __popc(bm & ((1u << lane) - 1u))] = d;
